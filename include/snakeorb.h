@@ -1,0 +1,307 @@
+/*
+ * snakeorb.h — C ABI of libsnakeorb.so: the B200 (sm_100a) implementation of Snake-SLAM's ORB front end.
+ *
+ * Plain C, opaque handles, caller-owned buffers, int status codes (0 = OK, <0 = snk_status), no exceptions
+ * and no aborts across the boundary. One handle per host thread; handles are not thread-safe, the library is
+ * re-entrant. There is no CPU fallback: every entry point fails with SNK_ERR_CUDA if no sm_100 device is usable.
+ *
+ * Each entry point names the reference interface it replaces. Reference paths:
+ *   saiga/  = /root/reference/External/saiga/src/saiga/
+ *   Snake/  = /root/reference/Snake/
+ * INTEGRATION.md shows the C++ binding (snakeorb_saiga_adapter.h) a maintainer adds on the reference side.
+ */
+#ifndef SNAKEORB_H
+#define SNAKEORB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#    define SNK_API
+#else
+#    define SNK_API __attribute__((visibility("default")))
+#endif
+
+typedef enum snk_status
+{
+    SNK_OK              = 0,
+    SNK_ERR_INVALID     = -1, /* bad argument (null pointer, size mismatch, unsupported parameter) */
+    SNK_ERR_CUDA        = -2, /* CUDA runtime error or no usable device; snk_last_error() has the text */
+    SNK_ERR_CAPACITY    = -3, /* an output or internal buffer is too small for this input */
+    SNK_ERR_UNSUPPORTED = -4
+} snk_status;
+
+/* Text of the last error raised on the calling thread (never NULL). */
+SNK_API const char* snk_last_error(void);
+SNK_API const char* snk_version(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Wire types
+ * ---------------------------------------------------------------------------------------------------------- */
+
+/* == Saiga::KeyPoint<float>, saiga/vision/features/Features.h:21-67 (24 bytes, align 4) */
+typedef struct snk_keypoint_f32
+{
+    float x, y;
+    float size;
+    float angle;    /* degrees, [0,360) */
+    float response; /* FAST score */
+    int32_t octave;
+} snk_keypoint_f32;
+
+/* == Saiga::KeyPoint<double> (Snake::KeyPoint, Snake/System/SnakeGlobal.h:53), 48 bytes, align 16 */
+typedef struct snk_keypoint_f64
+{
+    double x, y;
+    double size;
+    double angle;
+    double response;
+    int32_t octave;
+    int32_t _pad;
+} snk_keypoint_f64;
+
+/* A descriptor is 4 x uint64_t == Saiga::DescriptorORB (Features.h:70); byte i holds pattern pairs 8i..8i+7, LSB first. */
+#define SNK_DESC_WORDS 4
+
+/* ------------------------------------------------------------------------------------------------------------
+ * ORB extractor   — replaces Saiga::ORBExtractor (saiga/vision/features/ORBExtractor.h:44-90, .cpp:82-289) and
+ *                   Saiga::ORBExtractorGPU (saiga/cuda/imageProcessing/ORBExtractorGPU.h:38-112) as called from
+ *                   Snake/Preprocess/FeatureDetector.cpp:31-41,119-124,149-154.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct snk_orb snk_orb;
+
+typedef struct snk_orb_params
+{
+    int32_t nfeatures;    /* fd_features      (ORBExtractor ctor arg 1) */
+    float scale_factor;   /* fd_scale_factor  (arg 2; float, widened to double like the reference) */
+    int32_t nlevels;      /* fd_levels        (arg 3), 1..16 */
+    int32_t th_fast;      /* fd_iniThFAST     (arg 4) */
+    int32_t th_fast_min;  /* fd_minThFAST     (arg 5) */
+    int32_t max_batch;    /* images per call the handle is sized for (>=1); the reference processes 1 */
+    int32_t device;       /* CUDA device ordinal */
+} snk_orb_params;
+
+/* ORBExtractor::ORBExtractor (ORBExtractor.cpp:82-88). Device buffers are allocated lazily for the first image
+ * size seen (ORBExtractor::AllocatePyramid, :236-259) and re-allocated if the size changes. */
+SNK_API int snk_orb_create(const snk_orb_params* params, snk_orb** out);
+SNK_API void snk_orb_destroy(snk_orb* h);
+
+/* Run all work of this handle on `cuda_stream` (a cudaStream_t; NULL = the handle's own stream). */
+SNK_API int snk_orb_set_stream(snk_orb* h, void* cuda_stream);
+
+/* ORBExtractor::Detect (ORBExtractor.cpp:178-233): one image, results in host memory. `img` is rows x cols u8 with
+ * `pitch` bytes per row, in host memory (img_is_device = 0) or device memory (1). At most `capacity` keypoints are
+ * written (SNK_ERR_CAPACITY if there are more; snk_orb_max_keypoints() is always enough). Empty image => *n_out = 0. */
+SNK_API int snk_orb_detect(snk_orb* h, const uint8_t* img, int rows, int cols, size_t pitch, int img_is_device,
+                           snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
+
+/* Batched Detect: n_imgs (<= max_batch) images of identical size, image i at imgs + i*img_stride. Results for image
+ * i are written at kps + i*capacity / desc + 4*i*capacity, counts in n_out[i]. Frames are independent, exactly as if
+ * ORBExtractor::Detect had been called n_imgs times (FeatureDetector.cpp:124,154 calls it twice per stereo frame). */
+SNK_API int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
+                                 size_t img_stride, int imgs_are_device, snk_keypoint_f32* kps, uint64_t* desc,
+                                 int capacity, int* n_out);
+
+/* Asynchronous halves of the call above, for pipelines that keep results on the device:
+ * enqueue = copy-in (if host) + all kernels on the handle's stream; no host synchronisation. */
+SNK_API int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
+                            size_t img_stride, int imgs_are_device);
+/* Device-resident results of the last enqueue: keypoints [max_batch][stride] (24-byte records), descriptors
+ * [max_batch][stride][4] u64, counts [max_batch] i32. Valid until the next enqueue on this handle. */
+SNK_API int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps_dev, const uint64_t** desc_dev,
+                                   const int32_t** counts_dev, int* stride);
+/* Copy the results of the last enqueue to the host (synchronises the stream). */
+SNK_API int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
+
+/* Upper bound of keypoints per image for this handle (sum over levels of quota+3). */
+SNK_API int snk_orb_max_keypoints(const snk_orb* h);
+
+/* ORBExtractor::getPyramid (ORBExtractor.h:61) / ScalePyramid accessors (saiga/vision/util/ScalePyramid.h:78-84):
+ * per-level scale (double) and feature quota. Arrays of nlevels entries; either may be NULL. */
+SNK_API int snk_orb_pyramid(const snk_orb* h, double* scale, int32_t* features);
+
+/* ORBExtractor::GetImage(level) (ORBExtractor.h:55-59): device pointer to level `level` of image `img` of the last
+ * batch (blurred = 0) or to its Gaussian-blurred copy (blurred = 1). Valid until the next enqueue. */
+SNK_API int snk_orb_get_level(snk_orb* h, int img, int level, int blurred, const uint8_t** dev_ptr, int* rows,
+                              int* cols, size_t* pitch);
+/* Same, copied to host memory with `dst_pitch` bytes per row (test/debug helper). */
+SNK_API int snk_orb_read_level(snk_orb* h, int img, int level, int blurred, uint8_t* dst, size_t dst_pitch);
+/* Raw FAST candidates of one level before distribution (ORBExtractor.cpp:133-155 order), as x | y<<12 | score<<24
+ * with coordinates relative to (16,16). Test/debug helper. */
+SNK_API int snk_orb_read_candidates(snk_orb* h, int img, int level, uint32_t* packed, int capacity, int* n_out);
+
+/* Per-stage device time accumulated since the last reset, in milliseconds (cudaEvents on the handle's stream).
+ * stage: 0 copy-in, 1 pyramid, 2 FAST, 3 distribute, 4 orientation, 5 blur, 6 descriptors, 7 total.
+ * Profiling costs two event records per stage; it is off by default. */
+#define SNK_ORB_NUM_STAGES 8
+SNK_API int snk_orb_set_profiling(snk_orb* h, int enabled);
+SNK_API int snk_orb_stage_ms(snk_orb* h, float* ms /*[SNK_ORB_NUM_STAGES]*/, int* launches /*[SNK_ORB_NUM_STAGES]*/, int reset);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Matching context (device, stream, growable scratch) shared by all matchers below.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct snk_ctx snk_ctx;
+SNK_API int snk_ctx_create(int device, snk_ctx** out);
+SNK_API void snk_ctx_destroy(snk_ctx* c);
+SNK_API int snk_ctx_set_stream(snk_ctx* c, void* cuda_stream);
+
+/* Saiga::distance(DescriptorORB, DescriptorORB) (saiga/vision/features/Features.h:124-138) for n pairs
+ * (a[i] vs b[i]); host pointers. */
+SNK_API int snk_hamming_pairs(snk_ctx* c, const uint64_t* a, const uint64_t* b, int n, int32_t* dist);
+
+/* BruteForceMatcher<DescriptorORB>::matchKnn2 / matchKnn2_omp (Features.h:323-388): for each of the n descriptors
+ * d1[i], the best and second-best of the m descriptors d2 (strict <, first minimum wins; {1000,-1} if none).
+ * == the public `knn2` member (Features.h:420). Host pointers. */
+typedef struct snk_knn2
+{
+    int32_t dist0, idx0, dist1, idx1;
+} snk_knn2;
+SNK_API int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t* d2, int m, snk_knn2* out);
+/* Batched form on device memory: problem p matches d1 + 4*p*stride1 (n[p] rows) against d2 + 4*p*stride2 (m[p]);
+ * n, m are device int arrays; out is device [n_problems][stride1]. Asynchronous on the context stream. */
+SNK_API int snk_match_knn2_batch_device(snk_ctx* c, const uint64_t* d1_dev, const int32_t* n_dev, int stride1,
+                                        const uint64_t* d2_dev, const int32_t* m_dev, int stride2, int n_problems,
+                                        snk_knn2* out_dev);
+/* BruteForceMatcher::filterMatches (Features.h:394-414): threshold + float ratio test over knn2; writes (i, j) pairs
+ * in ascending i == the public `matches` member; returns the count in *n_matches. Host pointers. */
+SNK_API int snk_filter_matches(const snk_knn2* knn2, int n, int threshold, float ratio, int32_t* matches_ij,
+                               int* n_matches);
+
+/* Preprocess::StereoMatching (Snake/Preprocess/Preprocess.cpp:122-242) after the two Rectification::Forward loops
+ * (:140-150): left/right are the *rectified* keypoints. */
+typedef struct snk_stereo_params
+{
+    double bf;             /* rect_left.bf */
+    int32_t relaxed;       /* settings.fd_relaxed_stereo: thresholds 75 / 0.9 / 25 deg, else 40 / 0.7 / 5 deg */
+    int32_t nlevels;       /* entries of scale[] */
+    double scale[16];      /* scalePyramid.Scale(level) */
+} snk_stereo_params;
+/* right_points / depth: nl floats each, -1000 where unmatched (Frame::allocateTmp, Snake/Map/Frame.cpp:25-26). */
+SNK_API int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl,
+                             int nl, const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points,
+                             float* depth, int* n_matches);
+/* Batched, device-resident form fed directly by an extractor handle: images 2p and 2p+1 of the last enqueue are the
+ * left / right image of stereo pair p (identity rectification, i.e. EuRoC/KITTI rectified input). Outputs are device
+ * arrays [n_pairs][stride] (stride from snk_orb_device_results) and n_matches_dev[n_pairs]. Asynchronous on the
+ * extractor's stream. */
+SNK_API int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_stereo_params* p,
+                                        float* right_points_dev, float* depth_dev, int32_t* n_matches_dev);
+
+/* Camera, grid and frame views used by the projection searches. */
+typedef struct snk_camera
+{
+    double fx, fy, cx, cy, s; /* Saiga::IntrinsicsPinholed (saiga/vision/cameraModel/Intrinsics4.h) — global K */
+    double bf;                /* stereo_cam.bf (Intrinsics4.h:214) */
+} snk_camera;
+
+/* Saiga::FeatureGridBounds2<double,20> + FeatureGrid2 (saiga/vision/util/FeatureGrid2.h:10-211): cells[row*cols+col]
+ * = (begin,end) index range into the (already grid-permuted) keypoint arrays. */
+typedef struct snk_grid_view
+{
+    double bmin_x, bmin_y, bmax_x, bmax_y;
+    double cell_size_inv_x, cell_size_inv_y;
+    int32_t rows, cols;
+    const int32_t* cells; /* 2*rows*cols ints */
+} snk_grid_view;
+
+/* The parts of Snake::Frame / Snake::Features the searches read (Snake/Map/Features.h:18-41, Frame.h). */
+typedef struct snk_frame_view
+{
+    int32_t n;
+    const snk_keypoint_f64* kp_un;   /* undistorted_keypoints */
+    const uint64_t* desc;            /* descriptors */
+    const float* right_points;       /* right_points */
+    const int32_t* kp_to_point;      /* mvpMapPoints as ids: >=0 already matched, -1 free */
+    double pose_q[4];                /* Frame::Pose() unit quaternion x,y,z,w */
+    double pose_t[3];
+    snk_grid_view grid;
+} snk_frame_view;
+
+/* Snake::FineTrackingPoint (Snake/Map/LocalMap.h:32-55) */
+typedef struct snk_point_fine
+{
+    uint64_t desc[4];
+    double pos[3];
+    double normal[3];
+    float ref_depth;
+    int32_t ref_level;
+    int32_t valid;
+    int32_t id; /* stands for MapPoint* */
+} snk_point_fine;
+
+/* Snake::CoarseTrackingPoint (Snake/Map/LocalMap.h:17-30) */
+typedef struct snk_point_coarse
+{
+    uint64_t desc[4];
+    double pos[3];
+    double normal[3];
+    int32_t octave;
+    float angle;
+    int32_t id;
+    int32_t _pad;
+} snk_point_coarse;
+
+typedef struct snk_scale_pyramid
+{
+    int32_t nlevels;
+    int32_t _pad;
+    double scale_factor; /* ScalePyramid::scale_factor (float 1.2f widened) */
+    double scale[16];
+} snk_scale_pyramid;
+
+/* SnakeORBMatcher::SearchByProjection2 (Snake/Tracking/SnakeORBMatcher.cpp:365-526).
+ * In/out: points[i].valid is cleared where the reference clears lmp.valid; visible[i] = 1 where it calls
+ * IncreaseVisible(). Out: kp_to_point_out[n] = frame.kp_to_point with new assignments (point ids) added,
+ * best_idx/best_dist [n_points] = tmp_matches_world_image (-1 if none). Returns matches in *n_matches. */
+SNK_API int snk_search_projection_fine(snk_ctx* c, const snk_frame_view* frame, snk_point_fine* points, int n_points,
+                                       const snk_camera* cam, const snk_scale_pyramid* pyr, float th, float ratio,
+                                       int32_t* kp_to_point_out, int32_t* best_idx, int32_t* best_dist,
+                                       uint8_t* visible, int* n_matches);
+
+/* SnakeORBMatcher::SearchByProjectionFrameFrame2 (Snake/Tracking/SnakeORBMatcher.cpp:191-354).
+ * motion: 0 neither, 1 bForward, 2 bBackward (the caller evaluates :209-212). */
+SNK_API int snk_search_projection_coarse(snk_ctx* c, const snk_frame_view* frame, const snk_point_coarse* points,
+                                         int n_points, const snk_camera* cam, const snk_scale_pyramid* pyr, float th,
+                                         int feature_error, int motion, int32_t* kp_to_point_out, int* n_matches);
+
+/* SnakeORBMatcher::SearchByProjectionFrameToKeyframe (Snake/Tracking/SnakeORBMatcher.cpp:71-188): fully serial in
+ * the reference (each match removes a keypoint for later points); points with id < 0 are skipped (null MapPoint),
+ * ids already present in frame.kp_to_point are skipped (sAlreadyFound). */
+typedef struct snk_point_kf
+{
+    uint64_t desc[4];
+    double pos[3];
+    int32_t id;
+    int32_t _pad;
+} snk_point_kf;
+SNK_API int snk_search_projection_frame_to_kf(snk_ctx* c, const snk_frame_view* frame, const snk_point_kf* points,
+                                              int n_points, const snk_camera* cam, float th, int feature_error,
+                                              int32_t* kp_to_point_out, int* n_matches);
+
+/* LoopORBmatcher::MatchBoW (Snake/LoopClosing/LoopORBMatcher.cpp:121-215). A FeatureVector
+ * (saiga/vision/slam/MiniBow2.h:98-132) is given as CSR: node_ids[n_nodes] ascending, offsets[n_nodes+1], indices[]. */
+typedef struct snk_featvec_view
+{
+    int32_t n_nodes;
+    const int32_t* node_ids;
+    const int32_t* offsets;
+    const int32_t* indices;
+} snk_featvec_view;
+/* valid1/valid2: 1 where the keyframe has a good map point at that feature (vpMapPoints[i] && !isBad()).
+ * match12[n1] = matched feature index in keyframe 2, or -1. */
+SNK_API int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, int n2,
+                          const snk_featvec_view* fv1, const snk_featvec_view* fv2, const uint8_t* valid1,
+                          const uint8_t* valid2, int th, float ratio, int32_t* match12, int* n_matches);
+
+/* Register-resident popc microbenchmark: measured 256-bit Hamming distances per second of this device, the
+ * denominator of the matcher roofline. */
+SNK_API int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SNAKEORB_H */

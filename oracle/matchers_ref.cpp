@@ -1,0 +1,578 @@
+// TEST INFRASTRUCTURE ONLY — CPU oracle, never on the product path.
+//
+// Restatements of the reference's Hamming matchers on the plain structs of include/snakeorb.h (the originals are
+// entangled with Snake::Frame / Map / globals and do not compile standalone). Paths relative to /root/reference/.
+// Built with -ffp-contract=off: the double geometry is evaluated unfused, in the reference's operation order.
+#include "matchers_ref.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <set>
+#include <vector>
+
+namespace orbref
+{
+// External/saiga/src/saiga/vision/features/Features.h:124-138
+int hamming(const uint64_t* a, const uint64_t* b)
+{
+    int d = 0;
+    for (int i = 0; i < 4; ++i) d += __builtin_popcountll(a[i] ^ b[i]);
+    return d;
+}
+
+// Features.h:323-354
+void match_knn2(const uint64_t* d1, int n, const uint64_t* d2, int m, snk_knn2* out, int threads)
+{
+#pragma omp parallel for num_threads(threads)
+    for (int i = 0; i < n; ++i)
+    {
+        snk_knn2 r{1000, -1, 1000, -1};
+        for (int j = 0; j < m; ++j)
+        {
+            int dis = hamming(d1 + 4 * (size_t)i, d2 + 4 * (size_t)j);
+            if (dis < r.dist0)
+            {
+                r.dist1 = r.dist0;
+                r.idx1  = r.idx0;
+                r.dist0 = dis;
+                r.idx0  = j;
+            }
+            else if (dis < r.dist1)
+            {
+                r.dist1 = dis;
+                r.idx1  = j;
+            }
+        }
+        out[i] = r;
+    }
+}
+
+// Features.h:394-414
+int filter_matches(const snk_knn2* knn2, int n, int threshold, float ratio, int32_t* matches_ij)
+{
+    int c = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        if (knn2[i].dist0 > threshold) continue;
+        if (float(knn2[i].dist0) > float(knn2[i].dist1) * ratio) continue;
+        matches_ij[2 * c]     = i;
+        matches_ij[2 * c + 1] = knn2[i].idx0;
+        ++c;
+    }
+    return c;
+}
+
+static inline int iRoundF(float v) { return (int)(v + (v >= 0 ? 0.5f : -0.5f)); }
+
+// Snake/Preprocess/Preprocess.cpp:122-242 (after the Rectification::Forward loops)
+int stereo_match(const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
+                 const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points, float* depth,
+                 long long* pair_ops)
+{
+    for (int i = 0; i < nl; ++i) right_points[i] = depth[i] = -1000.f;  // Frame::allocateTmp
+    long long ops = 0;
+    if (nl == 0 || nr == 0)
+    {
+        if (pair_ops) *pair_ops = 0;
+        return 0;
+    }
+    int min_y = 1023123, max_y = -19284;
+    const float min_disp = 0;
+    const float max_disp = (float)(p->bf * 0.5);
+    for (int i = 0; i < nr; ++i)
+    {
+        int r = iRoundF((float)right[i].y);  // iRound(float) receives a double
+        min_y = std::min(min_y, r);
+        max_y = std::max(max_y, r);
+    }
+    std::vector<std::vector<int>> row_map(max_y - min_y + 1);
+    for (int i = 0; i < nr; ++i) row_map[iRoundF((float)right[i].y) - min_y].push_back(i);
+
+    int num_matches = 0;
+    for (int i = 0; i < nl; ++i)
+    {
+        const snk_keypoint_f64& kp = left[i];
+        int y                      = iRoundF((float)kp.y);
+        int y_center               = y - min_y;
+        float r                    = (float)std::ceil(2.0f * p->scale[kp.octave]);
+        int best_id = -1, best_dist = 250, second = 250;
+        for (int row = (int)(y_center - r); row <= y_center + r; ++row)
+        {
+            if (row < 0 || row >= (int)row_map.size()) continue;
+            for (int o : row_map[row])
+            {
+                double disparity = kp.x - right[o].x;
+                if (disparity < min_disp || disparity > max_disp) continue;
+                if (std::abs(kp.octave - right[o].octave) > 1) continue;
+                int dist = hamming(dl + 4 * (size_t)i, dr + 4 * (size_t)o);
+                ++ops;
+                if (dist < best_dist)
+                {
+                    second    = best_dist;
+                    best_dist = dist;
+                    best_id   = o;
+                }
+                else if (dist < second)
+                {
+                    second = dist;
+                }
+            }
+        }
+        if (best_dist > (p->relaxed ? 75 : 40)) continue;
+        if (best_dist > (p->relaxed ? 0.9 : 0.7) * second) continue;
+        double a1 = kp.angle, a2 = right[best_id].angle;
+        float rot = (float)std::min(std::abs(a1 - a2), std::min(std::abs((a1 + 365) - a2), std::abs(a1 - (a2 + 365))));
+        if (rot > (p->relaxed ? 25 : 5)) continue;
+        double right_point = right[best_id].x;
+        double disparity   = kp.x - right_point;
+        if (disparity <= 0.001)
+        {
+            disparity   = 0.001;
+            right_point = kp.x - disparity;
+        }
+        right_points[i] = (float)right_point;
+        depth[i]        = (float)(p->bf / disparity);
+        ++num_matches;
+    }
+    if (pair_ops) *pair_ops = ops;
+    return num_matches;
+}
+
+// ---------------------------------------------------------------------------------------------
+// projection geometry helpers
+// ---------------------------------------------------------------------------------------------
+namespace
+{
+struct V3
+{
+    double x, y, z;
+};
+inline V3 cross(const V3& a, const V3& b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+
+// Eigen::QuaternionBase::_transformVector: uv = 2 * (q.vec x v); v + w*uv + q.vec x uv
+inline V3 rotate(const double q[4], const V3& v)
+{
+    V3 qv{q[0], q[1], q[2]};
+    V3 uv = cross(qv, v);
+    uv    = {uv.x + uv.x, uv.y + uv.y, uv.z + uv.z};
+    V3 c  = cross(qv, uv);
+    return {v.x + q[3] * uv.x + c.x, v.y + q[3] * uv.y + c.y, v.z + q[3] * uv.z + c.z};
+}
+// Sophus SE3 * point
+inline V3 se3_apply(const double q[4], const double t[3], const V3& p)
+{
+    V3 r = rotate(q, p);
+    return {r.x + t[0], r.y + t[1], r.z + t[2]};
+}
+// Sophus SE3::inverse().translation(): conj(q) * (t * -1)
+inline V3 camera_position(const double q[4], const double t[3])
+{
+    double qi[4] = {-q[0], -q[1], -q[2], q[3]};
+    return rotate(qi, V3{t[0] * -1, t[1] * -1, t[2] * -1});
+}
+inline int iFloorD(double v) { return ((int)v) - (((int)v) > v); }
+
+struct Cell
+{
+    int cx, cy;
+};
+// External/saiga/src/saiga/vision/util/FeatureGrid2.h:24-60
+inline Cell cell_clamped(const snk_grid_view& g, double px, double py)
+{
+    double x = (px - g.bmin_x) * g.cell_size_inv_x;
+    double y = (py - g.bmin_y) * g.cell_size_inv_y;
+    Cell c{iFloorD(x), iFloorD(y)};
+    c.cx = std::min(std::max(c.cx, 0), g.cols - 1);
+    c.cy = std::min(std::max(c.cy, 0), g.rows - 1);
+    return c;
+}
+inline bool in_image(const snk_grid_view& g, double x, double y)
+{
+    return x >= g.bmin_x && y >= g.bmin_y && x < g.bmax_x && y < g.bmax_y;
+}
+
+// Visit grid candidates in the reference's order: cx outer, cy inner, index ascending (Snake/Map/Features.cpp:13-76).
+// minMaxCellWithRadius takes a *float* radius (FeatureGrid2.h:24) while the distance test uses the caller's r*r.
+template <typename F>
+inline void for_candidates(const snk_frame_view* f, double px, double py, float r_cells, double r2, F&& fn)
+{
+    const snk_grid_view& g = f->grid;
+    Cell lo                = cell_clamped(g, px - r_cells, py - r_cells);
+    Cell hi                = cell_clamped(g, px + r_cells, py + r_cells);
+    for (int cx = lo.cx; cx <= hi.cx; ++cx)
+        for (int cy = lo.cy; cy <= hi.cy; ++cy)
+        {
+            int b = g.cells[2 * (cy * g.cols + cx)], e = g.cells[2 * (cy * g.cols + cx) + 1];
+            for (int pid = b; pid < e; ++pid)
+            {
+                double dx = f->kp_un[pid].x - px, dy = f->kp_un[pid].y - py;
+                bool inside = (dx * dx + dy * dy) < r2;
+                fn(pid, inside);
+            }
+        }
+}
+
+// Intrinsics4.h:53-59
+inline void project(const snk_camera* K, const V3& X, double& u, double& v)
+{
+    double invz = 1.0 / X.z;
+    double x = X.x * invz, y = X.y * invz;
+    u = K->fx * x + K->s * y + K->cx;
+    v = K->fy * y + K->cy;
+}
+}  // namespace
+
+// Snake/Tracking/SnakeORBMatcher.cpp:365-526
+int search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
+                           const snk_scale_pyramid* sp, float th, float ratio, int32_t* kp_to_point_out,
+                           int32_t* best_idx, int32_t* best_dist, uint8_t* visible, long long* pair_ops)
+{
+    const V3 cam       = camera_position(f->pose_q, f->pose_t);
+    const bool bFactor = th != 1.0;
+    const double logsf = std::log(sp->scale_factor);
+    long long ops      = 0;
+    std::memcpy(kp_to_point_out, f->kp_to_point, sizeof(int32_t) * f->n);
+    for (int i = 0; i < n; ++i)
+    {
+        best_idx[i]  = -1;
+        best_dist[i] = 0;
+        visible[i]   = 0;
+        snk_point_fine& lmp = pts[i];
+        if (!lmp.valid) continue;
+        V3 P{lmp.pos[0], lmp.pos[1], lmp.pos[2]};
+        V3 Pc    = se3_apply(f->pose_q, f->pose_t, P);
+        double z = Pc.z;
+        if (z < 0)
+        {
+            lmp.valid = 0;
+            continue;
+        }
+        double u, v;
+        project(K, Pc, u, v);
+        if (!in_image(f->grid, u, v))
+        {
+            lmp.valid = 0;
+            continue;
+        }
+        V3 PO{cam.x - P.x, cam.y - P.y, cam.z - P.z};
+        double dist = std::sqrt(PO.x * PO.x + PO.y * PO.y + PO.z * PO.z);
+        // ScalePyramid::EstimateMinMaxDistance (ScalePyramid.h:26-41)
+        double max_d = (double)lmp.ref_depth * sp->scale[lmp.ref_level];
+        double min_d = max_d / sp->scale[sp->nlevels - 1];
+        min_d /= sp->scale_factor;
+        max_d *= sp->scale_factor;
+        if (dist < min_d || dist > max_d)
+        {
+            lmp.valid = 0;
+            continue;
+        }
+        double viewCos = (PO.x * lmp.normal[0] + PO.y * lmp.normal[1] + PO.z * lmp.normal[2]) / dist;
+        if (viewCos < 0.5)
+        {
+            lmp.valid = 0;
+            continue;
+        }
+        visible[i] = 1;
+        // RadiusByViewingCos(float) (:357-363): the double viewCos is narrowed to float first
+        float r = ((float)viewCos > 0.998) ? 2.5f : 4.0f;
+        if (bFactor) r *= th;
+        // PredictScaleLevel (ScalePyramid.h:44-57), ScaleForContiniousLevel (:78)
+        double pmax       = (double)lmp.ref_depth * sp->scale[lmp.ref_level];
+        double prediction = std::log(pmax / dist) / logsf;
+        r                 = (float)(r * std::pow(sp->scale_factor, prediction));
+        const double rd   = r;
+        const double r2   = rd * rd;
+
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        const double right_pred = u - K->bf / z;  // stereo_cam.LeftPointToRight
+        for_candidates(f, u, v, r, r2, [&](int pid, bool inside) {
+            double e = prediction - f->kp_un[pid].octave;
+            if (!(e * e < (1.2 * 1.2))) return;
+            if (!inside) return;
+            if (f->kp_to_point[pid] >= 0) return;
+            if (f->right_points[pid] > 0)
+            {
+                double er = std::abs(right_pred - f->right_points[pid]);
+                if (er > r * 0.5) return;
+            }
+            int d = hamming(lmp.desc, f->desc + 4 * (size_t)pid);
+            ++ops;
+            if (d < bestDist)
+            {
+                bestDist2  = bestDist;
+                bestDist   = d;
+                bestLevel2 = bestLevel;
+                bestLevel  = f->kp_un[pid].octave;
+                bestIdx    = pid;
+            }
+            else if (d < bestDist2)
+            {
+                bestLevel2 = f->kp_un[pid].octave;
+                bestDist2  = d;
+            }
+        });
+        if (bestIdx >= 0 && bestDist <= 100)  // TH_HIGH
+        {
+            if (bestLevel == bestLevel2 && bestDist > ratio * bestDist2) continue;
+            best_idx[i]  = bestIdx;
+            best_dist[i] = bestDist;
+        }
+    }
+    int matches = 0;
+    for (int i = 0; i < n; ++i)  // :516-524 first come, first served
+    {
+        int b = best_idx[i];
+        if (b == -1) continue;
+        if (kp_to_point_out[b] >= 0) continue;
+        kp_to_point_out[b] = pts[i].id;
+        ++matches;
+    }
+    if (pair_ops) *pair_ops = ops;
+    return matches;
+}
+
+// Snake/Tracking/SnakeORBMatcher.cpp:27-68
+static void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; ++i)
+    {
+        const int s = (int)histo[i].size();
+        if (s > max1)
+        {
+            max3 = max2;
+            max2 = max1;
+            max1 = s;
+            ind3 = ind2;
+            ind2 = ind1;
+            ind1 = i;
+        }
+        else if (s > max2)
+        {
+            max3 = max2;
+            max2 = s;
+            ind3 = ind2;
+            ind2 = i;
+        }
+        else if (s > max3)
+        {
+            max3 = s;
+            ind3 = i;
+        }
+    }
+    if (max2 < 0.1f * (float)max1)
+    {
+        ind2 = -1;
+        ind3 = -1;
+    }
+    else if (max3 < 0.1f * (float)max1)
+    {
+        ind3 = -1;
+    }
+}
+
+// Snake/Tracking/SnakeORBMatcher.cpp:191-354
+int search_projection_coarse(const snk_frame_view* f, const snk_point_coarse* pts, int n, const snk_camera* K,
+                             const snk_scale_pyramid* sp, float th, int feature_error, int motion,
+                             int32_t* kp_to_point_out, long long* pair_ops)
+{
+    const int HISTO    = 30;
+    const float factor = 1.0f / HISTO;
+    std::vector<int> hist[30];
+    const V3 cam  = camera_position(f->pose_q, f->pose_t);
+    long long ops = 0;
+    std::memcpy(kp_to_point_out, f->kp_to_point, sizeof(int32_t) * f->n);
+    std::vector<int> bidx(n, -1), bbin(n, 0);
+    for (int i = 0; i < n; ++i)
+    {
+        const snk_point_coarse& lmp = pts[i];
+        V3 wp{lmp.pos[0], lmp.pos[1], lmp.pos[2]};
+        V3 Pc = se3_apply(f->pose_q, f->pose_t, wp);
+        double u, v;
+        project(K, Pc, u, v);
+        double z = Pc.z;
+        if (z <= 0) continue;
+        if (!in_image(f->grid, u, v)) continue;
+        V3 PO{cam.x - wp.x, cam.y - wp.y, cam.z - wp.z};
+        double dist    = std::sqrt(PO.x * PO.x + PO.y * PO.y + PO.z * PO.z);
+        double viewCos = (PO.x * lmp.normal[0] + PO.y * lmp.normal[1] + PO.z * lmp.normal[2]) / dist;
+        if (viewCos < 0.5) continue;
+        int lvl = lmp.octave;
+        float r = th;
+        r       = (float)(r * sp->scale[lvl]);
+        int lo, hi;
+        if (motion == 1)
+            lo = lvl - 1, hi = 100;
+        else if (motion == 2)
+            lo = 0, hi = lvl;
+        else
+            lo = lvl - 1, hi = lvl + 1;
+        const double rd = r, r2 = rd * rd;
+        int bestDist = 256, bestIdx = -1;
+        const double right_pred = u - K->bf / z;
+        for_candidates(f, u, v, r, r2, [&](int pid, bool inside) {
+            int oc = f->kp_un[pid].octave;
+            if (oc < lo || oc > hi) return;
+            if (!inside) return;
+            if (f->kp_to_point[pid] >= 0) return;
+            if (f->right_points[pid] > 0)
+            {
+                double er = std::abs(right_pred - f->right_points[pid]);
+                if (er > r * 0.5) return;
+            }
+            int d = hamming(lmp.desc, f->desc + 4 * (size_t)pid);
+            ++ops;
+            if (d < bestDist)
+            {
+                bestDist = d;
+                bestIdx  = pid;
+            }
+        });
+        if (bestIdx >= 0 && bestDist <= feature_error)
+        {
+            float rot = (float)(lmp.angle - f->kp_un[bestIdx].angle);
+            if (rot < 0.0) rot += 360.0f;
+            int bin = (int)std::round(rot * factor);
+            if (bin == HISTO) bin = 0;
+            bidx[i] = bestIdx;
+            bbin[i] = bin;
+        }
+    }
+    int matches = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        int b = bidx[i];
+        if (b == -1) continue;
+        if (kp_to_point_out[b] >= 0) continue;
+        kp_to_point_out[b] = pts[i].id;
+        hist[bbin[i]].push_back(b);
+        ++matches;
+    }
+    int i1 = -1, i2 = -1, i3 = -1;
+    three_maxima(hist, HISTO, i1, i2, i3);
+    for (int i = 0; i < HISTO; ++i)
+        if (i != i1 && i != i2 && i != i3)
+            for (int b : hist[i])
+            {
+                kp_to_point_out[b] = -1;
+                --matches;
+            }
+    if (pair_ops) *pair_ops = ops;
+    return matches;
+}
+
+// Snake/Tracking/SnakeORBMatcher.cpp:71-188 (mbCheckOrientation = false, :87)
+int search_projection_frame_to_kf(const snk_frame_view* f, const snk_point_kf* pts, int n, const snk_camera* K,
+                                  float th, int feature_error, int32_t* kp_to_point_out, long long* pair_ops)
+{
+    std::set<int> found;
+    long long ops = 0;
+    std::memcpy(kp_to_point_out, f->kp_to_point, sizeof(int32_t) * f->n);
+    for (int i = 0; i < f->n; ++i)
+        if (f->kp_to_point[i] >= 0) found.insert(f->kp_to_point[i]);
+    int matches = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        if (pts[i].id < 0) continue;
+        if (found.count(pts[i].id)) continue;
+        V3 wp{pts[i].pos[0], pts[i].pos[1], pts[i].pos[2]};
+        V3 Pc = se3_apply(f->pose_q, f->pose_t, wp);
+        double u, v;
+        project(K, Pc, u, v);
+        double z = Pc.z;
+        if (z <= 0) continue;
+        if (!in_image(f->grid, u, v)) continue;
+        float r          = th;
+        const float r2f  = r * r;  // GetFeaturesInArea(…, float r): r2 is float (Features.cpp:17)
+        int bestDist = 256, bestIdx = -1;
+        const double right_pred = u - K->bf / z;
+        for_candidates(f, u, v, r, (double)r2f, [&](int pid, bool inside) {
+            if (!inside) return;
+            if (kp_to_point_out[pid] >= 0) return;
+            if (f->right_points[pid] > 0)
+            {
+                const float er = (float)std::abs(right_pred - f->right_points[pid]);
+                if (er > r * 0.5) return;
+            }
+            int d = hamming(pts[i].desc, f->desc + 4 * (size_t)pid);
+            ++ops;
+            if (d < bestDist)
+            {
+                bestDist = d;
+                bestIdx  = pid;
+            }
+        });
+        if (bestIdx >= 0 && bestDist <= feature_error)
+        {
+            kp_to_point_out[bestIdx] = pts[i].id;
+            ++matches;
+        }
+    }
+    if (pair_ops) *pair_ops = ops;
+    return matches;
+}
+
+// Snake/LoopClosing/LoopORBMatcher.cpp:121-215
+int match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_featvec_view* fv1,
+              const snk_featvec_view* fv2, const uint8_t* valid1, const uint8_t* valid2, int th, float ratio,
+              int32_t* match12, long long* pair_ops)
+{
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    std::vector<char> matched2(n2, 0);
+    long long ops = 0;
+    int nmatches  = 0;
+    int a = 0, b = 0;
+    while (a < fv1->n_nodes && b < fv2->n_nodes)
+    {
+        int ida = fv1->node_ids[a], idb = fv2->node_ids[b];
+        if (ida == idb)
+        {
+            for (int i1 = fv1->offsets[a]; i1 < fv1->offsets[a + 1]; ++i1)
+            {
+                int idx1 = fv1->indices[i1];
+                if (!valid1[idx1]) continue;
+                int best1 = 256, bestIdx2 = -1, best2 = 256;
+                for (int i2 = fv2->offsets[b]; i2 < fv2->offsets[b + 1]; ++i2)
+                {
+                    int idx2 = fv2->indices[i2];
+                    if (matched2[idx2] || !valid2[idx2]) continue;
+                    int dist = hamming(d1 + 4 * (size_t)idx1, d2 + 4 * (size_t)idx2);
+                    ++ops;
+                    if (dist < best1)
+                    {
+                        best2    = best1;
+                        best1    = dist;
+                        bestIdx2 = idx2;
+                    }
+                    else if (dist < best2)
+                    {
+                        best2 = dist;
+                    }
+                }
+                if (best1 < th)
+                {
+                    if ((float)best1 < ratio * (float)best2)
+                    {
+                        matched2[bestIdx2] = 1;
+                        match12[idx1]      = bestIdx2;
+                        ++nmatches;
+                    }
+                }
+            }
+            ++a;
+            ++b;
+        }
+        else if (ida < idb)
+        {
+            while (a < fv1->n_nodes && fv1->node_ids[a] < idb) ++a;  // std::lower_bound on a sorted vector
+        }
+        else
+        {
+            while (b < fv2->n_nodes && fv2->node_ids[b] < ida) ++b;
+        }
+    }
+    if (pair_ops) *pair_ops = ops;
+    return nmatches;
+}
+}  // namespace orbref

@@ -1,0 +1,204 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes view of oracle/liborb_oracle.so (the CPU restatement) and, when present,
+oracle/_ref/libsaiga_orb_ref.so (the reference's own translation units). Imported by tests/,
+__graft_entry__.smoke() and the cpu_baseline / --impl reference legs of bench.py — never by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+KP32 = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")])
+KP64 = np.dtype([("x", "<f8"), ("y", "<f8"), ("size", "<f8"), ("angle", "<f8"), ("response", "<f8"),
+                 ("octave", "<i4"), ("_pad", "<i4")])
+KNN2 = np.dtype([("dist0", "<i4"), ("idx0", "<i4"), ("dist1", "<i4"), ("idx1", "<i4")])
+assert KP32.itemsize == 24 and KP64.itemsize == 48
+
+
+def build(force=False):
+    so = os.path.join(HERE, "liborb_oracle.so")
+    if force or not os.path.exists(so) or os.path.isdir("/root/reference"):
+        subprocess.check_call(["make", "-s", "-C", HERE, "all"])
+    return so
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        so = os.path.join(HERE, "liborb_oracle.so")
+        if not os.path.exists(so):
+            build()
+        _lib = C.CDLL(so)
+        _lib.orc_extractor_create.restype = C.c_void_p
+    return _lib
+
+
+def ref():
+    """The compiled reference pieces, or None when oracle/_ref was not built (no /root/reference)."""
+    global _ref
+    if _ref is None:
+        so = os.path.join(HERE, "_ref", "libsaiga_orb_ref.so")
+        if not os.path.exists(so):
+            return None
+        _ref = C.CDLL(so)
+    return _ref
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+def resize(src, dh, dw):
+    src = np.ascontiguousarray(src)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize(_p(src), src.shape[0], src.shape[1], C.c_size_t(src.shape[1]), _p(dst), dh, dw, C.c_size_t(dw))
+    return dst
+
+
+def blur(src):
+    src = np.ascontiguousarray(src)
+    dst = np.zeros_like(src)
+    lib().orc_blur(_p(src), src.shape[0], src.shape[1], C.c_size_t(src.shape[1]), _p(dst), C.c_size_t(src.shape[1]))
+    return dst
+
+
+def fast(roi_parent, y0, x0, h, w, th):
+    """FAST on the ROI [y0:y0+h, x0:x0+w] of a C-contiguous parent; returns int32 (n,3) x,y,score."""
+    out = np.zeros((h * w, 3), np.int32)
+    ptr = C.c_void_p(roi_parent.ctypes.data + y0 * roi_parent.strides[0] + x0)
+    n = lib().orc_fast(ptr, h, w, C.c_size_t(roi_parent.strides[0]), th, _p(out), h * w)
+    return out[:n]
+
+
+def scale_pyramid(levels, scale_factor, nfeatures):
+    s = np.zeros(levels, np.float64)
+    f = np.zeros(levels, np.int32)
+    lib().orc_scale_pyramid(levels, C.c_float(scale_factor), nfeatures, _p(s), _p(f))
+    return s, f
+
+
+def cell_grid(rows, cols):
+    o = np.zeros(7, np.int32)
+    lib().orc_cell_grid(rows, cols, _p(o))
+    return dict(zip(["nCols", "nRows", "wCell", "hCell", "minB", "maxBX", "maxBY"], [int(v) for v in o]))
+
+
+def angles(img, xy):
+    img = np.ascontiguousarray(img)
+    xy = np.ascontiguousarray(xy, np.float32)
+    out = np.zeros(len(xy), np.float32)
+    lib().orc_angles(_p(img), C.c_size_t(img.shape[1]), _p(xy), len(xy), _p(out))
+    return out
+
+
+def descriptors(img, xy, ang):
+    img = np.ascontiguousarray(img)
+    xy = np.ascontiguousarray(xy, np.float32)
+    ang = np.ascontiguousarray(ang, np.float32)
+    out = np.zeros((len(xy), 4), np.uint64)
+    lib().orc_descriptors(_p(img), C.c_size_t(img.shape[1]), _p(xy), _p(ang), len(xy), _p(out))
+    return out
+
+
+def distribute(kps, mn, mx, target, which="oracle"):
+    """Returns (selected records, permuted input)."""
+    kps = np.array(kps, dtype=KP32, copy=True)
+    out = np.zeros(len(kps) + 8, KP32)
+    if which == "oracle":
+        fn = lib().orc_distribute
+    else:
+        fn = ref().ref_distribute
+    n = fn(_p(kps), len(kps), C.c_float(mn[0]), C.c_float(mn[1]), C.c_float(mx[0]), C.c_float(mx[1]), target,
+           _p(out), len(out))
+    return out[:n].copy(), kps
+
+
+class Extractor:
+    """orbref::OrbExtractor == Saiga::ORBExtractor restated (oracle/orb_ref.cpp)."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, th=20, thmin=7, threads=1):
+        self.h = C.c_void_p(lib().orc_extractor_create(nfeatures, C.c_float(scale), nlevels, th, thmin, threads))
+        self.nlevels = nlevels
+        self.cap = nfeatures + 8 * nlevels + 64
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_extractor_destroy(self.h)
+            self.h = None
+
+    def detect(self, img):
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        kps = np.zeros(self.cap, KP32)
+        desc = np.zeros((self.cap, 4), np.uint64)
+        n = lib().orc_extractor_detect(self.h, _p(img), img.shape[0], img.shape[1], C.c_size_t(img.strides[0]),
+                                       _p(kps), _p(desc), self.cap)
+        assert n <= self.cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l, blurred=False):
+        r, c = C.c_int32(), C.c_int32()
+        lib().orc_extractor_level_dims(self.h, l, C.byref(r), C.byref(c))
+        out = np.zeros((r.value, c.value), np.uint8)
+        lib().orc_extractor_level(self.h, l, int(blurred), _p(out))
+        return out
+
+    def level_kps(self, l, which):
+        out = np.zeros(200000, KP32)
+        n = lib().orc_extractor_level_kps(self.h, l, which, _p(out), len(out))
+        return out[:n].copy()
+
+
+def hamming(a, b):
+    return lib().orc_hamming(_p(np.ascontiguousarray(a, np.uint64)), _p(np.ascontiguousarray(b, np.uint64)))
+
+
+def match_knn2(d1, d2, threads=1):
+    d1 = np.ascontiguousarray(d1, np.uint64)
+    d2 = np.ascontiguousarray(d2, np.uint64)
+    out = np.zeros(len(d1), KNN2)
+    lib().orc_match_knn2(_p(d1), len(d1), _p(d2), len(d2), _p(out), threads)
+    return out
+
+
+def filter_matches(knn2, th, ratio):
+    out = np.zeros((len(knn2), 2), np.int32)
+    n = lib().orc_filter_matches(_p(knn2), len(knn2), th, C.c_float(ratio), _p(out))
+    return out[:n].copy()
+
+
+class StereoParams(C.Structure):
+    _fields_ = [("bf", C.c_double), ("relaxed", C.c_int32), ("nlevels", C.c_int32), ("scale", C.c_double * 16)]
+
+
+def stereo_params(bf, relaxed, scales):
+    p = StereoParams()
+    p.bf = bf
+    p.relaxed = int(relaxed)
+    p.nlevels = len(scales)
+    for i, s in enumerate(scales):
+        p.scale[i] = s
+    return p
+
+
+def kp32_to_kp64(k):
+    o = np.zeros(len(k), KP64)
+    for f in ("x", "y", "size", "angle", "response", "octave"):
+        o[f] = k[f]
+    return o
+
+
+def stereo_match(params, left, dl, right, dr):
+    left = np.ascontiguousarray(left, KP64)
+    right = np.ascontiguousarray(right, KP64)
+    dl = np.ascontiguousarray(dl, np.uint64)
+    dr = np.ascontiguousarray(dr, np.uint64)
+    rp = np.zeros(len(left), np.float32)
+    dp = np.zeros(len(left), np.float32)
+    ops = C.c_longlong(0)
+    n = lib().orc_stereo_match(C.byref(params), _p(left), _p(dl), len(left), _p(right), _p(dr), len(right), _p(rp),
+                               _p(dp), C.byref(ops))
+    return n, rp, dp, ops.value

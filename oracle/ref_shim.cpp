@@ -1,0 +1,135 @@
+// TEST INFRASTRUCTURE ONLY. Thin extern "C" shim over the reference's own classes, compiled together with the
+// reference's unmodified translation units (see Makefile: REF_TUS) into oracle/_ref/libsaiga_orb_ref.so.
+// Used to pin the restatement in orb_ref.cpp / matchers_ref.cpp and to generate tests/golden.
+#include "saiga/vision/features/FeatureDistribution.h"
+#include "saiga/vision/features/Features.h"
+#include "saiga/vision/features/OrbDescriptors.h"
+#include "saiga/vision/features/OrbPattern.h"
+#include "saiga/vision/util/FeatureGrid2.h"
+#include "saiga/vision/util/ScalePyramid.h"
+
+#include <cstring>
+#include <vector>
+
+using namespace Saiga;
+#define REF_API extern "C" __attribute__((visibility("default")))
+
+REF_API void ref_scale_pyramid(int levels, float scale_factor, int nfeatures, double* scale, int* features)
+{
+    ScalePyramid p(levels, scale_factor, nfeatures);
+    for (int i = 0; i < levels; ++i)
+    {
+        scale[i]    = p.Scale(i);
+        features[i] = p.Features(i);
+    }
+}
+REF_API void ref_scale_pyramid_fn(int levels, float scale_factor, double ref_dist, int ref_level, double dist,
+                                  double* out4)
+{
+    ScalePyramid p(levels, scale_factor, 1000);
+    auto mm = p.EstimateMinMaxDistance(ref_dist, ref_level);
+    out4[0] = mm.first;
+    out4[1] = mm.second;
+    out4[2] = p.PredictScaleLevel(ref_dist, ref_level, dist);
+    out4[3] = p.ScaleForContiniousLevel(out4[2]);
+}
+REF_API void ref_umax(int* out16)
+{
+    auto u = ORBPattern::AngleUmax();
+    for (int i = 0; i < 16; ++i) out16[i] = u[i];
+}
+REF_API void ref_pattern(int* out1024)
+{
+    auto p = ORBPattern::DescriptorPattern();
+    for (int i = 0; i < 512; ++i)
+    {
+        out1024[2 * i]     = p[i].x();
+        out1024[2 * i + 1] = p[i].y();
+    }
+}
+REF_API void ref_angles(const unsigned char* img, int rows, int cols, size_t pitch, const float* xy, int n, float* out)
+{
+    ORB orb;
+    ImageView<unsigned char> view(rows, cols, pitch, (void*)img);
+    for (int i = 0; i < n; ++i) out[i] = orb.ComputeAngle(view, vec2(xy[2 * i], xy[2 * i + 1]));
+}
+REF_API void ref_descriptors(const unsigned char* img, int rows, int cols, size_t pitch, const float* xy,
+                             const float* angle, int n, uint64_t* out)
+{
+    ORB orb;
+    ImageView<unsigned char> view(rows, cols, pitch, (void*)img);
+    for (int i = 0; i < n; ++i)
+    {
+        DescriptorORB d = orb.ComputeDescriptor(view, vec2(xy[2 * i], xy[2 * i + 1]), angle[i]);
+        std::memcpy(out + 4 * (size_t)i, d.data(), 32);
+    }
+}
+static_assert(sizeof(KeyPoint<float>) == 24, "KeyPoint<float> layout");
+static_assert(sizeof(KeyPoint<double>) == 48, "KeyPoint<double> layout");
+REF_API int ref_distribute(KeyPoint<float>* kps, int n, float minx, float miny, float maxx, float maxy, int target,
+                           KeyPoint<float>* out, int cap)
+{
+    QuadtreeFeatureDistributor d;
+    auto r = d.Distribute(ArrayView<KeyPoint<float>>(kps, n), vec2(minx, miny), vec2(maxx, maxy), target);
+    for (int i = 0; i < (int)r.size() && i < cap; ++i) out[i] = r[i];
+    return (int)r.size();
+}
+REF_API int ref_distance(const uint64_t* a, const uint64_t* b)
+{
+    DescriptorORB x, y;
+    std::memcpy(x.data(), a, 32);
+    std::memcpy(y.data(), b, 32);
+    return distance(x, y);
+}
+REF_API void ref_knn2(const uint64_t* d1, int n, const uint64_t* d2, int m, int* out4)
+{
+    std::vector<DescriptorORB> a(n), b(m);
+    std::memcpy(a.data(), d1, 32 * (size_t)n);
+    std::memcpy(b.data(), d2, 32 * (size_t)m);
+    BruteForceMatcher<DescriptorORB> bf;
+    bf.matchKnn2(a, b);
+    for (int i = 0; i < n; ++i)
+    {
+        out4[4 * i]     = bf.knn2(i, 0).first;
+        out4[4 * i + 1] = bf.knn2(i, 0).second;
+        out4[4 * i + 2] = bf.knn2(i, 1).first;
+        out4[4 * i + 3] = bf.knn2(i, 1).second;
+    }
+}
+REF_API int ref_knn2_filter(const uint64_t* d1, int n, const uint64_t* d2, int m, int th, float ratio, int* ij)
+{
+    std::vector<DescriptorORB> a(n), b(m);
+    std::memcpy(a.data(), d1, 32 * (size_t)n);
+    std::memcpy(b.data(), d2, 32 * (size_t)m);
+    BruteForceMatcher<DescriptorORB> bf;
+    bf.matchKnn2(a, b);
+    int c = bf.filterMatches(th, ratio);
+    for (int i = 0; i < c; ++i)
+    {
+        ij[2 * i]     = bf.matches[i].first;
+        ij[2 * i + 1] = bf.matches[i].second;
+    }
+    return c;
+}
+// FeatureGrid2::create with explicit bounds; cells out as (begin,end) per row-major cell; returns permutation
+REF_API void ref_feature_grid(double bminx, double bminy, double bmaxx, double bmaxy, int rows, int cols,
+                              const KeyPoint<double>* kps, int n, int* permutation, int* cells)
+{
+    FeatureGridBounds2<double, 20> b;
+    b.bmin        = Vec2(bminx, bminy);
+    b.bmax        = Vec2(bmaxx, bmaxy);
+    b.cellSize    = Vec2(20, 20);
+    b.cellSizeInv = b.cellSize.array().inverse();
+    b.Rows        = rows;
+    b.Cols        = cols;
+    std::vector<KeyPoint<double>> v(kps, kps + n);
+    FeatureGrid2 g;
+    auto perm = g.create(b, v);
+    for (int i = 0; i < n; ++i) permutation[i] = perm[i];
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < cols; ++c)
+        {
+            cells[2 * (r * cols + c)]     = g.grid(r, c).first;
+            cells[2 * (r * cols + c) + 1] = g.grid(r, c).second;
+        }
+}
