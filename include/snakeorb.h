@@ -135,7 +135,8 @@ SNK_API int snk_orb_read_level(snk_orb* h, int img, int level, int blurred, uint
 SNK_API int snk_orb_read_candidates(snk_orb* h, int img, int level, uint32_t* packed, int capacity, int* n_out);
 
 /* Per-stage device time accumulated since the last reset, in milliseconds (cudaEvents on the handle's stream).
- * stage: 0 copy-in, 1 pyramid, 2 FAST, 3 distribute, 4 orientation, 5 blur, 6 descriptors, 7 total.
+ * stage: 0 copy-in, 1 pyramid, 2 FAST, 3 distribute, 4 blur, 5 orientation + descriptors + output records,
+ * 6 reserved, 7 total.
  * Profiling costs two event records per stage; it is off by default. */
 #define SNK_ORB_NUM_STAGES 8
 SNK_API int snk_orb_set_profiling(snk_orb* h, int enabled);

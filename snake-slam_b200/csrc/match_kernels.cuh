@@ -1,0 +1,246 @@
+// Hamming matching kernels. A descriptor is 256 bits = 8 x u32 held in registers; one distance is 8 LOP3 (xor) +
+// 8 POPC + 7 IADD. Every matcher reproduces the reference's tie-breaking: strict '<' keeps the first candidate in
+// the reference's iteration order.
+#pragma once
+#include "common.cuh"
+
+namespace snk
+{
+struct Desc
+{
+    uint32_t w[8];
+};
+
+__device__ __forceinline__ Desc load_desc(const uint64_t* __restrict__ p)
+{
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1];
+    return Desc{{a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w}};
+}
+__device__ __forceinline__ int hamming(const Desc& a, const Desc& b)
+{
+    int d = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d += __popc(a.w[i] ^ b.w[i]);
+    return d;
+}
+
+// Saiga::distance for n independent pairs (Features.h:124-138)
+__global__ void k_hamming_pairs(const uint64_t* __restrict__ a, const uint64_t* __restrict__ b, int n, int* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = hamming(load_desc(a + 4 * (size_t)i), load_desc(b + 4 * (size_t)i));
+}
+
+// --------------------------------------------------------------------------------------------------------------
+// BruteForceMatcher::matchKnn2 (Features.h:323-354). One thread per query keeps the query in registers and walks the
+// train set in ascending j (tiles staged in shared memory, read as broadcasts), so strict '<' picks exactly the
+// reference's first minimum and its second-best.
+// --------------------------------------------------------------------------------------------------------------
+constexpr int KNN_NT = 128, KNN_TILE = 128;
+
+__global__ void __launch_bounds__(KNN_NT) k_knn2(const uint64_t* __restrict__ d1, const int* __restrict__ n_arr, int n_fixed,
+                                                 int stride1, const uint64_t* __restrict__ d2,
+                                                 const int* __restrict__ m_arr, int m_fixed, int stride2,
+                                                 snk_knn2* __restrict__ out)
+{
+    __shared__ uint4 tile[KNN_TILE][2];
+    const int prob = blockIdx.y;
+    const int n    = n_arr ? n_arr[prob] : n_fixed;
+    const int m    = m_arr ? m_arr[prob] : m_fixed;
+    const int i    = blockIdx.x * KNN_NT + threadIdx.x;
+    if (blockIdx.x * KNN_NT >= n) return;
+    const uint64_t* q1 = d1 + 4 * (size_t)prob * stride1;
+    const uint64_t* q2 = d2 + 4 * (size_t)prob * stride2;
+    Desc q{};
+    if (i < n) q = load_desc(q1 + 4 * (size_t)i);
+    int b0 = 1000, i0 = -1, b1 = 1000, i1 = -1;
+    for (int base = 0; base < m; base += KNN_TILE)
+    {
+        const int cnt = min(KNN_TILE, m - base);
+        __syncthreads();
+        for (int k = threadIdx.x; k < 2 * cnt; k += KNN_NT)
+            tile[k >> 1][k & 1] = reinterpret_cast<const uint4*>(q2 + 4 * (size_t)base)[k];
+        __syncthreads();
+        for (int j = 0; j < cnt; ++j)
+        {
+            const uint4 a = tile[j][0], b = tile[j][1];
+            const int d = __popc(q.w[0] ^ a.x) + __popc(q.w[1] ^ a.y) + __popc(q.w[2] ^ a.z) + __popc(q.w[3] ^ a.w) +
+                          __popc(q.w[4] ^ b.x) + __popc(q.w[5] ^ b.y) + __popc(q.w[6] ^ b.z) + __popc(q.w[7] ^ b.w);
+            if (d < b0)
+            {
+                b1 = b0, i1 = i0;
+                b0 = d, i0 = base + j;
+            }
+            else if (d < b1)
+            {
+                b1 = d, i1 = base + j;
+            }
+        }
+    }
+    if (i < n) out[(size_t)prob * stride1 + i] = snk_knn2{b0, i0, b1, i1};
+}
+
+// --------------------------------------------------------------------------------------------------------------
+// Preprocess::StereoMatching (Snake/Preprocess/Preprocess.cpp:152-239). One CTA per stereo pair.
+// The reference buckets right keypoints by iRound(y) and scans rows y-r..y+r, each bucket in ascending index: the
+// candidate order is (row, index). Here the right keypoints are sorted by that key in shared memory (bitonic), each
+// left keypoint binary-searches its first row and walks the sorted run — same candidates, same order.
+// --------------------------------------------------------------------------------------------------------------
+constexpr int ST_NT = 256;
+
+__device__ __forceinline__ int iround_f(float v) { return (int)__fadd_rn(v, v >= 0.f ? 0.5f : -0.5f); }
+
+template <typename KP>
+__global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, const uint64_t* __restrict__ desc,
+                                                  const int* __restrict__ counts, int stride, int nl_fixed, int nr_fixed,
+                                                  snk_stereo_params prm, int sort_cap, float* __restrict__ right_points,
+                                                  float* __restrict__ depth, int* __restrict__ n_matches,
+                                                  int* __restrict__ err)
+{
+    extern __shared__ uint32_t keys[];  // sort_cap entries: (iRound(y) + 32768) << 16 | index
+    __shared__ int s_matches;
+    const int pair = blockIdx.x;
+    // layout: left image = entry 2*pair, right image = entry 2*pair+1 of [..][stride] arrays
+    const KP* L           = kps + (size_t)(2 * pair) * stride;
+    const KP* R           = kps + (size_t)(2 * pair + 1) * stride;
+    const uint64_t* DL    = desc + 4 * (size_t)(2 * pair) * stride;
+    const uint64_t* DR    = desc + 4 * (size_t)(2 * pair + 1) * stride;
+    const int nl          = counts ? counts[2 * pair] : nl_fixed;
+    const int nr          = counts ? counts[2 * pair + 1] : nr_fixed;
+    float* rp             = right_points + (size_t)pair * stride;
+    float* dp             = depth + (size_t)pair * stride;
+    const int tid         = threadIdx.x;
+    if (tid == 0) s_matches = 0;
+    for (int i = tid; i < nl; i += ST_NT) rp[i] = dp[i] = -1000.f;  // Frame::allocateTmp (Snake/Map/Frame.cpp:25-26)
+    if (nr > sort_cap)
+    {
+        if (tid == 0) atomicExch(err, 1);
+        return;
+    }
+    int np2 = 1;
+    while (np2 < nr) np2 <<= 1;
+    for (int i = tid; i < np2; i += ST_NT)
+    {
+        uint32_t k = 0xffffffffu;
+        if (i < nr)
+        {
+            const int row = iround_f((float)R[i].y);
+            if (row < -32768 || row > 32766) atomicExch(err, 2);
+            k = ((uint32_t)(row + 32768) << 16) | (uint32_t)i;
+        }
+        keys[i] = k;
+    }
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1)
+        {
+            for (int i = tid; i < np2; i += ST_NT)
+            {
+                const int ixj = i ^ j;
+                if (ixj > i)
+                {
+                    const uint32_t a = keys[i], b = keys[ixj];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up)
+                    {
+                        keys[i]   = b;
+                        keys[ixj] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+
+    const float min_disp = 0.f;
+    const float max_disp = (float)(prm.bf * 0.5);
+    const int th_dist    = prm.relaxed ? 75 : 40;
+    const double ratio   = prm.relaxed ? 0.9 : 0.7;
+    const float th_rot   = prm.relaxed ? 25.f : 5.f;
+    int local = 0;
+    for (int i = tid; i < nl; i += ST_NT)
+    {
+        const double lx = (double)L[i].x;
+        const int oct   = L[i].octave;
+        const int y     = iround_f((float)L[i].y);
+        const float r   = (float)ceil(2.0f * prm.scale[oct]);  // float * double -> double, ceil, narrowed to float
+        const int row_lo = y - (int)r, row_hi = y + (int)r;
+        // lower_bound of (row_lo, 0)
+        const uint32_t klo = (uint32_t)(max(row_lo, -32768) + 32768) << 16;
+        int lo = 0, hi = nr;
+        while (lo < hi)
+        {
+            const int mid = (lo + hi) >> 1;
+            if (keys[mid] < klo)
+                lo = mid + 1;
+            else
+                hi = mid;
+        }
+        const Desc q = load_desc(DL + 4 * (size_t)i);
+        int best_id = -1, best = 250, second = 250;
+        for (int k = lo; k < nr; ++k)
+        {
+            const uint32_t key = keys[k];
+            if ((int)(key >> 16) - 32768 > row_hi) break;
+            const int o = (int)(key & 0xffffu);
+            const double disparity = lx - (double)R[o].x;
+            if (disparity < min_disp || disparity > max_disp) continue;
+            if (abs(oct - R[o].octave) > 1) continue;
+            const int d = hamming(q, load_desc(DR + 4 * (size_t)o));
+            if (d < best)
+            {
+                second  = best;
+                best    = d;
+                best_id = o;
+            }
+            else if (d < second)
+                second = d;
+        }
+        if (best > th_dist) continue;
+        if ((double)best > ratio * (double)second) continue;
+        const double a1 = (double)L[i].angle, a2 = (double)R[best_id].angle;
+        // the reference really adds 365 (sic), Preprocess.cpp:216-217
+        const float rot = (float)fmin(fabs(a1 - a2), fmin(fabs((a1 + 365) - a2), fabs(a1 - (a2 + 365))));
+        if (rot > th_rot) continue;
+        double right_point = (double)R[best_id].x;
+        double disparity   = lx - right_point;
+        if (disparity <= 0.001)
+        {
+            disparity   = 0.001;
+            right_point = lx - disparity;
+        }
+        rp[i] = (float)right_point;
+        dp[i] = (float)(prm.bf / disparity);
+        ++local;
+    }
+    local = warp_sum(local);
+    if ((tid & 31) == 0 && local) atomicAdd(&s_matches, local);
+    __syncthreads();
+    if (tid == 0) n_matches[pair] = s_matches;
+}
+
+// --------------------------------------------------------------------------------------------------------------
+// popc issue-rate probe: 256-bit distances between register-resident operands (denominator of the matcher roofline)
+// --------------------------------------------------------------------------------------------------------------
+__global__ void k_popc_peak(int iters, unsigned seed, int* __restrict__ sink)
+{
+    uint32_t a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+    {
+        a[k] = seed * (2654435761u + k) + threadIdx.x * 40503u + blockIdx.x;
+        b[k] = a[k] ^ (0x9e3779b9u * (k + 1));
+    }
+    int acc = 0;
+    for (int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+        {
+            b[k] ^= b[(k + 1) & 7] + it;  // new operand every iteration, stays in registers
+            acc += __popc(a[k] ^ b[k]);
+        }
+    }
+    if (acc == 0x7fffffff) sink[0] = acc;
+}
+}  // namespace snk

@@ -1,0 +1,285 @@
+// Host side of the matching context (snk_ctx) and the matcher entry points of include/snakeorb.h.
+#include "match_kernels.cuh"
+#include "project_kernels.cuh"
+
+#include <algorithm>
+#include <vector>
+
+using namespace snk;
+
+struct snk_ctx
+{
+    int device              = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    // growable device scratch, carved sequentially per call
+    unsigned char* d_buf = nullptr;
+    size_t d_cap         = 0;
+    int* d_err           = nullptr;
+    int* h_pin           = nullptr;  // pinned, 16 ints
+};
+
+namespace
+{
+int ctx_reserve(snk_ctx* c, size_t bytes)
+{
+    if (bytes <= c->d_cap) return SNK_OK;
+    SNK_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->d_buf) SNK_CUDA(cudaFree(c->d_buf));
+    c->d_buf = nullptr;
+    c->d_cap = 0;
+    size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
+    SNK_CUDA(cudaMalloc(&c->d_buf, cap));
+    c->d_cap = cap;
+    return SNK_OK;
+}
+
+struct Carver
+{
+    unsigned char* base;
+    size_t off = 0;
+    template <typename T>
+    T* take(size_t n)
+    {
+        off     = align_up(off, (size_t)256);
+        T* p    = reinterpret_cast<T*>(base + off);
+        off += n * sizeof(T);
+        return p;
+    }
+};
+template <typename T>
+size_t padded(size_t n)
+{
+    return align_up(n * sizeof(T), (size_t)256) + 256;
+}
+
+int check_err(snk_ctx* c, const char* what)
+{
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin, c->d_err, 4, cudaMemcpyDeviceToHost, c->stream));
+    SNK_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->h_pin[0])
+    {
+        set_error("%s: capacity error %d", what, c->h_pin[0]);
+        cudaMemsetAsync(c->d_err, 0, 4, c->stream);
+        return SNK_ERR_CAPACITY;
+    }
+    return SNK_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int snk_ctx_create(int device, snk_ctx** out)
+{
+    SNK_REQUIRE(out, "null argument");
+    int rc = select_device(device);
+    if (rc) return rc;
+    snk_ctx* c = new snk_ctx;
+    c->device  = device;
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMalloc(&c->d_err, 4) != cudaSuccess || cudaMemset(c->d_err, 0, 4) != cudaSuccess ||
+        cudaHostAlloc(&c->h_pin, 64, cudaHostAllocDefault) != cudaSuccess)
+    {
+        set_error("context setup failed: %s", cudaGetErrorString(cudaGetLastError()));
+        delete c;
+        return SNK_ERR_CUDA;
+    }
+    c->stream = c->own_stream;
+    *out      = c;
+    return SNK_OK;
+}
+
+void snk_ctx_destroy(snk_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->d_buf) cudaFree(c->d_buf);
+    if (c->d_err) cudaFree(c->d_err);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+int snk_ctx_set_stream(snk_ctx* c, void* s)
+{
+    SNK_REQUIRE(c, "null context");
+    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    return SNK_OK;
+}
+
+int snk_hamming_pairs(snk_ctx* c, const uint64_t* a, const uint64_t* b, int n, int32_t* dist)
+{
+    SNK_REQUIRE(c && a && b && dist && n >= 0, "bad argument");
+    if (n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, 2 * padded<uint64_t>(4 * (size_t)n) + padded<int>(n));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    uint64_t* da = cv.take<uint64_t>(4 * (size_t)n);
+    uint64_t* db = cv.take<uint64_t>(4 * (size_t)n);
+    int* dd      = cv.take<int>(n);
+    SNK_CUDA(cudaMemcpyAsync(da, a, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    SNK_CUDA(cudaMemcpyAsync(db, b, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    k_hamming_pairs<<<(n + 255) / 256, 256, 0, c->stream>>>(da, db, n, dd);
+    SNK_CUDA(cudaMemcpyAsync(dist, dd, 4 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    SNK_CUDA(cudaStreamSynchronize(c->stream));
+    return SNK_OK;
+}
+
+int snk_match_knn2_batch_device(snk_ctx* c, const uint64_t* d1, const int32_t* n_dev, int stride1, const uint64_t* d2,
+                                const int32_t* m_dev, int stride2, int n_problems, snk_knn2* out)
+{
+    SNK_REQUIRE(c && d1 && d2 && out && n_dev && m_dev && n_problems >= 0, "bad argument");
+    if (n_problems == 0 || stride1 == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    k_knn2<<<dim3((stride1 + KNN_NT - 1) / KNN_NT, n_problems), KNN_NT, 0, c->stream>>>(d1, n_dev, 0, stride1, d2, m_dev,
+                                                                                        0, stride2, out);
+    SNK_CUDA(cudaGetLastError());
+    return SNK_OK;
+}
+
+int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t* d2, int m, snk_knn2* out)
+{
+    SNK_REQUIRE(c && out && n >= 0 && m >= 0 && (n == 0 || d1) && (m == 0 || d2), "bad argument");
+    if (n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, padded<uint64_t>(4 * (size_t)n) + padded<uint64_t>(4 * (size_t)std::max(m, 1)) + padded<snk_knn2>(n));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    uint64_t* a = cv.take<uint64_t>(4 * (size_t)n);
+    uint64_t* b = cv.take<uint64_t>(4 * (size_t)std::max(m, 1));
+    snk_knn2* o = cv.take<snk_knn2>(n);
+    SNK_CUDA(cudaMemcpyAsync(a, d1, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    if (m) SNK_CUDA(cudaMemcpyAsync(b, d2, 32 * (size_t)m, cudaMemcpyHostToDevice, c->stream));
+    k_knn2<<<dim3((n + KNN_NT - 1) / KNN_NT, 1), KNN_NT, 0, c->stream>>>(a, nullptr, n, n, b, nullptr, m, m, o);
+    SNK_CUDA(cudaMemcpyAsync(out, o, sizeof(snk_knn2) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    SNK_CUDA(cudaStreamSynchronize(c->stream));
+    return SNK_OK;
+}
+
+// BruteForceMatcher::filterMatches (Features.h:394-414): a serial pass over n small records on the caller's thread —
+// it is host bookkeeping in the reference too (the result is a std::vector built in index order).
+int snk_filter_matches(const snk_knn2* k, int n, int threshold, float ratio, int32_t* ij, int* n_matches)
+{
+    SNK_REQUIRE(k && ij && n_matches && n >= 0, "bad argument");
+    int cnt = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        if (k[i].dist0 > threshold) continue;
+        if (float(k[i].dist0) > float(k[i].dist1) * ratio) continue;
+        ij[2 * cnt]     = i;
+        ij[2 * cnt + 1] = k[i].idx0;
+        ++cnt;
+    }
+    *n_matches = cnt;
+    return SNK_OK;
+}
+
+static int stereo_smem(int sort_cap) { return sort_cap * 4; }
+
+int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
+                     const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points, float* depth,
+                     int* n_matches)
+{
+    SNK_REQUIRE(c && p && n_matches && nl >= 0 && nr >= 0, "bad argument");
+    SNK_REQUIRE(nl == 0 || (left && dl && right_points && depth), "null left arrays");
+    SNK_REQUIRE(nr == 0 || (right && dr), "null right arrays");
+    SNK_REQUIRE(p->nlevels >= 1 && p->nlevels <= 16, "bad nlevels");
+    *n_matches = 0;
+    if (nl == 0) return SNK_OK;
+    if (nr == 0)
+    {
+        for (int i = 0; i < nl; ++i) right_points[i] = depth[i] = -1000.f;
+        return SNK_OK;
+    }
+    for (int i = 0; i < nl; ++i) SNK_REQUIRE(left[i].octave >= 0 && left[i].octave < p->nlevels, "octave out of range");
+    SNK_REQUIRE(nr <= 16384, "more than 16384 right keypoints");
+    SNK_CUDA(cudaSetDevice(c->device));
+    const int stride = std::max(nl, nr);
+    int rc = ctx_reserve(c, padded<snk_keypoint_f64>(2 * (size_t)stride) + padded<uint64_t>(8 * (size_t)stride) +
+                                2 * padded<float>(stride) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    snk_keypoint_f64* dk = cv.take<snk_keypoint_f64>(2 * (size_t)stride);
+    uint64_t* dd         = cv.take<uint64_t>(8 * (size_t)stride);
+    float* drp           = cv.take<float>(stride);
+    float* ddp           = cv.take<float>(stride);
+    int* dn              = cv.take<int>(4);
+    cudaStream_t st      = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(dk, left, sizeof(snk_keypoint_f64) * (size_t)nl, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(dk + stride, right, sizeof(snk_keypoint_f64) * (size_t)nr, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(dd, dl, 32 * (size_t)nl, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(dd + 4 * (size_t)stride, dr, 32 * (size_t)nr, cudaMemcpyHostToDevice, st));
+    int cap = 1;
+    while (cap < nr) cap <<= 1;
+    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+    k_stereo<snk_keypoint_f64><<<1, ST_NT, stereo_smem(cap), st>>>(dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn,
+                                                                  c->d_err);
+    SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    rc = check_err(c, "stereo_match");
+    if (rc) return rc;
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_stereo_params* p, float* right_points,
+                                float* depth, int32_t* n_matches)
+{
+    SNK_REQUIRE(c && h && p && right_points && depth && n_matches && n_pairs >= 0, "bad argument");
+    if (n_pairs == 0) return SNK_OK;
+    const snk_keypoint_f32* kps;
+    const uint64_t* desc;
+    const int32_t* counts;
+    int stride;
+    int rc = snk_orb_device_results(h, &kps, &desc, &counts, &stride);
+    if (rc) return rc;
+    SNK_CUDA(cudaSetDevice(c->device));
+    int cap = 1;
+    while (cap < stride) cap <<= 1;
+    SNK_REQUIRE(cap <= 16384, "more than 16384 keypoints per image");
+    static bool attr_set = false;
+    if (!attr_set)
+    {
+        SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+        attr_set = true;
+    }
+    k_stereo<snk_keypoint_f32><<<n_pairs, ST_NT, stereo_smem(cap), c->stream>>>(kps, desc, counts, stride, 0, 0, *p, cap,
+                                                                               right_points, depth, n_matches, c->d_err);
+    SNK_CUDA(cudaGetLastError());
+    return SNK_OK;
+}
+
+int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s)
+{
+    SNK_REQUIRE(c && pair_ops_per_s, "bad argument");
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, 256);
+    if (rc) return rc;
+    cudaDeviceProp prop;
+    SNK_CUDA(cudaGetDeviceProperties(&prop, c->device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 20000;
+    cudaEvent_t e0, e1;
+    SNK_CUDA(cudaEventCreate(&e0));
+    SNK_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep)
+    {
+        SNK_CUDA(cudaEventRecord(e0, c->stream));
+        k_popc_peak<<<blocks, threads, 0, c->stream>>>(iters, 12345u + rep, reinterpret_cast<int*>(c->d_buf));
+        SNK_CUDA(cudaEventRecord(e1, c->stream));
+        SNK_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        SNK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep) best = std::max(best, (double)blocks * threads * iters / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *pair_ops_per_s = best;
+    return SNK_OK;
+}
+
+}  // extern "C"
+
+#include "project_host.inl"

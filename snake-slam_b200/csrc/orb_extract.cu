@@ -1,0 +1,633 @@
+// Host side of the ORB extractor handle (snk_orb): geometry tables, device memory, launch sequence.
+// Mirrors Saiga::ORBExtractor (saiga/vision/features/ORBExtractor.cpp:82-289) stage by stage; see orb_kernels.cuh.
+#include "orb_kernels.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#define SNK_PATTERN_QUAL static const
+#include "../../include/snakeorb_pattern.h"
+
+namespace snk
+{
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int select_device(int device)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+    {
+        set_error("no CUDA device: %s (libsnakeorb has no CPU fallback)", cudaGetErrorString(e));
+        return SNK_ERR_CUDA;
+    }
+    if (device < 0 || device >= n)
+    {
+        set_error("device %d out of range (%d devices)", device, n);
+        return SNK_ERR_INVALID;
+    }
+    SNK_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    SNK_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+    {
+        set_error("device %d is sm_%d%d; libsnakeorb is built for sm_100a only", device, prop.major, prop.minor);
+        return SNK_ERR_UNSUPPORTED;
+    }
+    return SNK_OK;
+}
+
+// Saiga::iRound (saiga/core/math/imath.h:73)
+static inline int iround_f(float v) { return (int)(v + (v >= 0 ? 0.5f : -0.5f)); }
+
+// cv::resize INTER_LINEAR coefficient tables (11-bit); x taps get the fraction zeroed at the borders, y taps do not
+static void resize_tables(int ssize, int dsize, std::vector<int>& ofs, std::vector<short>& coef, bool clamp_coef)
+{
+    ofs.resize(dsize);
+    coef.resize(2 * (size_t)dsize);
+    const double scale = 1.0 / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; ++d)
+    {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s   = (int)std::floor(f);
+        f -= s;
+        if (clamp_coef)
+        {
+            if (s < 0) f = 0, s = 0;
+            if (s >= ssize - 1) f = 0, s = ssize - 1;
+        }
+        ofs[d]          = s;
+        coef[2 * d]     = (short)std::lrintf((1.f - f) * 2048.f);
+        coef[2 * d + 1] = (short)std::lrintf(f * 2048.f);
+    }
+}
+}  // namespace snk
+
+using namespace snk;
+
+struct snk_orb
+{
+    snk_orb_params prm{};
+    // ScalePyramid (saiga/vision/util/ScalePyramid.cpp:16-55)
+    double scale[SNK_MAX_LEVELS]{}, inv_scale[SNK_MAX_LEVELS]{};
+    int features[SNK_MAX_LEVELS]{};
+    int max_kp = 0;
+
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    int rows = 0, cols = 0;  // geometry the buffers are sized for (0 = none yet)
+    int last_n = 0;
+
+    PyrDev P{};
+    std::vector<CellDev> cells;
+    std::vector<TileDev> tiles;
+    int node_cap = 0;
+    size_t qt_smem = 0;
+
+    uint8_t* d_pyr = nullptr;    // levels 0..L-1 (level 0 unused when the caller's device buffer is aliased)
+    uint8_t* d_gauss = nullptr;
+    LevelDev own_l0{};           // level-0 descriptor of the internal buffer
+    int *d_xofs[SNK_MAX_LEVELS]{}, *d_yofs[SNK_MAX_LEVELS]{};
+    short *d_xa[SNK_MAX_LEVELS]{}, *d_yb[SNK_MAX_LEVELS]{};
+    CellDev* d_cells = nullptr;
+    TileDev* d_tiles = nullptr;
+    uint32_t *d_cand = nullptr, *d_workA = nullptr, *d_workB = nullptr, *d_sel = nullptr;
+    int *d_cell_count = nullptr, *d_cell_off = nullptr, *d_sel_count = nullptr, *d_counts = nullptr, *d_err = nullptr;
+    snk_keypoint_f32* d_kps = nullptr;
+    uint64_t* d_desc = nullptr;
+    int* h_counts = nullptr;  // pinned
+    int* h_err = nullptr;     // pinned
+
+    bool profiling = false;
+    cudaEvent_t ev[SNK_ORB_NUM_STAGES + 1]{};
+    float stage_ms[SNK_ORB_NUM_STAGES]{};
+    int stage_launches[SNK_ORB_NUM_STAGES]{};
+    bool ev_pending = false;
+    int pending_launches[SNK_ORB_NUM_STAGES]{};
+
+    void free_buffers()
+    {
+        auto F = [](auto*& p) {
+            if (p) cudaFree(p);
+            p = nullptr;
+        };
+        F(d_pyr), F(d_gauss), F(d_cells), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
+            F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
+        for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_xofs[l]), F(d_yofs[l]), F(d_xa[l]), F(d_yb[l]);
+        rows = cols = 0;
+    }
+};
+
+static int orb_allocate(snk_orb* h, int rows, int cols)
+{
+    if (h->rows == rows && h->cols == cols) return SNK_OK;
+    h->free_buffers();
+    const int L = h->prm.nlevels, B = h->prm.max_batch;
+    SNK_REQUIRE(rows <= 4000 && cols <= 4000, "image %dx%d too large (max 4000x4000)", cols, rows);
+    PyrDev& P = h->P;
+    memset(&P, 0, sizeof(P));
+    P.nlevels = L;
+    P.th_ini  = h->prm.th_fast;
+    P.th_min  = h->prm.th_fast_min;
+
+    // level sizes (ORBExtractor::AllocatePyramid, ORBExtractor.cpp:244-246) and FAST cell grid (:99-127)
+    h->cells.clear();
+    h->tiles.clear();
+    size_t pyr_bytes = 0, gauss_bytes = 0;
+    std::vector<size_t> pyr_off(L), gauss_off(L);
+    int cell_cap = 1, sel_acc = 0;
+    for (int l = 0; l < L; ++l)
+    {
+        LevelDev& lv   = P.lv[l];
+        const float s  = (float)h->inv_scale[l];
+        lv.h           = iround_f(rows * s);
+        lv.w           = iround_f(cols * s);
+        const int minB = 16, maxBX = lv.w - 16, maxBY = lv.h - 16;
+        const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+        const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f);
+        SNK_REQUIRE(nCols >= 1 && nRows >= 1,
+                    "level %d is %dx%d: too small for the 30-px FAST cell grid (the reference divides by zero here); "
+                    "use fewer levels",
+                    l, lv.w, lv.h);
+        const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
+        lv.pitch = lv.gauss_pitch = align_up(lv.w, 64);
+        lv.img_stride = lv.gauss_stride = (size_t)lv.pitch * lv.h;
+        pyr_off[l]   = pyr_bytes;
+        gauss_off[l] = gauss_bytes;
+        pyr_bytes += align_up(lv.img_stride * B, (size_t)256);
+        gauss_bytes += align_up(lv.gauss_stride * B, (size_t)256);
+        lv.quota     = h->features[l];
+        lv.scale     = (float)h->scale[l];
+        lv.size      = (float)(int)(31 * h->scale[l]);
+        lv.cell_base = (int)h->cells.size();
+        for (int i = 0; i < nRows; ++i)
+        {
+            const int iniY = minB + i * hCell;
+            int maxY       = iniY + hCell + 6;
+            if (iniY >= maxBY - 3) continue;
+            if (maxY > maxBY) maxY = maxBY;
+            for (int j = 0; j < nCols; ++j)
+            {
+                const int iniX = minB + j * wCell;
+                int maxX       = iniX + wCell + 6;
+                if (iniX >= maxBX - 6) continue;
+                if (maxX > maxBX) maxX = maxBX;
+                CellDev c{(short)l, (short)iniX, (short)iniY, (short)(maxX - iniX), (short)(maxY - iniY),
+                          (short)(j * wCell), (short)(i * hCell), 0};
+                SNK_REQUIRE(c.w <= FAST_DIM && c.h <= FAST_DIM, "internal: cell %dx%d exceeds the tile", c.w, c.h);
+                h->cells.push_back(c);
+                // NMS survivors are strict local maxima inside the zone: no two are 8-neighbours
+                const int zw = std::max(c.w - 6, 0), zh = std::max(c.h - 6, 0);
+                cell_cap = std::max(cell_cap, ((zw + 1) / 2) * ((zh + 1) / 2));
+            }
+        }
+        lv.n_cells  = (int)h->cells.size() - lv.cell_base;
+        lv.sel_base = sel_acc;
+        sel_acc += lv.quota + 4;
+        for (int ty = 0; ty < (lv.h + BL_TH - 1) / BL_TH; ++ty)
+            for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
+    }
+    P.cells_per_img = (int)h->cells.size();
+    P.cell_cap      = cell_cap;
+    SNK_REQUIRE((size_t)P.cells_per_img * cell_cap < (1u << 30), "image too large for the candidate arrays");
+    P.cand_per_img = P.cells_per_img * cell_cap;
+    for (int l = 0; l < L; ++l) P.lv[l].cand_base = P.lv[l].cell_base * cell_cap;
+    P.sel_per_img = sel_acc;
+    P.kp_stride   = h->max_kp;
+
+    int max_quota = 0;
+    for (int l = 0; l < L; ++l) max_quota = std::max(max_quota, h->features[l]);
+    h->node_cap = max_quota + 8;
+    SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
+    h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES;
+    SNK_REQUIRE(h->qt_smem <= 200 * 1024, "nfeatures too large for the distribution kernel's shared memory");
+    SNK_CUDA(cudaFuncSetAttribute(k_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
+
+    SNK_CUDA(cudaMalloc(&h->d_pyr, pyr_bytes));
+    SNK_CUDA(cudaMalloc(&h->d_gauss, gauss_bytes));
+    for (int l = 0; l < L; ++l)
+    {
+        P.lv[l].img   = h->d_pyr + pyr_off[l];
+        P.lv[l].gauss = h->d_gauss + gauss_off[l];
+    }
+    h->own_l0 = P.lv[0];
+    for (int l = 1; l < L; ++l)
+    {
+        std::vector<int> xo, yo;
+        std::vector<short> xa, yb;
+        resize_tables(P.lv[l - 1].w, P.lv[l].w, xo, xa, true);
+        resize_tables(P.lv[l - 1].h, P.lv[l].h, yo, yb, false);
+        // the resize kernel stages a fixed-size source window per output tile
+        for (int t0 = 0; t0 < P.lv[l].w; t0 += RS_TW)
+        {
+            int t1 = std::min(t0 + RS_TW, P.lv[l].w) - 1;
+            SNK_REQUIRE(xo[t1] + 1 - xo[t0] + 1 <= RS_SW, "scale factor %.3f not supported (max 1.3)", h->prm.scale_factor);
+        }
+        for (int t0 = 0; t0 < P.lv[l].h; t0 += RS_TH)
+        {
+            int t1 = std::min(t0 + RS_TH, P.lv[l].h) - 1;
+            SNK_REQUIRE(yo[t1] + 1 - yo[t0] + 1 <= RS_SH, "scale factor %.3f not supported (max 1.3)", h->prm.scale_factor);
+        }
+        SNK_CUDA(cudaMalloc(&h->d_xofs[l], xo.size() * sizeof(int)));
+        SNK_CUDA(cudaMalloc(&h->d_yofs[l], yo.size() * sizeof(int)));
+        SNK_CUDA(cudaMalloc(&h->d_xa[l], xa.size() * sizeof(short)));
+        SNK_CUDA(cudaMalloc(&h->d_yb[l], yb.size() * sizeof(short)));
+        SNK_CUDA(cudaMemcpy(h->d_xofs[l], xo.data(), xo.size() * sizeof(int), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMemcpy(h->d_yofs[l], yo.data(), yo.size() * sizeof(int), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMemcpy(h->d_xa[l], xa.data(), xa.size() * sizeof(short), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMemcpy(h->d_yb[l], yb.data(), yb.size() * sizeof(short), cudaMemcpyHostToDevice));
+    }
+    SNK_CUDA(cudaMalloc(&h->d_cells, h->cells.size() * sizeof(CellDev)));
+    SNK_CUDA(cudaMemcpy(h->d_cells, h->cells.data(), h->cells.size() * sizeof(CellDev), cudaMemcpyHostToDevice));
+    SNK_CUDA(cudaMalloc(&h->d_tiles, h->tiles.size() * sizeof(TileDev)));
+    SNK_CUDA(cudaMemcpy(h->d_tiles, h->tiles.data(), h->tiles.size() * sizeof(TileDev), cudaMemcpyHostToDevice));
+    const size_t cand_n = (size_t)B * P.cand_per_img;
+    SNK_CUDA(cudaMalloc(&h->d_cand, cand_n * 4));
+    SNK_CUDA(cudaMalloc(&h->d_workA, cand_n * 4));
+    SNK_CUDA(cudaMalloc(&h->d_workB, cand_n * 4));
+    SNK_CUDA(cudaMalloc(&h->d_cell_count, (size_t)B * P.cells_per_img * 4));
+    SNK_CUDA(cudaMalloc(&h->d_cell_off, (size_t)B * P.cells_per_img * 4));
+    SNK_CUDA(cudaMalloc(&h->d_sel, (size_t)B * P.sel_per_img * 4));
+    SNK_CUDA(cudaMalloc(&h->d_sel_count, (size_t)B * L * 4));
+    SNK_CUDA(cudaMalloc(&h->d_counts, (size_t)B * 4));
+    SNK_CUDA(cudaMalloc(&h->d_err, 4));
+    SNK_CUDA(cudaMemset(h->d_err, 0, 4));
+    SNK_CUDA(cudaMalloc(&h->d_kps, (size_t)B * P.kp_stride * sizeof(snk_keypoint_f32)));
+    SNK_CUDA(cudaMalloc(&h->d_desc, (size_t)B * P.kp_stride * 32));
+    h->rows = rows;
+    h->cols = cols;
+    return SNK_OK;
+}
+
+extern "C" {
+
+const char* snk_last_error(void) { return g_err; }
+const char* snk_version(void) { return "snakeorb 0.1 (sm_100a)"; }
+
+int snk_orb_create(const snk_orb_params* p, snk_orb** out)
+{
+    SNK_REQUIRE(p && out, "null argument");
+    SNK_REQUIRE(p->nlevels >= 1 && p->nlevels <= SNK_MAX_LEVELS, "nlevels must be in 1..%d", SNK_MAX_LEVELS);
+    SNK_REQUIRE(p->nfeatures >= 1, "nfeatures must be positive");
+    SNK_REQUIRE(p->scale_factor > 1.0f && p->scale_factor <= 1.3f, "scale_factor must be in (1, 1.3]");
+    SNK_REQUIRE(p->th_fast >= 1 && p->th_fast <= 254 && p->th_fast_min >= 0 && p->th_fast_min <= 254,
+                "FAST thresholds out of range");
+    SNK_REQUIRE(p->max_batch >= 1, "max_batch must be >= 1");
+    int rc = select_device(p->device);
+    if (rc) return rc;
+    snk_orb* h = new snk_orb;
+    h->prm     = *p;
+    // ScalePyramid::ScalePyramid (saiga/vision/util/ScalePyramid.cpp:16-55); scale_factor is a float widened to double
+    const int L       = p->nlevels;
+    const double sf   = (double)p->scale_factor;
+    const double fac  = 1.0 / sf;
+    double per_level  = p->nfeatures * (1 - fac) / (1 - std::pow(fac, (double)L));
+    int sum           = 0;
+    h->scale[0] = h->inv_scale[0] = 1;
+    for (int i = 0; i < L - 1; ++i)
+    {
+        h->features[i] = iround_f((float)per_level);
+        sum += h->features[i];
+        per_level *= fac;
+    }
+    for (int i = 1; i < L; ++i)
+    {
+        h->scale[i]     = sf * h->scale[i - 1];
+        h->inv_scale[i] = 1 / h->scale[i];
+    }
+    h->features[L - 1] = std::max(p->nfeatures - sum, 0);
+    h->max_kp          = 0;
+    for (int i = 0; i < L; ++i) h->max_kp += h->features[i] + 3;  // Distribute returns at most quota + 3
+    if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess)
+    {
+        set_error("cudaStreamCreate failed");
+        delete h;
+        return SNK_ERR_CUDA;
+    }
+    h->stream = h->own_stream;
+    cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault);
+    cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault);
+    for (auto& e : h->ev) cudaEventCreate(&e);
+    // constants of the descriptor kernel
+    int umax[16];
+    {
+        // ORBPattern::AngleUmax (saiga/vision/features/OrbPattern.cpp:16-36)
+        const int R = 15;
+        int vmax    = (int)std::floor(R * std::sqrt(2.f) / 2 + 1);
+        int vmin    = (int)std::ceil(R * std::sqrt(2.f) / 2);
+        for (int v = 0; v <= vmax; ++v) umax[v] = iround_f((float)std::sqrt((double)R * R - v * v));
+        for (int v = R, v0 = 0; v >= vmin; --v)
+        {
+            while (umax[v0] == umax[v0 + 1]) ++v0;
+            umax[v] = v0;
+            ++v0;
+        }
+    }
+    if (cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)) != cudaSuccess ||
+        cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024) != cudaSuccess)
+    {
+        set_error("constant upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+        snk_orb_destroy(h);
+        return SNK_ERR_CUDA;
+    }
+    *out = h;
+    return SNK_OK;
+}
+
+void snk_orb_destroy(snk_orb* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->prm.device);
+    cudaStreamSynchronize(h->stream);
+    h->free_buffers();
+    if (h->h_counts) cudaFreeHost(h->h_counts);
+    if (h->h_err) cudaFreeHost(h->h_err);
+    for (auto& e : h->ev)
+        if (e) cudaEventDestroy(e);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+}
+
+int snk_orb_set_stream(snk_orb* h, void* s)
+{
+    SNK_REQUIRE(h, "null handle");
+    h->stream = s ? (cudaStream_t)s : h->own_stream;
+    return SNK_OK;
+}
+
+int snk_orb_max_keypoints(const snk_orb* h) { return h ? h->max_kp : 0; }
+
+int snk_orb_pyramid(const snk_orb* h, double* scale, int32_t* features)
+{
+    SNK_REQUIRE(h, "null handle");
+    for (int i = 0; i < h->prm.nlevels; ++i)
+    {
+        if (scale) scale[i] = h->scale[i];
+        if (features) features[i] = h->features[i];
+    }
+    return SNK_OK;
+}
+
+static void collect_events(snk_orb* h)
+{
+    if (!h->ev_pending) return;
+    cudaEventSynchronize(h->ev[SNK_ORB_NUM_STAGES - 1]);
+    float total = 0;
+    for (int s = 0; s < SNK_ORB_NUM_STAGES - 1; ++s)
+    {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, h->ev[s], h->ev[s + 1]) == cudaSuccess)
+        {
+            h->stage_ms[s] += ms;
+            total += ms;
+        }
+        h->stage_launches[s] += h->pending_launches[s];
+        h->stage_launches[SNK_ORB_NUM_STAGES - 1] += h->pending_launches[s];
+    }
+    h->stage_ms[SNK_ORB_NUM_STAGES - 1] += total;
+    h->ev_pending = false;
+}
+
+int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch, size_t img_stride,
+                    int on_device)
+{
+    SNK_REQUIRE(h, "null handle");
+    SNK_REQUIRE(n_imgs >= 0 && n_imgs <= h->prm.max_batch, "n_imgs %d exceeds max_batch %d", n_imgs, h->prm.max_batch);
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    h->last_n = 0;
+    if (n_imgs == 0 || !imgs || rows <= 0 || cols <= 0) return SNK_OK;  // ORBExtractor.cpp:182 — empty image: no output
+    SNK_REQUIRE(pitch >= (size_t)cols, "pitch smaller than a row");
+    SNK_REQUIRE(n_imgs == 1 || img_stride >= pitch * rows, "img_stride smaller than an image");
+    int rc = orb_allocate(h, rows, cols);
+    if (rc) return rc;
+    collect_events(h);
+    PyrDev& P      = h->P;
+    cudaStream_t st = h->stream;
+    const bool prof = h->profiling;
+    int* nl         = h->pending_launches;
+    if (prof) memset(nl, 0, sizeof(h->pending_launches));
+    if (prof) cudaEventRecord(h->ev[0], st);
+
+    // stage 0: level 0. Device input is used in place (the reference copies it, ORBExtractor.cpp:269; nothing reads the
+    // copy's apron, so aliasing is equivalent). Host input is copied straight into the level-0 buffer.
+    if (on_device)
+    {
+        P.lv[0].img        = const_cast<uint8_t*>(imgs);
+        P.lv[0].pitch      = (int)pitch;
+        P.lv[0].img_stride = img_stride;
+    }
+    else
+    {
+        P.lv[0].img        = h->own_l0.img;
+        P.lv[0].pitch      = h->own_l0.pitch;
+        P.lv[0].img_stride = h->own_l0.img_stride;
+        if (pitch == (size_t)P.lv[0].pitch && img_stride == P.lv[0].img_stride)
+            SNK_CUDA(cudaMemcpyAsync(P.lv[0].img, imgs, img_stride * n_imgs, cudaMemcpyHostToDevice, st));
+        else if (img_stride == pitch * rows)
+            SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img, P.lv[0].pitch, imgs, pitch, cols, (size_t)rows * n_imgs,
+                                       cudaMemcpyHostToDevice, st));
+        else
+            for (int i = 0; i < n_imgs; ++i)
+                SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img + i * P.lv[0].img_stride, P.lv[0].pitch, imgs + i * img_stride,
+                                           pitch, cols, rows, cudaMemcpyHostToDevice, st));
+    }
+    if (prof) cudaEventRecord(h->ev[1], st);
+
+    // stage 1: pyramid chain
+    for (int l = 1; l < P.nlevels; ++l)
+    {
+        const LevelDev& s = P.lv[l - 1];
+        const LevelDev& d = P.lv[l];
+        dim3 grid((d.w + RS_TW - 1) / RS_TW, (d.h + RS_TH - 1) / RS_TH, n_imgs);
+        k_resize<<<grid, 256, 0, st>>>(s.img, s.img_stride, s.pitch, s.w, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
+                                       h->d_xofs[l], h->d_xa[l], h->d_yofs[l], h->d_yb[l]);
+        ++nl[1];
+    }
+    if (prof) cudaEventRecord(h->ev[2], st);
+
+    // stage 2: FAST over every cell of every level
+    k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->d_cells, h->d_cand, h->d_cell_count);
+    ++nl[2];
+    if (prof) cudaEventRecord(h->ev[3], st);
+
+    // stage 3: quadtree distribution per (level, image)
+    k_distribute<<<dim3(P.nlevels, n_imgs), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
+                                                                     h->d_workA, h->d_workB, h->d_sel, h->d_sel_count,
+                                                                     h->node_cap, h->d_err);
+    ++nl[3];
+    if (prof) cudaEventRecord(h->ev[4], st);
+
+    // stage 4: blur of every level
+    k_blur<<<dim3((unsigned)h->tiles.size(), n_imgs), 256, 0, st>>>(P, h->d_tiles);
+    ++nl[4];
+    if (prof) cudaEventRecord(h->ev[5], st);
+
+    // stage 5: orientation + descriptors + output records
+    k_describe<<<dim3((P.kp_stride + DS_WARPS - 1) / DS_WARPS, n_imgs), DS_WARPS * 32, 0, st>>>(
+        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts);
+    ++nl[5];
+    if (prof)
+    {
+        cudaEventRecord(h->ev[6], st);
+        cudaEventRecord(h->ev[7], st);
+        h->ev_pending = true;
+    }
+    SNK_CUDA(cudaGetLastError());
+    h->last_n = n_imgs;
+    return SNK_OK;
+}
+
+int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps, const uint64_t** desc, const int32_t** counts,
+                           int* stride)
+{
+    SNK_REQUIRE(h && h->rows, "no results yet");
+    if (kps) *kps = h->d_kps;
+    if (desc) *desc = h->d_desc;
+    if (counts) *counts = h->d_counts;
+    if (stride) *stride = h->P.kp_stride;
+    return SNK_OK;
+}
+
+int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out)
+{
+    SNK_REQUIRE(h && n_out, "null argument");
+    const int n = h->last_n;
+    if (n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    cudaStream_t st = h->stream;
+    const int ks    = h->P.kp_stride;
+    SNK_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (capacity >= ks && n > 1)
+    {
+        // whole-batch copies (rows of the device arrays are kp_stride records long)
+        SNK_CUDA(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(snk_keypoint_f32), h->d_kps,
+                                   (size_t)ks * sizeof(snk_keypoint_f32), (size_t)ks * sizeof(snk_keypoint_f32), n,
+                                   cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->d_desc, (size_t)ks * 32, (size_t)ks * 32, n,
+                                   cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaStreamSynchronize(st));
+    }
+    else
+    {
+        SNK_CUDA(cudaStreamSynchronize(st));
+        for (int i = 0; i < n; ++i)
+        {
+            const int c = h->h_counts[i];
+            if (c > capacity)
+            {
+                set_error("image %d has %d keypoints, capacity is %d", i, c, capacity);
+                return SNK_ERR_CAPACITY;
+            }
+            if (c == 0) continue;
+            SNK_CUDA(cudaMemcpyAsync(kps + (size_t)i * capacity, h->d_kps + (size_t)i * ks, (size_t)c * sizeof(snk_keypoint_f32),
+                                     cudaMemcpyDeviceToHost, st));
+            SNK_CUDA(cudaMemcpyAsync(desc + (size_t)i * capacity * 4, h->d_desc + (size_t)i * ks * 4, (size_t)c * 32,
+                                     cudaMemcpyDeviceToHost, st));
+        }
+        SNK_CUDA(cudaStreamSynchronize(st));
+    }
+    if (*h->h_err)
+    {
+        set_error("internal capacity error %d in the extraction kernels", *h->h_err);
+        cudaMemsetAsync(h->d_err, 0, 4, st);
+        return SNK_ERR_CAPACITY;
+    }
+    for (int i = 0; i < n; ++i) n_out[i] = h->h_counts[i];
+    return SNK_OK;
+}
+
+int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
+                         size_t img_stride, int on_device, snk_keypoint_f32* kps, uint64_t* desc, int capacity,
+                         int* n_out)
+{
+    SNK_REQUIRE(h && n_out, "null argument");
+    for (int i = 0; i < n_imgs; ++i) n_out[i] = 0;
+    int rc = snk_orb_enqueue(h, imgs, n_imgs, rows, cols, pitch, img_stride, on_device);
+    if (rc) return rc;
+    return snk_orb_fetch(h, kps, desc, capacity, n_out);
+}
+
+int snk_orb_detect(snk_orb* h, const uint8_t* img, int rows, int cols, size_t pitch, int on_device,
+                   snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out)
+{
+    return snk_orb_detect_batch(h, img, 1, rows, cols, pitch, pitch * (size_t)(rows > 0 ? rows : 0), on_device, kps,
+                                desc, capacity, n_out);
+}
+
+int snk_orb_get_level(snk_orb* h, int img, int level, int blurred, const uint8_t** ptr, int* rows, int* cols,
+                      size_t* pitch)
+{
+    SNK_REQUIRE(h && h->rows, "no image processed yet");
+    SNK_REQUIRE(level >= 0 && level < h->prm.nlevels && img >= 0 && img < h->prm.max_batch, "index out of range");
+    const LevelDev& L = h->P.lv[level];
+    if (ptr) *ptr = blurred ? L.gauss + (size_t)img * L.gauss_stride : L.img + (size_t)img * L.img_stride;
+    if (rows) *rows = L.h;
+    if (cols) *cols = L.w;
+    if (pitch) *pitch = blurred ? L.gauss_pitch : L.pitch;
+    return SNK_OK;
+}
+
+int snk_orb_read_level(snk_orb* h, int img, int level, int blurred, uint8_t* dst, size_t dst_pitch)
+{
+    const uint8_t* p;
+    int r, c;
+    size_t pitch;
+    int rc = snk_orb_get_level(h, img, level, blurred, &p, &r, &c, &pitch);
+    if (rc) return rc;
+    SNK_CUDA(cudaStreamSynchronize(h->stream));
+    SNK_CUDA(cudaMemcpy2D(dst, dst_pitch, p, pitch, c, r, cudaMemcpyDeviceToHost));
+    return SNK_OK;
+}
+
+int snk_orb_read_candidates(snk_orb* h, int img, int level, uint32_t* packed, int capacity, int* n_out)
+{
+    SNK_REQUIRE(h && h->rows && n_out, "no image processed yet");
+    SNK_REQUIRE(level >= 0 && level < h->prm.nlevels && img >= 0 && img < h->prm.max_batch, "index out of range");
+    SNK_CUDA(cudaStreamSynchronize(h->stream));
+    const PyrDev& P   = h->P;
+    const LevelDev& L = P.lv[level];
+    std::vector<int> cnt(L.n_cells);
+    SNK_CUDA(cudaMemcpy(cnt.data(), h->d_cell_count + (size_t)img * P.cells_per_img + L.cell_base, L.n_cells * 4,
+                        cudaMemcpyDeviceToHost));
+    int n = 0;
+    for (int c = 0; c < L.n_cells; ++c)
+    {
+        if (n + cnt[c] <= capacity && cnt[c] > 0)
+            SNK_CUDA(cudaMemcpy(packed + n, h->d_cand + ((size_t)img * P.cells_per_img + L.cell_base + c) * P.cell_cap,
+                                cnt[c] * 4, cudaMemcpyDeviceToHost));
+        n += cnt[c];
+    }
+    *n_out = n;
+    return n <= capacity ? SNK_OK : SNK_ERR_CAPACITY;
+}
+
+int snk_orb_set_profiling(snk_orb* h, int enabled)
+{
+    SNK_REQUIRE(h, "null handle");
+    collect_events(h);
+    h->profiling = enabled != 0;
+    return SNK_OK;
+}
+
+int snk_orb_stage_ms(snk_orb* h, float* ms, int* launches, int reset)
+{
+    SNK_REQUIRE(h, "null handle");
+    collect_events(h);
+    for (int s = 0; s < SNK_ORB_NUM_STAGES; ++s)
+    {
+        if (ms) ms[s] = h->stage_ms[s];
+        if (launches) launches[s] = h->stage_launches[s];
+        if (reset) h->stage_ms[s] = 0, h->stage_launches[s] = 0;
+    }
+    return SNK_OK;
+}
+
+}  // extern "C"

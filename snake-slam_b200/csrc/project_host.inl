@@ -1,0 +1,252 @@
+// Host wrappers of the projection searches and BoW matching (included at the end of matchers.cu).
+namespace
+{
+struct FrameUpload
+{
+    FrameDev f{};
+    int* d_k2p_out = nullptr;
+    int* d_winner  = nullptr;
+    size_t bytes(const snk_frame_view* v) const
+    {
+        const size_t n = std::max(v->n, 1), cells = (size_t)std::max(v->grid.rows * v->grid.cols, 1);
+        return padded<snk_keypoint_f64>(n) + padded<uint64_t>(4 * n) + padded<float>(n) + 3 * padded<int>(n) +
+               padded<int>(2 * cells);
+    }
+};
+
+int upload_frame(snk_ctx* c, Carver& cv, const snk_frame_view* v, FrameUpload& u)
+{
+    const size_t n = std::max(v->n, 1), cells = (size_t)std::max(v->grid.rows * v->grid.cols, 1);
+    auto* kp  = cv.take<snk_keypoint_f64>(n);
+    auto* ds  = cv.take<uint64_t>(4 * n);
+    auto* rp  = cv.take<float>(n);
+    auto* k2p = cv.take<int>(n);
+    u.d_k2p_out = cv.take<int>(n);
+    u.d_winner  = cv.take<int>(n);
+    auto* cl  = cv.take<int>(2 * cells);
+    cudaStream_t st = c->stream;
+    if (v->n)
+    {
+        SNK_CUDA(cudaMemcpyAsync(kp, v->kp_un, sizeof(snk_keypoint_f64) * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(ds, v->desc, 32 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(rp, v->right_points, 4 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(k2p, v->kp_to_point, 4 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(u.d_k2p_out, v->kp_to_point, 4 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemsetAsync(u.d_winner, 0x7f, 4 * (size_t)v->n, st));  // 0x7f7f7f7f: replaced below
+    }
+    SNK_CUDA(cudaMemcpyAsync(cl, v->grid.cells, 8 * (size_t)v->grid.rows * v->grid.cols, cudaMemcpyHostToDevice, st));
+    FrameDev& f = u.f;
+    f.n = v->n, f.kp_un = kp, f.desc = ds, f.right_points = rp, f.kp_to_point = k2p;
+    for (int i = 0; i < 4; ++i) f.q[i] = v->pose_q[i];
+    for (int i = 0; i < 3; ++i) f.t[i] = v->pose_t[i];
+    f.bmin_x = v->grid.bmin_x, f.bmin_y = v->grid.bmin_y, f.bmax_x = v->grid.bmax_x, f.bmax_y = v->grid.bmax_y;
+    f.inv_x = v->grid.cell_size_inv_x, f.inv_y = v->grid.cell_size_inv_y;
+    f.rows = v->grid.rows, f.cols = v->grid.cols, f.cells = cl;
+    return SNK_OK;
+}
+
+__global__ void k_fill_int(int* p, int n, int v)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+int check_frame(const snk_frame_view* f)
+{
+    SNK_REQUIRE(f && f->n >= 0, "bad frame view");
+    SNK_REQUIRE(f->grid.rows >= 1 && f->grid.cols >= 1 && f->grid.cells, "bad feature grid");
+    SNK_REQUIRE(f->n == 0 || (f->kp_un && f->desc && f->right_points && f->kp_to_point), "null frame arrays");
+    return SNK_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int snk_search_projection_fine(snk_ctx* c, const snk_frame_view* frame, snk_point_fine* points, int n_points,
+                               const snk_camera* cam, const snk_scale_pyramid* pyr, float th, float ratio,
+                               int32_t* kp_to_point_out, int32_t* best_idx, int32_t* best_dist, uint8_t* visible,
+                               int* n_matches)
+{
+    SNK_REQUIRE(c && cam && pyr && n_matches && n_points >= 0, "bad argument");
+    int rc = check_frame(frame);
+    if (rc) return rc;
+    SNK_REQUIRE(n_points == 0 || (points && best_idx && best_dist && visible), "null point arrays");
+    SNK_REQUIRE(frame->n == 0 || kp_to_point_out, "null output");
+    SNK_REQUIRE(pyr->nlevels >= 1 && pyr->nlevels <= 16, "bad pyramid");
+    for (int i = 0; i < n_points; ++i)
+        SNK_REQUIRE(points[i].ref_level >= 0 && points[i].ref_level < pyr->nlevels, "ref_level out of range");
+    SNK_CUDA(cudaSetDevice(c->device));
+    FrameUpload u;
+    const size_t np = std::max(n_points, 1);
+    rc = ctx_reserve(c, u.bytes(frame) + padded<snk_point_fine>(np) + 2 * padded<int>(np) + padded<uint8_t>(np) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    rc = upload_frame(c, cv, frame, u);
+    if (rc) return rc;
+    auto* dp = cv.take<snk_point_fine>(np);
+    int* dbi = cv.take<int>(np);
+    int* dbd = cv.take<int>(np);
+    auto* dv = cv.take<uint8_t>(np);
+    int* dn  = cv.take<int>(4);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 16, st));
+    if (frame->n) k_fill_int<<<(frame->n + 255) / 256, 256, 0, st>>>(u.d_winner, frame->n, 0x7fffffff);
+    if (n_points)
+    {
+        SNK_CUDA(cudaMemcpyAsync(dp, points, sizeof(snk_point_fine) * (size_t)n_points, cudaMemcpyHostToDevice, st));
+        k_proj_fine<<<(n_points + 127) / 128, 128, 0, st>>>(u.f, dp, n_points, *cam, *pyr, th, ratio,
+                                                           std::log(pyr->scale_factor), dbi, dbd, dv, u.d_winner);
+    }
+    if (frame->n)
+        k_assign<snk_point_fine><<<(frame->n + 255) / 256, 256, 0, st>>>(u.f.kp_to_point, u.d_winner, dp, nullptr, frame->n,
+                                                                        u.d_k2p_out, nullptr, dn);
+    if (n_points)
+    {
+        SNK_CUDA(cudaMemcpyAsync(points, dp, sizeof(snk_point_fine) * (size_t)n_points, cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpyAsync(best_idx, dbi, 4 * (size_t)n_points, cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpyAsync(best_dist, dbd, 4 * (size_t)n_points, cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpyAsync(visible, dv, (size_t)n_points, cudaMemcpyDeviceToHost, st));
+    }
+    if (frame->n) SNK_CUDA(cudaMemcpyAsync(kp_to_point_out, u.d_k2p_out, 4 * (size_t)frame->n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+int snk_search_projection_coarse(snk_ctx* c, const snk_frame_view* frame, const snk_point_coarse* points, int n_points,
+                                 const snk_camera* cam, const snk_scale_pyramid* pyr, float th, int feature_error,
+                                 int motion, int32_t* kp_to_point_out, int* n_matches)
+{
+    SNK_REQUIRE(c && cam && pyr && n_matches && n_points >= 0, "bad argument");
+    int rc = check_frame(frame);
+    if (rc) return rc;
+    SNK_REQUIRE(n_points == 0 || points, "null point array");
+    SNK_REQUIRE(frame->n == 0 || kp_to_point_out, "null output");
+    SNK_REQUIRE(pyr->nlevels >= 1 && pyr->nlevels <= 16, "bad pyramid");
+    for (int i = 0; i < n_points; ++i)
+        SNK_REQUIRE(points[i].octave >= 0 && points[i].octave < pyr->nlevels, "octave out of range");
+    SNK_CUDA(cudaSetDevice(c->device));
+    FrameUpload u;
+    const size_t np = std::max(n_points, 1);
+    rc = ctx_reserve(c, u.bytes(frame) + padded<snk_point_coarse>(np) + 2 * padded<int>(np) + padded<int>(64));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    rc = upload_frame(c, cv, frame, u);
+    if (rc) return rc;
+    auto* dp = cv.take<snk_point_coarse>(np);
+    int* dbi = cv.take<int>(np);
+    int* dbb = cv.take<int>(np);
+    int* dn  = cv.take<int>(64);  // [0] matches, [32..61] histogram
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 256, st));
+    if (frame->n) k_fill_int<<<(frame->n + 255) / 256, 256, 0, st>>>(u.d_winner, frame->n, 0x7fffffff);
+    if (n_points)
+    {
+        SNK_CUDA(cudaMemcpyAsync(dp, points, sizeof(snk_point_coarse) * (size_t)n_points, cudaMemcpyHostToDevice, st));
+        k_proj_coarse<<<(n_points + 127) / 128, 128, 0, st>>>(u.f, dp, n_points, *cam, *pyr, th, feature_error, motion, dbi,
+                                                             dbb, u.d_winner);
+    }
+    if (frame->n)
+    {
+        k_assign<snk_point_coarse><<<(frame->n + 255) / 256, 256, 0, st>>>(u.f.kp_to_point, u.d_winner, dp, dbb, frame->n,
+                                                                          u.d_k2p_out, dn + 32, dn);
+        k_rot_cull<<<1, 256, 0, st>>>(u.f.kp_to_point, u.d_winner, dbb, frame->n, dn + 32, u.d_k2p_out, dn);
+        SNK_CUDA(cudaMemcpyAsync(kp_to_point_out, u.d_k2p_out, 4 * (size_t)frame->n, cudaMemcpyDeviceToHost, st));
+    }
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+int snk_search_projection_frame_to_kf(snk_ctx* c, const snk_frame_view* frame, const snk_point_kf* points, int n_points,
+                                      const snk_camera* cam, float th, int feature_error, int32_t* kp_to_point_out,
+                                      int* n_matches)
+{
+    SNK_REQUIRE(c && cam && n_matches && n_points >= 0, "bad argument");
+    int rc = check_frame(frame);
+    if (rc) return rc;
+    SNK_REQUIRE(n_points == 0 || points, "null point array");
+    SNK_REQUIRE(frame->n == 0 || kp_to_point_out, "null output");
+    SNK_CUDA(cudaSetDevice(c->device));
+    FrameUpload u;
+    const size_t np = std::max(n_points, 1);
+    rc = ctx_reserve(c, u.bytes(frame) + padded<snk_point_kf>(np) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    rc = upload_frame(c, cv, frame, u);
+    if (rc) return rc;
+    auto* dp = cv.take<snk_point_kf>(np);
+    int* dn  = cv.take<int>(4);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 16, st));
+    if (n_points)
+    {
+        SNK_CUDA(cudaMemcpyAsync(dp, points, sizeof(snk_point_kf) * (size_t)n_points, cudaMemcpyHostToDevice, st));
+        k_proj_frame_to_kf<<<1, 32, 0, st>>>(u.f, dp, n_points, *cam, th, feature_error, u.d_k2p_out, dn);
+    }
+    if (frame->n) SNK_CUDA(cudaMemcpyAsync(kp_to_point_out, u.d_k2p_out, 4 * (size_t)frame->n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_featvec_view* fv1,
+                  const snk_featvec_view* fv2, const uint8_t* valid1, const uint8_t* valid2, int th, float ratio,
+                  int32_t* match12, int* n_matches)
+{
+    SNK_REQUIRE(c && fv1 && fv2 && n_matches && n1 >= 0 && n2 >= 0, "bad argument");
+    SNK_REQUIRE(n1 == 0 || (d1 && valid1 && match12), "null keyframe-1 arrays");
+    SNK_REQUIRE(n2 == 0 || (d2 && valid2), "null keyframe-2 arrays");
+    *n_matches = 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    if (n1 == 0 || n2 == 0 || fv1->n_nodes == 0 || fv2->n_nodes == 0) return SNK_OK;
+    const int e1 = fv1->offsets[fv1->n_nodes], e2 = fv2->offsets[fv2->n_nodes];
+    SNK_REQUIRE(e2 < (1 << 20), "feature vector too long");
+    for (int i = 0; i < e1; ++i) SNK_REQUIRE(fv1->indices[i] >= 0 && fv1->indices[i] < n1, "fv1 index out of range");
+    for (int i = 0; i < e2; ++i) SNK_REQUIRE(fv2->indices[i] >= 0 && fv2->indices[i] < n2, "fv2 index out of range");
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, padded<uint64_t>(4 * (size_t)n1) + padded<uint64_t>(4 * (size_t)n2) + padded<uint8_t>(n1) +
+                                2 * padded<uint8_t>(n2) + padded<int>(n1) + 2 * padded<int>(fv1->n_nodes + 1) +
+                                2 * padded<int>(fv2->n_nodes + 1) + padded<int>(e1 + 1) + padded<int>(e2 + 1) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    auto* a   = cv.take<uint64_t>(4 * (size_t)n1);
+    auto* b   = cv.take<uint64_t>(4 * (size_t)n2);
+    auto* v1  = cv.take<uint8_t>(n1);
+    auto* v2  = cv.take<uint8_t>(n2);
+    auto* m2  = cv.take<uint8_t>(n2);
+    int* m12  = cv.take<int>(n1);
+    int* ids1 = cv.take<int>(fv1->n_nodes + 1);
+    int* of1  = cv.take<int>(fv1->n_nodes + 1);
+    int* ids2 = cv.take<int>(fv2->n_nodes + 1);
+    int* of2  = cv.take<int>(fv2->n_nodes + 1);
+    int* in1  = cv.take<int>(e1 + 1);
+    int* in2  = cv.take<int>(e2 + 1);
+    int* dn   = cv.take<int>(4);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(a, d1, 32 * (size_t)n1, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(b, d2, 32 * (size_t)n2, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(v1, valid1, n1, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(v2, valid2, n2, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemsetAsync(m2, 0, n2, st));
+    SNK_CUDA(cudaMemsetAsync(m12, 0xff, 4 * (size_t)n1, st));
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 16, st));
+    SNK_CUDA(cudaMemcpyAsync(ids1, fv1->node_ids, 4 * (size_t)fv1->n_nodes, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(of1, fv1->offsets, 4 * (size_t)(fv1->n_nodes + 1), cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(ids2, fv2->node_ids, 4 * (size_t)fv2->n_nodes, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(of2, fv2->offsets, 4 * (size_t)(fv2->n_nodes + 1), cudaMemcpyHostToDevice, st));
+    if (e1) SNK_CUDA(cudaMemcpyAsync(in1, fv1->indices, 4 * (size_t)e1, cudaMemcpyHostToDevice, st));
+    if (e2) SNK_CUDA(cudaMemcpyAsync(in2, fv2->indices, 4 * (size_t)e2, cudaMemcpyHostToDevice, st));
+    FeatVecDev f1{fv1->n_nodes, ids1, of1, in1}, f2{fv2->n_nodes, ids2, of2, in2};
+    k_match_bow<<<(fv1->n_nodes + 3) / 4, 128, 0, st>>>(a, b, f1, f2, v1, v2, th, ratio, m12, m2, dn);
+    SNK_CUDA(cudaMemcpyAsync(match12, m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,305 @@
+"""ctypes view of libsnakeorb.so (include/snakeorb.h) with the reference's class / method names.
+
+This is test-and-benchmark plumbing: the product is the shared library and its C ABI. There is no fallback —
+importing works without a GPU (so symbol tests can run), but every call needs a B200 and raises otherwise."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(HERE), "libsnakeorb.so")
+
+KP32 = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")])
+KP64 = np.dtype([("x", "<f8"), ("y", "<f8"), ("size", "<f8"), ("angle", "<f8"), ("response", "<f8"),
+                 ("octave", "<i4"), ("_pad", "<i4")])
+KNN2 = np.dtype([("dist0", "<i4"), ("idx0", "<i4"), ("dist1", "<i4"), ("idx1", "<i4")])
+POINT_FINE = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("normal", "<f8", 3), ("ref_depth", "<f4"),
+                       ("ref_level", "<i4"), ("valid", "<i4"), ("id", "<i4")])
+POINT_COARSE = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("normal", "<f8", 3), ("octave", "<i4"),
+                         ("angle", "<f4"), ("id", "<i4"), ("_pad", "<i4")])
+POINT_KF = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("id", "<i4"), ("_pad", "<i4")])
+assert KP32.itemsize == 24 and KP64.itemsize == 48 and POINT_FINE.itemsize == 96 and POINT_COARSE.itemsize == 96
+assert POINT_KF.itemsize == 64
+
+
+class SnakeOrbError(RuntimeError):
+    pass
+
+
+class OrbParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32), ("th_fast", C.c_int32),
+                ("th_fast_min", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
+
+
+class StereoParams(C.Structure):
+    _fields_ = [("bf", C.c_double), ("relaxed", C.c_int32), ("nlevels", C.c_int32), ("scale", C.c_double * 16)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("s", C.c_double),
+                ("bf", C.c_double)]
+
+
+class GridView(C.Structure):
+    _fields_ = [("bmin_x", C.c_double), ("bmin_y", C.c_double), ("bmax_x", C.c_double), ("bmax_y", C.c_double),
+                ("cell_size_inv_x", C.c_double), ("cell_size_inv_y", C.c_double), ("rows", C.c_int32),
+                ("cols", C.c_int32), ("cells", C.c_void_p)]
+
+
+class FrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("kp_un", C.c_void_p), ("desc", C.c_void_p), ("right_points", C.c_void_p),
+                ("kp_to_point", C.c_void_p), ("pose_q", C.c_double * 4), ("pose_t", C.c_double * 3),
+                ("grid", GridView)]
+
+
+class ScalePyramidC(C.Structure):
+    _fields_ = [("nlevels", C.c_int32), ("_pad", C.c_int32), ("scale_factor", C.c_double), ("scale", C.c_double * 16)]
+
+
+class FeatVecView(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("node_ids", C.c_void_p), ("offsets", C.c_void_p), ("indices", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    """Loads libsnakeorb.so; raises if it has not been built (no silent fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SnakeOrbError(f"{LIB_PATH} is missing: run `make -C snake-slam_b200` (or __graft_entry__.build())")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.snk_last_error.restype = C.c_char_p
+        _lib.snk_version.restype = C.c_char_p
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise SnakeOrbError(f"libsnakeorb error {rc}: {lib().snk_last_error().decode()}")
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def stereo_params(bf, relaxed, scales):
+    p = StereoParams()
+    p.bf, p.relaxed, p.nlevels = bf, int(relaxed), len(scales)
+    for i, s in enumerate(scales):
+        p.scale[i] = s
+    return p
+
+
+def scale_pyramid_c(scale_factor_f32, scales):
+    p = ScalePyramidC()
+    p.nlevels = len(scales)
+    p.scale_factor = float(np.float32(scale_factor_f32))
+    for i, s in enumerate(scales):
+        p.scale[i] = s
+    return p
+
+
+class ORBExtractor:
+    """Saiga::ORBExtractor(nfeatures, scaleFactor, num_levels, th_fast, th_fast_min, num_threads) —
+    saiga/vision/features/ORBExtractor.h:49-53. `num_threads` is accepted and ignored (the GPU path has no
+    per-level OpenMP loop); `max_batch` sizes the batched entry points."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, num_levels=8, th_fast=20, th_fast_min=7, num_threads=1,
+                 max_batch=1, device=0):
+        self.h = C.c_void_p()
+        prm = OrbParams(nfeatures, scaleFactor, num_levels, th_fast, th_fast_min, max_batch, device)
+        _check(lib().snk_orb_create(C.byref(prm), C.byref(self.h)))
+        self.nlevels, self.max_batch = num_levels, max_batch
+        self.cap = lib().snk_orb_max_keypoints(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().snk_orb_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def set_stream(self, cuda_stream):
+        _check(lib().snk_orb_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def getPyramid(self):
+        s = np.zeros(self.nlevels)
+        f = np.zeros(self.nlevels, np.int32)
+        _check(lib().snk_orb_pyramid(self.h, _p(s), _p(f)))
+        return s, f
+
+    def Detect(self, img):
+        """Detect(ImageView<uchar>, vector<KeyPoint<float>>&, vector<DescriptorORB>&) for a host numpy image."""
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        kps = np.zeros(self.cap, KP32)
+        desc = np.zeros((self.cap, 4), np.uint64)
+        n = C.c_int(0)
+        _check(lib().snk_orb_detect(self.h, _p(img), img.shape[0], img.shape[1], C.c_size_t(img.strides[0]), 0,
+                                    _p(kps), _p(desc), self.cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def DetectBatch(self, imgs):
+        """imgs: (B, rows, cols) uint8 C-contiguous host array. Returns per-image (kps, desc) lists."""
+        assert imgs.dtype == np.uint8 and imgs.ndim == 3 and imgs.flags.c_contiguous
+        B, rows, cols = imgs.shape
+        kps = np.zeros((B, self.cap), KP32)
+        desc = np.zeros((B, self.cap, 4), np.uint64)
+        n = np.zeros(B, np.int32)
+        _check(lib().snk_orb_detect_batch(self.h, _p(imgs), B, rows, cols, C.c_size_t(cols), C.c_size_t(rows * cols), 0,
+                                          _p(kps), _p(desc), self.cap, _p(n)))
+        return [(kps[i, :n[i]].copy(), desc[i, :n[i]].copy()) for i in range(B)]
+
+    def enqueue_ptr(self, ptr, n_imgs, rows, cols, pitch, stride, on_device):
+        _check(lib().snk_orb_enqueue(self.h, C.c_void_p(ptr), n_imgs, rows, cols, C.c_size_t(pitch), C.c_size_t(stride),
+                                     int(on_device)))
+
+    def fetch(self, n_imgs, kps=None, desc=None, counts=None):
+        kps = np.zeros((n_imgs, self.cap), KP32) if kps is None else kps
+        desc = np.zeros((n_imgs, self.cap, 4), np.uint64) if desc is None else desc
+        counts = np.zeros(n_imgs, np.int32) if counts is None else counts
+        _check(lib().snk_orb_fetch(self.h, _p(kps), _p(desc), self.cap, _p(counts)))
+        return kps, desc, counts
+
+    def device_results(self):
+        k, d, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        s = C.c_int()
+        _check(lib().snk_orb_device_results(self.h, C.byref(k), C.byref(d), C.byref(c), C.byref(s)))
+        return k.value, d.value, c.value, s.value
+
+    def GetImage(self, level, img=0, blurred=False):
+        """ORBExtractor::GetImage(level), copied to the host."""
+        r, c = C.c_int(), C.c_int()
+        pitch = C.c_size_t()
+        ptr = C.c_void_p()
+        _check(lib().snk_orb_get_level(self.h, img, level, int(blurred), C.byref(ptr), C.byref(r), C.byref(c), C.byref(pitch)))
+        out = np.zeros((r.value, c.value), np.uint8)
+        _check(lib().snk_orb_read_level(self.h, img, level, int(blurred), _p(out), C.c_size_t(c.value)))
+        return out
+
+    def candidates(self, level, img=0):
+        buf = np.zeros(400000, np.uint32)
+        n = C.c_int()
+        _check(lib().snk_orb_read_candidates(self.h, img, level, _p(buf), len(buf), C.byref(n)))
+        p = buf[:n.value]
+        return np.stack([p & 0xfff, (p >> 12) & 0xfff, p >> 24], 1).astype(np.int32)
+
+    def set_profiling(self, on):
+        _check(lib().snk_orb_set_profiling(self.h, int(on)))
+
+    def stage_ms(self, reset=True):
+        ms = np.zeros(8, np.float32)
+        ln = np.zeros(8, np.int32)
+        _check(lib().snk_orb_stage_ms(self.h, _p(ms), _p(ln), int(reset)))
+        return ms, ln
+
+
+class Context:
+    """snk_ctx: device + stream + scratch for the matchers."""
+
+    def __init__(self, device=0):
+        self.c = C.c_void_p()
+        _check(lib().snk_ctx_create(device, C.byref(self.c)))
+
+    def close(self):
+        if getattr(self, "c", None):
+            lib().snk_ctx_destroy(self.c)
+            self.c = None
+
+    __del__ = close
+
+    def set_stream(self, cuda_stream):
+        _check(lib().snk_ctx_set_stream(self.c, C.c_void_p(cuda_stream)))
+
+    def distance(self, a, b):
+        """Saiga::distance for n pairs."""
+        a = np.ascontiguousarray(a, np.uint64).reshape(-1, 4)
+        b = np.ascontiguousarray(b, np.uint64).reshape(-1, 4)
+        out = np.zeros(len(a), np.int32)
+        _check(lib().snk_hamming_pairs(self.c, _p(a), _p(b), len(a), _p(out)))
+        return out
+
+    def matchKnn2(self, d1, d2):
+        """BruteForceMatcher::matchKnn2 -> knn2 records."""
+        d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+        d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+        out = np.zeros(len(d1), KNN2)
+        _check(lib().snk_match_knn2(self.c, _p(d1), len(d1), _p(d2), len(d2), _p(out)))
+        return out
+
+    @staticmethod
+    def filterMatches(knn2, threshold, ratio):
+        out = np.zeros((max(len(knn2), 1), 2), np.int32)
+        n = C.c_int()
+        _check(lib().snk_filter_matches(_p(knn2), len(knn2), threshold, C.c_float(ratio), _p(out), C.byref(n)))
+        return out[:n.value].copy()
+
+    def StereoMatching(self, params, left, dl, right, dr):
+        """Preprocess::StereoMatching on rectified keypoints -> (matches, right_points, depth)."""
+        left = np.ascontiguousarray(left, KP64)
+        right = np.ascontiguousarray(right, KP64)
+        dl = np.ascontiguousarray(dl, np.uint64)
+        dr = np.ascontiguousarray(dr, np.uint64)
+        rp = np.zeros(max(len(left), 1), np.float32)
+        dp = np.zeros(max(len(left), 1), np.float32)
+        n = C.c_int()
+        _check(lib().snk_stereo_match(self.c, C.byref(params), _p(left), _p(dl), len(left), _p(right), _p(dr),
+                                      len(right), _p(rp), _p(dp), C.byref(n)))
+        return n.value, rp[:len(left)], dp[:len(left)]
+
+    def stereo_orb_device(self, orb, n_pairs, params, rp_ptr, depth_ptr, nm_ptr):
+        _check(lib().snk_stereo_match_orb_device(self.c, orb.h, n_pairs, C.byref(params), C.c_void_p(rp_ptr),
+                                                 C.c_void_p(depth_ptr), C.c_void_p(nm_ptr)))
+
+    def SearchByProjection2(self, frame, points, cam, pyr, th, ratio):
+        pts = np.array(points, dtype=POINT_FINE, copy=True)
+        n = len(pts)
+        k2p = np.zeros(max(frame.n, 1), np.int32)
+        bi = np.zeros(max(n, 1), np.int32)
+        bd = np.zeros(max(n, 1), np.int32)
+        vis = np.zeros(max(n, 1), np.uint8)
+        m = C.c_int()
+        _check(lib().snk_search_projection_fine(self.c, C.byref(frame), _p(pts), n, C.byref(cam), C.byref(pyr),
+                                                C.c_float(th), C.c_float(ratio), _p(k2p), _p(bi), _p(bd), _p(vis),
+                                                C.byref(m)))
+        return m.value, k2p[:frame.n], bi[:n], bd[:n], vis[:n], pts
+
+    def SearchByProjectionFrameFrame2(self, frame, points, cam, pyr, th, feature_error, motion):
+        pts = np.ascontiguousarray(points, POINT_COARSE)
+        k2p = np.zeros(max(frame.n, 1), np.int32)
+        m = C.c_int()
+        _check(lib().snk_search_projection_coarse(self.c, C.byref(frame), _p(pts), len(pts), C.byref(cam),
+                                                  C.byref(pyr), C.c_float(th), feature_error, motion, _p(k2p),
+                                                  C.byref(m)))
+        return m.value, k2p[:frame.n]
+
+    def SearchByProjectionFrameToKeyframe(self, frame, points, cam, th, feature_error):
+        pts = np.ascontiguousarray(points, POINT_KF)
+        k2p = np.zeros(max(frame.n, 1), np.int32)
+        m = C.c_int()
+        _check(lib().snk_search_projection_frame_to_kf(self.c, C.byref(frame), _p(pts), len(pts), C.byref(cam),
+                                                       C.c_float(th), feature_error, _p(k2p), C.byref(m)))
+        return m.value, k2p[:frame.n]
+
+    def MatchBoW(self, d1, d2, fv1, fv2, valid1, valid2, th, ratio):
+        d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+        d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+        m12 = np.zeros(max(len(d1), 1), np.int32)
+        m = C.c_int()
+        _check(lib().snk_match_bow(self.c, _p(d1), len(d1), _p(d2), len(d2), C.byref(fv1), C.byref(fv2), _p(valid1),
+                                   _p(valid2), th, C.c_float(ratio), _p(m12), C.byref(m)))
+        return m.value, m12[:len(d1)]
+
+    def hamming_peak(self):
+        v = C.c_double()
+        _check(lib().snk_hamming_peak_selftest(self.c, C.byref(v)))
+        return v.value
+
+
+def kp32_to_kp64(k):
+    o = np.zeros(len(k), KP64)
+    for f in ("x", "y", "size", "angle", "response", "octave"):
+        o[f] = k[f]
+    return o
