@@ -204,7 +204,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
 
     int max_quota = 0;
     for (int l = 0; l < L; ++l) max_quota = std::max(max_quota, h->features[l]);
-    h->node_cap = max_quota + 8;
+    h->node_cap = align_up(max_quota + 8, 4);  // multiple of 4 keeps the int2 array of the kernel 8-byte aligned
     SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
     h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES;
     SNK_REQUIRE(h->qt_smem <= 200 * 1024, "nfeatures too large for the distribution kernel's shared memory");

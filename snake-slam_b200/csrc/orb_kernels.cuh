@@ -125,11 +125,14 @@ constexpr int FAST_DIM = 66;  // wCell < 60  =>  ROI side <= 66
 constexpr int FAST_PITCH = 68;
 constexpr int FAST_NT = 128;
 
-// arc score: max over the 16 arcs of 9 contiguous ring pixels of min(v - ring) and min(ring - v)
+// arc score: max over the 16 arcs of 9 contiguous ring pixels of min(v - ring) and min(ring - v).
+// The differences are biased by +256 so that every intermediate is a positive integer: nvcc 12.9 narrows the
+// min/max network to 16-bit *unsigned* PTX ops (min.u16/max.u16), which is only correct for non-negative operands
+// (the signed formulation returned wrong scores on sm_100a; tools/dev_check.cu guards this on the device).
 __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], int y, int x)
 {
-    const int v = t[y][x];
-    int d[16];
+    const unsigned v = 256u + t[y][x];
+    unsigned d[16];
     d[0]  = v - t[y + 3][x];
     d[1]  = v - t[y + 3][x + 1];
     d[2]  = v - t[y + 2][x + 2];
@@ -147,29 +150,29 @@ __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], in
     d[14] = v - t[y + 2][x - 2];
     d[15] = v - t[y + 3][x - 1];
     // sliding-window min and max over 9 consecutive (circular) entries by doubling: 2, 4, 8, then +1
-    int lo[16], hi[16];
+    unsigned lo[16], hi[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k)
     {
         lo[k] = min(d[k], d[(k + 1) & 15]);
         hi[k] = max(d[k], d[(k + 1) & 15]);
     }
-    int lo4[16], hi4[16];
+    unsigned lo4[16], hi4[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k)
     {
         lo4[k] = min(lo[k], lo[(k + 2) & 15]);
         hi4[k] = max(hi[k], hi[(k + 2) & 15]);
     }
-    int best = -256;
+    unsigned best_lo = 0, best_hi = 1024;  // max of window minima, min of window maxima
 #pragma unroll
     for (int k = 0; k < 16; ++k)
     {
-        const int l9 = min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
-        const int h9 = max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
-        best         = max(best, max(l9, -h9));
+        best_lo = max(best_lo, min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]));
+        best_hi = min(best_hi, max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]));
     }
-    return best;
+    // un-bias: darker arc = best_lo - 256, brighter arc = 256 - best_hi
+    return max((int)best_lo - 256, 256 - (int)best_hi);
 }
 
 // One CTA == one cell == the (up to two) cv::FAST calls of ORBExtractor.cpp:133-140.
@@ -225,6 +228,11 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
         const int y = list[i] >> 8, x = list[i] & 255;
         const int arc = fast_arc_score(tile, y, x);
         score[y][x]   = (arc > t) ? (uint8_t)arc : 0;
+#ifdef SNK_DEBUG_FAST
+        if (blockIdx.x == 312 && blockIdx.y == 0 && y == 16 && x == 3)
+            printf("DBG cell x0=%d y0=%d w=%d h=%d off=%d,%d pitch=%d | v=%d ring0=%d ring4=%d ring8=%d ring12=%d arc=%d t=%d nl=%d\n", c.x0, c.y0, c.w,
+                   c.h, c.off_x, c.off_y, L.pitch, tile[y][x], tile[y + 3][x], tile[y][x + 3], tile[y - 3][x], tile[y][x - 3], arc, t, nl);
+#endif
     }
     __syncthreads();
 

@@ -133,7 +133,7 @@ class ORBExtractor:
 
     def Detect(self, img):
         """Detect(ImageView<uchar>, vector<KeyPoint<float>>&, vector<DescriptorORB>&) for a host numpy image."""
-        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        assert img.dtype == np.uint8 and img.ndim == 2 and (img.size == 0 or img.strides[1] == 1)
         kps = np.zeros(self.cap, KP32)
         desc = np.zeros((self.cap, 4), np.uint64)
         n = C.c_int(0)
