@@ -202,3 +202,45 @@ def stereo_match(params, left, dl, right, dr):
     n = lib().orc_stereo_match(C.byref(params), _p(left), _p(dl), len(left), _p(right), _p(dr), len(right), _p(rp),
                                _p(dp), C.byref(ops))
     return n, rp, dp, ops.value
+
+
+# ---- projection / BoW matchers: the caller passes ctypes structs laid out as in include/snakeorb.h ----------------
+def search_projection_fine(frame, points, cam, pyr, th, ratio):
+    pts = np.array(points, copy=True)
+    n = len(pts)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    bi = np.zeros(max(n, 1), np.int32)
+    bd = np.zeros(max(n, 1), np.int32)
+    vis = np.zeros(max(n, 1), np.uint8)
+    ops = C.c_longlong(0)
+    m = lib().orc_search_projection_fine(C.byref(frame), _p(pts), n, C.byref(cam), C.byref(pyr), C.c_float(th),
+                                         C.c_float(ratio), _p(k2p), _p(bi), _p(bd), _p(vis), C.byref(ops))
+    return m, k2p[:frame.n], bi[:n], bd[:n], vis[:n], pts, ops.value
+
+
+def search_projection_coarse(frame, points, cam, pyr, th, feature_error, motion):
+    pts = np.ascontiguousarray(points)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    ops = C.c_longlong(0)
+    m = lib().orc_search_projection_coarse(C.byref(frame), _p(pts), len(pts), C.byref(cam), C.byref(pyr),
+                                           C.c_float(th), feature_error, motion, _p(k2p), C.byref(ops))
+    return m, k2p[:frame.n], ops.value
+
+
+def search_projection_frame_to_kf(frame, points, cam, th, feature_error):
+    pts = np.ascontiguousarray(points)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    ops = C.c_longlong(0)
+    m = lib().orc_search_projection_frame_to_kf(C.byref(frame), _p(pts), len(pts), C.byref(cam), C.c_float(th),
+                                                feature_error, _p(k2p), C.byref(ops))
+    return m, k2p[:frame.n], ops.value
+
+
+def match_bow(d1, d2, fv1, fv2, valid1, valid2, th, ratio):
+    d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+    d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+    m12 = np.zeros(max(len(d1), 1), np.int32)
+    ops = C.c_longlong(0)
+    m = lib().orc_match_bow(_p(d1), len(d1), _p(d2), len(d2), C.byref(fv1), C.byref(fv2), _p(valid1), _p(valid2), th,
+                            C.c_float(ratio), _p(m12), C.byref(ops))
+    return m, m12[:len(d1)], ops.value

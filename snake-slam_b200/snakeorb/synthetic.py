@@ -85,3 +85,95 @@ def adversarial(kind, w, h, seed=0):
 
 
 SHAPES = {"euroc": (752, 480), "kitti": (1241, 376), "tum": (640, 480)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Matcher inputs. Everything below is plain numpy on host arrays.
+# ---------------------------------------------------------------------------------------------------------------
+KP64 = np.dtype([("x", "<f8"), ("y", "<f8"), ("size", "<f8"), ("angle", "<f8"), ("response", "<f8"),
+                 ("octave", "<i4"), ("_pad", "<i4")])
+
+
+def feature_grid(kps64, w, h, cell=20):
+    """Saiga::FeatureGridBounds2<double,20>::computeFromIntrinsicsDist for a distortion-free camera (bounding box of
+    the image border +-0.1) and FeatureGrid2::create (counting sort into row-major cells; the permutation keeps the
+    input order inside a cell). Returns (bounds dict, cells int32 [rows*cols,2], permutation)."""
+    bmin = np.array([0.0, 0.0]) - 0.1
+    bmax = np.array([w - 1.0, h - 1.0]) + 0.1
+    inv = 1.0 / cell
+    rows = int(np.ceil((bmax[1] - bmin[1]) / cell))
+    cols = int(np.ceil((bmax[0] - bmin[0]) / cell))
+    px = (kps64["x"] - bmin[0]) * inv
+    py = (kps64["y"] - bmin[1]) * inv
+    cx = np.floor(px).astype(np.int64)
+    cy = np.floor(py).astype(np.int64)
+    inside = (kps64["x"] >= bmin[0]) & (kps64["y"] >= bmin[1]) & (kps64["x"] < bmax[0]) & (kps64["y"] < bmax[1])
+    cid = np.where(inside, cy * cols + cx, rows * cols)
+    order = np.argsort(cid, kind="stable")
+    perm = np.empty(len(kps64), np.int32)
+    perm[order] = np.arange(len(kps64), dtype=np.int32)
+    counts = np.bincount(cid[inside], minlength=rows * cols)[: rows * cols]
+    begin = np.concatenate([[0], np.cumsum(counts)[:-1]])
+    cells = np.stack([begin, begin + counts], 1).astype(np.int32)
+    bounds = dict(bmin_x=bmin[0], bmin_y=bmin[1], bmax_x=bmax[0], bmax_y=bmax[1], inv=inv, rows=rows, cols=cols)
+    return bounds, cells, perm
+
+
+def apply_permutation(perm, *arrays):
+    out = []
+    for a in arrays:
+        b = np.empty_like(a)
+        b[perm] = a
+        out.append(b)
+    return out
+
+
+def flip_bits(desc, rng, max_flips):
+    """Copies of 256-bit descriptors with 0..max_flips random bits flipped."""
+    d = desc.copy().view(np.uint8).reshape(len(desc), 32)
+    for i in range(len(d)):
+        for b in rng.integers(0, 256, int(rng.integers(0, max_flips + 1))):
+            d[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    return d.view(np.uint64).reshape(len(desc), 4)
+
+
+def quat_from_axis_angle(axis, angle):
+    axis = np.asarray(axis, np.float64)
+    axis = axis / np.linalg.norm(axis)
+    s = np.sin(angle / 2)
+    return np.array([axis[0] * s, axis[1] * s, axis[2] * s, np.cos(angle / 2)])
+
+
+def map_points_from_keypoints(kps64, desc, K, rng, n_points, scale_table, max_flips=20, depth_range=(3.0, 60.0)):
+    """Local-map points back-projected from (a resampling of) the frame's own keypoints at seeded depths, the
+    descriptor a noisy copy of the keypoint's. Returns dict of arrays (pos, normal, desc, ref_depth, ref_level,
+    octave, angle, src)."""
+    fx, fy, cx, cy = K
+    src = rng.integers(0, len(kps64), n_points)
+    jitter = rng.normal(0, 0.7, (n_points, 2))
+    u = kps64["x"][src] + jitter[:, 0]
+    v = kps64["y"][src] + jitter[:, 1]
+    depth = rng.uniform(depth_range[0], depth_range[1], n_points)
+    pos = np.stack([(u - cx) / fx * depth, (v - cy) / fy * depth, depth], 1)
+    normal = -pos / np.linalg.norm(pos, axis=1, keepdims=True)  # facing the camera at the origin
+    lvl = kps64["octave"][src].astype(np.int32)
+    # consistent with the scale prediction: seen at `depth` on level `lvl`
+    return dict(pos=pos, normal=normal, desc=flip_bits(desc[src], rng, max_flips), ref_depth=depth.astype(np.float32),
+                ref_level=lvl, octave=lvl, angle=(kps64["angle"][src] + rng.normal(0, 4, n_points)).astype(np.float32),
+                src=src.astype(np.int32))
+
+
+def bow_feature_vector(desc, rng, n_nodes=100, bits=7):
+    """A FeatureVector-shaped grouping (MiniBow2.h:98-132) without the vocabulary blob: the node of a descriptor is
+    a hash of its leading bits (similar descriptors share nodes), node ids ascending, feature order inside a node
+    shuffled like the std::sort in FeatureVector::setFeatures leaves it. Returns (node_ids, offsets, indices)."""
+    key = (desc[:, 0] & np.uint64((1 << bits) - 1)).astype(np.int64) % n_nodes
+    ids = np.unique(key)
+    offsets = [0]
+    indices = []
+    for nid in ids:
+        members = np.nonzero(key == nid)[0]
+        rng.shuffle(members)
+        indices.append(members)
+        offsets.append(offsets[-1] + len(members))
+    return ids.astype(np.int32) * 3 + 11, np.array(offsets, np.int32), np.concatenate(indices).astype(np.int32)

@@ -1,0 +1,78 @@
+"""Builds the host-side views (snk_frame_view & co.) the projection / BoW matchers take, from extractor output.
+Shared by the CPU and GPU matcher tests; keeps every numpy buffer alive on the returned object."""
+import numpy as np
+
+import snakeorb
+from snakeorb import synthetic as S
+
+
+class FrameData:
+    pass
+
+
+def make_frame(kps32, desc, w, h, rng, pose_q, pose_t, prematched_frac=0.15, right_frac=0.5, bf=386.1):
+    k64 = snakeorb.kp32_to_kp64(kps32)
+    bounds, cells, perm = S.feature_grid(k64, w, h)
+    k64, desc = S.apply_permutation(perm, k64, np.ascontiguousarray(desc))
+    n = len(k64)
+    f = FrameData()
+    f.kp = np.ascontiguousarray(k64)
+    f.desc = np.ascontiguousarray(desc)
+    f.right = np.where(rng.random(n) < right_frac, f.kp["x"] - bf / rng.uniform(3, 60, n), -1000.0).astype(np.float32)
+    f.k2p = np.where(rng.random(n) < prematched_frac, rng.integers(100000, 200000, n), -1).astype(np.int32)
+    f.cells = np.ascontiguousarray(cells)
+    v = snakeorb.FrameView()
+    v.n = n
+    v.kp_un, v.desc, v.right_points, v.kp_to_point = f.kp.ctypes.data, f.desc.ctypes.data, f.right.ctypes.data, f.k2p.ctypes.data
+    for i in range(4):
+        v.pose_q[i] = pose_q[i]
+    for i in range(3):
+        v.pose_t[i] = pose_t[i]
+    g = v.grid
+    g.bmin_x, g.bmin_y, g.bmax_x, g.bmax_y = bounds["bmin_x"], bounds["bmin_y"], bounds["bmax_x"], bounds["bmax_y"]
+    g.cell_size_inv_x = g.cell_size_inv_y = bounds["inv"]
+    g.rows, g.cols = bounds["rows"], bounds["cols"]
+    g.cells = f.cells.ctypes.data
+    f.view = v
+    return f
+
+
+def camera(fx, fy, cx, cy, bf):
+    c = snakeorb.Camera()
+    c.fx, c.fy, c.cx, c.cy, c.s, c.bf = fx, fy, cx, cy, 0.0, bf
+    return c
+
+
+def fine_points(mp, rng, invalid_frac=0.05):
+    p = np.zeros(len(mp["pos"]), snakeorb.POINT_FINE)
+    p["desc"], p["pos"], p["normal"] = mp["desc"], mp["pos"], mp["normal"]
+    p["ref_depth"], p["ref_level"] = mp["ref_depth"], mp["ref_level"]
+    p["valid"] = (rng.random(len(p)) >= invalid_frac).astype(np.int32)
+    p["id"] = np.arange(len(p), dtype=np.int32) + 7
+    return p
+
+
+def coarse_points(mp):
+    p = np.zeros(len(mp["pos"]), snakeorb.POINT_COARSE)
+    p["desc"], p["pos"], p["normal"] = mp["desc"], mp["pos"], mp["normal"]
+    p["octave"], p["angle"] = mp["octave"], mp["angle"]
+    p["id"] = np.arange(len(p), dtype=np.int32) + 7
+    return p
+
+
+def kf_points(mp, rng, null_frac=0.1):
+    p = np.zeros(len(mp["pos"]), snakeorb.POINT_KF)
+    p["desc"], p["pos"] = mp["desc"], mp["pos"]
+    ids = np.arange(len(p), dtype=np.int32) + 7
+    ids[rng.random(len(p)) < null_frac] = -1
+    p["id"] = ids
+    return p
+
+
+def featvec(desc, rng, n_nodes=100):
+    ids, off, idx = S.bow_feature_vector(desc, rng, n_nodes)
+    fv = snakeorb.FeatVecView()
+    fv.n_nodes = len(ids)
+    fv.node_ids, fv.offsets, fv.indices = ids.ctypes.data, off.ctypes.data, idx.ctypes.data
+    fv._keep = (ids, off, idx)
+    return fv

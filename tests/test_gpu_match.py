@@ -1,0 +1,183 @@
+"""GPU parity tests of the Hamming matchers: every output index and distance must equal the oracle's."""
+import os
+
+import numpy as np
+import pytest
+
+import matchdata as M
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def so():
+    import snakeorb
+
+    return snakeorb
+
+
+@pytest.fixture(scope="module")
+def ctx(so):
+    return so.Context()
+
+
+@pytest.fixture(scope="module")
+def feats(oracle):
+    """Oracle-extracted features of a KITTI-shaped stereo pair and a second frame (inputs only)."""
+    from snakeorb import synthetic as S
+
+    ex = oracle.Extractor(2000, 1.2, 8, 20, 7, 4)
+    left = S.image(3000, 1241, 376)
+    right = S.stereo_right(left, 3001, 4.0, 40.0)
+    other = S.image(3002, 1241, 376)
+    return dict(l=ex.detect(left), r=ex.detect(right), o=ex.detect(other), scales=oracle.scale_pyramid(8, 1.2, 2000)[0])
+
+
+def test_distance_and_knn2(so, ctx, oracle, feats):
+    rng = np.random.default_rng(0)
+    a, b = feats["l"][1], feats["r"][1]
+    n = min(len(a), len(b))
+    d = ctx.distance(a[:n], b[:n])
+    assert all(d[i] == oracle.hamming(a[i], b[i]) for i in range(0, n, 37))
+    for (x, y) in ((a, b), (a[:1], b), (a, b[:1]), (a[:130], a[:130]), (a[:5], b[:0])):
+        got = ctx.matchKnn2(x, y)
+        want = oracle.match_knn2(x, y)
+        assert got.tobytes() == want.tobytes()
+        for th, ratio in ((60, 0.8), (256, 1.0), (30, 0.5)):
+            assert np.array_equal(so.Context.filterMatches(got, th, ratio), oracle.filter_matches(want, th, ratio))
+    # heavy ties: many duplicates of few descriptors — first-minimum semantics must hold
+    base = a[rng.integers(0, 8, 700)]
+    got = ctx.matchKnn2(a[:300], base)
+    assert got.tobytes() == oracle.match_knn2(a[:300], base).tobytes()
+    g = np.load(os.path.join(HERE, "golden", "golden_ref.npz"))
+    k = ctx.matchKnn2(g["knn_a"], g["knn_b"])
+    assert np.array_equal(np.stack([k["dist0"], k["idx0"], k["dist1"], k["idx1"]], 1), g["knn_out"])
+
+
+@pytest.mark.parametrize("relaxed,bf", [(True, 386.1), (False, 386.1), (True, 47.9)])
+def test_stereo_row_search(so, ctx, oracle, feats, relaxed, bf):
+    kl, dl = feats["l"]
+    kr, dr = feats["r"]
+    p = so.stereo_params(bf, relaxed, feats["scales"])
+    n, rp, dp = ctx.StereoMatching(p, so.kp32_to_kp64(kl), dl, so.kp32_to_kp64(kr), dr)
+    n2, rp2, dp2, ops = oracle.stereo_match(oracle.stereo_params(bf, relaxed, feats["scales"]), oracle.kp32_to_kp64(kl), dl,
+                                            oracle.kp32_to_kp64(kr), dr)
+    assert n == n2 and n > 0 and ops > 0
+    assert rp.tobytes() == rp2.tobytes() and dp.tobytes() == dp2.tobytes()
+    # empty sides
+    n, rp, dp = ctx.StereoMatching(p, so.kp32_to_kp64(kl), dl, so.kp32_to_kp64(kr[:0]), dr[:0])
+    assert n == 0 and np.all(rp == -1000) and np.all(dp == -1000)
+    n, rp, dp = ctx.StereoMatching(p, so.kp32_to_kp64(kl[:0]), dl[:0], so.kp32_to_kp64(kr), dr)
+    assert n == 0 and len(rp) == 0
+
+
+def test_stereo_device_path_equals_host_path(so, ctx, oracle):
+    """Extractor results consumed on the device (images 2p, 2p+1 = stereo pair p), as bench.py does."""
+    import ctypes as C
+
+    from snakeorb import synthetic as S
+
+    pairs = []
+    for i in range(3):
+        l = S.image(700 + i, 752, 480)
+        pairs += [l, S.stereo_right(l, 800 + i, 4.0, 20.0)]
+    imgs = np.stack(pairs)
+    ex = so.ORBExtractor(1200, 1.2, 8, 20, 7, max_batch=6)
+    res = ex.DetectBatch(imgs)
+    scales, _ = ex.getPyramid()
+    p = so.stereo_params(47.9, True, scales)
+    # device outputs in a scratch buffer obtained through the hamming context's own allocator: use cudart directly
+    cudart = C.CDLL("libcudart.so")
+    stride = ex.device_results()[3]
+    bufs = [C.c_void_p() for _ in range(3)]
+    for b, nbytes in zip(bufs, (3 * stride * 4, 3 * stride * 4, 3 * 4)):
+        assert cudart.cudaMalloc(C.byref(b), C.c_size_t(nbytes)) == 0
+    ex.enqueue_ptr(imgs.ctypes.data, 6, 480, 752, 752, 752 * 480, False)
+    ctx.set_stream(0)
+    ex.set_stream(0)
+    ex.enqueue_ptr(imgs.ctypes.data, 6, 480, 752, 752, 752 * 480, False)
+    ctx.stereo_orb_device(ex, 3, p, bufs[0].value, bufs[1].value, bufs[2].value)
+    rp = np.zeros((3, stride), np.float32)
+    dp = np.zeros((3, stride), np.float32)
+    nm = np.zeros(3, np.int32)
+    assert cudart.cudaDeviceSynchronize() == 0
+    for host, dev in ((rp, bufs[0]), (dp, bufs[1]), (nm, bufs[2])):
+        assert cudart.cudaMemcpy(C.c_void_p(host.ctypes.data), dev, C.c_size_t(host.nbytes), 2) == 0
+    for i in range(3):
+        (kl, dl), (kr, dr) = res[2 * i], res[2 * i + 1]
+        n2, rp2, dp2, _ = oracle.stereo_match(oracle.stereo_params(47.9, True, scales), oracle.kp32_to_kp64(kl), dl,
+                                              oracle.kp32_to_kp64(kr), dr)
+        assert nm[i] == n2 and n2 > 0
+        assert rp[i, :len(kl)].tobytes() == rp2.tobytes() and dp[i, :len(kl)].tobytes() == dp2.tobytes()
+    for b in bufs:
+        cudart.cudaFree(b)
+    ex.set_stream(None)
+    ctx.set_stream(None)
+
+
+def _c3(so, feats, seed, n_points):
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(seed)
+    K = (718.856, 718.856, 607.19, 185.22)
+    q = S.quat_from_axis_angle(rng.normal(size=3), np.radians(rng.uniform(0, 0.5)))
+    t = rng.uniform(-0.05, 0.05, 3)
+    kl, dl = feats["l"]
+    frame = M.make_frame(kl, dl, 1241, 376, rng, q, t)
+    mp = S.map_points_from_keypoints(frame.kp, frame.desc, K, rng, n_points, feats["scales"])
+    cam = M.camera(*K, 386.1)
+    pyr = so.scale_pyramid_c(1.2, feats["scales"])
+    return rng, frame, mp, cam, pyr
+
+
+@pytest.mark.parametrize("th,n_points", [(4.0, 20000), (1.0, 3000), (5.0, 0)])
+def test_search_by_projection_fine(so, ctx, oracle, feats, th, n_points):
+    rng, frame, mp, cam, pyr = _c3(so, feats, 11, n_points)
+    pts = M.fine_points(mp, rng)
+    m, k2p, bi, bd, vis, pout = ctx.SearchByProjection2(frame.view, pts, cam, pyr, th, 0.8)
+    m2, k2p2, bi2, bd2, vis2, pout2, ops = oracle.search_projection_fine(frame.view, pts, cam, pyr, th, 0.8)
+    assert m == m2
+    assert np.array_equal(bi, bi2) and np.array_equal(bd, bd2) and np.array_equal(vis, vis2)
+    assert np.array_equal(k2p, k2p2) and np.array_equal(pout["valid"], pout2["valid"])
+    if n_points:
+        assert m > 100 and ops > 1000
+
+
+@pytest.mark.parametrize("motion", [0, 1, 2])
+def test_search_by_projection_coarse(so, ctx, oracle, feats, motion):
+    rng, frame, mp, cam, pyr = _c3(so, feats, 12 + motion, 3000)
+    pts = M.coarse_points(mp)
+    m, k2p = ctx.SearchByProjectionFrameFrame2(frame.view, pts, cam, pyr, 15.0, 75, motion)
+    m2, k2p2, ops = oracle.search_projection_coarse(frame.view, pts, cam, pyr, 15.0, 75, motion)
+    assert m == m2 and np.array_equal(k2p, k2p2) and m > 50
+
+
+def test_search_by_projection_frame_to_keyframe(so, ctx, oracle, feats):
+    rng, frame, mp, cam, pyr = _c3(so, feats, 21, 1500)
+    pts = M.kf_points(mp, rng)
+    # some ids already found in the frame (sAlreadyFound)
+    frame.k2p[np.nonzero(frame.k2p < 0)[0][:40]] = pts["id"][pts["id"] >= 0][:40]
+    m, k2p = ctx.SearchByProjectionFrameToKeyframe(frame.view, pts, cam, 10.0, 60)
+    m2, k2p2, ops = oracle.search_projection_frame_to_kf(frame.view, pts, cam, 10.0, 60)
+    assert m == m2 and np.array_equal(k2p, k2p2) and m > 50
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_match_bow(so, ctx, oracle, feats, seed):
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(seed)
+    d1 = feats["l"][1][:1000]
+    d2 = np.concatenate([S.flip_bits(d1[rng.permutation(len(d1))[:600]], rng, 12), feats["o"][1][:400]])
+    fv1, fv2 = M.featvec(d1, rng), M.featvec(d2, rng)
+    v1 = (rng.random(len(d1)) < 0.7).astype(np.uint8)
+    v2 = (rng.random(len(d2)) < 0.7).astype(np.uint8)
+    m, m12 = ctx.MatchBoW(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+    m2, m122, ops = oracle.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+    assert m == m2 and np.array_equal(m12, m122) and m > 20 and ops > 1000
+
+
+def test_hamming_peak_probe(so, ctx):
+    v = ctx.hamming_peak()
+    assert 1e10 < v < 5e12
