@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""Benchmark of the ORB front-end hot path on B200 (contract: one JSON line on stdout from rank 0).
+
+Workload (BASELINE.json configs[1], "C2"): EuRoC-shaped stereo pairs 752x480, ORB extraction on both images
+(1200 keypoints, 8 levels, scale 1.2, FAST 20/7) + stereo row-search Hamming matching. One step = one batch of
+`--pairs` synthetic stereo pairs through libsnakeorb.so's C ABI:
+
+  value : pairs/s with the batch already resident in HBM (snk_orb_enqueue on device memory + snk_stereo_match_orb_device),
+          timed with CUDA events on the launching stream, max over ranks
+  e2e   : same metric with HOST (pinned) buffers: H2D of the images, all kernels, D2H of keypoints, descriptors,
+          right_points, depth and match counts inside the timed region
+  roofline     : dominant extraction kernel, algorithmic bytes / its event-timed duration
+  cpu_baseline : the CPU oracle (port of the reference's CPU ORBExtractor + StereoMatching) on the host cores
+
+`--impl reference` times the reference's CPU path (the oracle port; the reference's own ORBExtractor.cpp needs OpenCV
+C++ and cannot be compiled here) on all host threads, same config/metric.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "snake-slam_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+W, H, NFEAT, NLEVELS, SCALE, TH, THMIN = 752, 480, 1200, 8, 1.2, 20, 7
+BF = 47.9  # EuRoC-like fx*baseline: max disparity bf/2
+METRIC = "frames/s (EuRoC stereo pair 752x480: ORB extract x2, 1200 kp, 8 levels + stereo row-search Hamming match)"
+
+
+def level_sizes():
+    out = []
+    sc = 1.0
+    for l in range(NLEVELS):
+        if l:
+            sc = float(np.float32(SCALE)) * sc
+        s = np.float32(1.0 / sc)
+        r = lambda v: int(np.float32(np.float32(v) * s) + np.float32(0.5))
+        out.append((r(H), r(W)) if l else (H, W))
+    return out
+
+
+def algorithmic_bytes(n_kp_img, n_cand_img):
+    """per-image algorithmic bytes of each extraction stage."""
+    S = [h * w for h, w in level_sizes()]
+    sig = sum(S)
+    return {
+        "pyramid": (sig - S[-1]) + (sig - S[0]),
+        "fast": sig + 8 * n_cand_img,
+        "blur": 2 * sig,
+        "describe": 2386 * n_kp_img,
+    }
+
+
+def synth_pairs(n_distinct, seed0=10000):
+    from snakeorb import synthetic as S
+
+    imgs = []
+    for i in range(n_distinct):
+        l = S.image(seed0 + i, W, H)
+        imgs += [l, S.stereo_right(l, seed0 + 5000 + i, 4.0, BF / 2 - 2.0)]
+    return np.stack(imgs)
+
+
+def fill_batch(distinct, n_imgs):
+    """Tile the distinct pairs to the batch size with a per-copy circular row shift, so every image of the batch has
+    different bytes (no accidental cache reuse) while generation stays cheap."""
+    out = np.empty((n_imgs, H, W), np.uint8)
+    nd = len(distinct)
+    for i in range(0, n_imgs, 2):
+        src = (i // 2) % (nd // 2)
+        shift = (i // 2) // (nd // 2) * 7
+        out[i] = np.roll(distinct[2 * src], shift, axis=0)
+        out[i + 1] = np.roll(distinct[2 * src + 1], shift, axis=0)
+    return out
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        rows = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.2] or [r for (_, r) in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_pairs_per_s(distinct, threads, budget_s, stereo_params_fn):
+    """The CPU oracle (oracle/orb_ref.cpp + matchers_ref.cpp) on `threads` host threads, one extractor per thread
+    (the reference's class is not thread-safe), frames statically partitioned. Returns (pairs/s, pairs timed)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+
+    O.build()
+    n_pairs_avail = len(distinct) // 2
+    scales, _ = O.scale_pyramid(NLEVELS, SCALE, NFEAT)
+    sp = O.stereo_params(BF, True, scales)
+    exs = [O.Extractor(NFEAT, SCALE, NLEVELS, TH, THMIN, 1) for _ in range(threads)]
+
+    def work(tid, lo, hi, out):
+        kp = 0
+        for p in range(lo, hi):
+            q = p % n_pairs_avail
+            kl, dl = exs[tid].detect(distinct[2 * q])
+            kr, dr = exs[tid].detect(distinct[2 * q + 1])
+            O.stereo_match(sp, O.kp32_to_kp64(kl), dl, O.kp32_to_kp64(kr), dr)
+            kp += len(kl) + len(kr)
+        out[tid] = kp
+
+    def run(n):
+        out = [0] * threads
+        ts = []
+        t0 = time.perf_counter()
+        for t in range(threads):
+            lo, hi = n * t // threads, n * (t + 1) // threads
+            th = threading.Thread(target=work, args=(t, lo, hi, out))
+            th.start()
+            ts.append(th)
+        for th in ts:
+            th.join()
+        return time.perf_counter() - t0, sum(out)
+
+    run(threads)  # warm-up: allocations, page-in
+    dt, _ = run(2 * threads)
+    n = int(max(2 * threads, min(4096, budget_s / (dt / (2 * threads)))))
+    dt, kp = run(n)
+    return n / dt, n, kp / dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=256, help="stereo pairs per step per GPU")
+    ap.add_argument("--impl", default="snakeorb", choices=["snakeorb", "reference"])
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    config = {"workload": "C2 EuRoC stereo 752x480, 1200 kp/image, 8 levels, scale 1.2, FAST 20/7, stereo row search "
+                          f"(bf={BF}, relaxed)", "pairs_per_step_per_gpu": args.pairs, "images_per_step_per_gpu": 2 * args.pairs,
+              "parallelism": f"frame-sharded x{world}, no collective",
+              "l2": f"inputs {2 * args.pairs * W * H / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        distinct = synth_pairs(8)
+        K, Wm = args.steps, args.warmup
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_py as O
+
+        O.build()
+        scales, _ = O.scale_pyramid(NLEVELS, SCALE, NFEAT)
+        sp = O.stereo_params(BF, True, scales)
+        threads = cores
+        exs = [O.Extractor(NFEAT, SCALE, NLEVELS, TH, THMIN, 1) for _ in range(threads)]
+        per_step = 2 * threads  # bounded sample of the workload per step
+
+        def step():
+            def work(t):
+                for p in range(2):
+                    q = (t * 2 + p) % (len(distinct) // 2)
+                    kl, dl = exs[t].detect(distinct[2 * q])
+                    kr, dr = exs[t].detect(distinct[2 * q + 1])
+                    O.stereo_match(sp, O.kp32_to_kp64(kl), dl, O.kp32_to_kp64(kr), dr)
+
+            ts = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+
+        for _ in range(Wm):
+            step()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            step()
+        dt = time.perf_counter() - t0
+        v = per_step * K / dt
+        line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": K,
+                "warmup": Wm, "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": dict(config, pairs_per_step=per_step),
+                "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
+                                 "sample": f"{per_step} stereo pairs per step x {K} steps, one extractor per thread"},
+                "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    import snakeorb
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (libsnakeorb has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    P, NI = args.pairs, 2 * args.pairs
+    distinct = synth_pairs(16, seed0=10000 + 100 * rank)
+    batch = fill_batch(distinct, NI)
+    host = torch.empty((NI, H, W), dtype=torch.uint8, pin_memory=True)
+    host.numpy()[:] = batch
+    dev = host.cuda(non_blocking=False)
+
+    ex = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=NI, device=local_rank)
+    ctx = snakeorb.Context(device=local_rank)
+    # a dedicated (non-default) torch stream: handle 0 means "the library's own stream" in the C ABI, and
+    # torch.cuda.Event only sees the stream it is recorded on
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
+    ex.set_stream(stream)
+    ctx.set_stream(stream)
+    scales, _ = ex.getPyramid()
+    sp = snakeorb.stereo_params(BF, True, scales)
+    cap = ex.cap
+    rp = torch.empty((P, cap), dtype=torch.float32, device="cuda")
+    dp = torch.empty((P, cap), dtype=torch.float32, device="cuda")
+    nm = torch.empty((P,), dtype=torch.int32, device="cuda")
+
+    def step_device():
+        ex.enqueue_ptr(dev.data_ptr(), NI, H, W, W, W * H, True)
+        ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+
+    # host-side result buffers of the end-to-end path (pinned)
+    h_kps = torch.empty((NI, cap, 24), dtype=torch.uint8, pin_memory=True)
+    h_desc = torch.empty((NI, cap, 4), dtype=torch.int64, pin_memory=True)
+    h_cnt = torch.empty((NI,), dtype=torch.int32, pin_memory=True)
+    h_rp = torch.empty((P, cap), dtype=torch.float32, pin_memory=True)
+    h_dp = torch.empty((P, cap), dtype=torch.float32, pin_memory=True)
+    h_nm = torch.empty((P,), dtype=torch.int32, pin_memory=True)
+    import ctypes as C
+
+    def step_e2e():
+        ex.enqueue_ptr(host.data_ptr(), NI, H, W, W, W * H, False)
+        ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+        h_rp.copy_(rp, non_blocking=True)
+        h_dp.copy_(dp, non_blocking=True)
+        h_nm.copy_(nm, non_blocking=True)
+        snakeorb._check(snakeorb.lib().snk_orb_fetch(ex.h, C.c_void_p(h_kps.data_ptr()), C.c_void_p(h_desc.data_ptr()), cap,
+                                                     C.c_void_p(h_cnt.data_ptr())))
+
+    # ---- device-resident timing --------------------------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    ex.set_profiling(True)
+    ex.stage_ms(reset=True)
+    sampler = ClockSampler(local_rank)
+    time.sleep(0.25)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    t_wall1 = time.time()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop(t_wall0, t_wall1)
+    stage_ms, stage_launches = ex.stage_ms(reset=True)
+    ex.set_profiling(False)
+    kps_ptr, desc_ptr, cnt_ptr, stride = ex.device_results()
+    cudart = C.CDLL("libcudart.so")
+    cnt_host = np.zeros(NI, np.int32)
+    cudart.cudaMemcpy(C.c_void_p(cnt_host.ctypes.data), C.c_void_p(cnt_ptr), C.c_size_t(4 * NI), 2)
+    n_kp_step = int(cnt_host.sum())
+    n_match_step = int(nm.sum().item())
+
+    # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(2):
+            step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tw0 = time.perf_counter()
+        f0.record()
+        for _ in range(args.steps):
+            step_e2e()
+        f1.record()
+        barrier()
+        ms_e2e = max(f0.elapsed_time(f1), (time.perf_counter() - tw0) * 1e3)  # fetch blocks the host: wall >= device
+        e2e = ms_e2e
+
+    t = torch.tensor([ms, e2e if e2e is not None else 0.0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_max = float(t[0]), float(t[1])
+    value = world * P * args.steps / (ms_max * 1e-3)
+    kp_per_s = world * n_kp_step * args.steps / (ms_max * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+        # dominant extraction kernel by event time inside the timed region
+        names = {1: "pyramid", 2: "fast", 3: "distribute", 4: "blur", 5: "describe"}
+        # raw FAST candidates per image: not fetched in the timed path; use the per-image mean of a probe image
+        n_cand_img = sum(len(ex.candidates(l, 0)) for l in range(NLEVELS))
+        ab = algorithmic_bytes(n_kp_step / NI, n_cand_img)
+        ab["distribute"] = 8 * n_cand_img + 4 * n_kp_step / NI  # candidate records in, selected records out
+        stage = {names[i]: float(stage_ms[i]) / args.steps for i in names}
+        dom = max(stage, key=stage.get)
+        launches = {names[i]: int(stage_launches[i]) // args.steps for i in names}
+        bytes_launch = ab[dom] * NI / max(launches[dom], 1)
+        dur = stage[dom] * 1e-3 / max(launches[dom], 1)
+        achieved = bytes_launch / dur / 1e9
+        e2e_bytes = sum(algorithmic_bytes(n_kp_step / NI, n_cand_img)[k] for k in ("pyramid", "fast", "blur", "describe"))
+        extraction_ms = sum(stage.values())
+        roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_image": ab[dom], "images_per_launch": NI / max(launches[dom], 1),
+                    "stage_ms_per_step": stage,
+                    "extraction_e2e": {"bytes_per_image": e2e_bytes, "achieved_gbs": e2e_bytes * NI / (extraction_ms * 1e-3) / 1e9,
+                                       "frac": e2e_bytes * NI / (extraction_ms * 1e-3) / 1e9 / hbm_peak}}
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
+                "keypoints_per_s": kp_per_s, "images_per_s": 2 * value,
+                "keypoints_per_step": n_kp_step, "stereo_matches_per_step": n_match_step,
+                "raw_fast_candidates_per_image": n_cand_img, "clocks": clocks,
+                "gpu_launches": int(sum(int(x) for x in stage_launches[1:6])) + args.steps,  # + stereo kernel per step
+                "roofline": roofline}
+        if e2e is not None:
+            h2d = NI * W * H
+            d2h = NI * cap * (24 + 32) + NI * 4 + P * cap * 8 + P * 4 + 4
+            line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
+                           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps}
+        if not args.no_cpu:
+            try:
+                popc = ctx.hamming_peak()
+                line["popc_peak_pair_ops_per_s"] = popc
+            except Exception as exc:  # noqa: BLE001
+                line["popc_peak_pair_ops_per_s"] = None
+            v, n, kps = cpu_pairs_per_s(distinct, cores, args.cpu_budget, None)
+            line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
+                                    "sample": f"{n} stereo pairs of the same workload, one oracle extractor per thread, "
+                                              f"{cores} threads", "keypoints_per_s": kps}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

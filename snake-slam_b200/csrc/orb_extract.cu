@@ -105,12 +105,15 @@ struct snk_orb
     int* h_counts = nullptr;  // pinned
     int* h_err = nullptr;     // pinned
 
+    // per-stage timing: a ring of event sets so that up to PROF_RING enqueues can be in flight without a host sync
+    static constexpr int PROF_RING = 32;
     bool profiling = false;
-    cudaEvent_t ev[SNK_ORB_NUM_STAGES + 1]{};
+    cudaEvent_t ev[PROF_RING][SNK_ORB_NUM_STAGES]{};
+    bool ev_pending[PROF_RING]{};
+    int ev_launches[PROF_RING][SNK_ORB_NUM_STAGES]{};
+    int ev_next = 0;
     float stage_ms[SNK_ORB_NUM_STAGES]{};
     int stage_launches[SNK_ORB_NUM_STAGES]{};
-    bool ev_pending = false;
-    int pending_launches[SNK_ORB_NUM_STAGES]{};
 
     void free_buffers()
     {
@@ -157,8 +160,12 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
                     "use fewer levels",
                     l, lv.w, lv.h);
         const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
-        lv.pitch = lv.gauss_pitch = align_up(lv.w, 64);
-        lv.img_stride = lv.gauss_stride = (size_t)lv.pitch * lv.h;
+        // level 0 only ever receives the caller's bytes: a dense pitch makes the host->device copy one contiguous
+        // transfer when the caller's rows are dense too
+        lv.pitch       = (l == 0) ? lv.w : align_up(lv.w, 64);
+        lv.gauss_pitch = align_up(lv.w, 64);
+        lv.img_stride  = (size_t)lv.pitch * lv.h;
+        lv.gauss_stride = (size_t)lv.gauss_pitch * lv.h;
         pyr_off[l]   = pyr_bytes;
         gauss_off[l] = gauss_bytes;
         pyr_bytes += align_up(lv.img_stride * B, (size_t)256);
@@ -314,7 +321,8 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
     h->stream = h->own_stream;
     cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault);
     cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault);
-    for (auto& e : h->ev) cudaEventCreate(&e);
+    for (auto& set : h->ev)
+        for (auto& e : set) cudaEventCreate(&e);
     // constants of the descriptor kernel
     int umax[16];
     {
@@ -349,8 +357,9 @@ void snk_orb_destroy(snk_orb* h)
     h->free_buffers();
     if (h->h_counts) cudaFreeHost(h->h_counts);
     if (h->h_err) cudaFreeHost(h->h_err);
-    for (auto& e : h->ev)
-        if (e) cudaEventDestroy(e);
+    for (auto& set : h->ev)
+        for (auto& e : set)
+            if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -375,24 +384,28 @@ int snk_orb_pyramid(const snk_orb* h, double* scale, int32_t* features)
     return SNK_OK;
 }
 
-static void collect_events(snk_orb* h)
+static void collect_set(snk_orb* h, int r)
 {
-    if (!h->ev_pending) return;
-    cudaEventSynchronize(h->ev[SNK_ORB_NUM_STAGES - 1]);
+    if (!h->ev_pending[r]) return;
+    cudaEventSynchronize(h->ev[r][SNK_ORB_NUM_STAGES - 1]);
     float total = 0;
     for (int s = 0; s < SNK_ORB_NUM_STAGES - 1; ++s)
     {
         float ms = 0;
-        if (cudaEventElapsedTime(&ms, h->ev[s], h->ev[s + 1]) == cudaSuccess)
+        if (cudaEventElapsedTime(&ms, h->ev[r][s], h->ev[r][s + 1]) == cudaSuccess)
         {
             h->stage_ms[s] += ms;
             total += ms;
         }
-        h->stage_launches[s] += h->pending_launches[s];
-        h->stage_launches[SNK_ORB_NUM_STAGES - 1] += h->pending_launches[s];
+        h->stage_launches[s] += h->ev_launches[r][s];
+        h->stage_launches[SNK_ORB_NUM_STAGES - 1] += h->ev_launches[r][s];
     }
     h->stage_ms[SNK_ORB_NUM_STAGES - 1] += total;
-    h->ev_pending = false;
+    h->ev_pending[r] = false;
+}
+static void collect_events(snk_orb* h)
+{
+    for (int r = 0; r < snk_orb::PROF_RING; ++r) collect_set(h, r);
 }
 
 int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch, size_t img_stride,
@@ -407,13 +420,20 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     SNK_REQUIRE(n_imgs == 1 || img_stride >= pitch * rows, "img_stride smaller than an image");
     int rc = orb_allocate(h, rows, cols);
     if (rc) return rc;
-    collect_events(h);
     PyrDev& P      = h->P;
     cudaStream_t st = h->stream;
     const bool prof = h->profiling;
-    int* nl         = h->pending_launches;
-    if (prof) memset(nl, 0, sizeof(h->pending_launches));
-    if (prof) cudaEventRecord(h->ev[0], st);
+    const int ring  = h->ev_next;
+    int scratch_launches[SNK_ORB_NUM_STAGES] = {};
+    int* nl         = prof ? h->ev_launches[ring] : scratch_launches;
+    cudaEvent_t* ev = h->ev[ring];
+    if (prof)
+    {
+        collect_set(h, ring);  // only blocks when the ring has wrapped onto a set that is still in flight
+        memset(nl, 0, sizeof(scratch_launches));
+        h->ev_next = (ring + 1) % snk_orb::PROF_RING;
+        cudaEventRecord(ev[0], st);
+    }
 
     // stage 0: level 0. Device input is used in place (the reference copies it, ORBExtractor.cpp:269; nothing reads the
     // copy's apron, so aliasing is equivalent). Host input is copied straight into the level-0 buffer.
@@ -438,7 +458,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
                 SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img + i * P.lv[0].img_stride, P.lv[0].pitch, imgs + i * img_stride,
                                            pitch, cols, rows, cudaMemcpyHostToDevice, st));
     }
-    if (prof) cudaEventRecord(h->ev[1], st);
+    if (prof) cudaEventRecord(ev[1], st);
 
     // stage 1: pyramid chain
     for (int l = 1; l < P.nlevels; ++l)
@@ -450,24 +470,24 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
                                        h->d_xofs[l], h->d_xa[l], h->d_yofs[l], h->d_yb[l]);
         ++nl[1];
     }
-    if (prof) cudaEventRecord(h->ev[2], st);
+    if (prof) cudaEventRecord(ev[2], st);
 
     // stage 2: FAST over every cell of every level
     k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->d_cells, h->d_cand, h->d_cell_count);
     ++nl[2];
-    if (prof) cudaEventRecord(h->ev[3], st);
+    if (prof) cudaEventRecord(ev[3], st);
 
     // stage 3: quadtree distribution per (level, image)
     k_distribute<<<dim3(P.nlevels, n_imgs), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
                                                                      h->d_workA, h->d_workB, h->d_sel, h->d_sel_count,
                                                                      h->node_cap, h->d_err);
     ++nl[3];
-    if (prof) cudaEventRecord(h->ev[4], st);
+    if (prof) cudaEventRecord(ev[4], st);
 
     // stage 4: blur of every level
     k_blur<<<dim3((unsigned)h->tiles.size(), n_imgs), 256, 0, st>>>(P, h->d_tiles);
     ++nl[4];
-    if (prof) cudaEventRecord(h->ev[5], st);
+    if (prof) cudaEventRecord(ev[5], st);
 
     // stage 5: orientation + descriptors + output records
     k_describe<<<dim3((P.kp_stride + DS_WARPS - 1) / DS_WARPS, n_imgs), DS_WARPS * 32, 0, st>>>(
@@ -475,9 +495,9 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     ++nl[5];
     if (prof)
     {
-        cudaEventRecord(h->ev[6], st);
-        cudaEventRecord(h->ev[7], st);
-        h->ev_pending = true;
+        cudaEventRecord(ev[6], st);
+        cudaEventRecord(ev[7], st);
+        h->ev_pending[ring] = true;
     }
     SNK_CUDA(cudaGetLastError());
     h->last_n = n_imgs;
