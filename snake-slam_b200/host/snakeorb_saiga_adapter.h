@@ -1,0 +1,208 @@
+// snakeorb_saiga_adapter.h — header-only C++ binding of libsnakeorb.so with the reference's class shapes.
+//
+// Inside the reference tree, define SNAKEORB_WITH_SAIGA before including it: the adapter then takes Saiga's own
+// ImageView / KeyPoint / DescriptorORB types, and `Snake/Preprocess/FeatureDetector.cpp:31-41` only has to construct
+// `Saiga::ORBExtractorB200` instead of `Saiga::ORBExtractor` / `Saiga::ORBExtractorGPU`.
+// Without the macro it ships layout-identical stand-ins so it compiles (and is compile-tested) on its own.
+//
+// Error convention: the reference aborts through SAIGA_ASSERT / SAIGA_EXIT_ERROR (saiga/core/util/assert.h;
+// FeatureDetector.cpp:35); the library returns codes — the adapter is where a code becomes an abort.
+#pragma once
+#include "../../include/snakeorb.h"
+
+#include <array>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#ifdef SNAKEORB_WITH_SAIGA
+#    include "saiga/core/image/imageView.h"
+#    include "saiga/vision/features/Features.h"
+#    include "saiga/vision/util/ScalePyramid.h"
+namespace snkadapter
+{
+template <typename T>
+using ImageView = Saiga::ImageView<T>;
+using KeyPointF = Saiga::KeyPoint<float>;
+using KeyPointD = Saiga::KeyPoint<double>;
+using DescriptorORB = Saiga::DescriptorORB;
+}  // namespace snkadapter
+#else
+namespace snkadapter
+{
+// saiga/core/image/imageView.h:79-160 — non-owning {height, width, pitchBytes, data}
+template <typename T>
+struct ImageView
+{
+    int rows = 0, cols = 0;
+    size_t pitchBytes = 0;
+    T* data           = nullptr;
+    bool empty() const { return rows <= 0 || cols <= 0 || !data; }
+};
+struct KeyPointF  // saiga/vision/features/Features.h:21-67, T = float
+{
+    float x, y, size, angle, response;
+    int octave;
+};
+struct alignas(16) KeyPointD  // T = double (Snake::KeyPoint)
+{
+    double x, y, size, angle, response;
+    int octave;
+};
+using DescriptorORB = std::array<uint64_t, 4>;  // Features.h:70
+}  // namespace snkadapter
+#endif
+
+namespace snkadapter
+{
+static_assert(sizeof(KeyPointF) == sizeof(snk_keypoint_f32), "KeyPoint<float> must be 24 bytes");
+static_assert(sizeof(KeyPointD) == sizeof(snk_keypoint_f64), "KeyPoint<double> must be 48 bytes");
+static_assert(sizeof(DescriptorORB) == 32, "DescriptorORB must be 32 bytes");
+
+inline void check(int rc, const char* what)
+{
+    if (rc != SNK_OK)
+    {
+        std::fprintf(stderr, "snakeorb: %s failed (%d): %s\n", what, rc, snk_last_error());
+        std::abort();  // == SAIGA_ASSERT behaviour
+    }
+}
+
+// Drop-in for Saiga::ORBExtractor (ORBExtractor.h:44-90) and Saiga::ORBExtractorGPU (ORBExtractorGPU.h:38-49).
+// Same constructor arguments; `num_threads` is accepted and ignored. Not thread-safe, exactly like the originals.
+class ORBExtractorB200
+{
+   public:
+    ORBExtractorB200(int nfeatures, float scaleFactor, int num_levels, int th_fast, int th_fast_min, int /*num_threads*/ = 1,
+                     int device = 0)
+    {
+        snk_orb_params p{nfeatures, scaleFactor, num_levels, th_fast, th_fast_min, /*max_batch=*/2, device};
+        check(snk_orb_create(&p, &h_), "snk_orb_create");
+        num_levels_ = num_levels;
+    }
+    ~ORBExtractorB200() { snk_orb_destroy(h_); }
+    ORBExtractorB200(const ORBExtractorB200&)            = delete;
+    ORBExtractorB200& operator=(const ORBExtractorB200&) = delete;
+
+    // void ORBExtractor::Detect(ImageView<uchar>, std::vector<KeyPoint<float>>&, std::vector<DescriptorORB>&)
+    // (ORBExtractor.cpp:178). Returns the number of keypoints like ORBExtractorGPU::Detect does.
+    int Detect(ImageView<unsigned char> image, std::vector<KeyPointF>& keypoints, std::vector<DescriptorORB>& descriptors)
+    {
+        descriptors.clear();
+        if (image.empty()) return 0;  // ORBExtractor.cpp:182
+        const int cap = snk_orb_max_keypoints(h_);
+        keypoints.resize(cap);
+        descriptors.resize(cap);
+        int n = 0;
+#ifdef SNAKEORB_WITH_SAIGA
+        const unsigned char* ptr = image.data8;
+        const int rows = image.rows, cols = image.cols;
+#else
+        const unsigned char* ptr = image.data;
+        const int rows = image.rows, cols = image.cols;
+#endif
+        check(snk_orb_detect(h_, ptr, rows, cols, image.pitchBytes, /*img_is_device=*/0,
+                             reinterpret_cast<snk_keypoint_f32*>(keypoints.data()),
+                             reinterpret_cast<uint64_t*>(descriptors.data()), cap, &n),
+              "snk_orb_detect");
+        keypoints.resize(n);
+        descriptors.resize(n);
+        return n;
+    }
+
+    // Left and right image of a stereo frame in one batched call (FeatureDetector.cpp:124 + :154 back to back).
+    void DetectStereo(ImageView<unsigned char> left, ImageView<unsigned char> right, std::vector<KeyPointF>& kl,
+                      std::vector<DescriptorORB>& dl, std::vector<KeyPointF>& kr, std::vector<DescriptorORB>& dr)
+    {
+        Detect(left, kl, dl);
+        Detect(right, kr, dr);
+    }
+
+    // ScalePyramid accessors used by the matchers (ScalePyramid.h:78-84)
+    std::vector<double> Scales() const
+    {
+        std::vector<double> s(num_levels_);
+        check(snk_orb_pyramid(h_, s.data(), nullptr), "snk_orb_pyramid");
+        return s;
+    }
+    std::vector<int32_t> Features() const
+    {
+        std::vector<int32_t> f(num_levels_);
+        check(snk_orb_pyramid(h_, nullptr, f.data()), "snk_orb_pyramid");
+        return f;
+    }
+    snk_orb* handle() { return h_; }
+
+   private:
+    snk_orb* h_     = nullptr;
+    int num_levels_ = 0;
+};
+
+// Drop-in for Saiga::BruteForceMatcher<DescriptorORB> (Features.h:299-423): same public members.
+struct BruteForceMatcherB200
+{
+    explicit BruteForceMatcherB200(int device = 0) { check(snk_ctx_create(device, &c_), "snk_ctx_create"); }
+    ~BruteForceMatcherB200() { snk_ctx_destroy(c_); }
+    BruteForceMatcherB200(const BruteForceMatcherB200&)            = delete;
+    BruteForceMatcherB200& operator=(const BruteForceMatcherB200&) = delete;
+
+    void matchKnn2(const std::vector<DescriptorORB>& d1, const std::vector<DescriptorORB>& d2)
+    {
+        knn2.resize(d1.size());
+        check(snk_match_knn2(c_, reinterpret_cast<const uint64_t*>(d1.data()), (int)d1.size(),
+                             reinterpret_cast<const uint64_t*>(d2.data()), (int)d2.size(), knn2.data()),
+              "snk_match_knn2");
+    }
+    void matchKnn2_omp(const std::vector<DescriptorORB>& d1, const std::vector<DescriptorORB>& d2, int /*threads*/)
+    {
+        matchKnn2(d1, d2);
+    }
+    int filterMatches(int threshold, float ratioThreshold)
+    {
+        std::vector<int32_t> ij(2 * knn2.size() + 2);
+        int n = 0;
+        check(snk_filter_matches(knn2.data(), (int)knn2.size(), threshold, ratioThreshold, ij.data(), &n), "snk_filter_matches");
+        matches.clear();
+        for (int i = 0; i < n; ++i) matches.push_back({ij[2 * i], ij[2 * i + 1]});
+        return n;
+    }
+    std::vector<snk_knn2> knn2;                   // {dist0, idx0, dist1, idx1} == knn2(i,0/1).{first,second}
+    std::vector<std::pair<int, int>> matches;     // == BruteForceMatcher::matches
+    snk_ctx* context() { return c_; }
+
+   private:
+    snk_ctx* c_ = nullptr;
+};
+
+// Preprocess::StereoMatching (Preprocess.cpp:122-242) body after the two Rectification::Forward loops.
+// left/right: rectified keypoints; right_points/depth: Frame::right_points / Frame::depth (resized by the caller's
+// Frame::allocateTmp); returns the number of matches.
+inline int StereoMatchingB200(snk_ctx* c, double bf, bool relaxed, const std::vector<double>& scales,
+                              const std::vector<KeyPointD>& left, const std::vector<DescriptorORB>& dl,
+                              const std::vector<KeyPointD>& right, const std::vector<DescriptorORB>& dr,
+                              std::vector<float>& right_points, std::vector<float>& depth)
+{
+    snk_stereo_params p{};
+    p.bf      = bf;
+    p.relaxed = relaxed;
+    p.nlevels = (int)scales.size();
+    for (size_t i = 0; i < scales.size() && i < 16; ++i) p.scale[i] = scales[i];
+    right_points.resize(left.size());
+    depth.resize(left.size());
+    int n = 0;
+    check(snk_stereo_match(c, &p, reinterpret_cast<const snk_keypoint_f64*>(left.data()),
+                           reinterpret_cast<const uint64_t*>(dl.data()), (int)left.size(),
+                           reinterpret_cast<const snk_keypoint_f64*>(right.data()),
+                           reinterpret_cast<const uint64_t*>(dr.data()), (int)right.size(), right_points.data(),
+                           depth.data(), &n),
+          "snk_stereo_match");
+    return n;
+}
+}  // namespace snkadapter
+
+#ifdef SNAKEORB_WITH_SAIGA
+namespace Saiga
+{
+using ORBExtractorB200 = snkadapter::ORBExtractorB200;
+}
+#endif

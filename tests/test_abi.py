@@ -69,3 +69,11 @@ def test_struct_layouts_match_header():
     assert C.sizeof(snakeorb.GridView) == 6 * 8 + 8 + 8
     assert C.sizeof(snakeorb.ScalePyramidC) == 8 + 8 + 128
     assert snakeorb.POINT_FINE.itemsize == 96 and snakeorb.POINT_COARSE.itemsize == 96 and snakeorb.POINT_KF.itemsize == 64
+
+
+def test_adapter_header_compiles_standalone():
+    hdr = os.path.join(ROOT, "snake-slam_b200", "host", "snakeorb_saiga_adapter.h")
+    src = '#include "%s"\nint main(){ return 0; }\n' % hdr
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    r = subprocess.run([cxx, "-std=c++17", "-fsyntax-only", "-x", "c++", "-"], input=src, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
