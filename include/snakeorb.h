@@ -167,6 +167,36 @@ SNK_API int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t
 SNK_API int snk_match_knn2_batch_device(snk_ctx* c, const uint64_t* d1_dev, const int32_t* n_dev, int stride1,
                                         const uint64_t* d2_dev, const int32_t* m_dev, int stride2, int n_problems,
                                         snk_knn2* out_dev);
+/* kNN-2 matching without any device allocation. This entry point has no counterpart in the reference.
+ *
+ * Who it is for: callers that are not allowed to allocate GPU memory at the moment they need a brute-force match.
+ * In Snake-SLAM that is the tracking thread's relocalisation / brute-force fallback (TrackBruteForce), which runs in
+ * the middle of the real-time loop: snk_match_knn2 may call cudaMalloc to grow its context scratch, and cudaMalloc /
+ * cudaFree stall the whole device (they wait for every running kernel, including the extractor's, on every stream)
+ * and can fail outright when the rest of the system — dense mapper, viewer, other processes — has already reserved
+ * the card's memory. Integrations that hand the library a fixed memory budget at start-up have the same constraint.
+ *
+ * What it does: the same result as snk_match_knn2 (same kernel, same tie-breaking), with the device-side staging of
+ * d1, d2 and the result records placed in a fixed array inside the library instead of allocated memory. The array is
+ * SNK_KNN2_NOALLOC_BYTES (320 KiB) and is held by every GPU that loads the library until the process exits.
+ * Inputs and outputs are the caller's host arrays, exactly as for snk_match_knn2. It calls no cudaMalloc, cudaFree or
+ * any other allocating routine.
+ *
+ * Limits and rules:
+ *  - at most SNK_KNN2_NOALLOC_MAX (4096) descriptors per side; larger n or m is rejected with SNK_ERR_INVALID and a
+ *    message naming the limit (use snk_match_knn2 there);
+ *  - the first call on a device looks up the array's device address (a one-time set-up for that device); make that
+ *    first call before starting any CUDA stream capture;
+ *  - all calls on a device share the one array and it keeps whatever the previous call left in it. Nothing in it
+ *    needs to be zero at entry (each call overwrites what it reads), but two calls whose GPU work overlaps — from
+ *    two threads, or on two streams — race on it: serialise them;
+ *  - `cuda_stream` is the cudaStream_t the copies and the kernel run on (NULL = the default stream); the call returns
+ *    after that stream has finished this call's work. */
+#define SNK_KNN2_NOALLOC_MAX 4096
+#define SNK_KNN2_NOALLOC_BYTES (SNK_KNN2_NOALLOC_MAX * (32 + 32 + 16))
+SNK_API int snk_match_knn2_noalloc(int device, void* cuda_stream, const uint64_t* d1, int n, const uint64_t* d2, int m,
+                                   snk_knn2* out);
+
 /* BruteForceMatcher::filterMatches (Features.h:394-414): threshold + float ratio test over knn2; writes (i, j) pairs
  * in ascending i == the public `matches` member; returns the count in *n_matches. Host pointers. */
 SNK_API int snk_filter_matches(const snk_knn2* knn2, int n, int threshold, float ratio, int32_t* matches_ij,

@@ -3,6 +3,7 @@
 #include "project_kernels.cuh"
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 using namespace snk;
@@ -281,5 +282,72 @@ int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s)
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// kNN-2 matching for callers that must not allocate device memory
+// ------------------------------------------------------------------------------------------------------------------
+// The staging area that snk_match_knn2 obtains from cudaMalloc (device copies of both descriptor sets and of the
+// result records) lives here in a fixed array that is part of the library image: every GPU that loads libsnakeorb.so
+// carries these 320 KiB until the process exits. In host code the name `g_knn2_noalloc_scratch` is only a stand-in for
+// the symbol, not a device address, so the address is looked up once per device with cudaGetSymbolAddress (below) and
+// that pointer is what the kernel receives.
+static __device__ __align__(256) unsigned char g_knn2_noalloc_scratch[SNK_KNN2_NOALLOC_BYTES];
+
+namespace
+{
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+unsigned char* g_noalloc_ptr[kMaxDevices] = {};  // device address of the scratch array, per device ordinal
+
+// One-time set-up for `device`, which must be the current device.
+int noalloc_scratch(int device, unsigned char** out)
+{
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device])
+    {
+        unsigned char* ptr = nullptr;
+        cudaError_t e      = cudaGetSymbolAddress((void**)&ptr, g_knn2_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+        {
+            set_error("cudaGetSymbolAddress(g_knn2_noalloc_scratch) failed on device %d: %s", device, cudaGetErrorString(e));
+            return SNK_ERR_CUDA;
+        }
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return SNK_OK;
+}
+}  // namespace
+
+extern "C" int snk_match_knn2_noalloc(int device, void* cuda_stream, const uint64_t* d1, int n, const uint64_t* d2, int m,
+                                      snk_knn2* out)
+{
+    SNK_REQUIRE(out && n >= 0 && m >= 0 && (n == 0 || d1) && (m == 0 || d2), "bad argument");
+    SNK_REQUIRE(device >= 0 && device < kMaxDevices, "device ordinal %d out of range", device);
+    SNK_REQUIRE(n <= SNK_KNN2_NOALLOC_MAX && m <= SNK_KNN2_NOALLOC_MAX,
+                "snk_match_knn2_noalloc handles at most %d descriptors per side (got n=%d, m=%d); "
+                "use snk_match_knn2 for larger sets",
+                SNK_KNN2_NOALLOC_MAX, n, m);
+    if (n == 0) return SNK_OK;
+    int rc = select_device(device);  // makes `device` current and checks it is an sm_100 part
+    if (rc) return rc;
+    unsigned char* base = nullptr;
+    rc                  = noalloc_scratch(device, &base);
+    if (rc) return rc;
+    // fixed carve-up of the array: [d1 | d2 | results]
+    uint64_t* a = reinterpret_cast<uint64_t*>(base);
+    uint64_t* b = reinterpret_cast<uint64_t*>(base + (size_t)SNK_KNN2_NOALLOC_MAX * 32);
+    snk_knn2* o = reinterpret_cast<snk_knn2*>(base + (size_t)SNK_KNN2_NOALLOC_MAX * 64);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // Nothing in the array has to start at zero: the kernel reads only the first n / m descriptors, which the two
+    // copies below have just overwritten, and it writes all n result records before they are copied back.
+    SNK_CUDA(cudaMemcpyAsync(a, d1, 32 * (size_t)n, cudaMemcpyHostToDevice, st));
+    if (m) SNK_CUDA(cudaMemcpyAsync(b, d2, 32 * (size_t)m, cudaMemcpyHostToDevice, st));
+    k_knn2<<<dim3((n + KNN_NT - 1) / KNN_NT, 1), KNN_NT, 0, st>>>(a, nullptr, n, n, b, nullptr, m, m, o);
+    SNK_CUDA(cudaGetLastError());
+    SNK_CUDA(cudaMemcpyAsync(out, o, sizeof(snk_knn2) * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    return SNK_OK;
+}
 
 #include "project_host.inl"
