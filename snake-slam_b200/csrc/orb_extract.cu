@@ -94,8 +94,9 @@ struct snk_orb
     uint8_t* d_pyr = nullptr;    // levels 0..L-1 (level 0 unused when the caller's device buffer is aliased)
     uint8_t* d_gauss = nullptr;
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
-    int *d_xofs[SNK_MAX_LEVELS]{}, *d_yofs[SNK_MAX_LEVELS]{};
-    short *d_xa[SNK_MAX_LEVELS]{}, *d_yb[SNK_MAX_LEVELS]{};
+    ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
+    int* d_yofs[SNK_MAX_LEVELS]{};
+    short* d_yb[SNK_MAX_LEVELS]{};
     CellDev* d_cells = nullptr;
     TileDev* d_tiles = nullptr;
     uint32_t *d_cand = nullptr, *d_workA = nullptr, *d_workB = nullptr, *d_sel = nullptr;
@@ -123,7 +124,7 @@ struct snk_orb
         };
         F(d_pyr), F(d_gauss), F(d_cells), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
             F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
-        for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_xofs[l]), F(d_yofs[l]), F(d_xa[l]), F(d_yb[l]);
+        for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_yofs[l]), F(d_yb[l]);
         rows = cols = 0;
     }
 };
@@ -162,7 +163,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
         // level 0 only ever receives the caller's bytes: a dense pitch makes the host->device copy one contiguous
         // transfer when the caller's rows are dense too
-        lv.pitch       = (l == 0) ? lv.w : align_up(lv.w, 64);
+        lv.pitch       = (l == 0) ? align_up(lv.w, 4) : align_up(lv.w, 64);
         lv.gauss_pitch = align_up(lv.w, 64);
         lv.img_stride  = (size_t)lv.pitch * lv.h;
         lv.gauss_stride = (size_t)lv.gauss_pitch * lv.h;
@@ -198,7 +199,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         lv.n_cells  = (int)h->cells.size() - lv.cell_base;
         lv.sel_base = sel_acc;
         sel_acc += lv.quota + 4;
-        for (int ty = 0; ty < (lv.h + BL_TH - 1) / BL_TH; ++ty)
+        for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
     }
     P.cells_per_img = (int)h->cells.size();
@@ -231,24 +232,35 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         std::vector<short> xa, yb;
         resize_tables(P.lv[l - 1].w, P.lv[l].w, xo, xa, true);
         resize_tables(P.lv[l - 1].h, P.lv[l].h, yo, yb, false);
-        // the resize kernel stages a fixed-size source window per output tile
-        for (int t0 = 0; t0 < P.lv[l].w; t0 += RS_TW)
+        // per-quad table of the resize kernel: 4 output pixels read a window of at most 8 source bytes
+        const int sw = P.lv[l - 1].w, dw = P.lv[l].w;
+        std::vector<ResizeQuad> quads((dw + 3) / 4);
+        for (int qx = 0; qx < (int)quads.size(); ++qx)
         {
-            int t1 = std::min(t0 + RS_TW, P.lv[l].w) - 1;
-            SNK_REQUIRE(xo[t1] + 1 - xo[t0] + 1 <= RS_SW, "scale factor %.3f not supported (max 1.3)", h->prm.scale_factor);
+            ResizeQuad& q = quads[qx];
+            const int x0  = 4 * qx;
+            const int s0  = xo[x0];
+            q.word        = s0 >> 2;
+            q.shift_bits  = 8 * (s0 & 3);
+            q._pad        = 0;
+            unsigned nib[8];
+            for (int j = 0; j < 4; ++j)
+            {
+                const int x  = std::min(x0 + j, dw - 1);  // lanes past the right edge repeat the last pixel (never stored)
+                const int t0 = xo[x] - s0, t1 = std::min(xo[x] + 1, sw - 1) - s0;
+                SNK_REQUIRE(t0 >= 0 && t1 <= 7, "scale factor %.3f not supported (max 1.3)", h->prm.scale_factor);
+                nib[2 * j]     = (unsigned)t0;
+                nib[2 * j + 1] = (unsigned)t1;
+                q.coef[j]      = (unsigned)(unsigned short)xa[2 * x] | ((unsigned)(unsigned short)xa[2 * x + 1] << 16);
+            }
+            q.sel = 0;
+            for (int k = 0; k < 8; ++k) q.sel |= nib[k] << (4 * k);
         }
-        for (int t0 = 0; t0 < P.lv[l].h; t0 += RS_TH)
-        {
-            int t1 = std::min(t0 + RS_TH, P.lv[l].h) - 1;
-            SNK_REQUIRE(yo[t1] + 1 - yo[t0] + 1 <= RS_SH, "scale factor %.3f not supported (max 1.3)", h->prm.scale_factor);
-        }
-        SNK_CUDA(cudaMalloc(&h->d_xofs[l], xo.size() * sizeof(int)));
+        SNK_CUDA(cudaMalloc(&h->d_quads[l], quads.size() * sizeof(ResizeQuad)));
         SNK_CUDA(cudaMalloc(&h->d_yofs[l], yo.size() * sizeof(int)));
-        SNK_CUDA(cudaMalloc(&h->d_xa[l], xa.size() * sizeof(short)));
         SNK_CUDA(cudaMalloc(&h->d_yb[l], yb.size() * sizeof(short)));
-        SNK_CUDA(cudaMemcpy(h->d_xofs[l], xo.data(), xo.size() * sizeof(int), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMemcpy(h->d_quads[l], quads.data(), quads.size() * sizeof(ResizeQuad), cudaMemcpyHostToDevice));
         SNK_CUDA(cudaMemcpy(h->d_yofs[l], yo.data(), yo.size() * sizeof(int), cudaMemcpyHostToDevice));
-        SNK_CUDA(cudaMemcpy(h->d_xa[l], xa.data(), xa.size() * sizeof(short), cudaMemcpyHostToDevice));
         SNK_CUDA(cudaMemcpy(h->d_yb[l], yb.data(), yb.size() * sizeof(short), cudaMemcpyHostToDevice));
     }
     SNK_CUDA(cudaMalloc(&h->d_cells, h->cells.size() * sizeof(CellDev)));
@@ -337,6 +349,13 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
             umax[v] = v0;
             ++v0;
         }
+    }
+    static const int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    if (memcmp(umax, kUmax, sizeof(umax)) != 0)
+    {
+        set_error("internal: AngleUmax table mismatch");
+        snk_orb_destroy(h);
+        return SNK_ERR_INVALID;
     }
     if (cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)) != cudaSuccess ||
         cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024) != cudaSuccess)
@@ -437,7 +456,9 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
 
     // stage 0: level 0. Device input is used in place (the reference copies it, ORBExtractor.cpp:269; nothing reads the
     // copy's apron, so aliasing is equivalent). Host input is copied straight into the level-0 buffer.
-    if (on_device)
+    // the kernels read rows as aligned 32-bit words
+    const bool aligned = ((uintptr_t)imgs % 4 == 0) && (pitch % 4 == 0) && (img_stride % 4 == 0 || n_imgs == 1);
+    if (on_device && aligned)
     {
         P.lv[0].img        = const_cast<uint8_t*>(imgs);
         P.lv[0].pitch      = (int)pitch;
@@ -448,15 +469,15 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         P.lv[0].img        = h->own_l0.img;
         P.lv[0].pitch      = h->own_l0.pitch;
         P.lv[0].img_stride = h->own_l0.img_stride;
+        const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
         if (pitch == (size_t)P.lv[0].pitch && img_stride == P.lv[0].img_stride)
-            SNK_CUDA(cudaMemcpyAsync(P.lv[0].img, imgs, img_stride * n_imgs, cudaMemcpyHostToDevice, st));
+            SNK_CUDA(cudaMemcpyAsync(P.lv[0].img, imgs, img_stride * n_imgs, kind, st));
         else if (img_stride == pitch * rows)
-            SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img, P.lv[0].pitch, imgs, pitch, cols, (size_t)rows * n_imgs,
-                                       cudaMemcpyHostToDevice, st));
+            SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img, P.lv[0].pitch, imgs, pitch, cols, (size_t)rows * n_imgs, kind, st));
         else
             for (int i = 0; i < n_imgs; ++i)
                 SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img + i * P.lv[0].img_stride, P.lv[0].pitch, imgs + i * img_stride,
-                                           pitch, cols, rows, cudaMemcpyHostToDevice, st));
+                                           pitch, cols, rows, kind, st));
     }
     if (prof) cudaEventRecord(ev[1], st);
 
@@ -465,9 +486,9 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     {
         const LevelDev& s = P.lv[l - 1];
         const LevelDev& d = P.lv[l];
-        dim3 grid((d.w + RS_TW - 1) / RS_TW, (d.h + RS_TH - 1) / RS_TH, n_imgs);
-        k_resize<<<grid, 256, 0, st>>>(s.img, s.img_stride, s.pitch, s.w, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
-                                       h->d_xofs[l], h->d_xa[l], h->d_yofs[l], h->d_yb[l]);
+        dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + RS_ROWS - 1) / RS_ROWS + 3) / 4, n_imgs);
+        k_resize<<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
+                                       h->d_quads[l], h->d_yofs[l], h->d_yb[l]);
         ++nl[1];
     }
     if (prof) cudaEventRecord(ev[2], st);
@@ -485,7 +506,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     if (prof) cudaEventRecord(ev[4], st);
 
     // stage 4: blur of every level
-    k_blur<<<dim3((unsigned)h->tiles.size(), n_imgs), 256, 0, st>>>(P, h->d_tiles);
+    k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
     ++nl[4];
     if (prof) cudaEventRecord(ev[5], st);
 

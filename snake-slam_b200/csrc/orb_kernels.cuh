@@ -59,71 +59,99 @@ struct CellDev
 };
 
 // --------------------------------------------------------------------------------------------------------------
-// Pyramid
+// Pyramid: level l from level l-1, cv::resize INTER_LINEAR fixed point.
+//
+// One warp per 128 x RS_ROWS output strip, no shared memory. A lane owns 4 adjacent output pixels. Everything that
+// depends on x only (source word, byte shift, byte selectors, the four 11-bit coefficient pairs) comes from a per-level
+// table built on the host exactly as cv::resize builds xofs/ialpha, and is loaded once per lane. Per source row a lane
+// loads 3 aligned words, funnel-shifts them so the window starts at its first tap, permutes the (tap0, tap1) byte pairs
+// of its four pixels into two registers and gets the four horizontal sums with dp2a (u16 coefficient pair x u8 pair).
+// Consecutive output rows share a source row most of the time (scale 1.2), so the previous row's sums are reused.
 // --------------------------------------------------------------------------------------------------------------
-constexpr int RS_TW = 128, RS_TH = 16, RS_SW = 168, RS_SH = 24;
+constexpr int RS_TW = 128, RS_ROWS = 32;
+struct ResizeQuad  // 32 bytes per 4 output pixels
+{
+    int word;            // first source word of the window
+    int shift_bits;      // 8 * (xofs[x] & 3)
+    unsigned sel;        // byte selectors: low 16 bits pixels 0,1 / high 16 bits pixels 2,3: [t0 t1 t0 t1] each
+    unsigned _pad;
+    unsigned coef[4];    // ialpha pair per pixel: a0 | a1 << 16
+};
 
-__global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, size_t src_stride, int spitch, int sw,
-                                                int sh, uint8_t* __restrict__ dst, size_t dst_stride, int dpitch,
-                                                int dw, int dh, const int* __restrict__ xofs,
-                                                const short* __restrict__ xa, const int* __restrict__ yofs,
+__global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src, size_t src_stride, int spitch, int sh,
+                                                uint8_t* __restrict__ dst, size_t dst_stride, int dpitch, int dw, int dh,
+                                                const ResizeQuad* __restrict__ quads, const int* __restrict__ yofs,
                                                 const short* __restrict__ yb)
 {
-    __shared__ uint8_t tile[RS_SH][RS_SW];
-    const int tx0 = blockIdx.x * RS_TW, ty0 = blockIdx.y * RS_TH;
-    const int tx1 = min(tx0 + RS_TW, dw) - 1, ty1 = min(ty0 + RS_TH, dh) - 1;
+    const int lane  = threadIdx.x & 31;
+    const int strip = blockIdx.y * 4 + (threadIdx.x >> 5);
+    const int x     = blockIdx.x * RS_TW + 4 * lane;
+    const int y0    = strip * RS_ROWS;
+    if (y0 >= dh || x >= dw) return;  // no warp-wide primitives below
     const uint8_t* S = src + (size_t)blockIdx.z * src_stride;
     uint8_t* D       = dst + (size_t)blockIdx.z * dst_stride;
-    // source window covered by this output tile (taps sx, sx+1 and rows sy, sy+1; indices clamp at the border)
-    const int sx_lo = xofs[tx0], sx_hi = min(xofs[tx1] + 1, sw - 1);
-    const int sy_lo = max(yofs[ty0], 0), sy_hi = min(yofs[ty1] + 1, sh - 1);
-    const int cw = sx_hi - sx_lo + 1, ch = sy_hi - sy_lo + 1;
-    for (int i = threadIdx.x; i < cw * ch; i += 256)
+    const ResizeQuad q = quads[x >> 2];
+    const int wlast = (spitch >> 2) - 1;
+    const int i0 = min(q.word, wlast), i1 = min(q.word + 1, wlast), i2 = min(q.word + 2, wlast);
+    const unsigned sel01 = q.sel & 0xffffu, sel23 = q.sel >> 16;
+
+    auto hrow = [&](int sy, unsigned (&h)[4]) {
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)sy * spitch);
+        const unsigned w0 = __ldg(row + i0), w1 = __ldg(row + i1), w2 = __ldg(row + i2);
+        const unsigned v0 = __funnelshift_r(w0, w1, q.shift_bits), v1 = __funnelshift_r(w1, w2, q.shift_bits);
+        const unsigned r01 = __byte_perm(v0, v1, sel01), r23 = __byte_perm(v0, v1, sel23);
+        h[0] = __dp2a_lo(q.coef[0], r01, 0u);
+        h[1] = __dp2a_hi(q.coef[1], r01, 0u);
+        h[2] = __dp2a_lo(q.coef[2], r23, 0u);
+        h[3] = __dp2a_hi(q.coef[3], r23, 0u);
+    };
+
+    unsigned ha[4], hb[4];
+    int held = -1;  // source row whose sums are in hb
+    const int y1 = min(y0 + RS_ROWS, dh);
+    for (int y = y0; y < y1; ++y)
     {
-        int r = i / cw, c = i - r * cw;
-        tile[r][c] = S[(size_t)(sy_lo + r) * spitch + sx_lo + c];
-    }
-    __syncthreads();
-    // 256 threads: 32 quads across x, 8 rows at a time
-    const int qx = threadIdx.x & 31, qy = threadIdx.x >> 5;
-    for (int ry = qy; ry < RS_TH; ry += 8)
-    {
-        const int y = ty0 + ry;
-        if (y >= dh) break;
-        const int r0 = min(max(yofs[y], 0), sh - 1) - sy_lo;
-        const int r1 = min(max(yofs[y] + 1, 0), sh - 1) - sy_lo;
-        const int b0 = yb[2 * y], b1 = yb[2 * y + 1];
-        uint32_t packed = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
+        const int sy0 = min(max(yofs[y], 0), sh - 1), sy1 = min(max(yofs[y] + 1, 0), sh - 1);
+        if (sy0 == held)
         {
-            const int x = tx0 + qx * 4 + k;
-            if (x < dw)
-            {
-                const int c0 = xofs[x] - sx_lo;
-                const int c1 = min(xofs[x] + 1, sw - 1) - sx_lo;
-                const int a0 = xa[2 * x], a1 = xa[2 * x + 1];
-                const int h0 = tile[r0][c0] * a0 + tile[r0][c1] * a1;
-                const int h1 = tile[r1][c0] * a0 + tile[r1][c1] * a1;
-                int v        = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-                v            = min(max(v, 0), 255);
-                packed |= (uint32_t)v << (8 * k);
-            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ha[j] = hb[j];
         }
-        const int x = tx0 + qx * 4;
-        if (x + 3 < dw)
-            *reinterpret_cast<uint32_t*>(D + (size_t)y * dpitch + x) = packed;  // dpitch and x are multiples of 4
         else
-            for (int k = 0; k < 4 && x + k < dw; ++k) D[(size_t)y * dpitch + x + k] = (uint8_t)(packed >> (8 * k));
+            hrow(sy0, ha);
+        if (sy1 != sy0)
+            hrow(sy1, hb);
+        else
+        {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) hb[j] = ha[j];
+        }
+        held = sy1;
+        const int b0 = yb[2 * y], b1 = yb[2 * y + 1];
+        unsigned packed = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            int v = (((b0 * (int)(ha[j] >> 4)) >> 16) + ((b1 * (int)(hb[j] >> 4)) >> 16) + 2) >> 2;
+            v     = min(max(v, 0), 255);
+            packed |= (unsigned)v << (8 * j);
+        }
+        uint8_t* drow = D + (size_t)y * dpitch + x;
+        if (x + 4 <= dw)
+            *reinterpret_cast<uint32_t*>(drow) = packed;  // dpitch and x are multiples of 4
+        else
+            for (int j = 0; j < 4 && x + j < dw; ++j) drow[j] = (uint8_t)(packed >> (8 * j));
     }
 }
 
 // --------------------------------------------------------------------------------------------------------------
 // FAST
 // --------------------------------------------------------------------------------------------------------------
-constexpr int FAST_DIM = 66;  // wCell < 60  =>  ROI side <= 66
-constexpr int FAST_PITCH = 68;
+constexpr int FAST_DIM = 66;    // wCell < 60  =>  ROI side <= 66
+constexpr int FAST_PITCH = 72;  // ROI row + up to 3 bytes of word alignment, multiple of 4
 constexpr int FAST_NT = 128;
+constexpr int FAST_ZMAX = (FAST_DIM - 6) * (FAST_DIM - 6);  // detection-zone pixels
+constexpr int FAST_BMW = (FAST_ZMAX + 31) / 32;
 
 // arc score: max over the 16 arcs of 9 contiguous ring pixels of min(v - ring) and min(ring - v).
 // The differences are biased by +256 so that every intermediate is a positive integer: nvcc 12.9 narrows the
@@ -175,122 +203,205 @@ __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], in
     return max((int)best_lo - 256, 256 - (int)best_hi);
 }
 
+// is there an arc of 9 contiguous ring pixels all brighter than v+t or all darker than v-t ?
+__device__ __forceinline__ bool fast_is_corner(const uint8_t (*t)[FAST_PITCH], int y, int x, int th)
+{
+    const int v = t[y][x], hi = v + th, lo = v - th;
+    unsigned bm = 0, dm = 0;
+#define SNK_RING(k, yy, xx)                       \
+    {                                             \
+        const int r = t[yy][xx];                  \
+        bm |= (r > hi) ? (0x10001u << (k)) : 0u;  \
+        dm |= (r < lo) ? (0x10001u << (k)) : 0u;  \
+    }
+    SNK_RING(0, y + 3, x) SNK_RING(1, y + 3, x + 1) SNK_RING(2, y + 2, x + 2) SNK_RING(3, y + 1, x + 3)
+    SNK_RING(4, y, x + 3) SNK_RING(5, y - 1, x + 3) SNK_RING(6, y - 2, x + 2) SNK_RING(7, y - 3, x + 1)
+    SNK_RING(8, y - 3, x) SNK_RING(9, y - 3, x - 1) SNK_RING(10, y - 2, x - 2) SNK_RING(11, y - 1, x - 3)
+    SNK_RING(12, y, x - 3) SNK_RING(13, y + 1, x - 3) SNK_RING(14, y + 2, x - 2) SNK_RING(15, y + 3, x - 1)
+#undef SNK_RING
+    // masks are doubled (bit k and k+16) so a plain shift wraps around the ring
+    unsigned b = bm & (bm >> 1);
+    b &= b >> 2;
+    b &= b >> 4;
+    b &= bm >> 8;
+    unsigned d = dm & (dm >> 1);
+    d &= d >> 2;
+    d &= d >> 4;
+    d &= dm >> 8;
+    return ((b | d) & 0xffffu) != 0;
+}
+
 // One CTA == one cell == the (up to two) cv::FAST calls of ORBExtractor.cpp:133-140.
 // The arc score is threshold independent, and for a pixel that is a corner at threshold t every 8-neighbour that is
 // not a corner at t scores <= t < its own score, so "survives NMS at t" == "arc > t and arc > all neighbours' arcs
-// inside the ROI". The cell is therefore scored once; the threshold is chosen afterwards from the NMS survivors.
+// inside the ROI". The cell is therefore scored once at the lower threshold; the threshold is chosen afterwards from
+// the NMS survivors. Work is filtered in stages so that the expensive steps only see the pixels that need them:
+//   A  compass test on every zone pixel (two adjacent compass points both brighter / darker — necessary for any arc of 9)
+//   B  16-pixel ring test on the survivors of A            -> corners at the lower threshold
+//   B2 arc score of the corners
+//   C  3x3 NMS of the corners, survivors marked in a bitmap over the zone; popc-prefix of the bitmap gives every
+//      survivor its row-major rank (== cv::FAST output order) without sorting
 __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __restrict__ cells, uint32_t* __restrict__ cand,
                                                   int* __restrict__ cell_count)
 {
-    __shared__ uint8_t tile[FAST_DIM][FAST_PITCH];
-    __shared__ uint8_t score[FAST_DIM][FAST_PITCH];
-    __shared__ uint16_t list[(FAST_DIM - 6) * (FAST_DIM - 6)];
-    __shared__ int s_nlist;
-    __shared__ int s_warp[2][FAST_NT / 32];
+    __shared__ __align__(16) uint8_t tile[FAST_DIM][FAST_PITCH];
+    __shared__ __align__(16) uint8_t score[FAST_DIM][FAST_PITCH];
+    __shared__ uint16_t list1[FAST_ZMAX];
+    __shared__ uint16_t list2[FAST_ZMAX];
+    __shared__ uint32_t bm[2][FAST_BMW];  // [0] survivors at the lower threshold, [1] those also above th_ini
+    __shared__ uint16_t pre[FAST_BMW + 1];
+    __shared__ int s_n1, s_n2, s_ini, s_warp[FAST_NT / 32];
 
     const CellDev c   = cells[blockIdx.x];
     const LevelDev& L = P.lv[c.level];
     const int img     = blockIdx.y;
-    const uint8_t* src = L.img + (size_t)img * L.img_stride + (size_t)c.y0 * L.pitch + c.x0;
     const int w = c.w, h = c.h;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int a = c.x0 & 3;  // the tile is stored from the aligned word that contains the ROI's first byte
+    const uint8_t* rows = L.img + (size_t)img * L.img_stride + (size_t)c.y0 * L.pitch + (c.x0 - a);
 
-    if (tid == 0) s_nlist = 0;
-    for (int i = tid; i < h * w; i += FAST_NT)
-    {
-        int y = i / w, x = i - y * w;
-        tile[y][x]  = src[(size_t)y * L.pitch + x];
-        score[y][x] = 0;
-    }
+    if (tid == 0) s_n1 = s_n2 = s_ini = 0;
+    for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
+    const int nw = (a + w + 3) >> 2;  // words per tile row, <= 18
+    for (int y = wid; y < h; y += FAST_NT / 32)
+        if (lane < nw)
+        {
+            reinterpret_cast<uint32_t*>(&tile[y][0])[lane] = __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + lane);
+            reinterpret_cast<uint32_t*>(&score[y][0])[lane] = 0;
+        }
     __syncthreads();
 
     const int zw = w - 6, zh = h - 6;  // detection zone: ROI minus the 3-px frame
     const int nz = (zw > 0 && zh > 0) ? zw * zh : 0;
     const int t  = P.th_min < P.th_ini ? P.th_min : P.th_ini;
-    // phase A: cheap rejection (any arc of 9 contains a pixel of every opposite pair)
-    for (int i = tid; i < nz; i += FAST_NT)
-    {
-        const int y = 3 + i / zw, x = 3 + i % zw;
-        const int v = tile[y][x];
-        const int a = abs(tile[y + 3][x] - v), b = abs(tile[y - 3][x] - v);
-        const int e = abs(tile[y][x + 3] - v), f = abs(tile[y][x - 3] - v);
-        if (!((a <= t && b <= t) || (e <= t && f <= t)))
-        {
-            int pos   = atomicAdd(&s_nlist, 1);
-            list[pos] = (uint16_t)((y << 8) | x);
-        }
-    }
-    __syncthreads();
-    // phase B: full score of the survivors (balanced across the CTA)
-    const int nl = s_nlist;
-    for (int i = tid; i < nl; i += FAST_NT)
-    {
-        const int y = list[i] >> 8, x = list[i] & 255;
-        const int arc = fast_arc_score(tile, y, x);
-        score[y][x]   = (arc > t) ? (uint8_t)arc : 0;
-#ifdef SNK_DEBUG_FAST
-        if (blockIdx.x == 312 && blockIdx.y == 0 && y == 16 && x == 3)
-            printf("DBG cell x0=%d y0=%d w=%d h=%d off=%d,%d pitch=%d | v=%d ring0=%d ring4=%d ring8=%d ring12=%d arc=%d t=%d nl=%d\n", c.x0, c.y0, c.w,
-                   c.h, c.off_x, c.off_y, L.pitch, tile[y][x], tile[y + 3][x], tile[y][x + 3], tile[y - 3][x], tile[y][x - 3], arc, t, nl);
-#endif
-    }
-    __syncthreads();
 
-    // phase C: NMS + threshold choice + row-major compaction
-    const int per = (nz + FAST_NT - 1) / FAST_NT;  // <= 29
-    uint32_t m_min = 0, m_ini = 0;
-    for (int k = 0; k < per; ++k)
+    // ---- A: compass test, 4 pixels (one aligned tile word) per thread ----
+    // |p - v| per byte with VABSDIFF4; "byte > t" as bit 7 of ((x & 0x7f) + (127 - t)) | x  (no carry between bytes);
+    // a corner needs two adjacent compass points beyond the threshold on the same side, so in particular
+    // (S or N far) and (E or W far). The sign is checked by the ring test that follows.
     {
-        const int i = tid * per + k;
-        if (i >= nz) break;
-        const int y = 3 + i / zw, x = 3 + i % zw;
-        const int s = score[y][x];
-        // cv response is s-1 and must beat 0 for empty neighbours: s >= 2
-        if (s > 1 && s > score[y - 1][x - 1] && s > score[y - 1][x] && s > score[y - 1][x + 1] && s > score[y][x - 1] &&
-            s > score[y][x + 1] && s > score[y + 1][x - 1] && s > score[y + 1][x] && s > score[y + 1][x + 1])
+        const int c0 = 3 + a, c1 = 3 + a + zw;          // zone columns [c0, c1) in tile coordinates
+        const int wz0 = c0 >> 2, nwz = nz ? ((c1 + 3) >> 2) - wz0 : 0;  // words that intersect the zone
+        const int ntask = nwz * (nz ? zh : 0);
+        const unsigned magic = nwz ? (0xffffffffu / (unsigned)nwz + 1u) : 0u;  // i / nwz == umulhi(i, magic), i < 2^16
+        const unsigned addc = (unsigned)(127 - min(t, 127)) * 0x01010101u;
+        for (int base = 0; base < ntask; base += FAST_NT)
         {
-            m_min |= 1u << k;
-            if (s > P.th_ini) m_ini |= 1u << k;
+            const int i = base + tid;
+            unsigned m4 = 0;  // bit 8j+7 set: pixel j of the word is a candidate
+            int y = 0, wx = 0;
+            if (i < ntask)
+            {
+                const int q = (int)__umulhi((unsigned)i, magic);
+                y  = 3 + q;
+                wx = wz0 + (i - q * nwz);
+                const uint32_t* rc = reinterpret_cast<const uint32_t*>(&tile[y][0]);
+                const unsigned v  = rc[wx];
+                const unsigned pl = rc[max(wx - 1, 0)], pr = rc[min(wx + 1, FAST_PITCH / 4 - 1)];
+                const unsigned pS = reinterpret_cast<const uint32_t*>(&tile[y + 3][0])[wx];
+                const unsigned pN = reinterpret_cast<const uint32_t*>(&tile[y - 3][0])[wx];
+                const unsigned pE = __funnelshift_r(v, pr, 24);  // bytes x+3
+                const unsigned pW = __funnelshift_r(pl, v, 8);   // bytes x-3
+                const unsigned dS = __vabsdiffu4(pS, v), dN = __vabsdiffu4(pN, v), dE = __vabsdiffu4(pE, v), dW = __vabsdiffu4(pW, v);
+                const unsigned fS = ((dS & 0x7f7f7f7fu) + addc) | dS, fN = ((dN & 0x7f7f7f7fu) + addc) | dN;
+                const unsigned fE = ((dE & 0x7f7f7f7fu) + addc) | dE, fW = ((dW & 0x7f7f7f7fu) + addc) | dW;
+                m4 = (fS | fN) & (fE | fW) & 0x80808080u;
+                // bytes outside the zone columns
+                const int xb = 4 * wx;
+                if (xb < c0) m4 &= 0xffffffffu << (8 * (c0 - xb));
+                if (xb + 4 > c1) m4 &= 0xffffffffu >> (8 * (xb + 4 - c1));
+            }
+            const int cnt = __popc(m4);
+            const int inc = warp_incl_scan(cnt, lane);
+            int off = 0;
+            if (lane == 31 && inc) off = atomicAdd(&s_n1, inc);
+            off = __shfl_sync(0xffffffffu, off, 31) + inc - cnt;
+            while (m4)
+            {
+                const int j = (__ffs(m4) - 1) >> 3;
+                m4 &= m4 - 1;
+                list1[off++] = (uint16_t)((y << 8) | (4 * wx + j - a));
+            }
         }
-    }
-    const int lane = tid & 31, wid = tid >> 5;
-    int c_min = __popc(m_min), c_ini = __popc(m_ini);
-    int i_min = warp_incl_scan(c_min, lane), i_ini = warp_incl_scan(c_ini, lane);
-    if (lane == 31)
-    {
-        s_warp[0][wid] = i_min;
-        s_warp[1][wid] = i_ini;
     }
     __syncthreads();
-    int base_min = 0, base_ini = 0, tot_min = 0, tot_ini = 0;
-#pragma unroll
-    for (int k = 0; k < FAST_NT / 32; ++k)
+    // ---- B: ring test ----
+    const int n1 = s_n1;
+    for (int base = 0; base < n1; base += FAST_NT)
     {
-        if (k < wid)
+        const int k = base + tid;
+        bool pass   = false;
+        uint16_t e  = 0;
+        if (k < n1)
         {
-            base_min += s_warp[0][k];
-            base_ini += s_warp[1][k];
+            e    = list1[k];
+            pass = fast_is_corner(tile, e >> 8, (e & 255) + a, t);
         }
-        tot_min += s_warp[0][k];
-        tot_ini += s_warp[1][k];
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        int off = 0;
+        if (lane == 0 && m) off = atomicAdd(&s_n2, __popc(m));
+        off = __shfl_sync(0xffffffffu, off, 0);
+        if (pass) list2[off + __popc(m & ((1u << lane) - 1))] = e;
     }
-    const bool use_ini = tot_ini > 0;  // "if (cv_KeysCell.empty()) retry with th_fast_min"
-    uint32_t m         = use_ini ? m_ini : m_min;
-    int pos            = use_ini ? (base_ini + i_ini - c_ini) : (base_min + i_min - c_min);
-    const int total    = use_ini ? tot_ini : tot_min;
-    const size_t slot  = (size_t)img * P.cells_per_img + blockIdx.x;
-    uint32_t* out      = cand + slot * P.cell_cap;
-    while (m)
+    __syncthreads();
+    // ---- B2: scores ----
+    const int n2 = s_n2;
+    for (int k = tid; k < n2; k += FAST_NT)
     {
-        const int k = __ffs(m) - 1;
-        m &= m - 1;
-        const int i = tid * per + k;
-        const int y = 3 + i / zw, x = 3 + i % zw;
-        if (pos < P.cell_cap)
-            out[pos] = (uint32_t)(x + c.off_x) | ((uint32_t)(y + c.off_y) << 12) | ((uint32_t)(score[y][x] - 1) << 24);
-        ++pos;
+        const int y = list2[k] >> 8, xa = (list2[k] & 255) + a;
+        score[y][xa] = (uint8_t)fast_arc_score(tile, y, xa);
     }
-    if (tid == 0) cell_count[slot] = total;
+    __syncthreads();
+    // ---- C: NMS, survivors into the bitmaps ----
+    for (int k = tid; k < n2; k += FAST_NT)
+    {
+        const int y = list2[k] >> 8, x = list2[k] & 255, xa = x + a;
+        const int s = score[y][xa];
+        // cv response is s-1 and must beat 0 for empty neighbours: s >= 2
+        if (s > 1 && s > score[y - 1][xa - 1] && s > score[y - 1][xa] && s > score[y - 1][xa + 1] && s > score[y][xa - 1] &&
+            s > score[y][xa + 1] && s > score[y + 1][xa - 1] && s > score[y + 1][xa] && s > score[y + 1][xa + 1])
+        {
+            const int i = (y - 3) * zw + (x - 3);
+            atomicOr(&bm[0][i >> 5], 1u << (i & 31));
+            if (s > P.th_ini)
+            {
+                atomicOr(&bm[1][i >> 5], 1u << (i & 31));
+                s_ini = 1;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- threshold choice ("if (cv_KeysCell.empty()) retry with th_fast_min") and row-major ranks ----
+    const uint32_t* B = bm[s_ini ? 1 : 0];
+    const int nwords  = (nz + 31) >> 5;  // <= FAST_BMW <= FAST_NT
+    {
+        const int cnt = (tid < nwords) ? __popc(B[tid]) : 0;
+        const int inc = warp_incl_scan(cnt, lane);
+        if (lane == 31) s_warp[wid] = inc;
+        __syncthreads();
+        int add = 0;
+#pragma unroll
+        for (int k = 0; k < FAST_NT / 32; ++k)
+            if (k < wid) add += s_warp[k];
+        if (tid < nwords) pre[tid] = (uint16_t)(add + inc - cnt);
+        if (tid == FAST_NT - 1) pre[FAST_BMW] = (uint16_t)(add + inc);  // total
+    }
+    __syncthreads();
+    const size_t slot = (size_t)img * P.cells_per_img + blockIdx.x;
+    uint32_t* out     = cand + slot * P.cell_cap;
+    for (int k = tid; k < n2; k += FAST_NT)
+    {
+        const int y = list2[k] >> 8, x = list2[k] & 255;
+        const int i = (y - 3) * zw + (x - 3);
+        const uint32_t word = B[i >> 5], bit = 1u << (i & 31);
+        if (word & bit)
+        {
+            const int pos = pre[i >> 5] + __popc(word & (bit - 1));
+            if (pos < P.cell_cap)
+                out[pos] = (uint32_t)(x + c.off_x) | ((uint32_t)(y + c.off_y) << 12) | ((uint32_t)(score[y][x + a] - 1) << 24);
+        }
+    }
+    if (tid == 0) cell_count[slot] = pre[FAST_BMW];
 }
 
 // --------------------------------------------------------------------------------------------------------------
@@ -580,8 +691,14 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
 
 // --------------------------------------------------------------------------------------------------------------
 // Gaussian blur 7x7, sigma 2, kernel {18,34,48,56,48,34,18}/256 in 8.8 fixed point, BORDER_REFLECT_101
+//
+// One warp per 128 x BL_ROWS strip, no shared memory. A lane owns 4 adjacent pixels (one aligned 32-bit word) and
+// walks down the rows: it loads its word, gets the two neighbouring words by shuffle, forms the four 7-tap horizontal
+// sums with byte permutes + dp4a (the taps fit in a byte), and keeps the last 7 rows of those sums in registers; the
+// vertical pass runs on that register window. ~15 instructions per pixel; every source byte is loaded once per strip.
+// Requires 4-byte aligned rows (internal buffers are; an unaligned caller buffer is copied first).
 // --------------------------------------------------------------------------------------------------------------
-constexpr int BL_TW = 128, BL_TH = 32;
+constexpr int BL_TW = 128, BL_GROUPS = 6, BL_ROWS = 7 * BL_GROUPS - 6;  // 36 output rows per warp task
 struct TileDev
 {
     short level, tx, ty, _pad;
@@ -589,43 +706,93 @@ struct TileDev
 
 __device__ __forceinline__ int reflect101(int p, int len)
 {
-    // valid for -len < p < 2*len-1 (halo of 3, levels are far larger)
+    // valid for -len < p < 2*len-1 (halo of 3..4, levels are far larger)
     p = p < 0 ? -p : p;
     return p >= len ? 2 * (len - 1) - p : p;
 }
 
-__global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restrict__ tiles)
+__global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restrict__ tiles, int n_tiles)
 {
-    __shared__ uint8_t src[BL_TH + 6][BL_TW + 8];
-    __shared__ uint16_t hor[BL_TH + 6][BL_TW];
-    const TileDev t   = tiles[blockIdx.x];
+    const int lane = threadIdx.x & 31;
+    const int task = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (task >= n_tiles) return;
+    const TileDev t   = tiles[task];
     const LevelDev& L = P.lv[t.level];
     const uint8_t* S  = L.img + (size_t)blockIdx.y * L.img_stride;
     uint8_t* D        = L.gauss + (size_t)blockIdx.y * L.gauss_stride;
-    const int x0 = t.tx * BL_TW, y0 = t.ty * BL_TH;
-    const int tw = min(BL_TW, L.w - x0), th = min(BL_TH, L.h - y0);
-    const int tid = threadIdx.x;
+    const int W = L.w, H = L.h, pitch = L.pitch;
+    const int x0 = t.tx * BL_TW, y0 = t.ty * BL_ROWS;
+    const int x  = x0 + 4 * lane;               // first of my 4 pixels
+    const int words_in_row = pitch >> 2;        // addressable words of a row
+    const int xw = x >> 2;
+    const bool own_ok = xw < words_in_row;      // my word can be read
+    // all 12 bytes x-4 .. x+7 inside the image: the shuffle path is exact; otherwise gather bytes with reflection
+    const bool fast = (x - 4 >= 0) && (x + 8 <= W);
+    const bool active = x < W;                  // I produce at least one output pixel
+    const unsigned KLO = 0x38302212u;           // taps 18,34,48,56 (little endian)
+    const unsigned KHI = 0x00122230u;           // taps 48,34,18,0
 
-    for (int i = tid; i < (th + 6) * (tw + 6); i += 256)
+    unsigned hw[7][4];  // horizontal sums of the last 7 rows (slot = row index mod 7)
+#pragma unroll 1
+    for (int g = 0; g < BL_GROUPS; ++g)
     {
-        const int r = i / (tw + 6), c = i - r * (tw + 6);
-        const int gy = reflect101(y0 + r - 3, L.h), gx = reflect101(x0 + c - 3, L.w);
-        src[r][c] = S[(size_t)gy * L.pitch + gx];
-    }
-    __syncthreads();
-    for (int i = tid; i < (th + 6) * tw; i += 256)
-    {
-        const int r = i / tw, c = i - r * tw;
-        const uint8_t* p = &src[r][c];
-        hor[r][c] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-    }
-    __syncthreads();
-    for (int i = tid; i < th * tw; i += 256)
-    {
-        const int r = i / tw, c = i - r * tw;
-        const uint32_t v = 18u * (hor[r][c] + hor[r + 6][c]) + 34u * (hor[r + 1][c] + hor[r + 5][c]) +
-                           48u * (hor[r + 2][c] + hor[r + 4][c]) + 56u * hor[r + 3][c];
-        D[(size_t)(y0 + r) * L.gauss_pitch + x0 + c] = (uint8_t)((v + 32768u) >> 16);
+        // issue the loads of all 7 rows of the group before using any of them (memory-level parallelism)
+        unsigned wcs[7], hal[7];
+#pragma unroll
+        for (int i = 0; i < 7; ++i)
+        {
+            const int gy = reflect101(min(y0 - 3 + 7 * g + i, H + 2), H);
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)gy * pitch);
+            wcs[i] = own_ok ? __ldg(row + xw) : 0u;
+            hal[i] = 0u;
+            if (lane == 0 && xw > 0) hal[i] = __ldg(row + xw - 1);
+            if (lane == 31 && xw + 1 < words_in_row) hal[i] = __ldg(row + xw + 1);
+        }
+#pragma unroll
+        for (int i = 0; i < 7; ++i)
+        {
+            const int r  = 7 * g + i;           // 0 .. 7*BL_GROUPS-1, source row y0 - 3 + r
+            unsigned wc = wcs[i];
+            unsigned wl = __shfl_up_sync(0xffffffffu, wc, 1);
+            unsigned wr = __shfl_down_sync(0xffffffffu, wc, 1);
+            if (lane == 0) wl = hal[i];
+            if (lane == 31) wr = hal[i];
+            if (!fast && active)
+            {
+                const int gy = reflect101(min(y0 - 3 + r, H + 2), H);
+                const uint8_t* rb = S + (size_t)gy * pitch;
+                unsigned b[12];
+#pragma unroll
+                for (int k = 0; k < 12; ++k) b[k] = rb[reflect101(x - 4 + k, W)];
+                wl = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+                wc = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
+                wr = b[8] | (b[9] << 8) | (b[10] << 16) | (b[11] << 24);
+            }
+            // pixel j of my word: taps are bytes (j+1 .. j+7) of the 12-byte window [wl wc wr]
+            hw[i][0] = __dp4a(__byte_perm(wc, wr, 0x4321), KHI, __dp4a(__byte_perm(wl, wc, 0x4321), KLO, 0u));
+            hw[i][1] = __dp4a(__byte_perm(wc, wr, 0x5432), KHI, __dp4a(__byte_perm(wl, wc, 0x5432), KLO, 0u));
+            hw[i][2] = __dp4a(__byte_perm(wc, wr, 0x6543), KHI, __dp4a(__byte_perm(wl, wc, 0x6543), KLO, 0u));
+            hw[i][3] = __dp4a(wr, KHI, __dp4a(wc, KLO, 0u));
+            // output row y0 + r - 6 is complete once row r is in the window
+            const int oy = y0 + r - 6;
+            if ((g > 0 || i == 6) && oy < H && active)
+            {
+                unsigned packed = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    // window rows r-6..r live in slots (i+1)%7 .. i
+                    const unsigned v = 18u * (hw[(i + 1) % 7][j] + hw[i][j]) + 34u * (hw[(i + 2) % 7][j] + hw[(i + 6) % 7][j]) +
+                                       48u * (hw[(i + 3) % 7][j] + hw[(i + 5) % 7][j]) + 56u * hw[(i + 4) % 7][j];
+                    packed |= ((v + 32768u) >> 16) << (8 * j);
+                }
+                uint8_t* drow = D + (size_t)oy * L.gauss_pitch + x;
+                if (x + 4 <= W)
+                    *reinterpret_cast<uint32_t*>(drow) = packed;
+                else
+                    for (int j = 0; j < 4 && x + j < W; ++j) drow[j] = (uint8_t)(packed >> (8 * j));
+            }
+        }
     }
 }
 
@@ -677,17 +844,21 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     int m10 = 0, m01 = 0;
     if (lane < 31)
     {
+        // u_max (ORBPattern::AngleUmax) as compile-time constants so the 31 row loads are independent and issue
+        // back to back; snk_orb_create checks the table against the host computation
+        constexpr int UMAX[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
         const int au = abs(u);
-#pragma unroll 1
+        int rowsum = 0;  // sum over v of v * I(v,u) for my column
+        int colsum = 0;  // sum over v of I(v,u)
+#pragma unroll
         for (int v = -15; v <= 15; ++v)
         {
-            if (au <= c_umax[abs(v)])
-            {
-                const int val = raw[v * L.pitch + u];
-                m10 += u * val;
-                m01 += v * val;
-            }
+            const int val = (au <= UMAX[v < 0 ? -v : v]) ? (int)raw[v * L.pitch + u] : 0;
+            colsum += val;
+            rowsum += v * val;
         }
+        m10 = u * colsum;
+        m01 = rowsum;
     }
     m10 = warp_sum(m10);
     m01 = warp_sum(m01);
