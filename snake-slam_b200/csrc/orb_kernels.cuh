@@ -263,12 +263,16 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
     if (tid == 0) s_n1 = s_n2 = s_ini = 0;
     for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
     const int nw = (a + w + 3) >> 2;  // words per tile row, <= 18
-    for (int y = wid; y < h; y += FAST_NT / 32)
-        if (lane < nw)
-        {
-            reinterpret_cast<uint32_t*>(&tile[y][0])[lane] = __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + lane);
-            reinterpret_cast<uint32_t*>(&score[y][0])[lane] = 0;
-        }
+    {
+        // a warp covers rpw rows x nw words per step; the (row, word) split of the lane is computed once
+        const int rpw = 32 / nw, sub = lane / nw, wx = lane - sub * nw;
+        if (sub < rpw)
+            for (int y = wid * rpw + sub; y < h; y += (FAST_NT / 32) * rpw)
+            {
+                reinterpret_cast<uint32_t*>(&tile[y][0])[wx] = __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + wx);
+                reinterpret_cast<uint32_t*>(&score[y][0])[wx] = 0;
+            }
+    }
     __syncthreads();
 
     const int zw = w - 6, zh = h - 6;  // detection zone: ROI minus the 3-px frame
@@ -279,50 +283,39 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
     // |p - v| per byte with VABSDIFF4; "byte > t" as bit 7 of ((x & 0x7f) + (127 - t)) | x  (no carry between bytes);
     // a corner needs two adjacent compass points beyond the threshold on the same side, so in particular
     // (S or N far) and (E or W far). The sign is checked by the ring test that follows.
+    if (nz)
     {
-        const int c0 = 3 + a, c1 = 3 + a + zw;          // zone columns [c0, c1) in tile coordinates
-        const int wz0 = c0 >> 2, nwz = nz ? ((c1 + 3) >> 2) - wz0 : 0;  // words that intersect the zone
-        const int ntask = nwz * (nz ? zh : 0);
-        const unsigned magic = nwz ? (0xffffffffu / (unsigned)nwz + 1u) : 0u;  // i / nwz == umulhi(i, magic), i < 2^16
+        const int c0 = 3 + a, c1 = 3 + a + zw;              // zone columns [c0, c1) in tile coordinates
+        const int wz0 = c0 >> 2, nwz = ((c1 + 3) >> 2) - wz0;  // words that intersect the zone, <= 17
+        const int rpw = 32 / nwz, sub = lane / nwz, wx = wz0 + lane - sub * nwz;
         const unsigned addc = (unsigned)(127 - min(t, 127)) * 0x01010101u;
-        for (int base = 0; base < ntask; base += FAST_NT)
-        {
-            const int i = base + tid;
-            unsigned m4 = 0;  // bit 8j+7 set: pixel j of the word is a candidate
-            int y = 0, wx = 0;
-            if (i < ntask)
+        unsigned zmask = 0x80808080u;  // bytes of my word that lie inside the zone columns
+        if (4 * wx < c0) zmask &= 0xffffffffu << (8 * (c0 - 4 * wx));
+        if (4 * wx + 4 > c1) zmask &= 0xffffffffu >> (8 * (4 * wx + 4 - c1));
+        const int wl = max(wx - 1, 0), wr = min(wx + 1, FAST_PITCH / 4 - 1);
+        if (sub < rpw)
+            for (int y = 3 + wid * rpw + sub; y < 3 + zh; y += (FAST_NT / 32) * rpw)
             {
-                const int q = (int)__umulhi((unsigned)i, magic);
-                y  = 3 + q;
-                wx = wz0 + (i - q * nwz);
                 const uint32_t* rc = reinterpret_cast<const uint32_t*>(&tile[y][0]);
                 const unsigned v  = rc[wx];
-                const unsigned pl = rc[max(wx - 1, 0)], pr = rc[min(wx + 1, FAST_PITCH / 4 - 1)];
-                const unsigned pS = reinterpret_cast<const uint32_t*>(&tile[y + 3][0])[wx];
-                const unsigned pN = reinterpret_cast<const uint32_t*>(&tile[y - 3][0])[wx];
-                const unsigned pE = __funnelshift_r(v, pr, 24);  // bytes x+3
-                const unsigned pW = __funnelshift_r(pl, v, 8);   // bytes x-3
+                const unsigned pS = rc[wx + 3 * (FAST_PITCH / 4)], pN = rc[wx - 3 * (FAST_PITCH / 4)];
+                const unsigned pE = __funnelshift_r(v, rc[wr], 24);  // bytes x+3
+                const unsigned pW = __funnelshift_r(rc[wl], v, 8);   // bytes x-3
                 const unsigned dS = __vabsdiffu4(pS, v), dN = __vabsdiffu4(pN, v), dE = __vabsdiffu4(pE, v), dW = __vabsdiffu4(pW, v);
                 const unsigned fS = ((dS & 0x7f7f7f7fu) + addc) | dS, fN = ((dN & 0x7f7f7f7fu) + addc) | dN;
                 const unsigned fE = ((dE & 0x7f7f7f7fu) + addc) | dE, fW = ((dW & 0x7f7f7f7fu) + addc) | dW;
-                m4 = (fS | fN) & (fE | fW) & 0x80808080u;
-                // bytes outside the zone columns
-                const int xb = 4 * wx;
-                if (xb < c0) m4 &= 0xffffffffu << (8 * (c0 - xb));
-                if (xb + 4 > c1) m4 &= 0xffffffffu >> (8 * (xb + 4 - c1));
+                unsigned m4 = (fS | fN) & (fE | fW) & zmask;  // bit 8j+7: pixel j of the word is a candidate
+                if (m4)
+                {
+                    int off = atomicAdd(&s_n1, __popc(m4));  // list order is irrelevant (ranks come from the bitmap)
+                    do
+                    {
+                        const int j = (__ffs(m4) - 1) >> 3;
+                        m4 &= m4 - 1;
+                        list1[off++] = (uint16_t)((y << 8) | (4 * wx + j - a));
+                    } while (m4);
+                }
             }
-            const int cnt = __popc(m4);
-            const int inc = warp_incl_scan(cnt, lane);
-            int off = 0;
-            if (lane == 31 && inc) off = atomicAdd(&s_n1, inc);
-            off = __shfl_sync(0xffffffffu, off, 31) + inc - cnt;
-            while (m4)
-            {
-                const int j = (__ffs(m4) - 1) >> 3;
-                m4 &= m4 - 1;
-                list1[off++] = (uint16_t)((y << 8) | (4 * wx + j - a));
-            }
-        }
     }
     __syncthreads();
     // ---- B: ring test ----
