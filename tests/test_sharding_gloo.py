@@ -1,0 +1,86 @@
+"""The N>1 path on CPU: two gloo ranks shard a short stereo sequence by frame (snakeorb.sharding), each rank runs its
+block (here through the CPU oracle — the sharding logic is what is under test, the GPU kernels are covered by the
+-m gpu tests), results are gathered in frame order and must equal the single-process run; the timing reduction
+bench.py uses (max over ranks) is exercised too."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shard_range_covers_and_balances():
+    from snakeorb.sharding import batches, shard_range
+
+    for F in (0, 1, 7, 3680):
+        for G in (1, 2, 4, 8):
+            blocks = [shard_range(F, r, G) for r in range(G)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == F
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(G - 1))
+            sizes = [b - a for a, b in blocks]
+            assert max(sizes) - min(sizes) <= 1
+    assert shard_range(3680, 3, 8) == (1380, 1840)
+    assert batches(10, 25, 6) == [(10, 16), (16, 22), (22, 25)]
+    with pytest.raises(ValueError):
+        shard_range(10, 2, 2)
+
+
+def _worker(rank, world, port, n_frames, out_dir):
+    for p in (ROOT, os.path.join(ROOT, "snake-slam_b200"), os.path.join(ROOT, "oracle")):
+        sys.path.insert(0, p)
+    import torch
+    import torch.distributed as dist
+
+    import oracle_py as O
+    from snakeorb import synthetic as S
+    from snakeorb.sharding import shard_range
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    lo, hi = shard_range(n_frames, rank, world)
+    ex = O.Extractor(300, 1.2, 4, 20, 7, 1)
+    counts = []
+    digest = []
+    for f in range(lo, hi):
+        left = S.image(900 + f, 240, 180)
+        k, d = ex.detect(left)
+        counts.append(len(k))
+        digest.append(int(np.bitwise_xor.reduce(d.reshape(-1)) & np.uint64(0x7fffffff)) if len(d) else 0)
+    # gather variable-length per-frame results in rank order
+    mine = torch.tensor([counts, digest], dtype=torch.int64).reshape(2, -1)
+    sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([hi - lo], dtype=torch.int64))
+    mx = int(max(s.item() for s in sizes))
+    pad = torch.zeros((2, mx), dtype=torch.int64)
+    pad[:, :hi - lo] = mine
+    got = [torch.zeros((2, mx), dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(got, pad)
+    # the timing reduction of bench.py: every rank contributes its elapsed time, the job time is the max
+    t = torch.tensor([10.0 + rank], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        allc = np.concatenate([g[:, :int(s.item())].numpy() for g, s in zip(got, sizes)], axis=1)
+        np.save(os.path.join(out_dir, "gathered.npy"), allc)
+        np.save(os.path.join(out_dir, "tmax.npy"), t.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_gloo_ranks_equal_single_process(tmp_path, oracle):
+    import torch.multiprocessing as mp
+
+    from snakeorb import synthetic as S
+
+    n_frames, world, port = 5, 2, 29000 + os.getpid() % 2000
+    mp.spawn(_worker, args=(world, port, n_frames, str(tmp_path)), nprocs=world, join=True)
+    got = np.load(tmp_path / "gathered.npy")
+    ex = oracle.Extractor(300, 1.2, 4, 20, 7, 1)
+    want_c, want_d = [], []
+    for f in range(n_frames):
+        k, d = ex.detect(S.image(900 + f, 240, 180))
+        want_c.append(len(k))
+        want_d.append(int(np.bitwise_xor.reduce(d.reshape(-1)) & np.uint64(0x7fffffff)) if len(d) else 0)
+    assert got.shape == (2, n_frames)
+    assert list(got[0]) == want_c and list(got[1]) == want_d
+    assert float(np.load(tmp_path / "tmax.npy")[0]) == 11.0
