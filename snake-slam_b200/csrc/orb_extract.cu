@@ -187,8 +187,17 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
                 int maxX       = iniX + wCell + 6;
                 if (iniX >= maxBX - 6) continue;
                 if (maxX > maxBX) maxX = maxBX;
-                CellDev c{(short)l, (short)iniX, (short)iniY, (short)(maxX - iniX), (short)(maxY - iniY),
-                          (short)(j * wCell), (short)(i * hCell), 0};
+                CellDev c{};
+                c.level = (short)l, c.x0 = (short)iniX, c.y0 = (short)iniY, c.w = (short)(maxX - iniX), c.h = (short)(maxY - iniY);
+                c.off_x = (short)(j * wCell), c.off_y = (short)(i * hCell);
+                {
+                    const int a = iniX & 3, nw = (a + c.w + 3) >> 2;
+                    c.ld_words = (unsigned short)nw, c.ld_inv = (unsigned short)(65536 / nw + 1), c.ld_rows = (unsigned short)(32 / nw);
+                    const int zw = std::max(c.w - 6, 1), c0 = 3 + a, c1 = 3 + a + zw;
+                    const int nwz = ((c1 + 3) >> 2) - (c0 >> 2);
+                    c.zn_word0 = (unsigned short)(c0 >> 2), c.zn_words = (unsigned short)nwz;
+                    c.zn_inv = (unsigned short)(65536 / nwz + 1), c.zn_rows = (unsigned short)(32 / nwz);
+                }
                 SNK_REQUIRE(c.w <= FAST_DIM && c.h <= FAST_DIM, "internal: cell %dx%d exceeds the tile", c.w, c.h);
                 h->cells.push_back(c);
                 // NMS survivors are strict local maxima inside the zone: no two are 8-neighbours

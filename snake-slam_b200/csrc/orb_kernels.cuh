@@ -55,8 +55,14 @@ struct CellDev
     short x0, y0;  // iniX, iniY
     short w, h;    // maxX-iniX, maxY-iniY
     short off_x, off_y;
-    short _pad;
+    // lane -> (row, word) splits of the kernel's two word-wise passes, precomputed on the host (no integer division
+    // on the device): a warp covers `rows` rows of `words` words per step; lane / words == (lane * inv) >> 16
+    unsigned short ld_words, ld_inv, ld_rows;   // tile load: words per tile row
+    unsigned short zn_words, zn_inv, zn_rows;   // compass pass: words intersecting the zone columns
+    unsigned short zn_word0;                    // first such word
+    unsigned short _pad[2];
 };
+static_assert(sizeof(CellDev) == 32, "CellDev layout");
 
 // --------------------------------------------------------------------------------------------------------------
 // Pyramid: level l from level l-1, cv::resize INTER_LINEAR fixed point.
@@ -262,10 +268,9 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
 
     if (tid == 0) s_n1 = s_n2 = s_ini = 0;
     for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
-    const int nw = (a + w + 3) >> 2;  // words per tile row, <= 18
     {
         // a warp covers rpw rows x nw words per step; the (row, word) split of the lane is computed once
-        const int rpw = 32 / nw, sub = lane / nw, wx = lane - sub * nw;
+        const int nw = c.ld_words, rpw = c.ld_rows, sub = (lane * c.ld_inv) >> 16, wx = lane - sub * nw;
         if (sub < rpw)
             for (int y = wid * rpw + sub; y < h; y += (FAST_NT / 32) * rpw)
             {
@@ -286,8 +291,8 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
     if (nz)
     {
         const int c0 = 3 + a, c1 = 3 + a + zw;              // zone columns [c0, c1) in tile coordinates
-        const int wz0 = c0 >> 2, nwz = ((c1 + 3) >> 2) - wz0;  // words that intersect the zone, <= 17
-        const int rpw = 32 / nwz, sub = lane / nwz, wx = wz0 + lane - sub * nwz;
+        const int wz0 = c.zn_word0, nwz = c.zn_words;  // words that intersect the zone, <= 17
+        const int rpw = c.zn_rows, sub = (lane * c.zn_inv) >> 16, wx = wz0 + lane - sub * nwz;
         const unsigned addc = (unsigned)(127 - min(t, 127)) * 0x01010101u;
         unsigned zmask = 0x80808080u;  // bytes of my word that lie inside the zone columns
         if (4 * wx < c0) zmask &= 0xffffffffu << (8 * (c0 - 4 * wx));
@@ -704,6 +709,22 @@ __device__ __forceinline__ int reflect101(int p, int len)
     return p >= len ? 2 * (len - 1) - p : p;
 }
 
+// byte selector that rebuilds one word of the 12-byte tap window [x-4, x+8) of a lane at an image border.
+// `first` is the pixel of the word's byte 0, `base` the pixel of byte 0 of the 8-byte register pair the selector reads
+// from; pixels outside [0, W) are replaced by their reflect-101 partner. Out-of-pair sources are clamped: they can
+// only be asked for by taps of outputs that are themselves outside the image and never stored.
+__device__ __forceinline__ unsigned reflect_selector(int first, int base, int W)
+{
+    unsigned sel = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+        const int src = reflect101(min(max(first + k, -(W - 1)), 2 * W - 2), W) - base;
+        sel |= (unsigned)min(max(src, 0), 7) << (4 * k);
+    }
+    return sel;
+}
+
 __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restrict__ tiles, int n_tiles)
 {
     const int lane = threadIdx.x & 31;
@@ -719,13 +740,23 @@ __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restric
     const int words_in_row = pitch >> 2;        // addressable words of a row
     const int xw = x >> 2;
     const bool own_ok = xw < words_in_row;      // my word can be read
-    // all 12 bytes x-4 .. x+7 inside the image: the shuffle path is exact; otherwise gather bytes with reflection
-    const bool fast = (x - 4 >= 0) && (x + 8 <= W);
     const bool active = x < W;                  // I produce at least one output pixel
-    const unsigned KLO = 0x38302212u;           // taps 18,34,48,56 (little endian)
-    const unsigned KHI = 0x00122230u;           // taps 48,34,18,0
+    // Borders without a slow path: the 12-byte window [wl wc wr] of a lane near the left / right image border is
+    // rebuilt from the register pair that holds the reflected pixels, one byte permute per word.
+    //   left  border (x == 0):          wl <- reflection of pixels -4..-1, read from (wc, wr)
+    //   right border (x+4 > W):         wc, wr <- read from (wl, wc)   (my own word is cut by the border)
+    //   right border (x+4 <= W < x+8):  wr <- read from (wc, wr)       (the next word is cut by the border)
+    const bool fixl = (x == 0), fix_own = active && (x + 4 > W), fix_next = (x + 4 <= W) && (x + 8 > W);
+    const unsigned sel_l = reflect_selector(-4, 0, W);
+    const unsigned sel_c = fix_own ? reflect_selector(x, x - 4, W) : 0x7654u;
+    const unsigned sel_r = fix_own ? reflect_selector(x + 4, x - 4, W) : (fix_next ? reflect_selector(x + 4, x, W) : 0x7654u);
+    const unsigned KLO = 0x38302212u;  // horizontal taps 18,34,48,56 (little-endian bytes)
+    const unsigned KHI = 0x00122230u;  // horizontal taps 48,34,18,0
+    const unsigned V01 = 0x2212u, V23 = 0x3830u, V45 = 0x2230u;  // vertical taps as byte pairs (18,34) (48,56) (48,34)
 
-    unsigned hw[7][4];  // horizontal sums of the last 7 rows (slot = row index mod 7)
+    // vertical window: q[s][j] = h[r-1] | h[r] << 16 of the row r with r mod 7 == s (horizontal sums fit 16 bits), so
+    // the 7-tap vertical sum is three dp2a on the pairs (r-6,r-5) (r-4,r-3) (r-2,r-1) plus 18*h[r]
+    unsigned q[7][4], hprev[4] = {0u, 0u, 0u, 0u};
 #pragma unroll 1
     for (int g = 0; g < BL_GROUPS; ++g)
     {
@@ -744,29 +775,27 @@ __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restric
 #pragma unroll
         for (int i = 0; i < 7; ++i)
         {
-            const int r  = 7 * g + i;           // 0 .. 7*BL_GROUPS-1, source row y0 - 3 + r
+            const int r = 7 * g + i;  // 0 .. 7*BL_GROUPS-1, source row y0 - 3 + r
             unsigned wc = wcs[i];
             unsigned wl = __shfl_up_sync(0xffffffffu, wc, 1);
             unsigned wr = __shfl_down_sync(0xffffffffu, wc, 1);
             if (lane == 0) wl = hal[i];
             if (lane == 31) wr = hal[i];
-            if (!fast && active)
             {
-                const int gy = reflect101(min(y0 - 3 + r, H + 2), H);
-                const uint8_t* rb = S + (size_t)gy * pitch;
-                unsigned b[12];
-#pragma unroll
-                for (int k = 0; k < 12; ++k) b[k] = rb[reflect101(x - 4 + k, W)];
-                wl = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
-                wc = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
-                wr = b[8] | (b[9] << 8) | (b[10] << 16) | (b[11] << 24);
+                const unsigned nl = __byte_perm(wc, wr, sel_l);
+                const unsigned nc = __byte_perm(wl, wc, sel_c);
+                const unsigned nr = fix_own ? __byte_perm(wl, wc, sel_r) : __byte_perm(wc, wr, sel_r);
+                wl = fixl ? nl : wl;
+                wc = nc;
+                wr = nr;
             }
             // pixel j of my word: taps are bytes (j+1 .. j+7) of the 12-byte window [wl wc wr]
-            hw[i][0] = __dp4a(__byte_perm(wc, wr, 0x4321), KHI, __dp4a(__byte_perm(wl, wc, 0x4321), KLO, 0u));
-            hw[i][1] = __dp4a(__byte_perm(wc, wr, 0x5432), KHI, __dp4a(__byte_perm(wl, wc, 0x5432), KLO, 0u));
-            hw[i][2] = __dp4a(__byte_perm(wc, wr, 0x6543), KHI, __dp4a(__byte_perm(wl, wc, 0x6543), KLO, 0u));
-            hw[i][3] = __dp4a(wr, KHI, __dp4a(wc, KLO, 0u));
-            // output row y0 + r - 6 is complete once row r is in the window
+            unsigned hc[4];
+            hc[0] = __dp4a(__byte_perm(wc, wr, 0x4321), KHI, __dp4a(__byte_perm(wl, wc, 0x4321), KLO, 0u));
+            hc[1] = __dp4a(__byte_perm(wc, wr, 0x5432), KHI, __dp4a(__byte_perm(wl, wc, 0x5432), KLO, 0u));
+            hc[2] = __dp4a(__byte_perm(wc, wr, 0x6543), KHI, __dp4a(__byte_perm(wl, wc, 0x6543), KLO, 0u));
+            hc[3] = __dp4a(wr, KHI, __dp4a(wc, KLO, 0u));
+            // output row y0 + r - 6 is complete once row r is known
             const int oy = y0 + r - 6;
             if ((g > 0 || i == 6) && oy < H && active)
             {
@@ -774,16 +803,23 @@ __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restric
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                 {
-                    // window rows r-6..r live in slots (i+1)%7 .. i
-                    const unsigned v = 18u * (hw[(i + 1) % 7][j] + hw[i][j]) + 34u * (hw[(i + 2) % 7][j] + hw[(i + 6) % 7][j]) +
-                                       48u * (hw[(i + 3) % 7][j] + hw[(i + 5) % 7][j]) + 56u * hw[(i + 4) % 7][j];
-                    packed |= ((v + 32768u) >> 16) << (8 * j);
+                    unsigned v = 18u * hc[j] + 32768u;
+                    v          = __dp2a_lo(q[(i + 2) % 7][j], V01, v);  // rows r-6, r-5
+                    v          = __dp2a_lo(q[(i + 4) % 7][j], V23, v);  // rows r-4, r-3
+                    v          = __dp2a_lo(q[(i + 6) % 7][j], V45, v);  // rows r-2, r-1
+                    packed |= (v >> 16) << (8 * j);
                 }
                 uint8_t* drow = D + (size_t)oy * L.gauss_pitch + x;
                 if (x + 4 <= W)
                     *reinterpret_cast<uint32_t*>(drow) = packed;
                 else
                     for (int j = 0; j < 4 && x + j < W; ++j) drow[j] = (uint8_t)(packed >> (8 * j));
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                q[i][j]  = __byte_perm(hprev[j], hc[j], 0x5410);  // h[r-1] | h[r] << 16
+                hprev[j] = hc[j];
             }
         }
     }
