@@ -138,13 +138,19 @@ SNK_SORT_HD void median_to_first(uint32_t* v, int result, int a, int b, int c)
 
 SNK_SORT_HD int partition_unguarded(uint32_t* v, int first, int last, int pivot)
 {
+    // the pivot slot lies outside [first, last) and is never written here: read it once (one dependent shared-memory
+    // load less per step of the single-threaded device sort)
+    const uint32_t pv = v[pivot];
     while (true)
     {
-        while (before(v[first], v[pivot])) ++first;
+        uint32_t a = v[first];
+        while (before(a, pv)) a = v[++first];
         --last;
-        while (before(v[pivot], v[last])) --last;
+        uint32_t b = v[last];
+        while (before(pv, b)) b = v[--last];
         if (!(first < last)) return first;
-        swp(v, first, last);
+        v[first] = b;
+        v[last]  = a;
         ++first;
     }
 }

@@ -82,6 +82,10 @@ struct snk_orb
     int max_kp = 0;
 
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    // the blur only depends on the pyramid: it runs on a side stream next to FAST + distribution and joins before the
+    // descriptor kernel (serialised on the main stream while per-stage profiling is on, so stage times stay separable)
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int rows = 0, cols = 0;  // geometry the buffers are sized for (0 = none yet)
     int last_n = 0;
 
@@ -340,6 +344,9 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
         return SNK_ERR_CUDA;
     }
     h->stream = h->own_stream;
+    cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault);
     cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault);
     for (auto& set : h->ev)
@@ -389,6 +396,9 @@ void snk_orb_destroy(snk_orb* h)
         for (auto& e : set)
             if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->side_stream) cudaStreamDestroy(h->side_stream);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     delete h;
 }
 
@@ -502,6 +512,17 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
     if (prof) cudaEventRecord(ev[2], st);
 
+    // blur of every level: on the side stream unless stages are being timed
+    const bool overlap = !prof && h->side_stream && h->ev_fork && h->ev_join;
+    if (overlap)
+    {
+        SNK_CUDA(cudaEventRecord(h->ev_fork, st));
+        SNK_CUDA(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+        k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, h->side_stream>>>(P, h->d_tiles, (int)h->tiles.size());
+        SNK_CUDA(cudaEventRecord(h->ev_join, h->side_stream));
+        ++nl[4];
+    }
+
     // stage 2: FAST over every cell of every level
     k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->d_cells, h->d_cand, h->d_cell_count);
     ++nl[2];
@@ -514,9 +535,14 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     ++nl[3];
     if (prof) cudaEventRecord(ev[4], st);
 
-    // stage 4: blur of every level
-    k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
-    ++nl[4];
+    // stage 4: blur (serial variant) / join
+    if (overlap)
+        SNK_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
+    else
+    {
+        k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
+        ++nl[4];
+    }
     if (prof) cudaEventRecord(ev[5], st);
 
     // stage 5: orientation + descriptors + output records

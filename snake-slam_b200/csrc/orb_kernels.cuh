@@ -160,81 +160,34 @@ constexpr int FAST_ZMAX = (FAST_DIM - 6) * (FAST_DIM - 6);  // detection-zone pi
 constexpr int FAST_BMW = (FAST_ZMAX + 31) / 32;
 
 // arc score: max over the 16 arcs of 9 contiguous ring pixels of min(v - ring) and min(ring - v).
-// The differences are biased by +256 so that every intermediate is a positive integer: nvcc 12.9 narrows the
-// min/max network to 16-bit *unsigned* PTX ops (min.u16/max.u16), which is only correct for non-negative operands
-// (the signed formulation returned wrong scores on sm_100a; tools/dev_check.cu guards this on the device).
+// Both polarities run through ONE min network on packed 16-bit pairs (VIMNMX3.U16x2): lane 0 carries d = 256 + v - ring
+// (always positive), lane 1 carries 1023 - d, so a window minimum of lane 1 is 1023 - (window maximum of d).
+// Window of 9 = min3 of three windows of 3. (An earlier signed 32-bit formulation was mis-narrowed by nvcc 12.9 to
+// min.u16/max.u16 and returned wrong scores on sm_100a; everything here is explicitly unsigned and non-negative, and
+// tools/dev_check.cu checks the function on the device against brute force.)
 __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], int y, int x)
 {
     const unsigned v = 256u + t[y][x];
-    unsigned d[16];
-    d[0]  = v - t[y + 3][x];
-    d[1]  = v - t[y + 3][x + 1];
-    d[2]  = v - t[y + 2][x + 2];
-    d[3]  = v - t[y + 1][x + 3];
-    d[4]  = v - t[y][x + 3];
-    d[5]  = v - t[y - 1][x + 3];
-    d[6]  = v - t[y - 2][x + 2];
-    d[7]  = v - t[y - 3][x + 1];
-    d[8]  = v - t[y - 3][x];
-    d[9]  = v - t[y - 3][x - 1];
-    d[10] = v - t[y - 2][x - 2];
-    d[11] = v - t[y - 1][x - 3];
-    d[12] = v - t[y][x - 3];
-    d[13] = v - t[y + 1][x - 3];
-    d[14] = v - t[y + 2][x - 2];
-    d[15] = v - t[y + 3][x - 1];
-    // sliding-window min and max over 9 consecutive (circular) entries by doubling: 2, 4, 8, then +1
-    unsigned lo[16], hi[16];
+    unsigned e[16];
+#define SNK_E(k, yy, xx) e[k] = (v - t[yy][xx]) * 0xFFFF0001u + 0x03FF0000u;  // d | (1023 - d) << 16
+    SNK_E(0, y + 3, x) SNK_E(1, y + 3, x + 1) SNK_E(2, y + 2, x + 2) SNK_E(3, y + 1, x + 3)
+    SNK_E(4, y, x + 3) SNK_E(5, y - 1, x + 3) SNK_E(6, y - 2, x + 2) SNK_E(7, y - 3, x + 1)
+    SNK_E(8, y - 3, x) SNK_E(9, y - 3, x - 1) SNK_E(10, y - 2, x - 2) SNK_E(11, y - 1, x - 3)
+    SNK_E(12, y, x - 3) SNK_E(13, y + 1, x - 3) SNK_E(14, y + 2, x - 2) SNK_E(15, y + 3, x - 1)
+#undef SNK_E
+    unsigned m3[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k)
-    {
-        lo[k] = min(d[k], d[(k + 1) & 15]);
-        hi[k] = max(d[k], d[(k + 1) & 15]);
-    }
-    unsigned lo4[16], hi4[16];
+    for (int k = 0; k < 16; ++k) m3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    unsigned best = 0;  // per-lane maximum over the 16 window minima
 #pragma unroll
-    for (int k = 0; k < 16; ++k)
+    for (int k = 0; k < 16; k += 2)
     {
-        lo4[k] = min(lo[k], lo[(k + 2) & 15]);
-        hi4[k] = max(hi[k], hi[(k + 2) & 15]);
+        const unsigned a = __vimin3_u16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+        const unsigned b = __vimin3_u16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]);
+        best             = __vimax3_u16x2(best, a, b);
     }
-    unsigned best_lo = 0, best_hi = 1024;  // max of window minima, min of window maxima
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-    {
-        best_lo = max(best_lo, min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]));
-        best_hi = min(best_hi, max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]));
-    }
-    // un-bias: darker arc = best_lo - 256, brighter arc = 256 - best_hi
-    return max((int)best_lo - 256, 256 - (int)best_hi);
-}
-
-// is there an arc of 9 contiguous ring pixels all brighter than v+t or all darker than v-t ?
-__device__ __forceinline__ bool fast_is_corner(const uint8_t (*t)[FAST_PITCH], int y, int x, int th)
-{
-    const int v = t[y][x], hi = v + th, lo = v - th;
-    unsigned bm = 0, dm = 0;
-#define SNK_RING(k, yy, xx)                       \
-    {                                             \
-        const int r = t[yy][xx];                  \
-        bm |= (r > hi) ? (0x10001u << (k)) : 0u;  \
-        dm |= (r < lo) ? (0x10001u << (k)) : 0u;  \
-    }
-    SNK_RING(0, y + 3, x) SNK_RING(1, y + 3, x + 1) SNK_RING(2, y + 2, x + 2) SNK_RING(3, y + 1, x + 3)
-    SNK_RING(4, y, x + 3) SNK_RING(5, y - 1, x + 3) SNK_RING(6, y - 2, x + 2) SNK_RING(7, y - 3, x + 1)
-    SNK_RING(8, y - 3, x) SNK_RING(9, y - 3, x - 1) SNK_RING(10, y - 2, x - 2) SNK_RING(11, y - 1, x - 3)
-    SNK_RING(12, y, x - 3) SNK_RING(13, y + 1, x - 3) SNK_RING(14, y + 2, x - 2) SNK_RING(15, y + 3, x - 1)
-#undef SNK_RING
-    // masks are doubled (bit k and k+16) so a plain shift wraps around the ring
-    unsigned b = bm & (bm >> 1);
-    b &= b >> 2;
-    b &= b >> 4;
-    b &= bm >> 8;
-    unsigned d = dm & (dm >> 1);
-    d &= d >> 2;
-    d &= d >> 4;
-    d &= dm >> 8;
-    return ((b | d) & 0xffffu) != 0;
+    // darker arc = lane0 - 256; brighter arc = 256 - min(window max) = lane1 - 767
+    return max((int)(best & 0xffffu) - 256, (int)(best >> 16) - 767);
 }
 
 // One CTA == one cell == the (up to two) cv::FAST calls of ORBExtractor.cpp:133-140.
@@ -242,9 +195,8 @@ __device__ __forceinline__ bool fast_is_corner(const uint8_t (*t)[FAST_PITCH], i
 // not a corner at t scores <= t < its own score, so "survives NMS at t" == "arc > t and arc > all neighbours' arcs
 // inside the ROI". The cell is therefore scored once at the lower threshold; the threshold is chosen afterwards from
 // the NMS survivors. Work is filtered in stages so that the expensive steps only see the pixels that need them:
-//   A  compass test on every zone pixel (two adjacent compass points both brighter / darker — necessary for any arc of 9)
-//   B  16-pixel ring test on the survivors of A            -> corners at the lower threshold
-//   B2 arc score of the corners
+//   A  compass test on every zone pixel, 4 pixels per thread with byte SIMD (necessary condition for any arc of 9)
+//   B  arc score of the survivors of A (packed 16-bit min network)  -> corners at the lower threshold
 //   C  3x3 NMS of the corners, survivors marked in a bitmap over the zone; popc-prefix of the bitmap gives every
 //      survivor its row-major rank (== cv::FAST output order) without sorting
 __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __restrict__ cells, uint32_t* __restrict__ cand,
@@ -272,11 +224,31 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
         // a warp covers rpw rows x nw words per step; the (row, word) split of the lane is computed once
         const int nw = c.ld_words, rpw = c.ld_rows, sub = (lane * c.ld_inv) >> 16, wx = lane - sub * nw;
         if (sub < rpw)
-            for (int y = wid * rpw + sub; y < h; y += (FAST_NT / 32) * rpw)
+        {
+            // all global loads of this lane are issued before the first shared store (up to 6 rows per lane:
+            // 66 rows / (4 warps * >=1 row)); a dependent load->store loop left the SM waiting on DRAM latency
+            const int ystep = (FAST_NT / 32) * rpw, ybeg = wid * rpw + sub;
+            for (int yb = ybeg; yb < h; yb += 6 * ystep)
             {
-                reinterpret_cast<uint32_t*>(&tile[y][0])[wx] = __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + wx);
-                reinterpret_cast<uint32_t*>(&score[y][0])[wx] = 0;
+                unsigned vals[6];
+#pragma unroll
+                for (int u = 0; u < 6; ++u)
+                {
+                    const int y = yb + u * ystep;
+                    vals[u] = (y < h) ? __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + wx) : 0u;
+                }
+#pragma unroll
+                for (int u = 0; u < 6; ++u)
+                {
+                    const int y = yb + u * ystep;
+                    if (y < h)
+                    {
+                        reinterpret_cast<uint32_t*>(&tile[y][0])[wx]  = vals[u];
+                        reinterpret_cast<uint32_t*>(&score[y][0])[wx] = 0;
+                    }
+                }
             }
+        }
     }
     __syncthreads();
 
@@ -323,7 +295,7 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
             }
     }
     __syncthreads();
-    // ---- B: ring test ----
+    // ---- B: arc score of every candidate; corners (arc > lower threshold) go to list2 ----
     const int n1 = s_n1;
     for (int base = 0; base < n1; base += FAST_NT)
     {
@@ -332,8 +304,11 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
         uint16_t e  = 0;
         if (k < n1)
         {
-            e    = list1[k];
-            pass = fast_is_corner(tile, e >> 8, (e & 255) + a, t);
+            e = list1[k];
+            const int y = e >> 8, xa = (e & 255) + a;
+            const int arc = fast_arc_score(tile, y, xa);
+            pass = arc > t;
+            if (pass) score[y][xa] = (uint8_t)arc;
         }
         const unsigned m = __ballot_sync(0xffffffffu, pass);
         int off = 0;
@@ -342,14 +317,7 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __res
         if (pass) list2[off + __popc(m & ((1u << lane) - 1))] = e;
     }
     __syncthreads();
-    // ---- B2: scores ----
     const int n2 = s_n2;
-    for (int k = tid; k < n2; k += FAST_NT)
-    {
-        const int y = list2[k] >> 8, xa = (list2[k] & 255) + a;
-        score[y][xa] = (uint8_t)fast_arc_score(tile, y, xa);
-    }
-    __syncthreads();
     // ---- C: NMS, survivors into the bitmaps ----
     for (int k = tid; k < n2; k += FAST_NT)
     {
