@@ -227,7 +227,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     for (int l = 0; l < L; ++l) max_quota = std::max(max_quota, h->features[l]);
     h->node_cap = align_up(max_quota + 8, 4);  // multiple of 4 keeps the int2 array of the kernel 8-byte aligned
     SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
-    h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES;
+    h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES + 2 * (size_t)QT_KP_SMEM * 4;
     SNK_REQUIRE(h->qt_smem <= 200 * 1024, "nfeatures too large for the distribution kernel's shared memory");
     SNK_CUDA(cudaFuncSetAttribute(k_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
 
@@ -531,7 +531,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     // stage 3: quadtree distribution per (level, image)
     k_distribute<<<dim3(P.nlevels, n_imgs), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
                                                                      h->d_workA, h->d_workB, h->d_sel, h->d_sel_count,
-                                                                     h->node_cap, h->d_err);
+                                                                     h->node_cap, QT_KP_SMEM, h->d_err);
     ++nl[3];
     if (prof) cudaEventRecord(ev[4], st);
 

@@ -385,11 +385,13 @@ __device__ __forceinline__ float kp_y(uint32_t p) { return (float)((p >> 12) & 0
 
 // dynamic shared memory: 3 node lists + sort keys + per-node child counts/positions = QT_NODE_BYTES per node
 constexpr int QT_NODE_BYTES = 3 * 24 + 4 + 16 + 8;
+constexpr int QT_SMALL = 24;      // nodes up to this many keypoints are processed by a single thread
+constexpr int QT_KP_SMEM = 2048;  // keypoints per (level, image) kept in shared memory (x2: array + partition buffer)
 __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* __restrict__ cand,
                                                       const int* __restrict__ cell_count, int* __restrict__ cell_off,
                                                       uint32_t* __restrict__ workA, uint32_t* __restrict__ workB,
                                                       uint32_t* __restrict__ sel, int* __restrict__ sel_count,
-                                                      int node_cap, int* __restrict__ err)
+                                                      int node_cap, int kp_cap, int* __restrict__ err)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     QNode* listA    = reinterpret_cast<QNode*>(smem);
@@ -398,14 +400,16 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     uint32_t* keys  = reinterpret_cast<uint32_t*>(leaves + node_cap);
     int* ccnt_big   = reinterpret_cast<int*>(keys + node_cap);           // child sizes of sorted node i (4 per node)
     int2* cpos      = reinterpret_cast<int2*>(ccnt_big + 4 * node_cap);  // (leaf position, next position) of node i
-    __shared__ int s_warp[QT_NT / 32], s_ctrl[8];
+    __shared__ int s_warp[QT_NT / 32], s_ctrl[10];
 
     const int level = blockIdx.x, img = blockIdx.y;
     const LevelDev& L = P.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const size_t wbase = (size_t)img * P.cand_per_img + L.cand_base;
-    uint32_t* A = workA + wbase;
-    uint32_t* B = workB + wbase;
+    // keypoint array and its partition buffer: in shared memory when the level's candidates fit (the split loop walks
+    // them node by node, a chain of dependent accesses), else in the global scratch (always large enough)
+    uint32_t* A = reinterpret_cast<uint32_t*>(cpos + node_cap);
+    uint32_t* B = A + kp_cap;
     uint32_t* out = sel + (size_t)img * P.sel_per_img + L.sel_base;
     const int target = L.quota;
     const int out_cap = target + 4;
@@ -434,11 +438,17 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         __syncthreads();
     }
     const int n = running;
-    for (int cidx = wid; cidx < L.n_cells; cidx += QT_NT / 32)
+    if (n > kp_cap)
+    {
+        A = workA + wbase;
+        B = workB + wbase;
+    }
+    // one thread per cell (cells hold a handful of candidates; the per-cell loads of different threads overlap)
+    for (int cidx = tid; cidx < L.n_cells; cidx += QT_NT)
     {
         const int cnt = min(cc[cidx], P.cell_cap), off = co[cidx];
         const uint32_t* s = cand + ((size_t)img * P.cells_per_img + L.cell_base + cidx) * P.cell_cap;
-        for (int k = lane; k < cnt; k += 32) A[off + k] = s[k];
+        for (int k = 0; k < cnt; ++k) A[off + k] = s[k];
     }
     __syncthreads();
 
@@ -495,11 +505,39 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         // std::sort by NumKeypoints descending (FeatureDistribution.cpp:124) — libstdc++ permutation
         for (int i = tid; i < m; i += QT_NT) keys[i] = ((uint32_t)(inner[i].to - inner[i].from) << gnusort::SHIFT) | (uint32_t)i;
         __syncthreads();
-        if (tid == 0) gnusort::sort(keys, m);
+        if (tid == 0)
+        {
+            gnusort::sort(keys, m);
+            // nodes are now ordered by size: [0, nbig) are handled by a warp each, the rest by a thread each
+            int lo = 0, hi = m;
+            while (lo < hi)
+            {
+                const int mid = (lo + hi) >> 1;
+                if ((int)(keys[mid] >> gnusort::SHIFT) > QT_SMALL)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            s_ctrl[8] = lo;
+        }
         __syncthreads();
+        const int nbig = s_ctrl[8];
 
         // child sizes of every inner node (the split itself is only applied to the nodes that get processed)
-        for (int i = wid; i < m; i += QT_NT / 32)
+        for (int i = nbig + tid; i < m; i += QT_NT)
+        {
+            const QNode nd = inner[keys[i] & ((1u << gnusort::SHIFT) - 1)];
+            const float mx = __fadd_rn(nd.cx, __fmul_rn(nd.sx, 0.5f)), my = __fadd_rn(nd.cy, __fmul_rn(nd.sy, 0.5f));
+            int cq[4] = {0, 0, 0, 0};
+            for (int k = nd.from; k < nd.to; ++k)
+            {
+                const uint32_t p = A[k];
+                const int q      = ((kp_y(p) > my) ? 2 : 0) + ((kp_x(p) > mx) ? 1 : 0);
+                cq[0] += (q == 0), cq[1] += (q == 1), cq[2] += (q == 2), cq[3] += (q == 3);
+            }
+            ccnt_big[4 * i + 0] = cq[0], ccnt_big[4 * i + 1] = cq[1], ccnt_big[4 * i + 2] = cq[2], ccnt_big[4 * i + 3] = cq[3];
+        }
+        for (int i = wid; i < nbig; i += QT_NT / 32)
         {
             const QNode nd = inner[keys[i] & ((1u << gnusort::SHIFT) - 1)];
             const float mx = __fadd_rn(nd.cx, __fmul_rn(nd.sx, 0.5f)), my = __fadd_rn(nd.cy, __fmul_rn(nd.sy, 0.5f));
@@ -561,7 +599,50 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         const int processed = s_ctrl[7];
 
         // splitAndSort (:15-70) of the processed nodes: stable 4-way partition, children appended in order
-        for (int i = wid; i < processed; i += QT_NT / 32)
+        for (int i = nbig + tid; i < processed; i += QT_NT)
+        {
+            // small node: the whole stable partition and the child bookkeeping by one thread
+            const QNode nd = inner[keys[i] & ((1u << gnusort::SHIFT) - 1)];
+            const float hx = __fmul_rn(nd.sx, 0.5f), hy = __fmul_rn(nd.sy, 0.5f);
+            const float mx = __fadd_rn(nd.cx, hx), my = __fadd_rn(nd.cy, hy);
+            const int cs[4] = {ccnt_big[4 * i], ccnt_big[4 * i + 1], ccnt_big[4 * i + 2], ccnt_big[4 * i + 3]};
+            int o[4];
+            o[0] = nd.from, o[1] = o[0] + cs[0], o[2] = o[1] + cs[1], o[3] = o[2] + cs[2];
+            for (int k = nd.from; k < nd.to; ++k)
+            {
+                const uint32_t p = A[k];
+                const int q      = ((kp_y(p) > my) ? 2 : 0) + ((kp_x(p) > mx) ? 1 : 0);
+                const int dst    = (q == 0) ? o[0]++ : (q == 1) ? o[1]++ : (q == 2) ? o[2]++ : o[3]++;
+                B[dst]           = p;
+            }
+            for (int k = nd.from; k < nd.to; ++k) A[k] = B[k];
+            int2 pos = cpos[i];
+            int from = nd.from;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+            {
+                const int c = cs[q];
+                QNode ch;
+                ch.cx   = (q & 1) ? mx : nd.cx;
+                ch.cy   = (q & 2) ? my : nd.cy;
+                ch.sx   = hx;
+                ch.sy   = hy;
+                ch.from = from;
+                ch.to   = from + c;
+                from += c;
+                if (c == 1)
+                {
+                    if (pos.x < node_cap) leaves[pos.x] = ch;
+                    ++pos.x;
+                }
+                else if (c > 1)
+                {
+                    if (pos.y < node_cap) next[pos.y] = ch;
+                    ++pos.y;
+                }
+            }
+        }
+        for (int i = wid; i < min(nbig, processed); i += QT_NT / 32)
         {
             const QNode nd = inner[keys[i] & ((1u << gnusort::SHIFT) - 1)];
             const float hx = __fmul_rn(nd.sx, 0.5f), hy = __fmul_rn(nd.sy, 0.5f);
@@ -632,7 +713,8 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     const int n_tail   = (lpi >= 0) ? (m - lpi) : 0;
     const int total    = n_leaves + n_next + n_tail;
     if (total > out_cap && tid == 0) atomicExch(err, 3);
-    for (int o = wid; o < total; o += QT_NT / 32)
+    // small nodes (all leaves, most others): one thread finds the first maximum serially
+    for (int o = tid; o < total; o += QT_NT)
     {
         QNode nd;
         if (o < n_leaves)
@@ -641,6 +723,26 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
             nd = next[o - n_leaves];
         else
             nd = inner[keys[lpi + (o - n_leaves - n_next)] & ((1u << gnusort::SHIFT) - 1)];
+        if (nd.to - nd.from > QT_SMALL) continue;
+        int bk = nd.from;
+        uint32_t br = A[bk] >> 24;
+        for (int k = nd.from + 1; k < nd.to; ++k)
+        {
+            const uint32_t r = A[k] >> 24;
+            if (br < r) br = r, bk = k;
+        }
+        if (o < out_cap) out[o] = A[bk];
+    }
+    for (int o = wid; o < total; o += QT_NT / 32)
+    {
+        QNode nd;
+        if (o < n_leaves)
+            continue;  // leaves hold one keypoint
+        else if (o < n_leaves + n_next)
+            nd = next[o - n_leaves];
+        else
+            nd = inner[keys[lpi + (o - n_leaves - n_next)] & ((1u << gnusort::SHIFT) - 1)];
+        if (nd.to - nd.from <= QT_SMALL) continue;
         // std::max_element on response: first maximum in range order
         uint32_t bestkey = 0;  // (response+1) << 20 | (0xfffff - relative index)
         for (int k = nd.from + lane; k < nd.to; k += 32)
