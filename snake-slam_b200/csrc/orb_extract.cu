@@ -101,6 +101,7 @@ struct snk_orb
     ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
     int* d_yofs[SNK_MAX_LEVELS]{};
     short* d_yb[SNK_MAX_LEVELS]{};
+    float2* d_pattern_t = nullptr;  // rBRIEF pattern as float2, transposed to [point-in-byte][lane]
     CellDev* d_cells = nullptr;
     TileDev* d_tiles = nullptr;
     uint32_t *d_cand = nullptr, *d_workA = nullptr, *d_workB = nullptr, *d_sel = nullptr;
@@ -231,8 +232,9 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     SNK_REQUIRE(h->qt_smem <= 200 * 1024, "nfeatures too large for the distribution kernel's shared memory");
     SNK_CUDA(cudaFuncSetAttribute(k_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
 
-    SNK_CUDA(cudaMalloc(&h->d_pyr, pyr_bytes));
-    SNK_CUDA(cudaMalloc(&h->d_gauss, gauss_bytes));
+    // + slack: the kernels read whole aligned words / short row segments that may extend a few bytes past a row's end
+    SNK_CUDA(cudaMalloc(&h->d_pyr, pyr_bytes + 256));
+    SNK_CUDA(cudaMalloc(&h->d_gauss, gauss_bytes + 256));
     for (int l = 0; l < L; ++l)
     {
         P.lv[l].img   = h->d_pyr + pyr_off[l];
@@ -373,7 +375,12 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
         snk_orb_destroy(h);
         return SNK_ERR_INVALID;
     }
-    if (cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)) != cudaSuccess ||
+    float2 pt[512];
+    for (int i = 0; i < 512; ++i)  // entry j*32 + lane holds point 16*lane + j
+        pt[(i & 15) * 32 + (i >> 4)] = make_float2((float)kOrbPattern[2 * i], (float)kOrbPattern[2 * i + 1]);
+    if (cudaMalloc(&h->d_pattern_t, sizeof(pt)) != cudaSuccess ||
+        cudaMemcpy(h->d_pattern_t, pt, sizeof(pt), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)) != cudaSuccess ||
         cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024) != cudaSuccess)
     {
         set_error("constant upload failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -390,6 +397,7 @@ void snk_orb_destroy(snk_orb* h)
     cudaSetDevice(h->prm.device);
     cudaStreamSynchronize(h->stream);
     h->free_buffers();
+    if (h->d_pattern_t) cudaFree(h->d_pattern_t);
     if (h->h_counts) cudaFreeHost(h->h_counts);
     if (h->h_err) cudaFreeHost(h->h_err);
     for (auto& set : h->ev)
@@ -546,8 +554,8 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     if (prof) cudaEventRecord(ev[5], st);
 
     // stage 5: orientation + descriptors + output records
-    k_describe<<<dim3((P.kp_stride + DS_WARPS - 1) / DS_WARPS, n_imgs), DS_WARPS * 32, 0, st>>>(
-        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts);
+    k_describe<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, 0, st>>>(
+        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t);
     ++nl[5];
     if (prof)
     {

@@ -902,18 +902,20 @@ __constant__ signed char c_pattern[1024];  // 512 points (x,y) — include/snake
 __constant__ int c_umax[16];               // ORBPattern::AngleUmax()
 
 constexpr int DS_WARPS = 8;
+constexpr int DS_KP_PER_WARP = 8;  // keypoints per warp: the CTA prologue (pattern, level prefix) is paid once per 64
 
 __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint32_t* __restrict__ sel,
                                                             const int* __restrict__ sel_count,
                                                             snk_keypoint_f32* __restrict__ kps,
-                                                            uint64_t* __restrict__ desc, int* __restrict__ counts)
+                                                            uint64_t* __restrict__ desc, int* __restrict__ counts,
+                                                            const float2* __restrict__ pattern_t)
 {
-    __shared__ char2 pat[16][32];  // pat[j][lane] = point 16*lane + j  (conflict-free: lanes are consecutive)
+    __shared__ float2 pat[16][32];  // pat[j][lane] = point 16*lane + j as floats (conflict-free: lanes are consecutive)
     __shared__ int s_pref[SNK_MAX_LEVELS + 1];
     const int img = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    for (int i = tid; i < 512; i += DS_WARPS * 32)
-        pat[i & 15][i >> 4] = make_char2(c_pattern[2 * i], c_pattern[2 * i + 1]);
+    // pattern_t is the rBRIEF table already transposed to [j][lane] and converted to float (built once per handle)
+    for (int i = tid; i < 512; i += DS_WARPS * 32) (&pat[0][0])[i] = __ldg(pattern_t + i);
     if (tid == 0)
     {
         int acc = 0;
@@ -927,7 +929,10 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     }
     __syncthreads();
     const int total = min(s_pref[P.nlevels], P.kp_stride);
-    const int g     = blockIdx.x * DS_WARPS + wid;
+#pragma unroll 1
+    for (int kk = 0; kk < DS_KP_PER_WARP; ++kk)
+    {
+    const int g     = (blockIdx.x * DS_KP_PER_WARP + kk) * DS_WARPS + wid;
     if (g >= total) return;
     int level = 0;
     while (level + 1 < P.nlevels && g >= s_pref[level + 1]) ++level;
@@ -938,7 +943,9 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     const float resp = (float)(p >> 24);
 
     // ---- ORB::ComputeAngle: integer moments over the radius-15 disc of the un-blurred level ----
-    const uint8_t* raw = L.img + (size_t)img * L.img_stride + (size_t)y * L.pitch + x;
+    // offsets inside one level image fit 32 bits (levels are at most 4000 x 4000)
+    const int pitch    = L.pitch;
+    const uint8_t* raw = L.img + (size_t)img * L.img_stride + (y * pitch + x);
     const int u        = lane - 15;  // lane 31 idles
     int m10 = 0, m01 = 0;
     if (lane < 31)
@@ -949,10 +956,11 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
         const int au = abs(u);
         int rowsum = 0;  // sum over v of v * I(v,u) for my column
         int colsum = 0;  // sum over v of I(v,u)
+        const uint8_t* col = raw + u;
 #pragma unroll
         for (int v = -15; v <= 15; ++v)
         {
-            const int val = (au <= UMAX[v < 0 ? -v : v]) ? (int)raw[v * L.pitch + u] : 0;
+            const int val = (au <= UMAX[v < 0 ? -v : v]) ? (int)col[v * pitch] : 0;
             colsum += val;
             rowsum += v * val;
         }
@@ -969,6 +977,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     // ---- ORB::ComputeDescriptor on the blurred level; lane i produces byte i ----
     const float rad = __fmul_rn(__fdiv_rn(angle, 180.0f), 3.14159265358979323846f);
     const float a = snkmath::cosf_glibc(rad), b = snkmath::sinf_glibc(rad);
+    const int gpitch  = L.gauss_pitch;
     const uint8_t* gs = L.gauss + (size_t)img * L.gauss_stride;
     const float px = (float)x, py = (float)y;
     uint32_t byte = 0;
@@ -979,13 +988,14 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
 #pragma unroll
         for (int e = 0; e < 2; ++e)
         {
-            const char2 q  = pat[2 * j + e][lane];
-            const float ux = (float)q.x, uy = (float)q.y;
-            const float fx = __fadd_rn(px, __fsub_rn(__fmul_rn(ux, a), __fmul_rn(uy, b)));
-            const float fy = __fadd_rn(py, __fadd_rn(__fmul_rn(ux, b), __fmul_rn(uy, a)));
-            const int ix   = (int)__fadd_rn(fx, fx >= 0.f ? 0.5f : -0.5f);  // Saiga::iRound
-            const int iy   = (int)__fadd_rn(fy, fy >= 0.f ? 0.5f : -0.5f);
-            tv[e]          = gs[(size_t)iy * L.gauss_pitch + ix];
+            const float2 q = pat[2 * j + e][lane];
+            const float fx = __fadd_rn(px, __fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
+            const float fy = __fadd_rn(py, __fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
+            // Saiga::iRound: (int)(v + (v >= 0 ? 0.5f : -0.5f)); the half takes the sign bit of v (v = -0.f gives
+            // -0.5f instead of +0.5f, both truncate to 0)
+            const int ix = (int)__fadd_rn(fx, __int_as_float(0x3f000000 | (__float_as_int(fx) & 0x80000000)));
+            const int iy = (int)__fadd_rn(fy, __int_as_float(0x3f000000 | (__float_as_int(fy) & 0x80000000)));
+            tv[e]        = gs[iy * gpitch + ix];
         }
         byte |= (uint32_t)(tv[0] < tv[1]) << j;
     }
@@ -1015,5 +1025,6 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
             f = __int_as_float(level);
         reinterpret_cast<float*>(kps + o)[lane] = f;
     }
+    }  // keypoints of this warp
 }
 }  // namespace snk
