@@ -174,6 +174,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--chunks", type=int, default=8, help="e2e path: chunks per step")
+    ap.add_argument("--lanes", type=int, default=4, help="e2e path: streams/handles the chunks alternate over")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -277,7 +279,7 @@ def main():
     # kernels (every byte still crosses PCIe inside the timed region)
     import ctypes as C
 
-    NCH = 4 if NI % 8 == 0 else 1
+    NCH = args.chunks if (NI % (2 * args.chunks) == 0) else 1
     CI, CP = NI // NCH, P // NCH
     h_kps = torch.empty((NI, cap, 24), dtype=torch.uint8, pin_memory=True)
     h_desc = torch.empty((NI, cap, 4), dtype=torch.int64, pin_memory=True)
@@ -287,7 +289,7 @@ def main():
     h_nm = torch.empty((P,), dtype=torch.int32, pin_memory=True)
     e2e_lanes = []
     if not args.no_e2e:
-        for _ in range(2 if NCH > 1 else 1):
+        for _ in range(min(args.lanes, NCH)):
             st = torch.cuda.Stream()
             exc = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=CI, device=local_rank)
             cxc = snakeorb.Context(device=local_rank)
@@ -308,16 +310,17 @@ def main():
 
     def e2e_fetch(k):
         _, exc, _, _, _, _ = e2e_lanes[k % len(e2e_lanes)]
-        snakeorb._check(snakeorb.lib().snk_orb_fetch(exc.h, C.c_void_p(h_kps.data_ptr() + k * CI * cap * 24),
-                                                     C.c_void_p(h_desc.data_ptr() + k * CI * cap * 32), cap,
-                                                     C.c_void_p(h_cnt.data_ptr() + k * CI * 4)))
+        snakeorb._check(snakeorb.lib().snk_orb_fetch_async(exc.h, C.c_void_p(h_kps.data_ptr() + k * CI * cap * 24),
+                                                           C.c_void_p(h_desc.data_ptr() + k * CI * cap * 32), cap,
+                                                           C.c_void_p(h_cnt.data_ptr() + k * CI * 4)))
 
     def step_e2e():
-        e2e_enqueue(0)
-        for k in range(1, NCH):
-            e2e_enqueue(k)      # chunk k is in flight on the other lane ...
-            e2e_fetch(k - 1)    # ... while the host waits for chunk k-1's results
-        e2e_fetch(NCH - 1)
+        # every chunk: H2D, kernels, D2H on its lane's stream, no host wait in between; one sync per step
+        for k in range(NCH):
+            e2e_enqueue(k)
+            e2e_fetch(k)
+        for st, *_ in e2e_lanes:
+            st.synchronize()
 
     # ---- device-resident timing --------------------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):

@@ -117,6 +117,13 @@ SNK_API int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps_dev,
 /* Copy the results of the last enqueue to the host (synchronises the stream). */
 SNK_API int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
 
+/* Same copies as snk_orb_fetch, enqueued on the handle's stream without waiting for them: keypoints, descriptors and
+ * counts of the last enqueue go to the caller's (pinned) host buffers and are valid once the stream has reached
+ * this point (cudaStreamSynchronize / an event). Lets a caller keep several batches in flight — the asynchronous
+ * counterpart of the download step of ORBExtractorGPU::Detect (saiga/cuda/imageProcessing/ORBExtractorGPU.cu:178-192).
+ * capacity must be >= snk_orb_max_keypoints(). */
+SNK_API int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
+
 /* Upper bound of keypoints per image for this handle (sum over levels of quota+3). */
 SNK_API int snk_orb_max_keypoints(const snk_orb* h);
 

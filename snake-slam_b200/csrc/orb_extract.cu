@@ -628,6 +628,32 @@ int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacit
     return SNK_OK;
 }
 
+int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out)
+{
+    SNK_REQUIRE(h && kps && desc && n_out, "null argument");
+    const int n = h->last_n;
+    if (n == 0) return SNK_OK;
+    const int ks = h->P.kp_stride;
+    SNK_REQUIRE(capacity >= ks, "capacity %d is below snk_orb_max_keypoints() = %d", capacity, ks);
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    cudaStream_t st = h->stream;
+    SNK_CUDA(cudaMemcpyAsync(n_out, h->d_counts, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (capacity == ks)
+    {
+        SNK_CUDA(cudaMemcpyAsync(kps, h->d_kps, (size_t)n * ks * sizeof(snk_keypoint_f32), cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpyAsync(desc, h->d_desc, (size_t)n * ks * 32, cudaMemcpyDeviceToHost, st));
+    }
+    else
+    {
+        SNK_CUDA(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(snk_keypoint_f32), h->d_kps,
+                                   (size_t)ks * sizeof(snk_keypoint_f32), (size_t)ks * sizeof(snk_keypoint_f32), n,
+                                   cudaMemcpyDeviceToHost, st));
+        SNK_CUDA(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->d_desc, (size_t)ks * 32, (size_t)ks * 32, n,
+                                   cudaMemcpyDeviceToHost, st));
+    }
+    return SNK_OK;
+}
+
 int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
                          size_t img_stride, int on_device, snk_keypoint_f32* kps, uint64_t* desc, int capacity,
                          int* n_out)
