@@ -229,6 +229,22 @@ SNK_API int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_k
 SNK_API int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_stereo_params* p,
                                         float* right_points_dev, float* depth_dev, int32_t* n_matches_dev);
 
+/* Preprocess::ComputeStereoFromRGBD (Snake/Preprocess/Preprocess.cpp:79-120): per undistorted keypoint, re-distort
+ * with the depth camera's model (saiga/vision/cameraModel/Distortion.h:128-170), look the depth up at the nearest
+ * pixel (int(v + 0.5)) and derive the virtual right-image coordinate x - bf/depth. right_points / depth get -1 where
+ * the depth image holds no measurement (<= 0). The reference asserts that the lookup lands inside the depth image;
+ * here such keypoints are reported like "no measurement". depth_img is a host float image, pitch in bytes. */
+typedef struct snk_rgbd_params
+{
+    double fx, fy, cx, cy;        /* K (colour camera; unproject2 ignores the skew, Intrinsics4.h:80) */
+    double dfx, dfy, dcx, dcy, ds; /* rgbd_intrinsics.depthModel.K */
+    double dist[8];               /* rgbd_intrinsics.depthModel.dis: k1 k2 k3 k4 k5 k6 p1 p2 */
+    double bf;                    /* rgbd_intrinsics.bf */
+} snk_rgbd_params;
+SNK_API int snk_stereo_from_rgbd(snk_ctx* c, const snk_rgbd_params* p, const snk_keypoint_f64* kp_un, int n,
+                                 const float* depth_img, int rows, int cols, size_t pitch, float* right_points,
+                                 float* depth, int* n_matches);
+
 /* Camera, grid and frame views used by the projection searches. */
 typedef struct snk_camera
 {

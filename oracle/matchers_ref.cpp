@@ -139,6 +139,48 @@ int stereo_match(const snk_stereo_params* p, const snk_keypoint_f64* left, const
     return num_matches;
 }
 
+// Snake/Preprocess/Preprocess.cpp:79-120 with distortNormalizedPoint of
+// External/saiga/src/saiga/vision/cameraModel/Distortion.h:128-170
+int stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f64* kp, int n, const float* depth_img, int rows,
+                     int cols, size_t pitch, float* right_points, float* depth)
+{
+    int num = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        const double x = (kp[i].x - p->cx) / p->fx, y = (kp[i].y - p->cy) / p->fy;
+        const double k1 = p->dist[0], k2 = p->dist[1], k3 = p->dist[2], k4 = p->dist[3], k5 = p->dist[4], k6 = p->dist[5];
+        const double p1 = p->dist[6], p2 = p->dist[7];
+        const double x2 = x * x, y2 = y * y;
+        const double r2 = x2 + y2, _2xy = 2.0 * x * y;
+        const double r4 = r2 * r2;
+        const double r6 = r4 * r2;
+        const double radial_u  = 1.0 + k1 * r2 + k2 * r4 + k3 * r6;
+        const double radial_v  = 1.0 + k4 * r2 + k5 * r4 + k6 * r6;
+        const double radial_iv = 1.0 / radial_v;
+        const double radial    = radial_u * radial_iv;
+        const double tx = p1 * _2xy + p2 * (r2 + 2.0 * x2);
+        const double ty = p1 * (r2 + 2.0 * y2) + p2 * _2xy;
+        double xd = x * radial + tx, yd = y * radial + ty;
+        if (r2 > 100000.0 * 100000.0) xd = yd = 100000;
+        const double u = p->dfx * xd + p->ds * yd + p->dcx, v = p->dfy * yd + p->dcy;
+        const int px = (int)(u + 0.5), py = (int)(v + 0.5);
+        float d = 0.f;  // the reference asserts the lookup is inside the image; outside counts as no measurement here
+        if (px >= 0 && px < cols && py >= 0 && py < rows) d = *(const float*)((const char*)depth_img + (size_t)py * pitch + (size_t)px * 4);
+        if (d > 0)
+        {
+            depth[i]        = d;
+            right_points[i] = (float)(kp[i].x - p->bf / d);
+            ++num;
+        }
+        else
+        {
+            depth[i]        = -1;
+            right_points[i] = -1;
+        }
+    }
+    return num;
+}
+
 // ---------------------------------------------------------------------------------------------
 // projection geometry helpers
 // ---------------------------------------------------------------------------------------------

@@ -10,6 +10,8 @@ int filter_matches(const snk_knn2* knn2, int n, int threshold, float ratio, int3
 int stereo_match(const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
                  const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points, float* depth,
                  long long* pair_ops);
+int stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f64* kp, int n, const float* depth_img, int rows,
+                     int cols, size_t pitch, float* right_points, float* depth);
 int search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
                            const snk_scale_pyramid* sp, float th, float ratio, int32_t* kp_to_point_out,
                            int32_t* best_idx, int32_t* best_dist, uint8_t* visible, long long* pair_ops);

@@ -142,6 +142,11 @@ ORC_API int orc_stereo_match(const snk_stereo_params* p, const snk_keypoint_f64*
 {
     return stereo_match(p, l, dl, nl, r, dr, nr, rp, depth, ops);
 }
+ORC_API int orc_stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f64* kp, int n, const float* img, int rows,
+                                 int cols, size_t pitch, float* rp, float* depth)
+{
+    return stereo_from_rgbd(p, kp, n, img, rows, cols, pitch, rp, depth);
+}
 ORC_API int orc_search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
                                        const snk_scale_pyramid* sp, float th, float ratio, int32_t* k2p, int32_t* bi,
                                        int32_t* bd, uint8_t* vis, long long* ops)

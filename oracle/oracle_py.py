@@ -244,3 +244,12 @@ def match_bow(d1, d2, fv1, fv2, valid1, valid2, th, ratio):
     m = lib().orc_match_bow(_p(d1), len(d1), _p(d2), len(d2), C.byref(fv1), C.byref(fv2), _p(valid1), _p(valid2), th,
                             C.c_float(ratio), _p(m12), C.byref(ops))
     return m, m12[:len(d1)], ops.value
+
+
+def stereo_from_rgbd(params, kp_un, depth_img):
+    kp_un = np.ascontiguousarray(kp_un, KP64)
+    rp = np.zeros(max(len(kp_un), 1), np.float32)
+    dp = np.zeros(max(len(kp_un), 1), np.float32)
+    n = lib().orc_stereo_from_rgbd(C.byref(params), _p(kp_un), len(kp_un), _p(depth_img), depth_img.shape[0],
+                                   depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp))
+    return n, rp[:len(kp_un)], dp[:len(kp_un)]

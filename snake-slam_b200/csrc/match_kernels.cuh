@@ -220,6 +220,56 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
 }
 
 // --------------------------------------------------------------------------------------------------------------
+// Preprocess::ComputeStereoFromRGBD (Snake/Preprocess/Preprocess.cpp:79-120), one thread per keypoint, double math in
+// the reference's operation order (library is built with -fmad=false)
+// --------------------------------------------------------------------------------------------------------------
+__global__ void k_stereo_rgbd(snk_rgbd_params p, const snk_keypoint_f64* __restrict__ kp, int n,
+                              const float* __restrict__ depth_img, int rows, int cols, int pitch_f,
+                              float* __restrict__ right_points, float* __restrict__ depth, int* __restrict__ n_matches)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int hit     = 0;
+    if (i < n)
+    {
+        // K.unproject2
+        const double x = (kp[i].x - p.cx) / p.fx, y = (kp[i].y - p.cy) / p.fy;
+        // distortNormalizedPoint (Distortion.h:128-170)
+        const double k1 = p.dist[0], k2 = p.dist[1], k3 = p.dist[2], k4 = p.dist[3], k5 = p.dist[4], k6 = p.dist[5];
+        const double p1 = p.dist[6], p2 = p.dist[7];
+        const double x2 = x * x, y2 = y * y;
+        const double r2 = x2 + y2, _2xy = 2.0 * x * y;
+        const double r4 = r2 * r2;
+        const double r6 = r4 * r2;
+        const double radial_u  = 1.0 + k1 * r2 + k2 * r4 + k3 * r6;
+        const double radial_v  = 1.0 + k4 * r2 + k5 * r4 + k6 * r6;
+        const double radial_iv = 1.0 / radial_v;
+        const double radial    = radial_u * radial_iv;
+        const double tx = p1 * _2xy + p2 * (r2 + 2.0 * x2);
+        const double ty = p1 * (r2 + 2.0 * y2) + p2 * _2xy;
+        double xd = x * radial + tx, yd = y * radial + ty;
+        if (r2 > 100000.0 * 100000.0) xd = yd = 100000;
+        // depthModel.K.normalizedToImage
+        const double u = p.dfx * xd + p.ds * yd + p.dcx, v = p.dfy * yd + p.dcy;
+        const int px = (int)(u + 0.5), py = (int)(v + 0.5);
+        float d = 0.f;
+        if (px >= 0 && px < cols && py >= 0 && py < rows) d = depth_img[(size_t)py * pitch_f + px];
+        if (d > 0)
+        {
+            depth[i]        = d;
+            right_points[i] = (float)(kp[i].x - p.bf / (double)d);
+            hit             = 1;
+        }
+        else
+        {
+            depth[i]        = -1.f;
+            right_points[i] = -1.f;
+        }
+    }
+    hit = warp_sum(hit);
+    if ((threadIdx.x & 31) == 0 && hit) atomicAdd(n_matches, hit);
+}
+
+// --------------------------------------------------------------------------------------------------------------
 // popc issue-rate probe: 256-bit distances between register-resident operands (denominator of the matcher roofline)
 // --------------------------------------------------------------------------------------------------------------
 __global__ void k_popc_peak(int iters, unsigned seed, int* __restrict__ sink)

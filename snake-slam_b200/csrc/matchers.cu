@@ -252,6 +252,38 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     return SNK_OK;
 }
 
+int snk_stereo_from_rgbd(snk_ctx* c, const snk_rgbd_params* p, const snk_keypoint_f64* kp_un, int n,
+                         const float* depth_img, int rows, int cols, size_t pitch, float* right_points, float* depth,
+                         int* n_matches)
+{
+    SNK_REQUIRE(c && p && n_matches && n >= 0, "bad argument");
+    SNK_REQUIRE(n == 0 || (kp_un && right_points && depth), "null keypoint arrays");
+    SNK_REQUIRE(depth_img && rows > 0 && cols > 0 && pitch >= (size_t)cols * 4 && pitch % 4 == 0, "bad depth image");
+    *n_matches = 0;
+    if (n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    const size_t img_floats = (size_t)rows * cols;
+    int rc = ctx_reserve(c, padded<snk_keypoint_f64>(n) + padded<float>(img_floats) + 2 * padded<float>(n) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    auto* dk  = cv.take<snk_keypoint_f64>(n);
+    float* di = cv.take<float>(img_floats);
+    float* dr = cv.take<float>(n);
+    float* dd = cv.take<float>(n);
+    int* dn   = cv.take<int>(4);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(dk, kp_un, sizeof(snk_keypoint_f64) * (size_t)n, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpy2DAsync(di, (size_t)cols * 4, depth_img, pitch, (size_t)cols * 4, rows, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 16, st));
+    k_stereo_rgbd<<<(n + 127) / 128, 128, 0, st>>>(*p, dk, n, di, rows, cols, cols, dr, dd, dn);
+    SNK_CUDA(cudaMemcpyAsync(right_points, dr, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(depth, dd, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
 int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s)
 {
     SNK_REQUIRE(c && pair_ops_per_s, "bad argument");

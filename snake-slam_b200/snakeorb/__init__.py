@@ -36,6 +36,12 @@ class StereoParams(C.Structure):
     _fields_ = [("bf", C.c_double), ("relaxed", C.c_int32), ("nlevels", C.c_int32), ("scale", C.c_double * 16)]
 
 
+class RgbdParams(C.Structure):
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("dfx", C.c_double),
+                ("dfy", C.c_double), ("dcx", C.c_double), ("dcy", C.c_double), ("ds", C.c_double),
+                ("dist", C.c_double * 8), ("bf", C.c_double)]
+
+
 class Camera(C.Structure):
     _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("s", C.c_double),
                 ("bf", C.c_double)]
@@ -248,6 +254,17 @@ class Context:
         _check(lib().snk_stereo_match(self.c, C.byref(params), _p(left), _p(dl), len(left), _p(right), _p(dr),
                                       len(right), _p(rp), _p(dp), C.byref(n)))
         return n.value, rp[:len(left)], dp[:len(left)]
+
+    def ComputeStereoFromRGBD(self, params, kp_un, depth_img):
+        """Preprocess::ComputeStereoFromRGBD -> (matches, right_points, depth)."""
+        kp_un = np.ascontiguousarray(kp_un, KP64)
+        assert depth_img.dtype == np.float32 and depth_img.ndim == 2 and depth_img.strides[1] == 4
+        rp = np.zeros(max(len(kp_un), 1), np.float32)
+        dp = np.zeros(max(len(kp_un), 1), np.float32)
+        n = C.c_int()
+        _check(lib().snk_stereo_from_rgbd(self.c, C.byref(params), _p(kp_un), len(kp_un), _p(depth_img), depth_img.shape[0],
+                                          depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp), C.byref(n)))
+        return n.value, rp[:len(kp_un)], dp[:len(kp_un)]
 
     def stereo_orb_device(self, orb, n_pairs, params, rp_ptr, depth_ptr, nm_ptr):
         _check(lib().snk_stereo_match_orb_device(self.c, orb.h, n_pairs, C.byref(params), C.c_void_p(rp_ptr),

@@ -178,6 +178,34 @@ def test_match_bow(so, ctx, oracle, feats, seed):
     assert m == m2 and np.array_equal(m12, m122) and m > 20 and ops > 1000
 
 
+def test_stereo_from_rgbd_c4(so, ctx, oracle):
+    """Config C4: TUM-shaped RGB-D frame, depth planes 0.5-8 m with 5 % holes, depth camera with distortion."""
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(4)
+    img = S.image(4000, 640, 480)
+    k, d = oracle.Extractor(1000, 1.2, 8, 20, 7, 2).detect(img)
+    depth = np.empty((480, 640), np.float32)
+    for r0 in range(0, 480, 60):
+        for c0 in range(0, 640, 80):
+            depth[r0:r0 + 60, c0:c0 + 80] = rng.uniform(0.5, 8.0)
+    depth[rng.random(depth.shape) < 0.05] = 0.0
+    wide = np.zeros((480, 650), np.float32)  # pitch larger than the row
+    wide[:, :640] = depth
+    p = so.RgbdParams()
+    p.fx, p.fy, p.cx, p.cy = 535.4, 539.2, 320.1, 247.6
+    p.dfx, p.dfy, p.dcx, p.dcy, p.ds = 535.4, 539.2, 320.1, 247.6, 0.0
+    for i, v in enumerate((0.2312, -0.7849, 0.9172, 0.0, 0.0, 0.0, -0.0033, -0.0001)):
+        p.dist[i] = v
+    p.bf = 40.0
+    kp = so.kp32_to_kp64(k)
+    for view in (depth, wide[:, :640]):
+        n, rp, dp = ctx.ComputeStereoFromRGBD(p, kp, view)
+        n2, rp2, dp2 = oracle.stereo_from_rgbd(p, oracle.kp32_to_kp64(k), view)
+        assert n == n2 and n > 800 and n < len(k)
+        assert rp.tobytes() == rp2.tobytes() and dp.tobytes() == dp2.tobytes()
+
+
 def test_hamming_peak_probe(so, ctx):
     v = ctx.hamming_peak()
     assert 1e10 < v < 5e12

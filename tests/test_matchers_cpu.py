@@ -96,3 +96,27 @@ def test_stereo_oracle_properties(oracle):
     n2, rp2, _, _ = oracle.stereo_match(oracle.stereo_params(47.9, False, scales), oracle.kp32_to_kp64(kl), dl,
                                         oracle.kp32_to_kp64(kr), dr)
     assert n2 <= n and np.all((rp2 > -1000) <= ok)
+
+
+def test_rgbd_stereo_oracle_properties(oracle):
+    """With identical colour/depth intrinsics and no distortion the lookup is the nearest pixel of the keypoint."""
+    import snakeorb as so
+
+    rng = np.random.default_rng(8)
+    depth = rng.uniform(0.5, 8.0, (120, 160)).astype(np.float32)
+    depth[rng.random(depth.shape) < 0.1] = 0
+    kp = np.zeros(300, oracle.KP64)
+    kp["x"], kp["y"] = rng.uniform(0, 159.4, 300), rng.uniform(0, 119.4, 300)
+    p = so.RgbdParams()
+    p.fx = p.dfx = 200.0
+    p.fy = p.dfy = 210.0
+    p.cx = p.dcx = 80.0
+    p.cy = p.dcy = 60.0
+    p.bf = 40.0
+    n, rp, dp = oracle.stereo_from_rgbd(p, kp, depth)
+    px, py = (kp["x"] + 0.5).astype(int), (kp["y"] + 0.5).astype(int)
+    want = depth[py, px]
+    ok = want > 0
+    assert n == ok.sum()
+    assert np.array_equal(dp[ok], want[ok]) and np.all(dp[~ok] == -1) and np.all(rp[~ok] == -1)
+    assert np.allclose(rp[ok], kp["x"][ok] - 40.0 / want[ok], rtol=1e-6, atol=1e-4)
