@@ -307,6 +307,15 @@ typedef struct snk_scale_pyramid
     double scale[16];
 } snk_scale_pyramid;
 
+/* Preprocess::computeFeatureGrid (Snake/Preprocess/Preprocess.cpp:244-266) == FeatureGrid2::create
+ * (saiga/vision/util/FeatureGrid2.h:130-192): counting sort of the undistorted keypoints into the 20-px cells of
+ * `bounds` (its `cells` member is ignored). permutation[i] = new index of keypoint i (keypoints outside the bounds
+ * go to the end, input order is kept inside a cell); cells_out[2*(row*cols+col)] = (begin, end) of the cell in the
+ * permuted arrays. The caller applies the permutation to its keypoint / descriptor arrays as the reference does
+ * (Preprocess.cpp:254-260). n <= 8192. */
+SNK_API int snk_feature_grid(snk_ctx* c, const snk_grid_view* bounds, const snk_keypoint_f64* kp_un, int n,
+                             int32_t* permutation, int32_t* cells_out);
+
 /* SnakeORBMatcher::SearchByProjection2 (Snake/Tracking/SnakeORBMatcher.cpp:365-526).
  * In/out: points[i].valid is cleared where the reference clears lmp.valid; visible[i] = 1 where it calls
  * IncreaseVisible(). Out: kp_to_point_out[n] = frame.kp_to_point with new assignments (point ids) added,
@@ -350,6 +359,15 @@ typedef struct snk_featvec_view
 SNK_API int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, int n2,
                           const snk_featvec_view* fv1, const snk_featvec_view* fv2, const uint8_t* valid1,
                           const uint8_t* valid2, int th, float ratio, int32_t* match12, int* n_matches);
+
+/* The reference's feature cache (Snake/Preprocess/FeatureDetector.cpp:97-111 read, :134-139 write; settings
+ * fd_bufferToFile), a saiga BinaryFile dump (saiga/core/util/BinaryFile.h:30-78): u64 n, n x KeyPoint<double>
+ * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of
+ * saiga/data/vision/{0,50}.features. */
+SNK_API int snk_features_write(const char* path, const snk_keypoint_f64* kps, const uint64_t* desc, int n);
+SNK_API int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64_t* desc, int capacity, int* n_out);
+/* KeyPoint<float>::cast<double>() as FeatureDetector.cpp:129-132 applies it to the extractor's output. */
+SNK_API int snk_keypoints_widen(const snk_keypoint_f32* in, int n, snk_keypoint_f64* out);
 
 /* Register-resident popc microbenchmark: measured 256-bit Hamming distances per second of this device, the
  * denominator of the matcher roofline. */

@@ -265,6 +265,35 @@ inline void project(const snk_camera* K, const V3& X, double& u, double& v)
 }
 }  // namespace
 
+// External/saiga/src/saiga/vision/util/FeatureGrid2.h:130-192 (FeatureGrid2::create) with the cell lookup of :37-52
+void feature_grid(const snk_grid_view* b, const snk_keypoint_f64* kps, int n, int32_t* permutation, int32_t* cells)
+{
+    const int ncell = b->rows * b->cols;
+    std::vector<int> cid(n), first(ncell, 0), second(ncell, 0);
+    for (int i = 0; i < n; ++i)
+    {
+        if (in_image(*b, kps[i].x, kps[i].y))
+        {
+            const int cx = iFloorD((kps[i].x - b->bmin_x) * b->cell_size_inv_x);
+            const int cy = iFloorD((kps[i].y - b->bmin_y) * b->cell_size_inv_y);
+            cid[i]       = cy * b->cols + cx;
+            first[cid[i]]++;
+        }
+        else
+            cid[i] = -1;
+    }
+    int total = 0;
+    for (int c = 0; c < ncell; ++c)
+    {
+        int count = first[c];
+        first[c] = second[c] = total;
+        total += count;
+    }
+    for (int i = 0; i < n; ++i)
+        permutation[i] = (cid[i] == -1) ? total++ : second[cid[i]]++;
+    for (int c = 0; c < ncell; ++c) cells[2 * c] = first[c], cells[2 * c + 1] = second[c];
+}
+
 // Snake/Tracking/SnakeORBMatcher.cpp:365-526
 int search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
                            const snk_scale_pyramid* sp, float th, float ratio, int32_t* kp_to_point_out,

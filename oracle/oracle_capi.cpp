@@ -147,6 +147,10 @@ ORC_API int orc_stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f6
 {
     return stereo_from_rgbd(p, kp, n, img, rows, cols, pitch, rp, depth);
 }
+ORC_API void orc_feature_grid(const snk_grid_view* b, const snk_keypoint_f64* kps, int n, int32_t* perm, int32_t* cells)
+{
+    feature_grid(b, kps, n, perm, cells);
+}
 ORC_API int orc_search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
                                        const snk_scale_pyramid* sp, float th, float ratio, int32_t* k2p, int32_t* bi,
                                        int32_t* bd, uint8_t* vis, long long* ops)

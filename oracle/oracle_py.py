@@ -253,3 +253,11 @@ def stereo_from_rgbd(params, kp_un, depth_img):
     n = lib().orc_stereo_from_rgbd(C.byref(params), _p(kp_un), len(kp_un), _p(depth_img), depth_img.shape[0],
                                    depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp))
     return n, rp[:len(kp_un)], dp[:len(kp_un)]
+
+
+def feature_grid(bounds, kp_un):
+    kp_un = np.ascontiguousarray(kp_un, KP64)
+    perm = np.zeros(max(len(kp_un), 1), np.int32)
+    cells = np.zeros((bounds.rows * bounds.cols, 2), np.int32)
+    lib().orc_feature_grid(C.byref(bounds), _p(kp_un), len(kp_un), _p(perm), _p(cells))
+    return perm[:len(kp_un)], cells

@@ -3,6 +3,7 @@
 #include "project_kernels.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <mutex>
 #include <vector>
 
@@ -314,6 +315,58 @@ int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s)
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// Feature cache files (host only)
+// ------------------------------------------------------------------------------------------------------------------
+extern "C" int snk_features_write(const char* path, const snk_keypoint_f64* kps, const uint64_t* desc, int n)
+{
+    SNK_REQUIRE(path && n >= 0 && (n == 0 || (kps && desc)), "bad argument");
+    FILE* f = std::fopen(path, "wb");
+    SNK_REQUIRE(f, "cannot open %s for writing", path);
+    const uint64_t cnt = (uint64_t)n;  // BinaryFile::write(vector): size_t count, then the raw elements
+    bool ok = std::fwrite(&cnt, 8, 1, f) == 1 && (n == 0 || std::fwrite(kps, sizeof(snk_keypoint_f64), n, f) == (size_t)n) &&
+              std::fwrite(&cnt, 8, 1, f) == 1 && (n == 0 || std::fwrite(desc, 32, n, f) == (size_t)n);
+    ok = (std::fclose(f) == 0) && ok;
+    SNK_REQUIRE(ok, "short write to %s", path);
+    return SNK_OK;
+}
+
+extern "C" int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64_t* desc, int capacity, int* n_out)
+{
+    SNK_REQUIRE(path && n_out && capacity >= 0, "bad argument");
+    FILE* f = std::fopen(path, "rb");
+    SNK_REQUIRE(f, "cannot open %s", path);
+    uint64_t nk = 0, nd = 0;
+    int rc = SNK_OK;
+    if (std::fread(&nk, 8, 1, f) != 1)
+        rc = SNK_ERR_INVALID;
+    else if (nk > (uint64_t)capacity)
+        rc = SNK_ERR_CAPACITY;
+    else if (nk && std::fread(kps, sizeof(snk_keypoint_f64), nk, f) != nk)
+        rc = SNK_ERR_INVALID;
+    else if (std::fread(&nd, 8, 1, f) != 1 || nd != nk)
+        rc = SNK_ERR_INVALID;
+    else if (nd && std::fread(desc, 32, nd, f) != nd)
+        rc = SNK_ERR_INVALID;
+    std::fclose(f);
+    if (rc == SNK_ERR_CAPACITY) set_error("%s holds %llu features, capacity is %d", path, (unsigned long long)nk, capacity);
+    if (rc == SNK_ERR_INVALID) set_error("%s is not a feature cache file", path);
+    if (rc) return rc;
+    *n_out = (int)nk;
+    return SNK_OK;
+}
+
+extern "C" int snk_keypoints_widen(const snk_keypoint_f32* in, int n, snk_keypoint_f64* out)
+{
+    SNK_REQUIRE(n >= 0 && (n == 0 || (in && out)), "bad argument");
+    for (int i = 0; i < n; ++i)
+    {
+        out[i].x = in[i].x, out[i].y = in[i].y, out[i].size = in[i].size, out[i].angle = in[i].angle;
+        out[i].response = in[i].response, out[i].octave = in[i].octave, out[i]._pad = 0;
+    }
+    return SNK_OK;
+}
 
 // ------------------------------------------------------------------------------------------------------------------
 // kNN-2 matching for callers that must not allocate device memory

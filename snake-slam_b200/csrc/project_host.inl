@@ -193,6 +193,36 @@ int snk_search_projection_frame_to_kf(snk_ctx* c, const snk_frame_view* frame, c
     return SNK_OK;
 }
 
+int snk_feature_grid(snk_ctx* c, const snk_grid_view* b, const snk_keypoint_f64* kp_un, int n, int32_t* permutation,
+                     int32_t* cells_out)
+{
+    SNK_REQUIRE(c && b && cells_out && n >= 0 && (n == 0 || (kp_un && permutation)), "bad argument");
+    SNK_REQUIRE(b->rows >= 1 && b->cols >= 1 && (long long)b->rows * b->cols < (1 << 18), "bad grid size");
+    SNK_REQUIRE(n <= 8192, "snk_feature_grid handles at most 8192 keypoints");
+    const int ncell = b->rows * b->cols;
+    SNK_CUDA(cudaSetDevice(c->device));
+    const size_t nn = std::max(n, 1);
+    int rc = ctx_reserve(c, padded<snk_keypoint_f64>(nn) + padded<int>(nn) + padded<int>(2 * (size_t)ncell));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    auto* dk = cv.take<snk_keypoint_f64>(nn);
+    int* dp  = cv.take<int>(nn);
+    int* dc  = cv.take<int>(2 * (size_t)ncell);
+    cudaStream_t st = c->stream;
+    if (n) SNK_CUDA(cudaMemcpyAsync(dk, kp_un, sizeof(snk_keypoint_f64) * (size_t)n, cudaMemcpyHostToDevice, st));
+    FrameDev f{};
+    f.n = n, f.kp_un = dk;
+    f.bmin_x = b->bmin_x, f.bmin_y = b->bmin_y, f.bmax_x = b->bmax_x, f.bmax_y = b->bmax_y;
+    f.inv_x = b->cell_size_inv_x, f.inv_y = b->cell_size_inv_y, f.rows = b->rows, f.cols = b->cols;
+    int np2 = 1;
+    while (np2 < n) np2 <<= 1;
+    k_feature_grid<<<1, 256, (size_t)np2 * 4, st>>>(f, n, np2, dp, dc);
+    if (n) SNK_CUDA(cudaMemcpyAsync(permutation, dp, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(cells_out, dc, 8 * (size_t)ncell, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    return SNK_OK;
+}
+
 int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_featvec_view* fv1,
                   const snk_featvec_view* fv2, const uint8_t* valid1, const uint8_t* valid2, int th, float ratio,
                   int32_t* match12, int* n_matches)

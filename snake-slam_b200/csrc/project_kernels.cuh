@@ -377,6 +377,74 @@ __global__ void k_proj_frame_to_kf(FrameDev f, const snk_point_kf* __restrict__ 
     if (lane == 0) *n_matches = matches;
 }
 
+// FeatureGrid2::create (saiga/vision/util/FeatureGrid2.h:130-192) for one frame: the stable counting sort is done as
+// a bitonic sort of (cell << 13 | index) keys in shared memory; cell ranges come from binary searches on the sorted keys
+// (an empty cell gets begin == end == number of keypoints in earlier cells, exactly the reference's running prefix).
+__global__ void __launch_bounds__(256) k_feature_grid(FrameDev f, int n, int np2, int* __restrict__ permutation,
+                                                      int* __restrict__ cells_out)
+{
+    extern __shared__ uint32_t gkeys[];
+    const int tid = threadIdx.x, ncell = f.rows * f.cols;
+    for (int i = tid; i < np2; i += 256)
+    {
+        uint32_t k = 0xffffffffu;
+        if (i < n)
+        {
+            const double x = f.kp_un[i].x, y = f.kp_un[i].y;
+            int cell = ncell;  // outside the bounds: sorted behind every cell, in input order
+            if (in_image(f, x, y))
+            {
+                // LogicalCell: iFloor((p - bmin) * cellSizeInv); inside the bounds it is a valid cell
+                const int cx = ifloor_d((x - f.bmin_x) * f.inv_x), cy = ifloor_d((y - f.bmin_y) * f.inv_y);
+                cell = min(max(cy, 0), f.rows - 1) * f.cols + min(max(cx, 0), f.cols - 1);
+            }
+            k = ((uint32_t)cell << 13) | (uint32_t)i;
+        }
+        gkeys[i] = k;
+    }
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1)
+        {
+            for (int i = tid; i < np2; i += 256)
+            {
+                const int ixj = i ^ j;
+                if (ixj > i)
+                {
+                    const uint32_t a = gkeys[i], b = gkeys[ixj];
+                    if ((a > b) == ((i & k) == 0))
+                    {
+                        gkeys[i]   = b;
+                        gkeys[ixj] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    for (int p = tid; p < n; p += 256) permutation[gkeys[p] & 8191u] = p;
+    for (int c = tid; c < ncell; c += 256)
+    {
+        int be[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+        {
+            const uint32_t target = (uint32_t)(c + e) << 13;
+            int lo = 0, hi = n;
+            while (lo < hi)
+            {
+                const int mid = (lo + hi) >> 1;
+                if (gkeys[mid] < target)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            be[e] = lo;
+        }
+        cells_out[2 * c]     = be[0];
+        cells_out[2 * c + 1] = be[1];
+    }
+}
+
 // LoopORBmatcher::MatchBoW: one warp per vocabulary node of keyframe 1. Features live in exactly one node, so nodes
 // are independent; inside a node the idx1 loop is sequential (greedy vbMatched2), the idx2 scan is split over lanes.
 struct FeatVecDev

@@ -309,6 +309,14 @@ class Context:
                                    _p(valid2), th, C.c_float(ratio), _p(m12), C.byref(m)))
         return m.value, m12[:len(d1)]
 
+    def computeFeatureGrid(self, bounds, kp_un):
+        """FeatureGrid2::create -> (permutation, cells[rows*cols, 2]); `bounds` is a GridView (cells ignored)."""
+        kp_un = np.ascontiguousarray(kp_un, KP64)
+        perm = np.zeros(max(len(kp_un), 1), np.int32)
+        cells = np.zeros((bounds.rows * bounds.cols, 2), np.int32)
+        _check(lib().snk_feature_grid(self.c, C.byref(bounds), _p(kp_un), len(kp_un), _p(perm), _p(cells)))
+        return perm[:len(kp_un)], cells
+
     def hamming_peak(self):
         v = C.c_double()
         _check(lib().snk_hamming_peak_selftest(self.c, C.byref(v)))
@@ -320,3 +328,24 @@ def kp32_to_kp64(k):
     for f in ("x", "y", "size", "angle", "response", "octave"):
         o[f] = k[f]
     return o
+
+
+def features_write(path, kps64, desc):
+    kps64 = np.ascontiguousarray(kps64, KP64)
+    desc = np.ascontiguousarray(desc, np.uint64).reshape(-1, 4)
+    _check(lib().snk_features_write(path.encode(), _p(kps64), _p(desc), len(kps64)))
+
+
+def features_read(path, capacity=100000):
+    kps = np.zeros(capacity, KP64)
+    desc = np.zeros((capacity, 4), np.uint64)
+    n = C.c_int()
+    _check(lib().snk_features_read(path.encode(), _p(kps), _p(desc), capacity, C.byref(n)))
+    return kps[:n.value].copy(), desc[:n.value].copy()
+
+
+def keypoints_widen(k32):
+    k32 = np.ascontiguousarray(k32, KP32)
+    out = np.zeros(max(len(k32), 1), KP64)
+    _check(lib().snk_keypoints_widen(_p(k32), len(k32), _p(out)))
+    return out[:len(k32)]

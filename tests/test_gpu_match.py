@@ -206,6 +206,23 @@ def test_stereo_from_rgbd_c4(so, ctx, oracle):
         assert rp.tobytes() == rp2.tobytes() and dp.tobytes() == dp2.tobytes()
 
 
+def test_feature_grid(so, ctx, oracle, feats):
+    """Preprocess::computeFeatureGrid on the device == FeatureGrid2::create (oracle restatement, itself checked
+    against the reference's compiled class in tests/test_matchers_cpu.py)."""
+    rng = np.random.default_rng(6)
+    kl, dl = feats["l"]
+    kp = so.kp32_to_kp64(kl)
+    kp["x"] += rng.normal(0, 0.3, len(kp))  # undistorted coordinates are not integers
+    kp["x"][:7] = [-5.0, 1300.0, 3.0, -0.05, 1240.09, 1240.11, 620.0]  # outside / on the border of the bounds
+    kp["y"][:7] = [10.0, 10.0, -2.0, 0.0, 375.09, 100.0, 375.2]
+    frame = M.make_frame(kl[:10], dl[:10], 1241, 376, rng, (0, 0, 0, 1), (0, 0, 0))
+    for sub in (kp, kp[:1], kp[:0], kp[:257]):
+        perm, cells = ctx.computeFeatureGrid(frame.view.grid, sub)
+        perm2, cells2 = oracle.feature_grid(frame.view.grid, sub)
+        assert np.array_equal(perm, perm2) and np.array_equal(cells, cells2)
+        assert sorted(perm) == list(range(len(sub)))
+
+
 def test_hamming_peak_probe(so, ctx):
     v = ctx.hamming_peak()
     assert 1e10 < v < 5e12

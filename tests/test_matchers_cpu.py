@@ -120,3 +120,53 @@ def test_rgbd_stereo_oracle_properties(oracle):
     assert n == ok.sum()
     assert np.array_equal(dp[ok], want[ok]) and np.all(dp[~ok] == -1) and np.all(rp[~ok] == -1)
     assert np.allclose(rp[ok], kp["x"][ok] - 40.0 / want[ok], rtol=1e-6, atol=1e-4)
+
+
+def test_feature_grid_oracle_vs_reference_and_numpy(oracle, refso):
+    import snakeorb as so
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(12)
+    kp = np.zeros(700, S.KP64)
+    kp["x"], kp["y"] = rng.uniform(-8, 765, 700), rng.uniform(-8, 490, 700)
+    bounds, cells_np, perm_np = S.feature_grid(kp, 752, 480)
+    g = so.GridView()
+    g.bmin_x, g.bmin_y, g.bmax_x, g.bmax_y = bounds["bmin_x"], bounds["bmin_y"], bounds["bmax_x"], bounds["bmax_y"]
+    g.cell_size_inv_x = g.cell_size_inv_y = bounds["inv"]
+    g.rows, g.cols = bounds["rows"], bounds["cols"]
+    perm, cells = oracle.feature_grid(g, kp)
+    assert np.array_equal(perm, perm_np) and np.array_equal(cells, cells_np)
+    perm2 = np.zeros(700, np.int32)
+    cells2 = np.zeros((g.rows * g.cols, 2), np.int32)
+    refso.ref_feature_grid(C.c_double(g.bmin_x), C.c_double(g.bmin_y), C.c_double(g.bmax_x), C.c_double(g.bmax_y), g.rows,
+                           g.cols, _p(kp), 700, _p(perm2), _p(cells2))
+    assert np.array_equal(perm, perm2) and np.array_equal(cells, cells2)
+
+
+def test_features_cache_roundtrip_and_reference_fixture(tmp_path):
+    """snk_features_read / write against the reference's own data/vision/*.features (when mounted) and a round trip."""
+    import snakeorb as so
+
+    rng = np.random.default_rng(3)
+    k32 = np.zeros(50, so.KP32)
+    for f in ("x", "y", "size", "angle", "response"):
+        k32[f] = rng.uniform(0, 500, 50).astype(np.float32)
+    k32["octave"] = rng.integers(0, 8, 50)
+    k64 = so.keypoints_widen(k32)
+    assert all(np.array_equal(k64[f], k32[f].astype(np.float64)) for f in ("x", "y", "size", "angle", "response"))
+    assert np.array_equal(k64["octave"], k32["octave"])
+    d = rng.integers(0, 2**63, (50, 4)).astype(np.uint64)
+    path = str(tmp_path / "7.features")
+    so.features_write(path, k64, d)
+    assert os.path.getsize(path) == 8 + 48 * 50 + 8 + 32 * 50
+    k2, d2 = so.features_read(path)
+    assert k2.tobytes() == k64.tobytes() and np.array_equal(d2, d)
+    with pytest.raises(so.SnakeOrbError):
+        so.features_read(path, capacity=10)
+    ref = "/root/reference/External/saiga/data/vision/0.features"
+    if os.path.exists(ref):
+        k, dd = so.features_read(ref)
+        assert len(k) == 1007 and k["y"].min() >= 19 and set(np.unique(k["octave"])) <= set(range(8))
+        out = str(tmp_path / "copy.features")
+        so.features_write(out, k, dd)
+        assert open(out, "rb").read() == open(ref, "rb").read()  # byte-identical re-serialisation
