@@ -379,11 +379,9 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
     for (int i = 0; i < 512; ++i)  // entry j*32 + lane holds point 16*lane + j
         pt[(i & 15) * 32 + (i >> 4)] = make_float2((float)kOrbPattern[2 * i], (float)kOrbPattern[2 * i + 1]);
     if (cudaMalloc(&h->d_pattern_t, sizeof(pt)) != cudaSuccess ||
-        cudaMemcpy(h->d_pattern_t, pt, sizeof(pt), cudaMemcpyHostToDevice) != cudaSuccess ||
-        cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)) != cudaSuccess ||
-        cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024) != cudaSuccess)
+        cudaMemcpy(h->d_pattern_t, pt, sizeof(pt), cudaMemcpyHostToDevice) != cudaSuccess)
     {
-        set_error("constant upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+        set_error("pattern upload failed: %s", cudaGetErrorString(cudaGetLastError()));
         snk_orb_destroy(h);
         return SNK_ERR_CUDA;
     }

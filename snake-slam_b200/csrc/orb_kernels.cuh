@@ -898,8 +898,6 @@ __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restric
 // --------------------------------------------------------------------------------------------------------------
 // Orientation + rBRIEF + output record. One warp per selected keypoint.
 // --------------------------------------------------------------------------------------------------------------
-__constant__ signed char c_pattern[1024];  // 512 points (x,y) — include/snakeorb_pattern.h
-__constant__ int c_umax[16];               // ORBPattern::AngleUmax()
 
 constexpr int DS_WARPS = 8;
 constexpr int DS_KP_PER_WARP = 8;  // keypoints per warp: the CTA prologue (pattern, level prefix) is paid once per 64

@@ -146,3 +146,24 @@ def test_no_cpu_fallback_symbols(so):
 
     out = subprocess.run(["nm", "-D", "--defined-only", so.LIB_PATH], capture_output=True, text=True).stdout
     assert "orc_" not in out and "cvlite" not in out
+
+
+def test_async_fetch_equals_sync_fetch(so, oracle):
+    """snk_orb_enqueue + snk_orb_fetch_async (no host wait) deliver the same records as the blocking fetch."""
+    import ctypes as C
+
+    from snakeorb import synthetic as S
+
+    imgs = np.stack([S.image(40 + i, 640, 480) for i in range(3)])
+    ex = so.ORBExtractor(1000, 1.2, 8, 20, 7, max_batch=3)
+    want = ex.DetectBatch(imgs)
+    kps = np.zeros((3, ex.cap), so.KP32)
+    desc = np.zeros((3, ex.cap, 4), np.uint64)
+    cnt = np.zeros(3, np.int32)
+    ex.enqueue_ptr(imgs.ctypes.data, 3, 480, 640, 640, 640 * 480, False)
+    so._check(so.lib().snk_orb_fetch_async(ex.h, C.c_void_p(kps.ctypes.data), C.c_void_p(desc.ctypes.data), ex.cap,
+                                           C.c_void_p(cnt.ctypes.data)))
+    assert C.CDLL("libcudart.so").cudaDeviceSynchronize() == 0
+    for i in range(3):
+        assert cnt[i] == len(want[i][0])
+        assert kps[i, :cnt[i]].tobytes() == want[i][0].tobytes() and desc[i, :cnt[i]].tobytes() == want[i][1].tobytes()
