@@ -91,6 +91,11 @@ struct snk_orb
 
     PyrDev P{};
     std::vector<CellDev> cells;
+    TmaMaps maps{};                 // one tensor map per level for the FAST tile loads
+    int box_h[SNK_MAX_LEVELS]{};
+    const void* map0_ptr = nullptr;  // what the level-0 map currently describes (it may alias a caller buffer)
+    int map0_pitch = 0;
+    size_t map0_stride = 0;
     std::vector<TileDev> tiles;
     int node_cap = 0;
     size_t qt_smem = 0;
@@ -134,6 +139,34 @@ struct snk_orb
     }
 };
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no libcuda link dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size_t img_stride)
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn)
+    {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        SNK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        SNK_REQUIRE(p && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = (EncodeTiledFn)p;
+    }
+    const LevelDev& L = h->P.lv[l];
+    SNK_REQUIRE(((uintptr_t)base % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
+    const cuuint64_t dims[3]    = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)h->prm.max_batch};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
+    const cuuint32_t box[3]     = {(cuuint32_t)FAST_PITCH, (cuuint32_t)h->box_h[l], 1};
+    const cuuint32_t estr[3]    = {1, 1, 1};
+    CUresult r = fn(&h->maps.level[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
+    return SNK_OK;
+}
+
 static int orb_allocate(snk_orb* h, int rows, int cols)
 {
     if (h->rows == rows && h->cols == cols) return SNK_OK;
@@ -168,7 +201,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
         // level 0 only ever receives the caller's bytes: a dense pitch makes the host->device copy one contiguous
         // transfer when the caller's rows are dense too
-        lv.pitch       = (l == 0) ? align_up(lv.w, 4) : align_up(lv.w, 64);
+        lv.pitch       = (l == 0) ? align_up(lv.w, 16) : align_up(lv.w, 64);  // TMA: row pitch multiple of 16 bytes
         lv.gauss_pitch = align_up(lv.w, 64);
         lv.img_stride  = (size_t)lv.pitch * lv.h;
         lv.gauss_stride = (size_t)lv.gauss_pitch * lv.h;
@@ -196,8 +229,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
                 c.level = (short)l, c.x0 = (short)iniX, c.y0 = (short)iniY, c.w = (short)(maxX - iniX), c.h = (short)(maxY - iniY);
                 c.off_x = (short)(j * wCell), c.off_y = (short)(i * hCell);
                 {
-                    const int a = iniX & 3, nw = (a + c.w + 3) >> 2;
-                    c.ld_words = (unsigned short)nw, c.ld_inv = (unsigned short)(65536 / nw + 1), c.ld_rows = (unsigned short)(32 / nw);
+                    const int a = iniX & 15;  // the TMA box starts at the 16-byte aligned column left of the ROI
+                    c.box_h = 0, c.ld_inv = 0, c.ld_rows = 0;  // box_h is filled in once the level's tallest cell is known
                     const int zw = std::max(c.w - 6, 1), c0 = 3 + a, c1 = 3 + a + zw;
                     const int nwz = ((c1 + 3) >> 2) - (c0 >> 2);
                     c.zn_word0 = (unsigned short)(c0 >> 2), c.zn_words = (unsigned short)nwz;
@@ -211,6 +244,12 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             }
         }
         lv.n_cells  = (int)h->cells.size() - lv.cell_base;
+        {
+            int box_h = 1;
+            for (size_t ci = lv.cell_base; ci < h->cells.size(); ++ci) box_h = std::max(box_h, (int)h->cells[ci].h);
+            for (size_t ci = lv.cell_base; ci < h->cells.size(); ++ci) h->cells[ci].box_h = (unsigned short)box_h;
+            h->box_h[l] = box_h;
+        }
         lv.sel_base = sel_acc;
         sel_acc += lv.quota + 4;
         for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
@@ -241,6 +280,12 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         P.lv[l].gauss = h->d_gauss + gauss_off[l];
     }
     h->own_l0 = P.lv[0];
+    for (int l = 0; l < L; ++l)
+    {
+        int rc = encode_level_map(h, l, P.lv[l].img, P.lv[l].pitch, P.lv[l].img_stride);
+        if (rc) return rc;
+    }
+    h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
     for (int l = 1; l < L; ++l)
     {
         std::vector<int> xo, yo;
@@ -481,8 +526,8 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
 
     // stage 0: level 0. Device input is used in place (the reference copies it, ORBExtractor.cpp:269; nothing reads the
     // copy's apron, so aliasing is equivalent). Host input is copied straight into the level-0 buffer.
-    // the kernels read rows as aligned 32-bit words
-    const bool aligned = ((uintptr_t)imgs % 4 == 0) && (pitch % 4 == 0) && (img_stride % 4 == 0 || n_imgs == 1);
+    // the kernels read rows as aligned 32-bit words and the FAST tiles through TMA (16-byte base / pitch / stride)
+    const bool aligned = ((uintptr_t)imgs % 16 == 0) && (pitch % 16 == 0) && (img_stride % 16 == 0 || n_imgs == 1);
     if (on_device && aligned)
     {
         P.lv[0].img        = const_cast<uint8_t*>(imgs);
@@ -503,6 +548,13 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
             for (int i = 0; i < n_imgs; ++i)
                 SNK_CUDA(cudaMemcpy2DAsync(P.lv[0].img + i * P.lv[0].img_stride, P.lv[0].pitch, imgs + i * img_stride,
                                            pitch, cols, rows, kind, st));
+    }
+    if (h->map0_ptr != P.lv[0].img || h->map0_pitch != P.lv[0].pitch || h->map0_stride != P.lv[0].img_stride)
+    {
+        const size_t stride0 = (n_imgs == 1 && P.lv[0].img_stride % 16) ? (size_t)P.lv[0].pitch * rows : P.lv[0].img_stride;
+        rc = encode_level_map(h, 0, P.lv[0].img, P.lv[0].pitch, stride0);
+        if (rc) return rc;
+        h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
     }
     if (prof) cudaEventRecord(ev[1], st);
 
@@ -530,7 +582,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
 
     // stage 2: FAST over every cell of every level
-    k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->d_cells, h->d_cand, h->d_cell_count);
+    k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->maps, h->d_cells, h->d_cand, h->d_cell_count, h->d_err);
     ++nl[2];
     if (prof) cudaEventRecord(ev[3], st);
 

@@ -13,6 +13,8 @@
 #include "glibc_math.cuh"
 #include "gnu_sort.cuh"
 
+#include <cuda.h>  // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint, no link dependency)
+
 #define SNK_MAX_LEVELS 16
 
 namespace snk
@@ -47,6 +49,12 @@ struct PyrDev
     int th_ini, th_min;
 };
 
+// One TMA descriptor per pyramid level: 3-D tensor (x, y, image) of u8 with box FAST_PITCH x (max cell height) x 1.
+struct TmaMaps
+{
+    CUtensorMap level[SNK_MAX_LEVELS];
+};
+
 // One FAST cell == one cv::FAST call of the reference: ROI origin/size inside its level and the offset the reference
 // adds to the ROI-relative coordinates (ORBExtractor.cpp:152-153).
 struct CellDev
@@ -57,7 +65,7 @@ struct CellDev
     short off_x, off_y;
     // lane -> (row, word) splits of the kernel's two word-wise passes, precomputed on the host (no integer division
     // on the device): a warp covers `rows` rows of `words` words per step; lane / words == (lane * inv) >> 16
-    unsigned short ld_words, ld_inv, ld_rows;   // tile load: words per tile row
+    unsigned short box_h, ld_inv, ld_rows;      // rows of the level's TMA box (tile bytes = FAST_PITCH * box_h)
     unsigned short zn_words, zn_inv, zn_rows;   // compass pass: words intersecting the zone columns
     unsigned short zn_word0;                    // first such word
     unsigned short _pad[2];
@@ -154,7 +162,7 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
 // FAST
 // --------------------------------------------------------------------------------------------------------------
 constexpr int FAST_DIM = 66;    // wCell < 60  =>  ROI side <= 66
-constexpr int FAST_PITCH = 72;  // ROI row + up to 3 bytes of word alignment, multiple of 4
+constexpr int FAST_PITCH = 96;  // tile row pitch == TMA box width: ROI (<= 66) + up to 15 bytes of alignment, multiple of 16
 constexpr int FAST_NT = 128;
 constexpr int FAST_ZMAX = (FAST_DIM - 6) * (FAST_DIM - 6);  // detection-zone pixels
 constexpr int FAST_BMW = (FAST_ZMAX + 31) / 32;
@@ -199,56 +207,58 @@ __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], in
 //   B  arc score of the survivors of A (packed 16-bit min network)  -> corners at the lower threshold
 //   C  3x3 NMS of the corners, survivors marked in a bitmap over the zone; popc-prefix of the bitmap gives every
 //      survivor its row-major rank (== cv::FAST output order) without sorting
-__global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const CellDev* __restrict__ cells, uint32_t* __restrict__ cand,
-                                                  int* __restrict__ cell_count)
+__global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constant__ TmaMaps maps,
+                                                  const CellDev* __restrict__ cells, uint32_t* __restrict__ cand,
+                                                  int* __restrict__ cell_count, int* __restrict__ err)
 {
-    __shared__ __align__(16) uint8_t tile[FAST_DIM][FAST_PITCH];
+    __shared__ __align__(128) uint8_t tile[FAST_DIM][FAST_PITCH];  // TMA destination
     __shared__ __align__(16) uint8_t score[FAST_DIM][FAST_PITCH];
     __shared__ uint16_t list1[FAST_ZMAX];
     __shared__ uint16_t list2[FAST_ZMAX];
     __shared__ uint32_t bm[2][FAST_BMW];  // [0] survivors at the lower threshold, [1] those also above th_ini
     __shared__ uint16_t pre[FAST_BMW + 1];
     __shared__ int s_n1, s_n2, s_ini, s_warp[FAST_NT / 32];
+    __shared__ __align__(8) unsigned long long tma_bar;
 
     const CellDev c   = cells[blockIdx.x];
-    const LevelDev& L = P.lv[c.level];
     const int img     = blockIdx.y;
     const int w = c.w, h = c.h;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int a = c.x0 & 3;  // the tile is stored from the aligned word that contains the ROI's first byte
-    const uint8_t* rows = L.img + (size_t)img * L.img_stride + (size_t)c.y0 * L.pitch + (c.x0 - a);
+    // TMA tiled loads need a 16-byte aligned innermost start coordinate (an unaligned one raises "illegal instruction" on
+    // sm_100a, tools/tma_check.cu): the box starts at the aligned column, the ROI sits `a` bytes into the tile rows
+    const int a = c.x0 & 15;
 
-    if (tid == 0) s_n1 = s_n2 = s_ini = 0;
-    for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
+    // ---- tile load: one TMA box copy (cp.async.bulk.tensor) per CTA, completion on an mbarrier ----
+    const unsigned bar_addr  = (unsigned)__cvta_generic_to_shared(&tma_bar);
+    const unsigned tile_addr = (unsigned)__cvta_generic_to_shared(&tile[0][0]);
+    if (tid == 0)
     {
-        // a warp covers rpw rows x nw words per step; the (row, word) split of the lane is computed once
-        const int nw = c.ld_words, rpw = c.ld_rows, sub = (lane * c.ld_inv) >> 16, wx = lane - sub * nw;
-        if (sub < rpw)
-        {
-            // all global loads of this lane are issued before the first shared store (up to 6 rows per lane:
-            // 66 rows / (4 warps * >=1 row)); a dependent load->store loop left the SM waiting on DRAM latency
-            const int ystep = (FAST_NT / 32) * rpw, ybeg = wid * rpw + sub;
-            for (int yb = ybeg; yb < h; yb += 6 * ystep)
-            {
-                unsigned vals[6];
-#pragma unroll
-                for (int u = 0; u < 6; ++u)
-                {
-                    const int y = yb + u * ystep;
-                    vals[u] = (y < h) ? __ldg(reinterpret_cast<const uint32_t*>(rows + (size_t)y * L.pitch) + wx) : 0u;
-                }
-#pragma unroll
-                for (int u = 0; u < 6; ++u)
-                {
-                    const int y = yb + u * ystep;
-                    if (y < h)
-                    {
-                        reinterpret_cast<uint32_t*>(&tile[y][0])[wx]  = vals[u];
-                        reinterpret_cast<uint32_t*>(&score[y][0])[wx] = 0;
-                    }
-                }
-            }
-        }
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_n1 = s_n2 = s_ini = 0;
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+        const unsigned bytes = (unsigned)(FAST_PITCH * c.box_h);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(tile_addr),
+            "l"(reinterpret_cast<unsigned long long>(&maps.level[c.level])), "r"((int)c.x0 - a), "r"((int)c.y0), "r"(img), "r"(bar_addr)
+            : "memory");
+    }
+    // while the copy is in flight: clear the score tile (16-byte stores) and the bitmaps
+    for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
+    for (int i = tid; i < (h * FAST_PITCH) >> 4; i += FAST_NT) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+    {
+        // bounded wait: a copy that never completes (bad descriptor) must not hang the device; it is reported instead
+        unsigned done = 0;
+        for (int spin = 0; !done && spin < (1 << 22); ++spin)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done)
+                         : "r"(bar_addr)
+                         : "memory");
+        if (!done && tid == 0) atomicExch(err, 4);
     }
     __syncthreads();
 
