@@ -93,6 +93,8 @@ struct snk_orb
     std::vector<CellDev> cells;
     TmaMaps maps{};                 // one tensor map per level for the FAST tile loads
     int box_h[SNK_MAX_LEVELS]{};
+    int fast_rows = 0, fast_list = 0;  // shared-memory sizing of k_fast: tallest TMA box, largest detection zone
+    size_t fast_smem = 0;
     const void* map0_ptr = nullptr;  // what the level-0 map currently describes (it may alias a caller buffer)
     int map0_pitch = 0;
     size_t map0_stride = 0;
@@ -181,6 +183,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
 
     // level sizes (ORBExtractor::AllocatePyramid, ORBExtractor.cpp:244-246) and FAST cell grid (:99-127)
     h->cells.clear();
+    h->fast_rows = h->fast_list = 0;
     h->tiles.clear();
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
@@ -249,6 +252,9 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             for (size_t ci = lv.cell_base; ci < h->cells.size(); ++ci) box_h = std::max(box_h, (int)h->cells[ci].h);
             for (size_t ci = lv.cell_base; ci < h->cells.size(); ++ci) h->cells[ci].box_h = (unsigned short)box_h;
             h->box_h[l] = box_h;
+            h->fast_rows = std::max(h->fast_rows, box_h);
+            for (size_t ci = lv.cell_base; ci < h->cells.size(); ++ci)
+                h->fast_list = std::max(h->fast_list, (std::max(h->cells[ci].w - 6, 0) * std::max(h->cells[ci].h - 6, 0) + 7) & ~7);
         }
         lv.sel_base = sel_acc;
         sel_acc += lv.quota + 4;
@@ -323,6 +329,9 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         SNK_CUDA(cudaMemcpy(h->d_yofs[l], yo.data(), yo.size() * sizeof(int), cudaMemcpyHostToDevice));
         SNK_CUDA(cudaMemcpy(h->d_yb[l], yb.data(), yb.size() * sizeof(short), cudaMemcpyHostToDevice));
     }
+    h->fast_rows = align_up(h->fast_rows, 4);  // keeps every tile buffer 128-byte aligned (4 rows x 96 bytes = 3 x 128)
+    h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
+    SNK_CUDA(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fast_smem, 48 * 1024)));
     SNK_CUDA(cudaMalloc(&h->d_cells, h->cells.size() * sizeof(CellDev)));
     SNK_CUDA(cudaMemcpy(h->d_cells, h->cells.data(), h->cells.size() * sizeof(CellDev), cudaMemcpyHostToDevice));
     SNK_CUDA(cudaMalloc(&h->d_tiles, h->tiles.size() * sizeof(TileDev)));
@@ -582,7 +591,8 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
 
     // stage 2: FAST over every cell of every level
-    k_fast<<<dim3(P.cells_per_img, n_imgs), FAST_NT, 0, st>>>(P, h->maps, h->d_cells, h->d_cand, h->d_cell_count, h->d_err);
+    k_fast<<<dim3((P.cells_per_img + FAST_CPB - 1) / FAST_CPB, n_imgs), FAST_NT, h->fast_smem, st>>>(
+        P, h->maps, h->d_cells, h->d_cand, h->d_cell_count, h->d_err, h->fast_rows, h->fast_list);
     ++nl[2];
     if (prof) cudaEventRecord(ev[3], st);
 

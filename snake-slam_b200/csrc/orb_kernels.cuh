@@ -207,56 +207,78 @@ __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], in
 //   B  arc score of the survivors of A (packed 16-bit min network)  -> corners at the lower threshold
 //   C  3x3 NMS of the corners, survivors marked in a bitmap over the zone; popc-prefix of the bitmap gives every
 //      survivor its row-major rank (== cv::FAST output order) without sorting
+// A CTA walks FAST_CPB consecutive cells; the tile of cell k+1 is fetched by TMA into the other buffer while cell k is
+// processed (two tile buffers, two mbarriers), so the load latency of all but the first cell is hidden.
+constexpr int FAST_CPB = 4;
 __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constant__ TmaMaps maps,
                                                   const CellDev* __restrict__ cells, uint32_t* __restrict__ cand,
-                                                  int* __restrict__ cell_count, int* __restrict__ err)
+                                                  int* __restrict__ cell_count, int* __restrict__ err, int tile_rows, int list_cap)
 {
-    __shared__ __align__(128) uint8_t tile[FAST_DIM][FAST_PITCH];  // TMA destination
-    __shared__ __align__(16) uint8_t score[FAST_DIM][FAST_PITCH];
-    __shared__ uint16_t list1[FAST_ZMAX];
-    __shared__ uint16_t list2[FAST_ZMAX];
+    // dynamic shared memory: 2 tile buffers + score tile (tile_rows x FAST_PITCH each, 128-byte aligned), 2 lists
+    extern __shared__ __align__(128) unsigned char fast_smem[];
+    const int tile_bytes = tile_rows * FAST_PITCH;
+    uint8_t(*score)[FAST_PITCH] = reinterpret_cast<uint8_t(*)[FAST_PITCH]>(fast_smem + 2 * tile_bytes);
+    uint16_t* list1 = reinterpret_cast<uint16_t*>(fast_smem + 3 * tile_bytes);
+    uint16_t* list2 = list1 + list_cap;
     __shared__ uint32_t bm[2][FAST_BMW];  // [0] survivors at the lower threshold, [1] those also above th_ini
     __shared__ uint16_t pre[FAST_BMW + 1];
     __shared__ int s_n1, s_n2, s_ini, s_warp[FAST_NT / 32];
-    __shared__ __align__(8) unsigned long long tma_bar;
+    __shared__ __align__(8) unsigned long long tma_bar[2];
 
-    const CellDev c   = cells[blockIdx.x];
-    const int img     = blockIdx.y;
-    const int w = c.w, h = c.h;
+    const int img = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    // TMA tiled loads need a 16-byte aligned innermost start coordinate (an unaligned one raises "illegal instruction" on
-    // sm_100a, tools/tma_check.cu): the box starts at the aligned column, the ROI sits `a` bytes into the tile rows
-    const int a = c.x0 & 15;
+    const int cell0 = blockIdx.x * FAST_CPB, ncell = min(FAST_CPB, P.cells_per_img - cell0);
+    const unsigned bar_addr0  = (unsigned)__cvta_generic_to_shared(&tma_bar[0]);
+    const unsigned tile_addr0 = (unsigned)__cvta_generic_to_shared(fast_smem);
 
-    // ---- tile load: one TMA box copy (cp.async.bulk.tensor) per CTA, completion on an mbarrier ----
-    const unsigned bar_addr  = (unsigned)__cvta_generic_to_shared(&tma_bar);
-    const unsigned tile_addr = (unsigned)__cvta_generic_to_shared(&tile[0][0]);
+    // one TMA box copy (cp.async.bulk.tensor) per cell, completion on the buffer's mbarrier. TMA tiled loads need a
+    // 16-byte aligned innermost start coordinate (an unaligned one raises "illegal instruction" on sm_100a,
+    // tools/tma_check.cu): the box starts at the aligned column, the ROI sits `a` = x0 & 15 bytes into the tile rows
+    auto issue = [&](const CellDev& cc, int buf) {
+        const unsigned bar = bar_addr0 + 8u * buf, dst = tile_addr0 + (unsigned)(buf * tile_bytes);
+        const unsigned bytes = (unsigned)(FAST_PITCH * cc.box_h);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+            "l"(reinterpret_cast<unsigned long long>(&maps.level[cc.level])), "r"((int)cc.x0 - (cc.x0 & 15)), "r"((int)cc.y0), "r"(img),
+            "r"(bar)
+            : "memory");
+    };
     if (tid == 0)
     {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr0 + 8u));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        s_n1 = s_n2 = s_ini = 0;
     }
     __syncthreads();
-    if (tid == 0)
+    CellDev c = cells[cell0];
+    if (tid == 0) issue(c, 0);
+
+#pragma unroll 1
+    for (int kc = 0; kc < ncell; ++kc)
     {
-        const unsigned bytes = (unsigned)(FAST_PITCH * c.box_h);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(tile_addr),
-            "l"(reinterpret_cast<unsigned long long>(&maps.level[c.level])), "r"((int)c.x0 - a), "r"((int)c.y0), "r"(img), "r"(bar_addr)
-            : "memory");
+    const int buf = kc & 1;
+    uint8_t(*tile)[FAST_PITCH] = reinterpret_cast<uint8_t(*)[FAST_PITCH]>(fast_smem + buf * tile_bytes);
+    CellDev cnext = c;
+    if (kc + 1 < ncell)
+    {
+        cnext = cells[cell0 + kc + 1];
+        if (tid == 0) issue(cnext, buf ^ 1);  // that buffer's last readers passed the barrier that ended iteration kc-1
     }
-    // while the copy is in flight: clear the score tile (16-byte stores) and the bitmaps
+    const int w = c.w, h = c.h;
+    const int a = c.x0 & 15;
+    // while the copies are in flight: reset the per-cell state, clear the score tile (16-byte stores) and the bitmaps
+    if (tid == 0) s_n1 = s_n2 = s_ini = 0;
     for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
     for (int i = tid; i < (h * FAST_PITCH) >> 4; i += FAST_NT) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
     {
         // bounded wait: a copy that never completes (bad descriptor) must not hang the device; it is reported instead
+        const unsigned bar = bar_addr0 + 8u * buf, parity = (unsigned)((kc >> 1) & 1);
         unsigned done = 0;
         for (int spin = 0; !done && spin < (1 << 22); ++spin)
-            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                          : "=r"(done)
-                         : "r"(bar_addr)
+                         : "r"(bar), "r"(parity)
                          : "memory");
         if (!done && tid == 0) atomicExch(err, 4);
     }
@@ -363,7 +385,7 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
         if (tid == FAST_NT - 1) pre[FAST_BMW] = (uint16_t)(add + inc);  // total
     }
     __syncthreads();
-    const size_t slot = (size_t)img * P.cells_per_img + blockIdx.x;
+    const size_t slot = (size_t)img * P.cells_per_img + cell0 + kc;
     uint32_t* out     = cand + slot * P.cell_cap;
     for (int k = tid; k < n2; k += FAST_NT)
     {
@@ -378,6 +400,9 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
         }
     }
     if (tid == 0) cell_count[slot] = pre[FAST_BMW];
+    c = cnext;
+    __syncthreads();  // every read of this cell's tile, lists and bitmaps is done before they are reused
+    }  // cells of this CTA
 }
 
 // --------------------------------------------------------------------------------------------------------------
