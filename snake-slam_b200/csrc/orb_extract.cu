@@ -572,9 +572,12 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     {
         const LevelDev& s = P.lv[l - 1];
         const LevelDev& d = P.lv[l];
-        dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + RS_ROWS - 1) / RS_ROWS + 3) / 4, n_imgs);
+        // strip height: enough warps to fill the machine, short serial chains on the small levels
+        const long long px = (long long)d.w * d.h * n_imgs;
+        const int rps = px >= (40ll << 20) ? RS_ROWS : (px >= (10ll << 20) ? RS_ROWS / 2 : RS_ROWS / 4);
+        dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + rps - 1) / rps + 3) / 4, n_imgs);
         k_resize<<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
-                                       h->d_quads[l], h->d_yofs[l], h->d_yb[l]);
+                                       h->d_quads[l], h->d_yofs[l], h->d_yb[l], rps);
         ++nl[1];
     }
     if (prof) cudaEventRecord(ev[2], st);

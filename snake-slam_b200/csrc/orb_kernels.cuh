@@ -95,12 +95,12 @@ struct ResizeQuad  // 32 bytes per 4 output pixels
 __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src, size_t src_stride, int spitch, int sh,
                                                 uint8_t* __restrict__ dst, size_t dst_stride, int dpitch, int dw, int dh,
                                                 const ResizeQuad* __restrict__ quads, const int* __restrict__ yofs,
-                                                const short* __restrict__ yb)
+                                                const short* __restrict__ yb, int rows_per_strip)
 {
     const int lane  = threadIdx.x & 31;
     const int strip = blockIdx.y * 4 + (threadIdx.x >> 5);
     const int x     = blockIdx.x * RS_TW + 4 * lane;
-    const int y0    = strip * RS_ROWS;
+    const int y0    = strip * rows_per_strip;  // shorter strips on small levels: the rows of a strip are a serial chain
     if (y0 >= dh || x >= dw) return;  // no warp-wide primitives below
     const uint8_t* S = src + (size_t)blockIdx.z * src_stride;
     uint8_t* D       = dst + (size_t)blockIdx.z * dst_stride;
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
 
     unsigned ha[4], hb[4];
     int held = -1;  // source row whose sums are in hb
-    const int y1 = min(y0 + RS_ROWS, dh);
+    const int y1 = min(y0 + rows_per_strip, dh);
     for (int y = y0; y < y1; ++y)
     {
         const int sy0 = min(max(yofs[y], 0), sh - 1), sy1 = min(max(yofs[y] + 1, 0), sh - 1);
