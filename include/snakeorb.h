@@ -110,6 +110,11 @@ SNK_API int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, in
  * enqueue = copy-in (if host) + all kernels on the handle's stream; no host synchronisation. */
 SNK_API int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
                             size_t img_stride, int imgs_are_device);
+/* Same, for 8-bit RGBA input (4 bytes per pixel, pitch / img_stride in bytes): Input::computeGrayscaleImage
+ * (Snake/Preprocess/Input.cpp:394-413, cv::cvtColor COLOR_RGBA2GRAY) fused in front of the pyramid — the grey image
+ * is written straight into the level-0 buffer: gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, alpha ignored. */
+SNK_API int snk_orb_enqueue_rgba(snk_orb* h, const uint8_t* rgba, int n_imgs, int rows, int cols, size_t pitch,
+                                 size_t img_stride, int imgs_are_device);
 /* Device-resident results of the last enqueue: keypoints [max_batch][stride] (24-byte records), descriptors
  * [max_batch][stride][4] u64, counts [max_batch] i32. Valid until the next enqueue on this handle. */
 SNK_API int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps_dev, const uint64_t** desc_dev,
@@ -245,6 +250,22 @@ SNK_API int snk_stereo_from_rgbd(snk_ctx* c, const snk_rgbd_params* p, const snk
                                  const float* depth_img, int rows, int cols, size_t pitch, float* right_points,
                                  float* depth, int* n_matches);
 
+/* Preprocess::undistortKeypoints (Snake/Preprocess/Preprocess.cpp:55-77): per keypoint K_src.unproject2
+ * (saiga/vision/cameraModel/Intrinsics4.h:78), undistortPointGN with the point as its own start (5 Gauss-Newton
+ * steps on distortNormalizedPoint and its Jacobian, 2x2 Eigen LDLT solve; Distortion.h:128-285), rotation by the
+ * rectification quaternion (Rectify.h:15-33), dehomogenisation -> normalized_points, K_dst.normalizedToImage ->
+ * undistorted keypoint. kp_un[i] is kps[i] with the point replaced. Double arithmetic in the reference's operation
+ * order, unfused. */
+typedef struct snk_rectify
+{
+    double fx, fy, cx, cy;         /* rect_left.K_src (unproject2 ignores the skew) */
+    double dist[8];                /* rect_left.D_src: k1 k2 k3 k4 k5 k6 p1 p2 */
+    double quat[4];                /* rect_left.R as x y z w (identity: 0 0 0 1) */
+    double dfx, dfy, dcx, dcy, ds; /* rect_left.K_dst */
+} snk_rectify;
+SNK_API int snk_undistort_keypoints(snk_ctx* c, const snk_rectify* r, const snk_keypoint_f64* kps, int n,
+                                    snk_keypoint_f64* kp_un, double* normalized_points /* 2n */);
+
 /* Camera, grid and frame views used by the projection searches. */
 typedef struct snk_camera
 {
@@ -368,6 +389,10 @@ SNK_API int snk_features_write(const char* path, const snk_keypoint_f64* kps, co
 SNK_API int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64_t* desc, int capacity, int* n_out);
 /* KeyPoint<float>::cast<double>() as FeatureDetector.cpp:129-132 applies it to the extractor's output. */
 SNK_API int snk_keypoints_widen(const snk_keypoint_f32* in, int n, snk_keypoint_f64* out);
+
+/* Input::computeGrayscaleImage alone (host RGBA in, host grey out), for callers that keep the grey image. */
+SNK_API int snk_rgba_to_gray(snk_ctx* c, const uint8_t* rgba, int rows, int cols, size_t pitch, uint8_t* gray,
+                             size_t gray_pitch);
 
 /* Register-resident popc microbenchmark: measured 256-bit Hamming distances per second of this device, the
  * denominator of the matcher roofline. */

@@ -220,4 +220,16 @@ void fast9_16_nms(const uint8_t* roi, int h, int w, size_t pitch, int threshold,
         }
     }
 }
+// cv::cvtColor RGBA -> GRAY for CV_8U (OpenCV imgproc color_rgb: RGB2Gray<uchar>, gray_shift = 15,
+// RY15 = 9798, GY15 = 19235, BY15 = 3735, CV_DESCALE adds 1 << 14); identical to cv2 4.13 for all 2^24 colours
+void rgba_to_gray_u8(const uint8_t* src, int h, int w, size_t spitch, uint8_t* dst, size_t dpitch)
+{
+    for (int y = 0; y < h; ++y)
+    {
+        const uint8_t* s = src + (size_t)y * spitch;
+        uint8_t* d       = dst + (size_t)y * dpitch;
+        for (int x = 0; x < w; ++x)
+            d[x] = (uint8_t)((s[4 * x] * 9798 + s[4 * x + 1] * 19235 + s[4 * x + 2] * 3735 + (1 << 14)) >> 15);
+    }
+}
 }  // namespace cvlite

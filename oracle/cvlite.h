@@ -23,6 +23,8 @@ struct FastKp
     int score;  // cv::KeyPoint::response
 };
 
+// cv::cvtColor(src, dst, COLOR_RGBA2GRAY), 8-bit (Input.cpp:407): 15-bit fixed point, alpha ignored
+void rgba_to_gray_u8(const uint8_t* src, int h, int w, size_t spitch, uint8_t* dst, size_t dpitch);
 void resize_linear_u8(const uint8_t* src, int sh, int sw, size_t spitch, uint8_t* dst, int dh, int dw, size_t dpitch);
 
 // coefficient tables exactly as cv::resize builds them (also used by tests to cross-check the device tables)

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <limits>
 #include <set>
 #include <vector>
 
@@ -179,6 +180,139 @@ int stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f64* kp, int n
         }
     }
     return num;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Preprocess::undistortKeypoints (Snake/Preprocess/Preprocess.cpp:55-77)
+// ---------------------------------------------------------------------------------------------
+namespace
+{
+// distortNormalizedPoint with its point Jacobian (saiga/vision/cameraModel/Distortion.h:128-212)
+inline void distort_with_jacobian(const double* D, double x, double y, double& xd, double& yd, double* J /*2x2 row-major or null*/)
+{
+    const double k1 = D[0], k2 = D[1], k3 = D[2], k4 = D[3], k5 = D[4], k6 = D[5], p1 = D[6], p2 = D[7];
+    const double x2 = x * x, y2 = y * y;
+    const double r2 = x2 + y2, _2xy = 2.0 * x * y;
+    const double r4 = r2 * r2;
+    const double r6 = r4 * r2;
+    const double radial_u  = 1.0 + k1 * r2 + k2 * r4 + k3 * r6;
+    const double radial_v  = 1.0 + k4 * r2 + k5 * r4 + k6 * r6;
+    const double radial_iv = 1.0 / radial_v;
+    const double radial    = radial_u * radial_iv;
+    const double tx = p1 * _2xy + p2 * (r2 + 2.0 * x2);
+    const double ty = p1 * (r2 + 2.0 * y2) + p2 * _2xy;
+    xd = x * radial + tx;
+    yd = y * radial + ty;
+    if (r2 > 100000.0 * 100000.0) xd = yd = 100000;
+    if (!J) return;
+    double u0 = k1 * (2 * x), u1 = k1 * (2 * y);
+    u0 += k2 * (4 * x * x * x + 4 * x * y * y);
+    u1 += k2 * (4 * y * y * y + 4 * y * x * x);
+    u0 += k3 * (6 * x2 * x2 * x + 12 * x2 * x * y2 + 6 * x * y2 * y2);
+    u1 += k3 * (6 * y2 * y2 * y + 12 * y2 * y * x2 + 6 * y * x2 * x2);
+    double v0 = k4 * (2 * x), v1 = k4 * (2 * y);
+    v0 += k5 * (4 * x * x * x + 4 * x * y * y);
+    v1 += k5 * (4 * y * y * y + 4 * y * x * x);
+    v0 += k6 * (6 * x2 * x2 * x + 12 * x2 * x * y2 + 6 * x * y2 * y2);
+    v1 += k6 * (6 * y2 * y2 * y + 12 * y2 * y * x2 + 6 * y * x2 * x2);
+    // J_rad: both rows equal (Distortion.h:181-196)
+    const double jr0 = (u0 * radial_v - v0 * radial_u) * radial_iv * radial_iv;
+    const double jr1 = (u1 * radial_v - v1 * radial_u) * radial_iv * radial_iv;
+    J[0] = (x * jr0 + radial) + (2 * p1 * y + 6 * p2 * x);
+    J[1] = (x * jr1) + (2 * p1 * x + 2 * p2 * y);
+    J[2] = (y * jr0) + (2 * p2 * y + 2 * p1 * x);
+    J[3] = (y * jr1 + radial) + (2 * p2 * x + 6 * p1 * y);
+}
+
+// Eigen::LDLT<Matrix2d>::solve as the vendored Eigen executes it for a 2x2 (Eigen/src/Cholesky/LDLT.h:300-400
+// unblocked factorisation with diagonal pivoting, :560-600 solve with the 1/min() pivot cut-off)
+inline void ldlt2_solve(double a, double b, double c, double r0, double r1, double& s0, double& s1)
+{
+    const bool swap = !(std::abs(a) >= std::abs(c));  // maxCoeff keeps the first of equal maxima; NaN never wins
+    double d0 = swap ? c : a, rest = swap ? a : c;
+    double l = b;
+    if (!(std::abs(d0) > 0))
+    {  // whole diagonal zero: transpositions reset, D = 0 => the solve zeroes both rows
+        s0 = s1 = 0;
+        return;
+    }
+    l /= d0;
+    const double d1 = rest - l * (d0 * l);
+    double y0 = swap ? r1 : r0, y1 = swap ? r0 : r1;
+    y1 -= l * y0;
+    const double tol = std::numeric_limits<double>::min();
+    y0 = (std::abs(d0) > tol) ? y0 / d0 : 0.0;
+    y1 = (std::abs(d1) > tol) ? y1 / d1 : 0.0;
+    y0 -= l * y1;
+    s0 = swap ? y1 : y0;
+    s1 = swap ? y0 : y1;
+}
+
+// undistortPointGN (Distortion.h:241-285), point == guess as Preprocess.cpp:68 calls it
+inline void undistort_gn(const double* D, double px, double py, double& ox, double& oy)
+{
+    double x = px, y = py, lx = px, ly = py;
+    double last_chi2 = std::numeric_limits<double>::infinity();
+    for (int it = 0; it < 5; ++it)
+    {
+        double J[4], xd, yd;
+        distort_with_jacobian(D, x, y, xd, yd, J);
+        const double r0 = xd - px, r1 = yd - py;
+        const double chi2 = r0 * r0 + r1 * r1;
+        if (chi2 > last_chi2)
+        {
+            x = lx;
+            y = ly;
+            continue;
+        }
+        const double a = J[0] * J[0] + J[2] * J[2], b = J[1] * J[0] + J[3] * J[2], c = J[1] * J[1] + J[3] * J[3];
+        const double g0 = (-J[0]) * r0 + (-J[2]) * r1, g1 = (-J[1]) * r0 + (-J[3]) * r1;
+        lx        = x;
+        ly        = y;
+        last_chi2 = chi2;
+        double d0, d1;
+        ldlt2_solve(a, b, c, g0, g1, d0, d1);
+        x += d0;
+        y += d1;
+    }
+    double xd, yd;
+    distort_with_jacobian(D, x, y, xd, yd, nullptr);
+    const double r0 = xd - px, r1 = yd - py;
+    if (r0 * r0 + r1 * r1 > last_chi2)
+    {
+        x = lx;
+        y = ly;
+    }
+    ox = x;
+    oy = y;
+}
+}  // namespace
+
+void undistort_keypoints(const snk_rectify* r, const snk_keypoint_f64* kps, int n, snk_keypoint_f64* kp_un,
+                         double* normalized)
+{
+    for (int i = 0; i < n; ++i)
+    {
+        kp_un[i] = kps[i];
+        const double px = (kps[i].x - r->cx) / r->fx, py = (kps[i].y - r->cy) / r->fy;  // unproject2 (no skew)
+        double nx, ny;
+        undistort_gn(r->dist, px, py, nx, ny);
+        // Eigen::Quaternion * Vector3 (Eigen/src/Geometry/Quaternion.h _transformVector): uv = 2 (q.vec x v);
+        // v + w uv + q.vec x uv
+        const double qx = r->quat[0], qy = r->quat[1], qz = r->quat[2], qw = r->quat[3];
+        const double v0 = nx, v1 = ny, v2 = 1.0;
+        double u0 = qy * v2 - qz * v1, u1 = qz * v0 - qx * v2, u2 = qx * v1 - qy * v0;
+        u0 += u0;
+        u1 += u1;
+        u2 += u2;
+        const double c0 = qy * u2 - qz * u1, c1 = qz * u0 - qx * u2, c2 = qx * u1 - qy * u0;
+        const double p0 = (v0 + qw * u0) + c0, p1 = (v1 + qw * u1) + c1, p2 = (v2 + qw * u2) + c2;
+        const double mx = p0 / p2, my = p1 / p2;
+        normalized[2 * i]     = mx;
+        normalized[2 * i + 1] = my;
+        kp_un[i].x = r->dfx * mx + r->ds * my + r->dcx;  // K_dst.normalizedToImage (Intrinsics4.h:80)
+        kp_un[i].y = r->dfy * my + r->dcy;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

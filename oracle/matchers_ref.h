@@ -12,6 +12,8 @@ int stereo_match(const snk_stereo_params* p, const snk_keypoint_f64* left, const
                  long long* pair_ops);
 int stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f64* kp, int n, const float* depth_img, int rows,
                      int cols, size_t pitch, float* right_points, float* depth);
+void undistort_keypoints(const snk_rectify* r, const snk_keypoint_f64* kps, int n, snk_keypoint_f64* kp_un,
+                         double* normalized);
 void feature_grid(const snk_grid_view* b, const snk_keypoint_f64* kps, int n, int32_t* permutation, int32_t* cells);
 int search_projection_fine(const snk_frame_view* f, snk_point_fine* pts, int n, const snk_camera* K,
                            const snk_scale_pyramid* sp, float th, float ratio, int32_t* kp_to_point_out,

@@ -19,6 +19,10 @@ ORC_API void orc_resize(const uint8_t* src, int sh, int sw, size_t sp, uint8_t* 
 {
     cvlite::resize_linear_u8(src, sh, sw, sp, dst, dh, dw, dp);
 }
+ORC_API void orc_rgba_to_gray(const uint8_t* src, int h, int w, size_t sp, uint8_t* dst, size_t dp)
+{
+    cvlite::rgba_to_gray_u8(src, h, w, sp, dst, dp);
+}
 ORC_API void orc_blur(const uint8_t* src, int h, int w, size_t sp, uint8_t* dst, size_t dp)
 {
     cvlite::gaussian7_u8(src, h, w, sp, dst, dp);
@@ -146,6 +150,11 @@ ORC_API int orc_stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint_f6
                                  int cols, size_t pitch, float* rp, float* depth)
 {
     return stereo_from_rgbd(p, kp, n, img, rows, cols, pitch, rp, depth);
+}
+ORC_API void orc_undistort_keypoints(const snk_rectify* r, const snk_keypoint_f64* kps, int n, snk_keypoint_f64* kp_un,
+                                     double* normalized)
+{
+    undistort_keypoints(r, kps, n, kp_un, normalized);
 }
 ORC_API void orc_feature_grid(const snk_grid_view* b, const snk_keypoint_f64* kps, int n, int32_t* perm, int32_t* cells)
 {

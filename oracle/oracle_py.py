@@ -59,6 +59,14 @@ def resize(src, dh, dw):
     return dst
 
 
+def rgba_to_gray(src):
+    assert src.dtype == np.uint8 and src.ndim == 3 and src.shape[2] == 4 and src.strides[1:] == (4, 1)
+    dst = np.zeros(src.shape[:2], np.uint8)
+    lib().orc_rgba_to_gray(_p(src), src.shape[0], src.shape[1], C.c_size_t(src.strides[0]), _p(dst),
+                           C.c_size_t(src.shape[1]))
+    return dst
+
+
 def blur(src):
     src = np.ascontiguousarray(src)
     dst = np.zeros_like(src)
@@ -253,6 +261,14 @@ def stereo_from_rgbd(params, kp_un, depth_img):
     n = lib().orc_stereo_from_rgbd(C.byref(params), _p(kp_un), len(kp_un), _p(depth_img), depth_img.shape[0],
                                    depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp))
     return n, rp[:len(kp_un)], dp[:len(kp_un)]
+
+
+def undistort_keypoints(rect, kps):
+    kps = np.ascontiguousarray(kps, KP64)
+    out = np.zeros(len(kps), KP64)
+    nrm = np.zeros((len(kps), 2), np.float64)
+    lib().orc_undistort_keypoints(C.byref(rect), _p(kps), len(kps), _p(out), _p(nrm))
+    return out, nrm
 
 
 def feature_grid(bounds, kp_un):

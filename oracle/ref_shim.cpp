@@ -133,3 +133,31 @@ REF_API void ref_feature_grid(double bminx, double bminy, double bmaxx, double b
             cells[2 * (r * cols + c) + 1] = g.grid(r, c).second;
         }
 }
+
+// ---- Preprocess::undistortKeypoints's per-keypoint math with the reference's own camera-model headers --------
+#include "saiga/vision/cameraModel/Rectify.h"
+// rect: K_src fx fy cx cy s | D_src k1..k6 p1 p2 | R x y z w | K_dst fx fy cx cy s   (22 doubles)
+REF_API void ref_undistort_points(const double* rect, const double* xy, int n, double* normalized, double* undistorted)
+{
+    Rectification r;
+    r.K_src = IntrinsicsPinholed(rect[0], rect[1], rect[2], rect[3], rect[4]);
+    Eigen::Matrix<double, 8, 1> c;
+    for (int i = 0; i < 8; ++i) c(i) = rect[5 + i];
+    r.D_src = Distortion(c);
+    r.R     = Quat(rect[16], rect[13], rect[14], rect[15]);
+    r.K_dst = IntrinsicsPinholed(rect[17], rect[18], rect[19], rect[20], rect[21]);
+    for (int i = 0; i < n; ++i)
+    {
+        // the statements of Snake/Preprocess/Preprocess.cpp:64-75
+        Vec2 p            = Vec2(xy[2 * i], xy[2 * i + 1]);
+        p                 = r.K_src.unproject2(p);
+        Vec2 p_normalized = undistortPointGN(p, p, r.D_src);
+        Vec3 p_r          = r.R * Vec3(p_normalized(0), p_normalized(1), 1);
+        p                 = Vec2(p_r(0) / p_r(2), p_r(1) / p_r(2));
+        normalized[2 * i]     = p(0);
+        normalized[2 * i + 1] = p(1);
+        p                      = r.K_dst.normalizedToImage(p);
+        undistorted[2 * i]     = p(0);
+        undistorted[2 * i + 1] = p(1);
+    }
+}

@@ -220,6 +220,130 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
 }
 
 // --------------------------------------------------------------------------------------------------------------
+// Preprocess::undistortKeypoints (Snake/Preprocess/Preprocess.cpp:55-77), one thread per keypoint. IEEE double in the
+// reference's operation order (-fmad=false): 5 Gauss-Newton steps of undistortPointGN (Distortion.h:241-285) with
+// the 2x2 pivoted LDLT solve Eigen performs (Eigen/src/Cholesky/LDLT.h:300-400), quaternion rotation, K_dst.
+// --------------------------------------------------------------------------------------------------------------
+struct DistortEval
+{
+    double xd, yd, j00, j01, j10, j11;
+};
+template <bool WITH_J>
+__device__ __forceinline__ DistortEval distort_point(const double* __restrict__ D, double x, double y)
+{
+    DistortEval e;
+    const double k1 = D[0], k2 = D[1], k3 = D[2], k4 = D[3], k5 = D[4], k6 = D[5], p1 = D[6], p2 = D[7];
+    const double x2 = x * x, y2 = y * y;
+    const double r2 = x2 + y2, _2xy = 2.0 * x * y;
+    const double r4 = r2 * r2;
+    const double r6 = r4 * r2;
+    const double radial_u  = 1.0 + k1 * r2 + k2 * r4 + k3 * r6;
+    const double radial_v  = 1.0 + k4 * r2 + k5 * r4 + k6 * r6;
+    const double radial_iv = 1.0 / radial_v;
+    const double radial    = radial_u * radial_iv;
+    const double tx = p1 * _2xy + p2 * (r2 + 2.0 * x2);
+    const double ty = p1 * (r2 + 2.0 * y2) + p2 * _2xy;
+    e.xd = x * radial + tx;
+    e.yd = y * radial + ty;
+    if (r2 > 100000.0 * 100000.0) e.xd = e.yd = 100000;
+    if (WITH_J)
+    {
+        const double cx3 = 4 * x * x * x + 4 * x * y * y, cy3 = 4 * y * y * y + 4 * y * x * x;
+        const double cx5 = 6 * x2 * x2 * x + 12 * x2 * x * y2 + 6 * x * y2 * y2;
+        const double cy5 = 6 * y2 * y2 * y + 12 * y2 * y * x2 + 6 * y * x2 * x2;
+        double u0 = k1 * (2 * x), u1 = k1 * (2 * y);
+        u0 += k2 * cx3;
+        u1 += k2 * cy3;
+        u0 += k3 * cx5;
+        u1 += k3 * cy5;
+        double v0 = k4 * (2 * x), v1 = k4 * (2 * y);
+        v0 += k5 * cx3;
+        v1 += k5 * cy3;
+        v0 += k6 * cx5;
+        v1 += k6 * cy5;
+        const double jr0 = (u0 * radial_v - v0 * radial_u) * radial_iv * radial_iv;
+        const double jr1 = (u1 * radial_v - v1 * radial_u) * radial_iv * radial_iv;
+        e.j00 = (x * jr0 + radial) + (2 * p1 * y + 6 * p2 * x);
+        e.j01 = (x * jr1) + (2 * p1 * x + 2 * p2 * y);
+        e.j10 = (y * jr0) + (2 * p2 * y + 2 * p1 * x);
+        e.j11 = (y * jr1 + radial) + (2 * p2 * x + 6 * p1 * y);
+    }
+    return e;
+}
+
+__global__ void k_undistort(snk_rectify r, const snk_keypoint_f64* __restrict__ kps, int n,
+                            snk_keypoint_f64* __restrict__ kp_un, double* __restrict__ normalized)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    snk_keypoint_f64 k = kps[i];
+    const double px = (k.x - r.cx) / r.fx, py = (k.y - r.cy) / r.fy;
+    double x = px, y = py, lx = px, ly = py;
+    double last_chi2 = __longlong_as_double(0x7ff0000000000000ll);  // +inf
+    for (int it = 0; it < 5; ++it)
+    {
+        const DistortEval e = distort_point<true>(r.dist, x, y);
+        const double r0 = e.xd - px, r1 = e.yd - py;
+        const double chi2 = r0 * r0 + r1 * r1;
+        if (chi2 > last_chi2)
+        {
+            x = lx;
+            y = ly;
+            continue;
+        }
+        // JtJ (lower part) and -Jt res
+        const double a = e.j00 * e.j00 + e.j10 * e.j10, b = e.j01 * e.j00 + e.j11 * e.j10,
+                     c = e.j01 * e.j01 + e.j11 * e.j11;
+        const double g0 = (-e.j00) * r0 + (-e.j10) * r1, g1 = (-e.j01) * r0 + (-e.j11) * r1;
+        lx        = x;
+        ly        = y;
+        last_chi2 = chi2;
+        // LDLT with the larger diagonal entry as first pivot (the first one on ties)
+        const bool swp  = !(fabs(a) >= fabs(c));
+        const double d0 = swp ? c : a, rest = swp ? a : c;
+        double s0 = 0, s1 = 0;
+        if (fabs(d0) > 0)
+        {
+            const double l  = b / d0;
+            const double d1 = rest - l * (d0 * l);
+            double y0 = swp ? g1 : g0, y1 = swp ? g0 : g1;
+            y1 -= l * y0;
+            const double tol = 2.2250738585072014e-308;  // numeric_limits<double>::min(): Eigen's pivot cut-off
+            y0 = (fabs(d0) > tol) ? y0 / d0 : 0.0;
+            y1 = (fabs(d1) > tol) ? y1 / d1 : 0.0;
+            y0 -= l * y1;
+            s0 = swp ? y1 : y0;
+            s1 = swp ? y0 : y1;
+        }
+        x += s0;
+        y += s1;
+    }
+    {
+        const DistortEval e = distort_point<false>(r.dist, x, y);
+        const double r0 = e.xd - px, r1 = e.yd - py;
+        if (r0 * r0 + r1 * r1 > last_chi2)
+        {
+            x = lx;
+            y = ly;
+        }
+    }
+    // Quaternion * Vector3 as Eigen evaluates it: uv = 2 (q.vec x v); v + w uv + q.vec x uv
+    const double qx = r.quat[0], qy = r.quat[1], qz = r.quat[2], qw = r.quat[3];
+    double u0 = qy * 1.0 - qz * y, u1 = qz * x - qx * 1.0, u2 = qx * y - qy * x;
+    u0 += u0;
+    u1 += u1;
+    u2 += u2;
+    const double c0 = qy * u2 - qz * u1, c1 = qz * u0 - qx * u2, c2 = qx * u1 - qy * u0;
+    const double p0 = (x + qw * u0) + c0, p1 = (y + qw * u1) + c1, p2 = (1.0 + qw * u2) + c2;
+    const double mx = p0 / p2, my = p1 / p2;
+    normalized[2 * i]     = mx;
+    normalized[2 * i + 1] = my;
+    k.x      = r.dfx * mx + r.ds * my + r.dcx;
+    k.y      = r.dfy * my + r.dcy;
+    kp_un[i] = k;
+}
+
+// --------------------------------------------------------------------------------------------------------------
 // Preprocess::ComputeStereoFromRGBD (Snake/Preprocess/Preprocess.cpp:79-120), one thread per keypoint, double math in
 // the reference's operation order (library is built with -fmad=false)
 // --------------------------------------------------------------------------------------------------------------

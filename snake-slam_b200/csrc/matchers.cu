@@ -1,6 +1,7 @@
 // Host side of the matching context (snk_ctx) and the matcher entry points of include/snakeorb.h.
 #include "match_kernels.cuh"
 #include "project_kernels.cuh"
+#include "image_kernels.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -282,6 +283,51 @@ int snk_stereo_from_rgbd(snk_ctx* c, const snk_rgbd_params* p, const snk_keypoin
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaStreamSynchronize(st));
     *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+int snk_undistort_keypoints(snk_ctx* c, const snk_rectify* r, const snk_keypoint_f64* kps, int n, snk_keypoint_f64* kp_un,
+                            double* normalized_points)
+{
+    SNK_REQUIRE(c && r && n >= 0, "bad argument");
+    SNK_REQUIRE(n == 0 || (kps && kp_un && normalized_points), "null keypoint arrays");
+    SNK_REQUIRE(r->fx != 0 && r->fy != 0, "K_src with zero focal length");
+    if (n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, 2 * padded<snk_keypoint_f64>(n) + padded<double>(2 * (size_t)n));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    auto* dk   = cv.take<snk_keypoint_f64>(n);
+    auto* du   = cv.take<snk_keypoint_f64>(n);
+    double* dn = cv.take<double>(2 * (size_t)n);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(dk, kps, sizeof(snk_keypoint_f64) * (size_t)n, cudaMemcpyHostToDevice, st));
+    k_undistort<<<(n + 127) / 128, 128, 0, st>>>(*r, dk, n, du, dn);
+    SNK_CUDA(cudaGetLastError());
+    SNK_CUDA(cudaMemcpyAsync(kp_un, du, sizeof(snk_keypoint_f64) * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(normalized_points, dn, 16 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    return SNK_OK;
+}
+
+int snk_rgba_to_gray(snk_ctx* c, const uint8_t* rgba, int rows, int cols, size_t pitch, uint8_t* gray, size_t gray_pitch)
+{
+    SNK_REQUIRE(c && rows >= 0 && cols >= 0, "bad argument");
+    if (rows == 0 || cols == 0) return SNK_OK;
+    SNK_REQUIRE(rgba && gray && pitch >= (size_t)cols * 4 && gray_pitch >= (size_t)cols, "bad image arguments");
+    SNK_CUDA(cudaSetDevice(c->device));
+    const size_t sp = ((size_t)cols * 4 + 15) & ~(size_t)15, dp = ((size_t)cols + 3) & ~(size_t)3;
+    int rc = ctx_reserve(c, padded<uint8_t>(sp * rows) + padded<uint8_t>(dp * rows));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    uint8_t* ds = cv.take<uint8_t>(sp * rows);
+    uint8_t* dd = cv.take<uint8_t>(dp * rows);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemcpy2DAsync(ds, sp, rgba, pitch, (size_t)cols * 4, rows, cudaMemcpyHostToDevice, st));
+    k_rgba_to_gray<<<dim3((cols + 511) / 512, rows, 1), 128, 0, st>>>(ds, 0, sp, dd, 0, (int)dp, cols, rows);
+    SNK_CUDA(cudaGetLastError());
+    SNK_CUDA(cudaMemcpy2DAsync(gray, gray_pitch, dd, dp, cols, rows, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
     return SNK_OK;
 }
 

@@ -1,6 +1,7 @@
 // Host side of the ORB extractor handle (snk_orb): geometry tables, device memory, launch sequence.
 // Mirrors Saiga::ORBExtractor (saiga/vision/features/ORBExtractor.cpp:82-289) stage by stage; see orb_kernels.cuh.
 #include "orb_kernels.cuh"
+#include "image_kernels.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -102,6 +103,8 @@ struct snk_orb
     int node_cap = 0;
     size_t qt_smem = 0;
 
+    uint8_t* d_rgba = nullptr;   // staging for host RGBA input (snk_orb_enqueue_rgba), grown on demand
+    size_t rgba_bytes = 0;
     uint8_t* d_pyr = nullptr;    // levels 0..L-1 (level 0 unused when the caller's device buffer is aliased)
     uint8_t* d_gauss = nullptr;
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
@@ -450,6 +453,7 @@ void snk_orb_destroy(snk_orb* h)
     cudaStreamSynchronize(h->stream);
     h->free_buffers();
     if (h->d_pattern_t) cudaFree(h->d_pattern_t);
+    if (h->d_rgba) cudaFree(h->d_rgba);
     if (h->h_counts) cudaFreeHost(h->h_counts);
     if (h->h_err) cudaFreeHost(h->h_err);
     for (auto& set : h->ev)
@@ -629,6 +633,52 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     SNK_CUDA(cudaGetLastError());
     h->last_n = n_imgs;
     return SNK_OK;
+}
+
+int snk_orb_enqueue_rgba(snk_orb* h, const uint8_t* rgba, int n_imgs, int rows, int cols, size_t pitch, size_t img_stride,
+                         int on_device)
+{
+    SNK_REQUIRE(h, "null handle");
+    SNK_REQUIRE(n_imgs >= 0 && n_imgs <= h->prm.max_batch, "n_imgs %d exceeds max_batch %d", n_imgs, h->prm.max_batch);
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    h->last_n = 0;
+    if (n_imgs == 0 || !rgba || rows <= 0 || cols <= 0) return SNK_OK;
+    SNK_REQUIRE(pitch >= (size_t)cols * 4, "pitch smaller than a row of RGBA pixels");
+    SNK_REQUIRE(n_imgs == 1 || img_stride >= pitch * rows, "img_stride smaller than an image");
+    int rc = orb_allocate(h, rows, cols);
+    if (rc) return rc;
+    cudaStream_t st    = h->stream;
+    const uint8_t* src = rgba;
+    size_t spitch = pitch, sstride = img_stride;
+    const bool aligned = ((uintptr_t)rgba % 16 == 0) && (pitch % 16 == 0) && (img_stride % 16 == 0 || n_imgs == 1);
+    if (!on_device || !aligned)
+    {
+        // host input (or a device layout the 16-byte loads cannot read): dense copy into the staging buffer
+        spitch  = ((size_t)cols * 4 + 15) & ~(size_t)15;
+        sstride = spitch * rows;
+        if (h->rgba_bytes < sstride * n_imgs)
+        {
+            SNK_CUDA(cudaStreamSynchronize(st));
+            if (h->d_rgba) cudaFree(h->d_rgba);
+            h->d_rgba = nullptr, h->rgba_bytes = 0;
+            SNK_CUDA(cudaMalloc(&h->d_rgba, sstride * n_imgs));
+            h->rgba_bytes = sstride * n_imgs;
+        }
+        const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        if (img_stride == pitch * rows || n_imgs == 1)
+            SNK_CUDA(cudaMemcpy2DAsync(h->d_rgba, spitch, rgba, pitch, (size_t)cols * 4, (size_t)rows * n_imgs, kind, st));
+        else
+            for (int i = 0; i < n_imgs; ++i)
+                SNK_CUDA(cudaMemcpy2DAsync(h->d_rgba + i * sstride, spitch, rgba + i * img_stride, pitch, (size_t)cols * 4,
+                                           rows, kind, st));
+        src = h->d_rgba;
+    }
+    const LevelDev& l0 = h->own_l0;
+    k_rgba_to_gray<<<dim3((cols + 511) / 512, rows, n_imgs), 128, 0, st>>>(src, sstride, spitch, l0.img, l0.img_stride,
+                                                                          l0.pitch, cols, rows);
+    SNK_CUDA(cudaGetLastError());
+    // the internal level-0 buffer is 16-byte aligned: the extractor uses it in place
+    return snk_orb_enqueue(h, l0.img, n_imgs, rows, cols, (size_t)l0.pitch, l0.img_stride, 1);
 }
 
 int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps, const uint64_t** desc, const int32_t** counts,

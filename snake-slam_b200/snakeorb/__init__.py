@@ -42,6 +42,25 @@ class RgbdParams(C.Structure):
                 ("dist", C.c_double * 8), ("bf", C.c_double)]
 
 
+class Rectify(C.Structure):
+    """snk_rectify == the fields of Saiga::Rectification (Rectify.h:15-33) that undistortKeypoints reads."""
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double),
+                ("dist", C.c_double * 8), ("quat", C.c_double * 4), ("dfx", C.c_double), ("dfy", C.c_double),
+                ("dcx", C.c_double), ("dcy", C.c_double), ("ds", C.c_double)]
+
+    @classmethod
+    def from_vector(cls, v):
+        """v: K_src fx fy cx cy s | D_src (8) | quaternion x y z w | K_dst fx fy cx cy s (22 doubles)."""
+        r = cls()
+        r.fx, r.fy, r.cx, r.cy = v[0:4]
+        for i in range(8):
+            r.dist[i] = v[5 + i]
+        for i in range(4):
+            r.quat[i] = v[13 + i]
+        r.dfx, r.dfy, r.dcx, r.dcy, r.ds = v[17:22]
+        return r
+
+
 class Camera(C.Structure):
     _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("s", C.c_double),
                 ("bf", C.c_double)]
@@ -162,6 +181,16 @@ class ORBExtractor:
         _check(lib().snk_orb_enqueue(self.h, C.c_void_p(ptr), n_imgs, rows, cols, C.c_size_t(pitch), C.c_size_t(stride),
                                      int(on_device)))
 
+    def DetectBatchRGBA(self, rgba):
+        """rgba: (B, rows, cols, 4) uint8 host array; rows may be padded (strides[1] >= 4*cols). Grey conversion
+        (Input::computeGrayscaleImage) fused in front of the extractor. Returns per-image (kps, desc)."""
+        assert rgba.dtype == np.uint8 and rgba.ndim == 4 and rgba.shape[3] == 4 and rgba.strides[2:] == (4, 1)
+        B, rows, cols, _ = rgba.shape
+        _check(lib().snk_orb_enqueue_rgba(self.h, _p(rgba), B, rows, cols, C.c_size_t(rgba.strides[1]),
+                                          C.c_size_t(rgba.strides[0]), 0))
+        kps, desc, n = self.fetch(B)
+        return [(kps[i, :n[i]].copy(), desc[i, :n[i]].copy()) for i in range(B)]
+
     def fetch(self, n_imgs, kps=None, desc=None, counts=None):
         kps = np.zeros((n_imgs, self.cap), KP32) if kps is None else kps
         desc = np.zeros((n_imgs, self.cap, 4), np.uint64) if desc is None else desc
@@ -254,6 +283,22 @@ class Context:
         _check(lib().snk_stereo_match(self.c, C.byref(params), _p(left), _p(dl), len(left), _p(right), _p(dr),
                                       len(right), _p(rp), _p(dp), C.byref(n)))
         return n.value, rp[:len(left)], dp[:len(left)]
+
+    def undistortKeypoints(self, rect, kps):
+        """Preprocess::undistortKeypoints -> (undistorted_keypoints, normalized_points[n,2])."""
+        kps = np.ascontiguousarray(kps, KP64)
+        out = np.zeros(len(kps), KP64)
+        nrm = np.zeros((len(kps), 2), np.float64)
+        _check(lib().snk_undistort_keypoints(self.c, C.byref(rect), _p(kps), len(kps), _p(out), _p(nrm)))
+        return out, nrm
+
+    def computeGrayscaleImage(self, rgba):
+        """Input::computeGrayscaleImage: (rows, cols, 4) uint8 -> (rows, cols) uint8."""
+        assert rgba.dtype == np.uint8 and rgba.ndim == 3 and rgba.shape[2] == 4 and rgba.strides[1:] == (4, 1)
+        out = np.zeros(rgba.shape[:2], np.uint8)
+        _check(lib().snk_rgba_to_gray(self.c, _p(rgba), rgba.shape[0], rgba.shape[1], C.c_size_t(rgba.strides[0]),
+                                      _p(out), C.c_size_t(out.strides[0] if out.size else 0)))
+        return out
 
     def ComputeStereoFromRGBD(self, params, kp_un, depth_img):
         """Preprocess::ComputeStereoFromRGBD -> (matches, right_points, depth)."""

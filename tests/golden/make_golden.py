@@ -5,6 +5,8 @@
 * golden_cv.npz        — cv2 4.13.0 outputs of the three OpenCV calls on the path (resize / GaussianBlur / FAST)
 * golden_ref.npz       — outputs of the reference's own compiled ScalePyramid / AngleUmax / ComputeAngle /
                          ComputeDescriptor / Distribute / BruteForceMatcher (oracle/_ref)
+* golden_next.npz      — rows after the extractor: undistortKeypoints' per-point math from the
+                         reference's camera-model headers (`python tests/golden/make_golden.py next` makes only this)
 * golden_extract.npz   — end-to-end keypoints + descriptors of the tier-1 hybrid (tests/hybrid.py: ORBExtractor
                          driver with real cv2 + reference pieces) on seeded images of every BASELINE shape
 """
@@ -131,7 +133,71 @@ def make_extract():
     np.savez_compressed(os.path.join(HERE, "golden_extract.npz"), **out)
 
 
+RECT_CASES = {
+    # name: (K_src fx fy cx cy, D_src k1..k6 p1 p2, R quaternion x y z w (normalised below), K_dst fx fy cx cy s, w, h)
+    "euroc": ((458.654, 457.296, 367.215, 248.375), (-0.28340811, 0.07395907, 0, 0, 0, 0, 0.00019359, 1.76187114e-05),
+              (0.003, -0.007, 0.001, 1.0), (435.2, 435.2, 367.4, 252.2, 0.0), 752, 480),
+    "tum": ((517.3, 516.5, 318.6, 255.3), (0.2624, -0.9531, 1.1633, 0, 0, 0, -0.0054, 0.0026), (0, 0, 0, 1.0),
+            (517.3, 516.5, 318.6, 255.3, 0.0), 640, 480),
+    "rational": ((700.0, 705.0, 620.0, 188.0), (-0.2, 0.05, 0.01, 0.02, -0.01, 0.003, 0.001, -0.002),
+                 (0.01, 0.02, -0.03, 1.0), (690.0, 690.0, 610.0, 180.0, 0.5), 1241, 376),
+    "identity": ((500.0, 500.0, 320.0, 240.0), (0,) * 8, (0, 0, 0, 1.0), (500.0, 500.0, 320.0, 240.0, 0.0), 640, 480),
+}
+
+
+def rect_vector(case):
+    k, d, q, kd, _, _ = RECT_CASES[case]
+    q = np.array(q, np.float64)
+    q = q / np.sqrt((q * q).sum())
+    return np.array(list(k) + [0.0] + list(d) + list(q) + list(kd), np.float64)  # ref_shim.cpp layout, 22 doubles
+
+
+def make_next():
+    """Golden vectors for the rows after the extractor, from the reference's own headers compiled into
+    oracle/_ref: Preprocess::undistortKeypoints' per-point math."""
+    rng = np.random.default_rng(21)
+    out = {}
+    for case, spec in RECT_CASES.items():
+        w, h = spec[4], spec[5]
+        n = 400
+        xy = np.stack([rng.uniform(0, w - 1, n), rng.uniform(0, h - 1, n)], 1)
+        xy[:100] = np.round(xy[:100])  # level-0 keypoints are integers
+        xy[100] = (0, 0)
+        xy[101] = (w - 1, h - 1)
+        rect = rect_vector(case)
+        nrm, und = np.zeros(2 * n), np.zeros(2 * n)
+        R.ref_undistort_points(_p(rect), _p(xy), n, _p(nrm), _p(und))
+        out[f"und_{case}_rect"] = rect
+        out[f"und_{case}_xy"] = xy
+        out[f"und_{case}_normalized"] = nrm.reshape(n, 2)
+        out[f"und_{case}_undistorted"] = und.reshape(n, 2)
+    # Input::computeGrayscaleImage == cv2.cvtColor(COLOR_RGBA2GRAY): a seeded image with a padded pitch and a colour
+    # lattice; the fixed-point formula itself is checked here against cv2 for all 2^24 colours
+    v = np.arange(1 << 24, dtype=np.uint32)
+    cube = np.zeros((4096, 4096, 4), np.uint8)
+    for ch in range(3):
+        cube[..., ch] = ((v >> (8 * ch)) & 255).reshape(4096, 4096)
+    cube[..., 3] = 77
+    want = cv2.cvtColor(cube, cv2.COLOR_RGBA2GRAY)
+    c64 = cube.astype(np.int64)
+    assert np.array_equal(want, (c64[..., 0] * 9798 + c64[..., 1] * 19235 + c64[..., 2] * 3735 + (1 << 14)) >> 15)
+    rgba = rng.integers(0, 256, (61, 97, 4), dtype=np.uint8)
+    lat = np.stack(np.meshgrid(*[np.arange(0, 256, 17)] * 3, indexing="ij"), -1).reshape(64, 64, 3).astype(np.uint8)
+    lat = np.concatenate([lat, np.full((64, 64, 1), 255, np.uint8)], -1)
+    out.update(gray_rgba=rgba, gray_out=cv2.cvtColor(rgba, cv2.COLOR_RGBA2GRAY), gray_lattice=lat,
+               gray_lattice_out=cv2.cvtColor(lat, cv2.COLOR_RGBA2GRAY))
+    np.savez_compressed(os.path.join(HERE, "golden_next.npz"), **out)
+
+
 if __name__ == "__main__":
-    make_cv()
-    make_ref()
-    make_extract()
+    import sys
+
+    which = sys.argv[1:] or ["cv", "ref", "extract", "next"]
+    if "cv" in which:
+        make_cv()
+    if "ref" in which:
+        make_ref()
+    if "extract" in which:
+        make_extract()
+    if "next" in which:
+        make_next()

@@ -167,3 +167,39 @@ def test_async_fetch_equals_sync_fetch(so, oracle):
     for i in range(3):
         assert cnt[i] == len(want[i][0])
         assert kps[i, :cnt[i]].tobytes() == want[i][0].tobytes() and desc[i, :cnt[i]].tobytes() == want[i][1].tobytes()
+
+
+def test_rgba_input(so, oracle):
+    """Input::computeGrayscaleImage on the device: standalone conversion equals cv2's committed outputs and the
+    oracle on odd sizes / padded pitches; the fused RGBA entry of the extractor returns exactly what the grey entry
+    returns for the converted image."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_next.npz"))
+    ctx = so.Context()
+    assert np.array_equal(ctx.computeGrayscaleImage(np.ascontiguousarray(g["gray_rgba"])), g["gray_out"])
+    assert np.array_equal(ctx.computeGrayscaleImage(np.ascontiguousarray(g["gray_lattice"])), g["gray_lattice_out"])
+    rng = np.random.default_rng(3)
+    for rows, cols, padw in ((5, 1, 3), (33, 510, 515), (480, 752, 752), (100, 127, 127)):
+        wide = rng.integers(0, 256, (rows, padw, 4), dtype=np.uint8)
+        view = wide[:, :cols]
+        assert np.array_equal(ctx.computeGrayscaleImage(view), oracle.rgba_to_gray(view)), (rows, cols)
+    # fused path: colourised synthetic frames -> same keypoints/descriptors as the grey path
+    from snakeorb import synthetic as S
+
+    grey = np.stack([S.image(70 + i, 640, 480) for i in range(3)])
+    rgba = np.zeros((3, 480, 648, 4), np.uint8)  # padded rows
+    rgba[..., 0] = 255  # padding content must not matter
+    noise = rng.integers(-40, 40, (3, 480, 640, 3))
+    rgba[:, :, :640, :3] = np.clip(grey[..., None].astype(np.int64) + noise, 0, 255).astype(np.uint8)
+    rgba[:, :, :640, 3] = rng.integers(0, 256, (3, 480, 640), dtype=np.uint8)
+    view = rgba[:, :, :640]
+    conv = np.stack([oracle.rgba_to_gray(view[i]) for i in range(3)])
+    ex = so.ORBExtractor(1000, 1.2, 8, 20, 7, max_batch=4)
+    a = ex.DetectBatchRGBA(view)
+    b = ex.DetectBatch(conv)
+    for (ka, da), (kb, db) in zip(a, b):
+        assert len(ka) > 500 and ka.tobytes() == kb.tobytes() and da.tobytes() == db.tobytes()
+    # and against the oracle's extraction of the converted image
+    ko, do = oracle.Extractor(1000, 1.2, 8, 20, 7, 1).detect(conv[1])
+    assert np.array_equal(a[1][1], do) and np.array_equal(a[1][0]["x"], ko["x"])

@@ -226,3 +226,31 @@ def test_feature_grid(so, ctx, oracle, feats):
 def test_hamming_peak_probe(so, ctx):
     v = ctx.hamming_peak()
     assert 1e10 < v < 5e12
+
+
+def test_undistort_keypoints(so, ctx, oracle):
+    """Preprocess::undistortKeypoints on the device: bit-identical doubles to the oracle and to the committed
+    vectors of the reference's own headers, for the EuRoC / TUM / rational-model / identity rectifications."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_next.npz"))
+    rng = np.random.default_rng(9)
+    for case in ("euroc", "tum", "rational", "identity"):
+        rect = so.Rectify.from_vector(g[f"und_{case}_rect"])
+        xy = g[f"und_{case}_xy"]
+        kp = np.zeros(len(xy), so.KP64)
+        kp["x"], kp["y"] = xy[:, 0], xy[:, 1]
+        kp["size"], kp["angle"], kp["response"], kp["octave"] = 31, 12.5, 40, 2
+        un, nrm = ctx.undistortKeypoints(rect, kp)
+        assert nrm.tobytes() == g[f"und_{case}_normalized"].tobytes(), case
+        assert np.stack([un["x"], un["y"]], 1).tobytes() == g[f"und_{case}_undistorted"].tobytes(), case
+        assert np.array_equal(un["octave"], kp["octave"]) and np.array_equal(un["size"], kp["size"])
+        # a larger random set, points outside the image included (the GN step rejection path)
+        n = 20000
+        kp = np.zeros(n, so.KP64)
+        kp["x"], kp["y"] = rng.uniform(-50, 1300, n), rng.uniform(-50, 520, n)
+        un, nrm = ctx.undistortKeypoints(rect, kp)
+        un2, nrm2 = oracle.undistort_keypoints(rect, kp)
+        assert un.tobytes() == un2.tobytes() and nrm.tobytes() == nrm2.tobytes(), case
+    un, nrm = ctx.undistortKeypoints(rect, np.zeros(0, so.KP64))
+    assert len(un) == 0

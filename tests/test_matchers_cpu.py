@@ -170,3 +170,54 @@ def test_features_cache_roundtrip_and_reference_fixture(tmp_path):
         out = str(tmp_path / "copy.features")
         so.features_write(out, k, dd)
         assert open(out, "rb").read() == open(ref, "rb").read()  # byte-identical re-serialisation
+
+
+def _golden_next():
+    import os
+
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_next.npz"))
+
+
+def test_undistort_oracle_vs_golden(oracle):
+    """Preprocess::undistortKeypoints: the restatement reproduces, bit for bit, what the reference's own headers
+    (undistortPointGN + Eigen LDLT + quaternion rotation, compiled into oracle/_ref) returned for the committed
+    vectors (tests/golden/make_golden.py next)."""
+    import snakeorb as so
+
+    g = _golden_next()
+    for case in ("euroc", "tum", "rational", "identity"):
+        rect = so.Rectify.from_vector(g[f"und_{case}_rect"])
+        xy = g[f"und_{case}_xy"]
+        kp = np.zeros(len(xy), oracle.KP64)
+        kp["x"], kp["y"] = xy[:, 0], xy[:, 1]
+        kp["size"], kp["angle"], kp["response"], kp["octave"] = 31, 12.5, 40, 2
+        un, nrm = oracle.undistort_keypoints(rect, kp)
+        assert nrm.tobytes() == g[f"und_{case}_normalized"].tobytes(), case
+        assert np.stack([un["x"], un["y"]], 1).tobytes() == g[f"und_{case}_undistorted"].tobytes(), case
+        for f in ("size", "angle", "response", "octave"):
+            assert np.array_equal(un[f], kp[f])
+    # identity rectification maps every point onto itself up to rounding
+    xy = g["und_identity_xy"]
+    assert np.abs(g["und_identity_undistorted"] - xy).max() < 1e-9
+
+
+def test_undistort_oracle_vs_reference_random(oracle, refso):
+    """Same comparison against the compiled reference on fresh random points, strong distortion included."""
+    import ctypes as C
+
+    import snakeorb as so
+
+    rng = np.random.default_rng(33)
+    g = _golden_next()
+    for case in ("euroc", "rational"):
+        v = g[f"und_{case}_rect"].copy()
+        v[5:13] *= 1.5
+        n = 3000
+        xy = np.stack([rng.uniform(-20, 1300, n), rng.uniform(-20, 500, n)], 1)
+        kp = np.zeros(n, oracle.KP64)
+        kp["x"], kp["y"] = xy[:, 0], xy[:, 1]
+        un, nrm = oracle.undistort_keypoints(so.Rectify.from_vector(v), kp)
+        n2, u2 = np.zeros((n, 2)), np.zeros((n, 2))
+        refso.ref_undistort_points(C.c_void_p(v.ctypes.data), C.c_void_p(xy.ctypes.data), n, C.c_void_p(n2.ctypes.data),
+                                   C.c_void_p(u2.ctypes.data))
+        assert nrm.tobytes() == n2.tobytes() and np.stack([un["x"], un["y"]], 1).tobytes() == u2.tobytes()

@@ -179,3 +179,16 @@ def test_live_hybrid_vs_oracle(oracle, refso):
     k, d, _ = hybrid.hybrid_detect(img, 700, 1.2, 6, 20, 7)
     k2, d2 = oracle.Extractor(700, 1.2, 6, 20, 7, 1).detect(img)
     assert k.tobytes() == k2.tobytes() and d.tobytes() == d2.tobytes()
+
+
+def test_rgba_to_gray_vs_cv2_golden(oracle):
+    """Input::computeGrayscaleImage: the restated fixed-point conversion against cv2 4.13's cvtColor outputs
+    (tests/golden/make_golden.py next also checks the formula exhaustively over all 2^24 colours)."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_next.npz"))
+    assert np.array_equal(oracle.rgba_to_gray(np.ascontiguousarray(g["gray_rgba"])), g["gray_out"])
+    assert np.array_equal(oracle.rgba_to_gray(np.ascontiguousarray(g["gray_lattice"])), g["gray_lattice_out"])
+    wide = np.zeros((61, 120, 4), np.uint8)
+    wide[:, :97] = g["gray_rgba"]
+    assert np.array_equal(oracle.rgba_to_gray(wide[:, :97]), g["gray_out"])  # padded pitch
