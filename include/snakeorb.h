@@ -381,6 +381,28 @@ SNK_API int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t
                           const snk_featvec_view* fv1, const snk_featvec_view* fv2, const uint8_t* valid1,
                           const uint8_t* valid2, int th, float ratio, int32_t* match12, int* n_matches);
 
+/* MiniBow2::TemplatedVocabulary (saiga/vision/slam/MiniBow2.h): the vocabulary tree on the device.
+ * snk_voc_load_raw reads the file format of loadRaw/saveRaw (:1020-1075: k, L, two unused ints, u64 node count,
+ * per node {i32 id, i32 parent, f64 weight, i32 word_id, 32-byte descriptor}, then the word table, which is
+ * redundant and ignored). snk_voc_create takes the same per-node arrays (node 0 = root, node id = array index,
+ * children in index order — what loadRaw builds). Fails like loadRaw when the file cannot be opened. */
+typedef struct snk_voc snk_voc;
+SNK_API int snk_voc_load_raw(int device, const char* path, snk_voc** out);
+SNK_API int snk_voc_create(int device, int k, int L, int n_nodes, const int32_t* parent, const double* weight,
+                           const int32_t* word_id, const uint64_t* desc, snk_voc** out);
+SNK_API void snk_voc_destroy(snk_voc* v);
+SNK_API int snk_voc_info(const snk_voc* v, int* k, int* L, int* n_nodes, int* n_words);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (MiniBow2.h:883-983), as
+ * Frame::computeBoW calls it. BowVector: (word id, L1-normalised weight) ascending in bow_ids / bow_vals;
+ * FeatureVector: CSR as in snk_featvec_view (node ids ascending, offsets[n_nodes + 1], feature indices in the
+ * reference's list order — the order its unstable std::sort leaves, reproduced exactly). Features that land on a
+ * word of weight <= 0 are in neither. Output arrays need n entries (fv_offsets n + 1). n <= 8192. */
+#define SNK_BOW_MAX_FEATURES 8192
+SNK_API int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int n, int levelsup,
+                              int32_t* bow_ids, float* bow_vals, int* n_bow, int32_t* fv_node_ids,
+                              int32_t* fv_offsets, int32_t* fv_indices, int* n_fv_nodes);
+
 /* The reference's feature cache (Snake/Preprocess/FeatureDetector.cpp:97-111 read, :134-139 write; settings
  * fd_bufferToFile), a saiga BinaryFile dump (saiga/core/util/BinaryFile.h:30-78): u64 n, n x KeyPoint<double>
  * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of

@@ -12,6 +12,7 @@
 
 using namespace orbref;
 
+#include "bow_ref.h"
 extern "C" {
 #define ORC_API __attribute__((visibility("default")))
 
@@ -183,4 +184,49 @@ ORC_API int orc_match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int n2
 {
     return match_bow(d1, n1, d2, n2, fv1, fv2, v1, v2, th, ratio, m12, ops);
 }
+
+// ---- MiniBow2 ----
+ORC_API void* orc_voc_load_raw(const char* path)
+{
+    auto* v = new bowref::Vocabulary;
+    if (!v->load_raw(path))
+    {
+        delete v;
+        return nullptr;
+    }
+    return v;
 }
+ORC_API void* orc_voc_from_arrays(int k, int L, int n, const int32_t* parent, const double* weight, const int32_t* word_id,
+                                  const uint64_t* desc)
+{
+    auto* v = new bowref::Vocabulary;
+    if (!v->from_arrays(k, L, n, parent, weight, word_id, desc))
+    {
+        delete v;
+        return nullptr;
+    }
+    return v;
+}
+ORC_API int orc_voc_save_raw(void* v, const char* path) { return ((bowref::Vocabulary*)v)->save_raw(path) ? 0 : 1; }
+ORC_API void orc_voc_destroy(void* v) { delete (bowref::Vocabulary*)v; }
+ORC_API void orc_voc_info(void* v, int* out4)
+{
+    auto* p = (bowref::Vocabulary*)v;
+    out4[0] = p->k, out4[1] = p->L, out4[2] = (int)p->parent.size(), out4[3] = p->n_words;
+}
+ORC_API void orc_bow_transform(void* v, const uint64_t* desc, int n, int levelsup, int32_t* bow_ids, float* bow_vals,
+                               int* n_bow, int32_t* fv_nodes, int32_t* fv_offsets, int32_t* fv_indices, int* n_fv)
+{
+    std::vector<int32_t> bi, fn, fo, fi;
+    std::vector<float> bv;
+    bowref::transform(*(bowref::Vocabulary*)v, desc, n, levelsup, bi, bv, fn, fo, fi);
+    *n_bow = (int)bi.size(), *n_fv = (int)fn.size();
+    std::copy(bi.begin(), bi.end(), bow_ids), std::copy(bv.begin(), bv.end(), bow_vals);
+    std::copy(fn.begin(), fn.end(), fv_nodes), std::copy(fo.begin(), fo.end(), fv_offsets);
+    std::copy(fi.begin(), fi.end(), fv_indices);
+}
+ORC_API float orc_bow_score(const int32_t* ids1, const float* v1, int n1, const int32_t* ids2, const float* v2, int n2)
+{
+    return bowref::score(ids1, v1, n1, ids2, v2, n2);
+}
+}  // extern "C"

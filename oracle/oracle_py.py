@@ -277,3 +277,52 @@ def feature_grid(bounds, kp_un):
     cells = np.zeros((bounds.rows * bounds.cols, 2), np.int32)
     lib().orc_feature_grid(C.byref(bounds), _p(kp_un), len(kp_un), _p(perm), _p(cells))
     return perm[:len(kp_un)], cells
+
+
+class Vocabulary:
+    """bowref::Vocabulary == MiniBow2::TemplatedVocabulary restated (oracle/bow_ref.cpp)."""
+
+    def __init__(self, path=None, arrays=None):
+        lib().orc_voc_load_raw.restype = C.c_void_p
+        lib().orc_voc_from_arrays.restype = C.c_void_p
+        lib().orc_bow_score.restype = C.c_float
+        if path is not None:
+            self.h = C.c_void_p(lib().orc_voc_load_raw(path.encode()))
+        else:
+            k, L, parent, weight, word_id, desc = arrays
+            parent = np.ascontiguousarray(parent, np.int32)
+            weight = np.ascontiguousarray(weight, np.float64)
+            word_id = np.ascontiguousarray(word_id, np.int32)
+            desc = np.ascontiguousarray(desc, np.uint64)
+            self.h = C.c_void_p(lib().orc_voc_from_arrays(k, L, len(parent), _p(parent), _p(weight), _p(word_id), _p(desc)))
+        if not self.h:
+            raise ValueError("bad vocabulary")
+        o = np.zeros(4, np.int32)
+        lib().orc_voc_info(self.h, _p(o))
+        self.k, self.L, self.n_nodes, self.n_words = [int(x) for x in o]
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_voc_destroy(self.h)
+            self.h = None
+
+    def save_raw(self, path):
+        assert lib().orc_voc_save_raw(self.h, path.encode()) == 0
+
+    def transform(self, desc, levelsup):
+        """-> bow_ids, bow_vals, fv_nodes, fv_offsets, fv_indices"""
+        desc = np.ascontiguousarray(desc, np.uint64).reshape(-1, 4)
+        n = len(desc)
+        ids, vals = np.zeros(n + 1, np.int32), np.zeros(n + 1, np.float32)
+        fn, fo, fi = np.zeros(n + 1, np.int32), np.zeros(n + 2, np.int32), np.zeros(n + 1, np.int32)
+        nb, nf = C.c_int(), C.c_int()
+        lib().orc_bow_transform(self.h, _p(desc), n, levelsup, _p(ids), _p(vals), C.byref(nb), _p(fn), _p(fo), _p(fi),
+                                C.byref(nf))
+        return ids[:nb.value], vals[:nb.value], fn[:nf.value], fo[:nf.value + 1], fi[:fo[nf.value]]
+
+
+def bow_score(ids1, v1, ids2, v2):
+    lib().orc_bow_score.restype = C.c_float
+    ids1, ids2 = np.ascontiguousarray(ids1, np.int32), np.ascontiguousarray(ids2, np.int32)
+    v1, v2 = np.ascontiguousarray(v1, np.float32), np.ascontiguousarray(v2, np.float32)
+    return float(lib().orc_bow_score(_p(ids1), _p(v1), len(ids1), _p(ids2), _p(v2), len(ids2)))

@@ -161,3 +161,62 @@ REF_API void ref_undistort_points(const double* rect, const double* xy, int n, d
         undistorted[2 * i + 1] = p(1);
     }
 }
+
+// ---- MiniBow2 vocabulary: the reference's own tree builder, file format and transform -------------------------
+#include "saiga/vision/slam/MiniBow2.h"
+// trains a vocabulary with the reference's create() (k-means++ seeded by rand()) and writes it with saveRaw()
+REF_API int ref_voc_create(const uint64_t* desc, const int* counts, int n_images, int k, int L, unsigned seed,
+                           const char* out_path)
+{
+    std::vector<std::vector<MiniBow2::Descriptor>> training(n_images);
+    size_t at = 0;
+    for (int i = 0; i < n_images; ++i)
+    {
+        training[i].resize(counts[i]);
+        std::memcpy(training[i].data(), desc + 4 * at, 32 * (size_t)counts[i]);
+        at += counts[i];
+    }
+    srand(seed);
+    MiniBow2::TemplatedVocabulary<MiniBow2::Descriptor> voc(k, L);
+    voc.create(training);
+    voc.saveRaw(out_path);
+    return (int)voc.size();
+}
+// loadRaw() + transform(); BowVector as (id, value) arrays, FeatureVector as CSR in list order
+REF_API int ref_voc_transform(const char* voc_path, const uint64_t* desc, int n, int levelsup, int* bow_ids,
+                              float* bow_vals, int* n_bow, int* fv_nodes, int* fv_offsets, int* fv_indices, int* n_fv)
+{
+    static std::string loaded;
+    static MiniBow2::TemplatedVocabulary<MiniBow2::Descriptor>* voc = nullptr;
+    if (loaded != voc_path)
+    {
+        delete voc;
+        voc    = new MiniBow2::TemplatedVocabulary<MiniBow2::Descriptor>(std::string(voc_path));
+        loaded = voc_path;
+    }
+    std::vector<MiniBow2::Descriptor> f(n);
+    std::memcpy(f.data(), desc, 32 * (size_t)n);
+    MiniBow2::BowVector bv;
+    MiniBow2::FeatureVector fv;
+    voc->transform(f, bv, fv, levelsup, 1);
+    *n_bow = (int)bv.size();
+    for (size_t i = 0; i < bv.size(); ++i) bow_ids[i] = bv[i].first, bow_vals[i] = bv[i].second;
+    *n_fv  = (int)fv.size();
+    int at = 0;
+    for (size_t i = 0; i < fv.size(); ++i)
+    {
+        fv_nodes[i]   = fv[i].first;
+        fv_offsets[i] = at;
+        for (int idx : fv[i].second) fv_indices[at++] = idx;
+    }
+    fv_offsets[fv.size()] = at;
+    return (int)voc->size();
+}
+// FeatureVector::score (MiniBow2.h:134-170) on two BowVectors
+REF_API float ref_bow_score(const int* ids1, const float* v1, int n1, const int* ids2, const float* v2, int n2)
+{
+    MiniBow2::BowVector a, b;
+    for (int i = 0; i < n1; ++i) a.push_back({ids1[i], v1[i]});
+    for (int i = 0; i < n2; ++i) b.push_back({ids2[i], v2[i]});
+    return MiniBow2::FeatureVector::score(a, b);
+}

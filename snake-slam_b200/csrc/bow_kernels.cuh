@@ -1,0 +1,355 @@
+// MiniBow2::TemplatedVocabulary::transform on the device (saiga/vision/slam/MiniBow2.h:883-983).
+//
+//   k_bow_descend   greedy descent of the vocabulary tree, 16 lanes per descriptor, children of a node contiguous
+//   k_bow_assemble  one CTA per frame: FeatureVector::setFeatures and BowVector::set/normalize
+//
+// The reference sorts the (node id, feature index) pairs with std::sort on the node id alone; std::sort is unstable
+// and the node ids repeat heavily, so the order of the features inside a node — which later decides the candidate
+// order of the BoW matchers — is whatever libstdc++'s introsort leaves behind. That permutation is reproduced
+// exactly, in parallel:
+//   * introsort's partition phase only depends on comparison outcomes. The sub-ranges of one recursion level are
+//     disjoint, so they are partitioned concurrently, one warp per range, level by level (the depth budget that
+//     triggers the heapsort fallback travels with each range).
+//   * one unguarded Hoare partition is data parallel once written on the ORIGINAL range: with l_1 < l_2 < ... the
+//     positions whose value is not before the pivot and r_1 > r_2 > ... those the pivot is not before, the serial
+//     loop swaps (l_t, r_t) for t = 1..T, T = #{t : l_t < r_t}, and returns min(l_{T+1}, r_T) (l_1 if T = 0).
+//   * the closing insertion pass is a stable sort by node id: a bitonic sort on (node id, position after the
+//     partition phase).
+// tests/test_gpu_bow.py compares against std::sort through the oracle on tie-heavy inputs of every size class.
+#pragma once
+#include "common.cuh"
+#include "gnu_sort.cuh"
+
+namespace snk
+{
+struct VocDev
+{
+    int k, L, n_nodes, n_words;
+    const int* child_begin;    // [n_nodes + 1] CSR over the children, in loadRaw's order
+    const int* child_id;       // [n_nodes - 1] node id per CSR slot
+    const uint4* child_desc;   // [2 * (n_nodes - 1)] descriptor per CSR slot (children of a node are contiguous)
+    const float* weight;       // [n_nodes]
+    const int* word_id;        // [n_nodes]
+};
+
+constexpr int BOW_MAX_FEATURES = 8192;
+
+// ---- descent: transform(feature, levelsup), MiniBow2.h:937-983 --------------------------------------------------
+// words[i] = (word id or -1) << 32 | weight bits;  feats[i] = (node id or -1) << 32 | i
+__global__ void __launch_bounds__(256) k_bow_descend(VocDev V, const uint4* __restrict__ desc, int n, int levelsup,
+                                                     unsigned long long* __restrict__ words,
+                                                     unsigned long long* __restrict__ feats)
+{
+    const int sub = threadIdx.x & 15;
+    const int i   = (blockIdx.x * 256 + threadIdx.x) >> 4;
+    const unsigned group = 0xffffu << (threadIdx.x & 16);
+    if (i >= n) return;  // whole 16-lane groups leave together
+    const uint4 a = desc[2 * i], b = desc[2 * i + 1];
+    const int nid_level = V.L - levelsup;
+    int node = 0, nid = 0, level = 0;
+    int begin = V.child_begin[0], cnt = V.child_begin[1] - begin;
+    do
+    {
+        ++level;
+        unsigned best = 0xffffffffu;  // distance << 20 | child slot: the first minimum wins (strict < at :961)
+        for (int c0 = 0; c0 < cnt; c0 += 16)
+        {
+            const int c = c0 + sub;
+            if (c < cnt)
+            {
+                const uint4 p = V.child_desc[2 * (begin + c)], q = V.child_desc[2 * (begin + c) + 1];
+                const int d = __popc(a.x ^ p.x) + __popc(a.y ^ p.y) + __popc(a.z ^ p.z) + __popc(a.w ^ p.w) +
+                              __popc(b.x ^ q.x) + __popc(b.y ^ q.y) + __popc(b.z ^ q.z) + __popc(b.w ^ q.w);
+                best = min(best, ((unsigned)d << 20) | (unsigned)c);
+            }
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(group, best, o));
+        node  = V.child_id[begin + (best & 0xfffffu)];
+        begin = V.child_begin[node];
+        cnt   = V.child_begin[node + 1] - begin;
+        if (level == nid_level) nid = node;
+    } while (cnt > 0);
+    if (sub == 0)
+    {
+        const float w = V.weight[node];
+        const int wid = (w > 0.f) ? V.word_id[node] : -1;
+        const int fn  = (w > 0.f) ? nid : -1;
+        words[i] = ((unsigned long long)(unsigned)wid << 32) | __float_as_uint(w);
+        feats[i] = ((unsigned long long)(unsigned)fn << 32) | (unsigned)i;
+    }
+}
+
+// ---- one exact libstdc++ partition step by a warp ------------------------------------------------------------
+// v[first, last) with last - first > 16; returns the cut of std::__unguarded_partition_pivot. Lp / Rq: scratch with
+// one u16 per element of the range (indexed like v).
+template <class C>
+__device__ int warp_partition_pivot(unsigned long long* v, int first, int last, uint16_t* Lp, uint16_t* Rq, int lane)
+{
+    if (lane == 0) gnusort::median_to_first<unsigned long long, C>(v, first, first + 1, first + (last - first) / 2, last - 1);
+    __syncwarp();
+    const unsigned long long P = v[first];
+    const int s = first + 1, e = last;
+    const unsigned lt = (1u << lane) - 1u;
+    int nL = 0, nR = 0;
+    for (int base = s; base < e; base += 32)
+    {
+        const int i      = base + lane;
+        const bool valid = i < e;
+        const unsigned long long x = valid ? v[i] : 0ull;
+        const bool isL = valid && !C::before(x, P), isR = valid && !C::before(P, x);
+        const unsigned mL = __ballot_sync(0xffffffffu, isL), mR = __ballot_sync(0xffffffffu, isR);
+        if (isL) Lp[s + nL + __popc(mL & lt)] = (uint16_t)i;
+        if (isR) Rq[s + nR + __popc(mR & lt)] = (uint16_t)i;
+        nL += __popc(mL);
+        nR += __popc(mR);
+    }
+    __syncwarp();
+    // T = number of leading t with l_t < r_t (monotone: l increases, r decreases)
+    const int m = min(nL, nR);
+    int T = 0;
+    for (int base = 0; base < m; base += 32)
+    {
+        const int t   = base + lane;
+        const bool ok = t < m && Lp[s + t] < Rq[s + nR - 1 - t];
+        const unsigned bm = __ballot_sync(0xffffffffu, ok);
+        if (bm == 0xffffffffu)
+            T += 32;
+        else
+        {
+            T += __ffs(~bm) - 1;
+            break;
+        }
+    }
+    for (int t = lane; t < T; t += 32)
+    {
+        const int a = Lp[s + t], b = Rq[s + nR - 1 - t];
+        const unsigned long long x = v[a];
+        v[a] = v[b];
+        v[b] = x;
+    }
+    int cut;
+    if (T == 0)
+        cut = Lp[s];
+    else
+    {
+        const int rT = Rq[s + nR - T];
+        cut          = (T < nL && Lp[s + T] < rT) ? (int)Lp[s + T] : rT;
+    }
+    __syncwarp();
+    return cut;
+}
+
+// bitonic sort of np2 (power of two) 64-bit keys in shared memory by the whole CTA
+__device__ __forceinline__ void cta_bitonic_u64(unsigned long long* key, int np2, int tid, int nt)
+{
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1)
+        {
+            for (int i = tid; i < np2; i += nt)
+            {
+                const int ixj = i ^ j;
+                if (ixj > i)
+                {
+                    const unsigned long long a = key[i], b = key[ixj];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up)
+                    {
+                        key[i]   = b;
+                        key[ixj] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+}
+
+constexpr int BOW_NT = 256;
+constexpr int BOW_SEG_MAX = 512;  // ranges of more than 16 elements in an array of <= 8192
+
+// exclusive rank of `flag` among the threads of the CTA for one 256-wide chunk; total returned in *total
+__device__ __forceinline__ int cta_rank(bool flag, int tid, int* s_warp, int* total)
+{
+    const unsigned m = __ballot_sync(0xffffffffu, flag);
+    const int lane = tid & 31, wid = tid >> 5;
+    if (lane == 0) s_warp[wid] = __popc(m);
+    __syncthreads();
+    int before = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < BOW_NT / 32; ++w)
+    {
+        const int c = s_warp[w];
+        if (w < wid) before += c;
+        all += c;
+    }
+    __syncthreads();
+    *total = all;
+    return before + __popc(m & ((1u << lane) - 1u));
+}
+
+// dynamic shared memory: key[np2] u64 | Lp[np2] u16 | Rq[np2] u16 (the two u16 arrays are reused as np2 floats)
+__global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long long* __restrict__ words,
+                                                          const unsigned long long* __restrict__ feats, int n, int np2,
+                                                          int* __restrict__ bow_ids, float* __restrict__ bow_vals,
+                                                          int* __restrict__ fv_nodes, int* __restrict__ fv_offsets,
+                                                          int* __restrict__ fv_indices, int* __restrict__ counts)
+{
+    extern __shared__ __align__(16) unsigned char bow_smem[];
+    unsigned long long* key = reinterpret_cast<unsigned long long*>(bow_smem);
+    uint16_t* Lp            = reinterpret_cast<uint16_t*>(key + np2);
+    uint16_t* Rq            = Lp + np2;
+    float* vals             = reinterpret_cast<float*>(Lp);
+    __shared__ uint2 segs[2][BOW_SEG_MAX];
+    __shared__ int nseg[2];
+    __shared__ int s_warp[BOW_NT / 32];
+    __shared__ int s_n;
+    __shared__ float s_norm;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    using Cmp = gnusort::AscHigh32;
+
+    // ================= FeatureVector::setFeatures (MiniBow2.h:101-126) =================
+    for (int i = tid; i < n; i += BOW_NT) key[i] = feats[i];
+    if (tid == 0)
+    {
+        int lg = 0;
+        while ((n >> (lg + 1)) != 0) ++lg;
+        nseg[0] = nseg[1] = 0;
+        if (n > 16)
+        {
+            segs[0][0] = make_uint2((unsigned)n << 16, (unsigned)(2 * lg));  // first = 0 | last << 16, depth budget
+            nseg[0]    = 1;
+        }
+    }
+    __syncthreads();
+    // introsort's partition phase, one recursion level per round
+    for (int cur = 0; nseg[cur] > 0; cur ^= 1)
+    {
+        const int ns = nseg[cur];
+        for (int sidx = wid; sidx < ns; sidx += BOW_NT / 32)
+        {
+            const uint2 sg  = segs[cur][sidx];
+            const int first = (int)(sg.x & 0xffffu), last = (int)(sg.x >> 16);
+            int depth       = (int)sg.y;
+            if (depth == 0)
+            {
+                if (lane == 0) gnusort::heap_sort<unsigned long long, Cmp>(key, first, last);  // __partial_sort(first, last, last)
+                __syncwarp();
+                continue;
+            }
+            --depth;
+            const int cut = warp_partition_pivot<Cmp>(key, first, last, Lp, Rq, lane);
+            if (lane == 0)
+            {
+                if (last - cut > 16) segs[cur ^ 1][atomicAdd(&nseg[cur ^ 1], 1)] = make_uint2((unsigned)cut | ((unsigned)last << 16), depth);
+                if (cut - first > 16) segs[cur ^ 1][atomicAdd(&nseg[cur ^ 1], 1)] = make_uint2((unsigned)first | ((unsigned)cut << 16), depth);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) nseg[cur] = 0;
+        __syncthreads();
+    }
+    // the insertion pass is a stable sort by node id: (node id + 1) << 26 | position << 13 | feature index
+    for (int i = tid; i < np2; i += BOW_NT)
+    {
+        unsigned long long k2 = ~0ull;
+        if (i < n)
+        {
+            const unsigned long long k1 = key[i];
+            const unsigned long long id1 = (unsigned long long)((long long)(int)(k1 >> 32) + 1);
+            k2 = (id1 << 26) | ((unsigned long long)i << 13) | (k1 & 0x1fffull);
+        }
+        key[i] = k2;  // slot i is read and written by this thread only
+    }
+    __syncthreads();
+    cta_bitonic_u64(key, np2, tid, BOW_NT);
+    {
+        // entries of zero-weight words (id -1 -> 0) sort first and are skipped (:111)
+        int skip_local = 0;
+        for (int i = tid; i < n; i += BOW_NT) skip_local += ((key[i] >> 26) == 0ull);
+        skip_local = warp_sum(skip_local);
+        if (tid == 0) s_n = 0;
+        __syncthreads();
+        if (lane == 0 && skip_local) atomicAdd(&s_n, skip_local);
+        __syncthreads();
+        const int skip = s_n;
+        __syncthreads();
+        int nodes_before = 0;
+        for (int base = 0; base < n; base += BOW_NT)
+        {
+            const int i = base + tid;
+            bool head = false;
+            int id = 0;
+            if (i < n && i >= skip)
+            {
+                id   = (int)(key[i] >> 26) - 1;
+                head = (i == skip) || ((int)(key[i - 1] >> 26) - 1 != id);
+                fv_indices[i - skip] = (int)(key[i] & 0x1fffull);
+            }
+            int total;
+            const int r = cta_rank(head, tid, s_warp, &total);
+            if (head)
+            {
+                fv_nodes[nodes_before + r]   = id;
+                fv_offsets[nodes_before + r] = i - skip;
+            }
+            nodes_before += total;
+        }
+        if (tid == 0)
+        {
+            fv_offsets[nodes_before] = n - skip;
+            counts[1]                = nodes_before;
+        }
+    }
+    __syncthreads();
+
+    // ================= BowVector::set + normalize (MiniBow2.h:46-93) =================
+    // equal word ids carry equal weights, so the order std::sort leaves inside a word does not influence the sums
+    for (int i = tid; i < np2; i += BOW_NT)
+    {
+        unsigned long long k2 = ~0ull;
+        if (i < n)
+        {
+            const unsigned long long w = words[i];
+            k2 = ((unsigned long long)((long long)(int)(w >> 32) + 1) << 32) | (w & 0xffffffffull);
+        }
+        key[i] = k2;
+    }
+    __syncthreads();
+    cta_bitonic_u64(key, np2, tid, BOW_NT);
+    int words_before = 0;
+    for (int base = 0; base < n; base += BOW_NT)
+    {
+        const int i = base + tid;
+        bool head = false;
+        unsigned id1 = 0;
+        if (i < n)
+        {
+            id1  = (unsigned)(key[i] >> 32);
+            head = id1 != 0u && (i == 0 || (unsigned)(key[i - 1] >> 32) != id1);
+        }
+        int total;
+        const int r = cta_rank(head, tid, s_warp, &total);
+        if (head)
+        {
+            // back().second += f.second once per further occurrence, in float (:66)
+            const float w = __uint_as_float((unsigned)key[i]);
+            float acc     = w;
+            for (int j = i + 1; j < n && (unsigned)(key[j] >> 32) == id1; ++j) acc += w;
+            bow_ids[words_before + r] = (int)id1 - 1;
+            vals[words_before + r]    = acc;
+        }
+        words_before += total;
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+        float norm = 0.f;
+        for (int i = 0; i < words_before; ++i) norm += fabsf(vals[i]);  // serial, in ascending word order (:86)
+        s_norm    = norm;
+        counts[0] = words_before;
+    }
+    __syncthreads();
+    const float norm = s_norm;
+    for (int i = tid; i < words_before; i += BOW_NT) bow_vals[i] = (norm > 0.f) ? vals[i] / norm : vals[i];
+}
+}  // namespace snk

@@ -10,34 +10,50 @@
 // the same places as sorting the node structs. Keys are (count << SHIFT | slot), SHIFT = 12: up to 4096 nodes per
 // sort (the node lists never exceed quota + 8 entries) and counts below 2^20.
 //
+// The functions are templates over the key type K and an ordering C (C::before(a, b) == "a sorts before b") so that
+// other unstable std::sort calls of the reference can reuse them: MiniBow2's FeatureVector::setFeatures sorts
+// (node id, feature index) pairs by node id alone (saiga/vision/slam/MiniBow2.h:104), see bow_kernels.cuh.
+//
 // tools/check_gnu_sort.cpp runs this code on the host against std::sort on millions of tie-heavy arrays.
 #pragma once
 #include <stdint.h>
 
 #if defined(__CUDACC__)
 #    define SNK_SORT_HD __host__ __device__ __forceinline__
+#    define SNK_SORT_MEMBER static __host__ __device__ __forceinline__
 #else
 #    define SNK_SORT_HD static inline
+#    define SNK_SORT_MEMBER static inline
 #endif
 
 namespace gnusort
 {
 constexpr int SHIFT = 12;
-// "a before b": descending count, count in the bits above SHIFT
-SNK_SORT_HD bool before(uint32_t a, uint32_t b) { return (a >> SHIFT) > (b >> SHIFT); }
-
-SNK_SORT_HD void swp(uint32_t* v, int i, int j)
+// the distributor's order: descending count, count in the bits above SHIFT
+struct DescCount
 {
-    uint32_t t = v[i];
+    SNK_SORT_MEMBER bool before(uint32_t a, uint32_t b) { return (a >> SHIFT) > (b >> SHIFT); }
+};
+// ascending signed high word of a 64-bit key (payload in the low word)
+struct AscHigh32
+{
+    SNK_SORT_MEMBER bool before(uint64_t a, uint64_t b) { return (int32_t)(a >> 32) < (int32_t)(b >> 32); }
+};
+
+template <class K, class C>
+SNK_SORT_HD void swp(K* v, int i, int j)
+{
+    K t = v[i];
     v[i]       = v[j];
     v[j]       = t;
 }
 
-SNK_SORT_HD void linear_insert_unguarded(uint32_t* v, int last)
+template <class K, class C>
+SNK_SORT_HD void linear_insert_unguarded(K* v, int last)
 {
-    uint32_t val = v[last];
+    K val = v[last];
     int next     = last - 1;
-    while (before(val, v[next]))
+    while (C::before(val, v[next]))
     {
         v[last] = v[next];
         last    = next;
@@ -46,26 +62,28 @@ SNK_SORT_HD void linear_insert_unguarded(uint32_t* v, int last)
     v[last] = val;
 }
 
-SNK_SORT_HD void insertion(uint32_t* v, int first, int last)
+template <class K, class C>
+SNK_SORT_HD void insertion(K* v, int first, int last)
 {
     if (first == last) return;
     for (int i = first + 1; i != last; ++i)
     {
-        if (before(v[i], v[first]))
+        if (C::before(v[i], v[first]))
         {
-            uint32_t val = v[i];
+            K val = v[i];
             for (int k = i; k > first; --k) v[k] = v[k - 1];
             v[first] = val;
         }
         else
-            linear_insert_unguarded(v, i);
+            linear_insert_unguarded<K, C>(v, i);
     }
 }
 
-SNK_SORT_HD void push_heap(uint32_t* v, int first, int hole, int top, uint32_t value)
+template <class K, class C>
+SNK_SORT_HD void push_heap(K* v, int first, int hole, int top, K value)
 {
     int parent = (hole - 1) / 2;
-    while (hole > top && before(v[first + parent], value))
+    while (hole > top && C::before(v[first + parent], value))
     {
         v[first + hole] = v[first + parent];
         hole            = parent;
@@ -74,14 +92,15 @@ SNK_SORT_HD void push_heap(uint32_t* v, int first, int hole, int top, uint32_t v
     v[first + hole] = value;
 }
 
-SNK_SORT_HD void adjust_heap(uint32_t* v, int first, int hole, int len, uint32_t value)
+template <class K, class C>
+SNK_SORT_HD void adjust_heap(K* v, int first, int hole, int len, K value)
 {
     const int top = hole;
     int second    = hole;
     while (second < (len - 1) / 2)
     {
         second = 2 * (second + 1);
-        if (before(v[first + second], v[first + second - 1])) --second;
+        if (C::before(v[first + second], v[first + second - 1])) --second;
         v[first + hole] = v[first + second];
         hole            = second;
     }
@@ -91,10 +110,11 @@ SNK_SORT_HD void adjust_heap(uint32_t* v, int first, int hole, int len, uint32_t
         v[first + hole] = v[first + second - 1];
         hole            = second - 1;
     }
-    push_heap(v, first, hole, top, value);
+    push_heap<K, C>(v, first, hole, top, value);
 }
 
-SNK_SORT_HD void heap_sort(uint32_t* v, int first, int last)
+template <class K, class C>
+SNK_SORT_HD void heap_sort(K* v, int first, int last)
 {
     const int len = last - first;
     if (len >= 2)
@@ -102,8 +122,8 @@ SNK_SORT_HD void heap_sort(uint32_t* v, int first, int last)
         int parent = (len - 2) / 2;
         while (true)
         {
-            uint32_t value = v[first + parent];
-            adjust_heap(v, first, parent, len, value);
+            K value = v[first + parent];
+            adjust_heap<K, C>(v, first, parent, len, value);
             if (parent == 0) break;
             --parent;
         }
@@ -111,43 +131,45 @@ SNK_SORT_HD void heap_sort(uint32_t* v, int first, int last)
     while (last - first > 1)
     {
         --last;
-        uint32_t value = v[last];
+        K value = v[last];
         v[last]        = v[first];
-        adjust_heap(v, first, 0, last - first, value);
+        adjust_heap<K, C>(v, first, 0, last - first, value);
     }
 }
 
-SNK_SORT_HD void median_to_first(uint32_t* v, int result, int a, int b, int c)
+template <class K, class C>
+SNK_SORT_HD void median_to_first(K* v, int result, int a, int b, int c)
 {
-    if (before(v[a], v[b]))
+    if (C::before(v[a], v[b]))
     {
-        if (before(v[b], v[c]))
-            swp(v, result, b);
-        else if (before(v[a], v[c]))
-            swp(v, result, c);
+        if (C::before(v[b], v[c]))
+            swp<K, C>(v, result, b);
+        else if (C::before(v[a], v[c]))
+            swp<K, C>(v, result, c);
         else
-            swp(v, result, a);
+            swp<K, C>(v, result, a);
     }
-    else if (before(v[a], v[c]))
-        swp(v, result, a);
-    else if (before(v[b], v[c]))
-        swp(v, result, c);
+    else if (C::before(v[a], v[c]))
+        swp<K, C>(v, result, a);
+    else if (C::before(v[b], v[c]))
+        swp<K, C>(v, result, c);
     else
-        swp(v, result, b);
+        swp<K, C>(v, result, b);
 }
 
-SNK_SORT_HD int partition_unguarded(uint32_t* v, int first, int last, int pivot)
+template <class K, class C>
+SNK_SORT_HD int partition_unguarded(K* v, int first, int last, int pivot)
 {
     // the pivot slot lies outside [first, last) and is never written here: read it once (one dependent shared-memory
     // load less per step of the single-threaded device sort)
-    const uint32_t pv = v[pivot];
+    const K pv = v[pivot];
     while (true)
     {
-        uint32_t a = v[first];
-        while (before(a, pv)) a = v[++first];
+        K a = v[first];
+        while (C::before(a, pv)) a = v[++first];
         --last;
-        uint32_t b = v[last];
-        while (before(pv, b)) b = v[--last];
+        K b = v[last];
+        while (C::before(pv, b)) b = v[--last];
         if (!(first < last)) return first;
         v[first] = b;
         v[last]  = a;
@@ -158,7 +180,8 @@ SNK_SORT_HD int partition_unguarded(uint32_t* v, int first, int last, int pivot)
 // std::sort(v, v + n). The recursion of the introsort loop (right part recursive, left part iterative) is unrolled
 // onto an explicit stack; the order in which sub-ranges are processed does not influence the result because they are
 // disjoint, but the depth budget each sub-range inherits does, so it is carried along.
-SNK_SORT_HD void sort(uint32_t* v, int n)
+template <class K, class C>
+SNK_SORT_HD void sort_as(K* v, int n)
 {
     if (n <= 1) return;
     int lg = 0;
@@ -174,23 +197,25 @@ SNK_SORT_HD void sort(uint32_t* v, int n)
         {
             if (depth == 0)
             {
-                heap_sort(v, first, last);
+                heap_sort<K, C>(v, first, last);
                 break;
             }
             --depth;
             const int mid = first + (last - first) / 2;
-            median_to_first(v, first, first + 1, mid, last - 1);
-            const int cut = partition_unguarded(v, first + 1, last, first);
+            median_to_first<K, C>(v, first, first + 1, mid, last - 1);
+            const int cut = partition_unguarded<K, C>(v, first + 1, last, first);
             stack_first[sp] = cut, stack_last[sp] = last, stack_depth[sp] = depth, ++sp;
             last = cut;
         }
     }
     if (n > 16)
     {
-        insertion(v, 0, 16);
-        for (int i = 16; i != n; ++i) linear_insert_unguarded(v, i);
+        insertion<K, C>(v, 0, 16);
+        for (int i = 16; i != n; ++i) linear_insert_unguarded<K, C>(v, i);
     }
     else
-        insertion(v, 0, n);
+        insertion<K, C>(v, 0, n);
 }
+// the quadtree distributor's call (keys = count << SHIFT | slot)
+SNK_SORT_HD void sort(uint32_t* v, int n) { sort_as<uint32_t, DescCount>(v, n); }
 }  // namespace gnusort

@@ -2,9 +2,11 @@
 #include "match_kernels.cuh"
 #include "project_kernels.cuh"
 #include "image_kernels.cuh"
+#include "bow_kernels.cuh"
 
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 #include <mutex>
 #include <vector>
 
@@ -482,3 +484,4 @@ extern "C" int snk_match_knn2_noalloc(int device, void* cuda_stream, const uint6
 }
 
 #include "project_host.inl"
+#include "bow_host.inl"

@@ -368,6 +368,44 @@ class Context:
         return v.value
 
 
+class Vocabulary:
+    """snk_voc == MiniBow2::TemplatedVocabulary on the device; transform() needs a Context."""
+
+    def __init__(self, path=None, arrays=None, device=0):
+        self.v = C.c_void_p()
+        if path is not None:
+            _check(lib().snk_voc_load_raw(device, path.encode(), C.byref(self.v)))
+        else:
+            k, L, parent, weight, word_id, desc = arrays
+            parent = np.ascontiguousarray(parent, np.int32)
+            weight = np.ascontiguousarray(weight, np.float64)
+            word_id = np.ascontiguousarray(word_id, np.int32)
+            desc = np.ascontiguousarray(desc, np.uint64)
+            _check(lib().snk_voc_create(device, k, L, len(parent), _p(parent), _p(weight), _p(word_id), _p(desc),
+                                        C.byref(self.v)))
+        k, L, nn, nw = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _check(lib().snk_voc_info(self.v, C.byref(k), C.byref(L), C.byref(nn), C.byref(nw)))
+        self.k, self.L, self.n_nodes, self.n_words = k.value, L.value, nn.value, nw.value
+
+    def close(self):
+        if getattr(self, "v", None):
+            lib().snk_voc_destroy(self.v)
+            self.v = None
+
+    __del__ = close
+
+    def transform(self, ctx, desc, levelsup):
+        """TemplatedVocabulary::transform -> bow_ids, bow_vals, fv_nodes, fv_offsets, fv_indices."""
+        desc = np.ascontiguousarray(desc, np.uint64).reshape(-1, 4)
+        n = len(desc)
+        ids, vals = np.zeros(n + 1, np.int32), np.zeros(n + 1, np.float32)
+        fn, fo, fi = np.zeros(n + 1, np.int32), np.zeros(n + 2, np.int32), np.zeros(n + 1, np.int32)
+        nb, nf = C.c_int(), C.c_int()
+        _check(lib().snk_bow_transform(ctx.c, self.v, _p(desc), n, levelsup, _p(ids), _p(vals), C.byref(nb), _p(fn),
+                                       _p(fo), _p(fi), C.byref(nf)))
+        return ids[:nb.value], vals[:nb.value], fn[:nf.value], fo[:nf.value + 1], fi[:fo[nf.value]]
+
+
 def kp32_to_kp64(k):
     o = np.zeros(len(k), KP64)
     for f in ("x", "y", "size", "angle", "response", "octave"):

@@ -177,3 +177,39 @@ def bow_feature_vector(desc, rng, n_nodes=100, bits=7):
         indices.append(members)
         offsets.append(offsets[-1] + len(members))
     return ids.astype(np.int32) * 3 + 11, np.array(offsets, np.int32), np.concatenate(indices).astype(np.int32)
+
+
+def vocabulary_arrays(seed, k, L, n_train=4000, zero_weight_fraction=0.1, ragged=True):
+    """A random but well-formed vocabulary tree in loadRaw's node order (depth-first creation as HKmeansStep numbers
+    the nodes): each node's children descriptors are the parent's with bits flipped, so a descent is meaningful.
+    ragged: some inner nodes get fewer than k children and some branches end early (create() produces both).
+    Returns (k, L, parent, weight, word_id, desc)."""
+    rng = np.random.default_rng(seed)
+    parent, weight, word_id, desc, level = [0], [0.0], [0], [rng.integers(0, 2**63, 4).astype(np.uint64)], [0]
+
+    def grow(node, lvl):
+        # HKmeansStep (MiniBow2.h:508-700): the k children are appended first, then each is expanded in turn
+        nk = k if not ragged or rng.random() > 0.15 else int(rng.integers(1, k + 1))
+        kids = []
+        for _ in range(nk):
+            d = desc[node].copy()
+            for _ in range(max(2, 96 >> lvl)):
+                d[rng.integers(0, 4)] ^= np.uint64(1) << np.uint64(rng.integers(0, 64))
+            parent.append(node), weight.append(0.0), word_id.append(0), desc.append(d), level.append(lvl + 1)
+            kids.append(len(parent) - 1)
+        if lvl + 1 < L:
+            for c in kids:
+                if not ragged or rng.random() > 0.05:
+                    grow(c, lvl + 1)
+
+    grow(0, 0)
+    n = len(parent)
+    has_child = np.zeros(n, bool)
+    has_child[np.array(parent[1:])] = True
+    nw = 0
+    for i in range(1, n):  # createWords (:799-819): leaves numbered in node order
+        if not has_child[i]:
+            word_id[i] = nw
+            nw += 1
+            weight[i] = 0.0 if rng.random() < zero_weight_fraction else float(np.log(rng.uniform(1.05, 40.0)))
+    return k, L, np.array(parent, np.int32), np.array(weight, np.float64), np.array(word_id, np.int32), np.stack(desc)

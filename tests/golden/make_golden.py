@@ -152,6 +152,48 @@ def rect_vector(case):
     return np.array(list(k) + [0.0] + list(d) + list(q) + list(kd), np.float64)  # ref_shim.cpp layout, 22 doubles
 
 
+VOC_FILE = os.path.join(HERE, "voc_k9_L3.bin")
+
+
+def ref_transform(voc_path, desc, levelsup):
+    n = len(desc)
+    ids, vals = np.zeros(n + 1, np.int32), np.zeros(n + 1, np.float32)
+    fn, fo, fi = np.zeros(n + 1, np.int32), np.zeros(n + 2, np.int32), np.zeros(n + 1, np.int32)
+    nb, nf = C.c_int(), C.c_int()
+    desc = np.ascontiguousarray(desc, np.uint64)
+    R.ref_voc_transform(voc_path.encode(), _p(desc), n, levelsup, _p(ids), _p(vals), C.byref(nb), _p(fn), _p(fo), _p(fi),
+                        C.byref(nf))
+    return ids[:nb.value], vals[:nb.value], fn[:nf.value], fo[:nf.value + 1], fi[:fo[nf.value]]
+
+
+def make_voc(out, rng):
+    """A small vocabulary trained by the reference's own MiniBow2 create() (k-means++ on descriptors of synthetic
+    frames, k=9, L=3, IDF weights) and written by its saveRaw(); plus transform() outputs of the reference for
+    descriptor sets of several sizes and levelsup values."""
+    train = []
+    for i in range(14):
+        k, d = O.Extractor(700, 1.2, 8, 20, 7, 2).detect(S.image(900 + i, 640, 480))
+        train.append(d)
+    counts = np.array([len(d) for d in train], np.int32)
+    alld = np.ascontiguousarray(np.concatenate(train))
+    nwords = R.ref_voc_create(_p(alld), _p(counts), len(train), 9, 3, 1234, VOC_FILE.encode())
+    print("vocabulary:", nwords, "words,", os.path.getsize(VOC_FILE), "bytes")
+    sets = {
+        "a": O.Extractor(1000, 1.2, 8, 20, 7, 2).detect(S.image(77, 752, 480))[1],
+        "b": O.Extractor(2500, 1.2, 8, 20, 7, 2).detect(S.image(78, 1241, 376))[1],
+        "c": train[3][:1],
+        "d": rng.integers(0, 2**63, (300, 4)).astype(np.uint64),
+    }
+    for name, d in sets.items():
+        out[f"bow_{name}_desc"] = d
+        for lu in (0, 1, 2, 3, 5):
+            ids, vals, fn, fo, fi = ref_transform(VOC_FILE, d, lu)
+            out[f"bow_{name}_{lu}_ids"], out[f"bow_{name}_{lu}_vals"] = ids, vals
+            out[f"bow_{name}_{lu}_fv_nodes"], out[f"bow_{name}_{lu}_fv_offsets"], out[f"bow_{name}_{lu}_fv_indices"] = fn, fo, fi
+        print(name, len(d), "->", len(out[f"bow_{name}_1_ids"]), "words,", len(out[f"bow_{name}_1_fv_nodes"]), "nodes,",
+              len(d) - len(out[f"bow_{name}_1_fv_indices"]), "features on zero-weight words")
+
+
 def make_next():
     """Golden vectors for the rows after the extractor, from the reference's own headers compiled into
     oracle/_ref: Preprocess::undistortKeypoints' per-point math."""
@@ -186,6 +228,7 @@ def make_next():
     lat = np.concatenate([lat, np.full((64, 64, 1), 255, np.uint8)], -1)
     out.update(gray_rgba=rgba, gray_out=cv2.cvtColor(rgba, cv2.COLOR_RGBA2GRAY), gray_lattice=lat,
                gray_lattice_out=cv2.cvtColor(lat, cv2.COLOR_RGBA2GRAY))
+    make_voc(out, rng)
     np.savez_compressed(os.path.join(HERE, "golden_next.npz"), **out)
 
 

@@ -67,6 +67,31 @@ int main()
                 break;
             }
     }
+    // MiniBow2 FeatureVector::setFeatures: std::sort of (node id, feature index) pairs on the node id alone, ids
+    // from a small set (k^(L-levelsup) nodes) plus -1 entries — 64-bit keys, ascending signed high word
+    for (int rep = 0; rep < 60000; ++rep)
+    {
+        int n     = 1 + rng() % (rep % 20 == 0 ? 8000 : 2500);
+        int nodes = 1 + rng() % (rep % 2 ? 100 : 1000);
+        std::vector<std::pair<int, int>> pairs(n);
+        std::vector<uint64_t> keys(n);
+        for (int i = 0; i < n; ++i)
+        {
+            int id   = (rng() % 16 == 0) ? -1 : (int)(rng() % nodes) * 7 + 3;
+            pairs[i] = {id, i};
+            keys[i]  = ((uint64_t)(uint32_t)id << 32) | (uint32_t)i;
+        }
+        std::sort(pairs.begin(), pairs.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        gnusort::sort_as<uint64_t, gnusort::AscHigh32>(keys.data(), n);
+        ++cases;
+        for (int i = 0; i < n; ++i)
+            if ((int)(uint32_t)keys[i] != pairs[i].second || (int32_t)(keys[i] >> 32) != pairs[i].first)
+            {
+                ++bad;
+                if (bad < 5) printf("pair mismatch n=%d at %d\n", n, i);
+                break;
+            }
+    }
     printf("%lld cases, %lld mismatches\n", cases, bad);
     return bad != 0;
 }
