@@ -403,6 +403,15 @@ SNK_API int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* de
                               int32_t* bow_ids, float* bow_vals, int* n_bow, int32_t* fv_node_ids,
                               int32_t* fv_offsets, int32_t* fv_indices, int* n_fv_nodes);
 
+/* Batched, device-resident form (e.g. straight from snk_orb_device_results: desc_dev [n_frames][stride][4],
+ * counts_dev [n_frames], stride <= 8192). Outputs are device arrays: bow_ids / bow_vals / fv_node_ids / fv_indices
+ * [n_frames][stride], fv_offsets [n_frames][stride + 1], out_counts [n_frames][2] = (words, nodes). Asynchronous on
+ * the context's stream. */
+SNK_API int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const uint64_t* desc_dev,
+                                           const int32_t* counts_dev, int n_frames, int stride, int levelsup,
+                                           int32_t* bow_ids_dev, float* bow_vals_dev, int32_t* fv_node_ids_dev,
+                                           int32_t* fv_offsets_dev, int32_t* fv_indices_dev, int32_t* out_counts_dev);
+
 /* The reference's feature cache (Snake/Preprocess/FeatureDetector.cpp:97-111 read, :134-139 write; settings
  * fd_bufferToFile), a saiga BinaryFile dump (saiga/core/util/BinaryFile.h:30-78): u64 n, n x KeyPoint<double>
  * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of

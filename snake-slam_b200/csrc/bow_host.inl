@@ -141,6 +141,28 @@ int snk_voc_info(const snk_voc* v, int* k, int* L, int* n_nodes, int* n_words)
     return SNK_OK;
 }
 
+namespace
+{
+int bow_smem_attr(int device)
+{
+    static std::mutex attr_mutex;
+    static bool attr_set[64] = {};
+    std::lock_guard<std::mutex> lock(attr_mutex);
+    if (device < 64 && !attr_set[device])
+    {
+        SNK_CUDA(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, BOW_MAX_FEATURES * 12));
+        attr_set[device] = true;
+    }
+    return SNK_OK;
+}
+int pow2_at_least(int n)
+{
+    int p = 32;
+    while (p < n) p <<= 1;
+    return p;
+}
+}  // namespace
+
 int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int n, int levelsup, int32_t* bow_ids,
                       float* bow_vals, int* n_bow, int32_t* fv_node_ids, int32_t* fv_offsets, int32_t* fv_indices,
                       int* n_fv_nodes)
@@ -153,8 +175,6 @@ int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int 
     if (n == 0) return SNK_OK;
     SNK_REQUIRE(desc && bow_ids && bow_vals && fv_node_ids && fv_indices, "null output arrays");
     SNK_CUDA(cudaSetDevice(c->device));
-    int np2 = 32;
-    while (np2 < n) np2 <<= 1;
     int rc = ctx_reserve(c, padded<uint64_t>(4 * (size_t)n) + 2 * padded<unsigned long long>(n) + 4 * padded<int>(n + 1) +
                                 padded<float>(n) + padded<int>(4));
     if (rc) return rc;
@@ -169,20 +189,10 @@ int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int 
     int* dfi   = cv.take<int>(n + 1);
     int* dcnt  = cv.take<int>(4);
     cudaStream_t st = c->stream;
-    const size_t smem = (size_t)np2 * 12;
-    static std::mutex attr_mutex;
-    static size_t attr_set[64] = {};
-    {
-        std::lock_guard<std::mutex> lock(attr_mutex);
-        if (c->device < 64 && attr_set[c->device] < smem)
-        {
-            SNK_CUDA(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)BOW_MAX_FEATURES * 12)));
-            attr_set[c->device] = (size_t)BOW_MAX_FEATURES * 12;
-        }
-    }
+    if ((rc = bow_smem_attr(c->device))) return rc;
     SNK_CUDA(cudaMemcpyAsync(dd, desc, 32 * (size_t)n, cudaMemcpyHostToDevice, st));
-    k_bow_descend<<<(n + 15) / 16, 256, 0, st>>>(voc->dev(), reinterpret_cast<const uint4*>(dd), n, levelsup, dw, df);
-    k_bow_assemble<<<1, BOW_NT, smem, st>>>(dw, df, n, np2, dbi, dbv, dfn, dfo, dfi, dcnt);
+    k_bow_descend<<<(n + 15) / 16, 256, 0, st>>>(voc->dev(), reinterpret_cast<const uint4*>(dd), nullptr, n, n, levelsup, dw, df);
+    k_bow_assemble<<<1, BOW_NT, (size_t)pow2_at_least(n) * 12, st>>>(dw, df, nullptr, n, n, dbi, dbv, dfn, dfo, dfi, dcnt);
     SNK_CUDA(cudaGetLastError());
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 8, dcnt, 8, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(bow_ids, dbi, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
@@ -193,5 +203,32 @@ int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int 
     SNK_CUDA(cudaStreamSynchronize(st));
     *n_bow      = c->h_pin[8];
     *n_fv_nodes = c->h_pin[9];
+    return SNK_OK;
+}
+
+int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const uint64_t* desc_dev, const int32_t* counts_dev,
+                                   int n_frames, int stride, int levelsup, int32_t* bow_ids_dev, float* bow_vals_dev,
+                                   int32_t* fv_node_ids_dev, int32_t* fv_offsets_dev, int32_t* fv_indices_dev,
+                                   int32_t* out_counts_dev)
+{
+    SNK_REQUIRE(c && voc && desc_dev && counts_dev && bow_ids_dev && bow_vals_dev && fv_node_ids_dev && fv_offsets_dev &&
+                    fv_indices_dev && out_counts_dev,
+                "null argument");
+    SNK_REQUIRE(n_frames >= 0 && stride >= 1 && stride <= BOW_MAX_FEATURES, "stride = %d outside [1, %d]", stride, BOW_MAX_FEATURES);
+    SNK_REQUIRE(voc->device == c->device, "vocabulary lives on device %d, context on %d", voc->device, c->device);
+    if (n_frames == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, 2 * padded<unsigned long long>((size_t)n_frames * stride));
+    if (rc) return rc;
+    if ((rc = bow_smem_attr(c->device))) return rc;
+    Carver cv{c->d_buf};
+    auto* dw = cv.take<unsigned long long>((size_t)n_frames * stride);
+    auto* df = cv.take<unsigned long long>((size_t)n_frames * stride);
+    cudaStream_t st = c->stream;
+    k_bow_descend<<<dim3((stride + 15) / 16, n_frames), 256, 0, st>>>(voc->dev(), reinterpret_cast<const uint4*>(desc_dev),
+                                                                      counts_dev, 0, stride, levelsup, dw, df);
+    k_bow_assemble<<<n_frames, BOW_NT, (size_t)pow2_at_least(stride) * 12, st>>>(
+        dw, df, counts_dev, 0, stride, bow_ids_dev, bow_vals_dev, fv_node_ids_dev, fv_offsets_dev, fv_indices_dev, out_counts_dev);
+    SNK_CUDA(cudaGetLastError());
     return SNK_OK;
 }

@@ -36,14 +36,21 @@ constexpr int BOW_MAX_FEATURES = 8192;
 
 // ---- descent: transform(feature, levelsup), MiniBow2.h:937-983 --------------------------------------------------
 // words[i] = (word id or -1) << 32 | weight bits;  feats[i] = (node id or -1) << 32 | i
-__global__ void __launch_bounds__(256) k_bow_descend(VocDev V, const uint4* __restrict__ desc, int n, int levelsup,
+// Batched: blockIdx.y = frame; frame f has counts[f] (or n_fixed when counts is null) descriptors at desc + 2*f*stride,
+// its outputs at words/feats + f*stride.
+__global__ void __launch_bounds__(256) k_bow_descend(VocDev V, const uint4* __restrict__ desc, const int* __restrict__ counts,
+                                                     int n_fixed, int stride, int levelsup,
                                                      unsigned long long* __restrict__ words,
                                                      unsigned long long* __restrict__ feats)
 {
     const int sub = threadIdx.x & 15;
     const int i   = (blockIdx.x * 256 + threadIdx.x) >> 4;
     const unsigned group = 0xffffu << (threadIdx.x & 16);
+    const int n = counts ? min(counts[blockIdx.y], stride) : n_fixed;
     if (i >= n) return;  // whole 16-lane groups leave together
+    desc += 2 * (size_t)blockIdx.y * stride;
+    words += (size_t)blockIdx.y * stride;
+    feats += (size_t)blockIdx.y * stride;
     const uint4 a = desc[2 * i], b = desc[2 * i + 1];
     const int nid_level = V.L - levelsup;
     int node = 0, nid = 0, level = 0;
@@ -188,12 +195,22 @@ __device__ __forceinline__ int cta_rank(bool flag, int tid, int* s_warp, int* to
 }
 
 // dynamic shared memory: key[np2] u64 | Lp[np2] u16 | Rq[np2] u16 (the two u16 arrays are reused as np2 floats)
+// Batched like k_bow_descend: blockIdx.x = frame, outputs of frame f at f*stride (fv_offsets: f*(stride+1), counts: 2f).
 __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long long* __restrict__ words,
-                                                          const unsigned long long* __restrict__ feats, int n, int np2,
+                                                          const unsigned long long* __restrict__ feats,
+                                                          const int* __restrict__ in_counts, int n_fixed, int stride,
                                                           int* __restrict__ bow_ids, float* __restrict__ bow_vals,
                                                           int* __restrict__ fv_nodes, int* __restrict__ fv_offsets,
                                                           int* __restrict__ fv_indices, int* __restrict__ counts)
 {
+    const int n = in_counts ? min(in_counts[blockIdx.x], stride) : n_fixed;
+    int np2     = 32;
+    while (np2 < n) np2 <<= 1;
+    {
+        const size_t f = blockIdx.x;
+        words += f * stride, feats += f * stride, bow_ids += f * stride, bow_vals += f * stride, fv_nodes += f * stride;
+        fv_offsets += f * (stride + 1), fv_indices += f * stride, counts += 2 * f;
+    }
     extern __shared__ __align__(16) unsigned char bow_smem[];
     unsigned long long* key = reinterpret_cast<unsigned long long*>(bow_smem);
     uint16_t* Lp            = reinterpret_cast<uint16_t*>(key + np2);

@@ -311,6 +311,17 @@ class Context:
                                           depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp), C.byref(n)))
         return n.value, rp[:len(kp_un)], dp[:len(kp_un)]
 
+    def knn2_batch_device(self, d1_ptr, n_ptr, stride1, d2_ptr, m_ptr, stride2, n_problems, out_ptr):
+        _check(lib().snk_match_knn2_batch_device(self.c, C.c_void_p(d1_ptr), C.c_void_p(n_ptr), stride1, C.c_void_p(d2_ptr),
+                                                 C.c_void_p(m_ptr), stride2, n_problems, C.c_void_p(out_ptr)))
+
+    def bow_transform_batch_device(self, voc, desc_ptr, counts_ptr, n_frames, stride, levelsup, bow_ids, bow_vals,
+                                   fv_nodes, fv_offsets, fv_indices, out_counts):
+        _check(lib().snk_bow_transform_batch_device(self.c, voc.v, C.c_void_p(desc_ptr), C.c_void_p(counts_ptr), n_frames,
+                                                    stride, levelsup, C.c_void_p(bow_ids), C.c_void_p(bow_vals),
+                                                    C.c_void_p(fv_nodes), C.c_void_p(fv_offsets), C.c_void_p(fv_indices),
+                                                    C.c_void_p(out_counts)))
+
     def stereo_orb_device(self, orb, n_pairs, params, rp_ptr, depth_ptr, nm_ptr):
         _check(lib().snk_stereo_match_orb_device(self.c, orb.h, n_pairs, C.byref(params), C.c_void_p(rp_ptr),
                                                  C.c_void_p(depth_ptr), C.c_void_p(nm_ptr)))

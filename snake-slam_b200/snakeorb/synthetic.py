@@ -213,3 +213,33 @@ def vocabulary_arrays(seed, k, L, n_train=4000, zero_weight_fraction=0.1, ragged
             nw += 1
             weight[i] = 0.0 if rng.random() < zero_weight_fraction else float(np.log(rng.uniform(1.05, 40.0)))
     return k, L, np.array(parent, np.int32), np.array(weight, np.float64), np.array(word_id, np.int32), np.stack(desc)
+
+
+def vocabulary_arrays_bfs(seed, k, L, zero_weight_fraction=0.02):
+    """A full k-ary vocabulary of depth L (ORBvoc: k=10, L=6, 1 111 111 nodes) numbered breadth-first, built with
+    array operations only: every child's descriptor is its parent's with a sparse random mask XORed in, sparser on
+    deeper levels. Returns (k, L, parent, weight, word_id, desc)."""
+    rng = np.random.default_rng(seed)
+    parent, desc = [np.zeros(1, np.int64)], [rng.integers(0, 2**63, (1, 4)).astype(np.uint64)]
+    start = 0
+    for lvl in range(1, L + 1):
+        prev = desc[-1]
+        n = len(prev) * k
+        par = start + np.arange(n) // k
+        mask = rng.integers(0, 2**63, (n, 4)).astype(np.uint64) << np.uint64(1) | rng.integers(0, 2, (n, 4)).astype(np.uint64)
+        for _ in range(min(lvl, 4)):  # bit density 1/2, 1/4, 1/8, ... with depth
+            mask &= rng.integers(0, 2**63, (n, 4)).astype(np.uint64) << np.uint64(1) | rng.integers(0, 2, (n, 4)).astype(np.uint64)
+        desc.append(prev[np.arange(n) // k] ^ mask)
+        parent.append(par)
+        start += len(prev)
+    parent = np.concatenate(parent).astype(np.int32)
+    desc = np.concatenate(desc)
+    n = len(parent)
+    n_leaf = k**L
+    weight = np.zeros(n, np.float64)
+    word_id = np.zeros(n, np.int32)
+    w = np.log(rng.uniform(1.05, 40.0, n_leaf))
+    w[rng.random(n_leaf) < zero_weight_fraction] = 0.0
+    weight[n - n_leaf:] = w
+    word_id[n - n_leaf:] = np.arange(n_leaf)
+    return k, L, parent, weight, word_id, desc

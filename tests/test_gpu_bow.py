@@ -103,3 +103,45 @@ def test_bow_errors(so, ctx, tmp_path):
     bad.write_bytes(open(VOC, "rb").read()[:1000])
     with pytest.raises(so.SnakeOrbError):
         so.Vocabulary(str(bad))
+
+
+def test_device_chain_extract_bow_knn2(so, ctx, oracle):
+    """Device-resident chain: extractor results -> batched BoW transform and batched kNN-2 (frame i against
+    frame i+1) without leaving the GPU; every frame equals the host-call results / the oracle."""
+    from devmem import DevBuf
+    from snakeorb import synthetic as S
+
+    B = 5
+    imgs = np.stack([S.image(40 + i // 2 if i < 4 else 99, 752, 480) for i in range(B)])  # frames 0/1 and 2/3 equal
+    ex = so.ORBExtractor(1200, 1.2, 8, 20, 7, max_batch=B)
+    ex.set_stream(0)
+    ctx.set_stream(0)
+    ex.enqueue_ptr(imgs.ctypes.data, B, 480, 752, 752, 752 * 480, False)
+    kps_ptr, desc_ptr, cnt_ptr, stride = ex.device_results()
+    v = so.Vocabulary(VOC)
+    vo = oracle.Vocabulary(VOC)
+    bi, bv, fn, fi = (DevBuf(4 * B * stride) for _ in range(4))
+    fo = DevBuf(4 * B * (stride + 1))
+    oc = DevBuf(8 * B)
+    ctx.bow_transform_batch_device(v, desc_ptr, cnt_ptr, B, stride, 1, bi.ptr, bv.ptr, fn.ptr, fo.ptr, fi.ptr, oc.ptr)
+    # kNN-2: problem p = frame p against frame p+1 (views into the same device arrays)
+    out = DevBuf(16 * (B - 1) * stride)
+    ctx.knn2_batch_device(desc_ptr, cnt_ptr, stride, desc_ptr + 32 * stride, cnt_ptr + 4, stride, B - 1, out.ptr)
+    kps, desc, counts = ex.fetch(B)
+    occ = oc.get(np.int32, (B, 2))
+    bih, bvh = bi.get(np.int32, (B, stride)), bv.get(np.float32, (B, stride))
+    fnh, fih, foh = fn.get(np.int32, (B, stride)), fi.get(np.int32, (B, stride)), fo.get(np.int32, (B, stride + 1))
+    knn = out.get(so.KNN2, (B - 1, stride))
+    for f in range(B):
+        d = desc[f, :counts[f]]
+        want = vo.transform(d, 1)
+        nb, nn = occ[f]
+        got = (bih[f, :nb], bvh[f, :nb], fnh[f, :nn], foh[f, :nn + 1], fih[f, :foh[f, nn]])
+        same(got, want, f)
+        same(v.transform(ctx, d, 1), want, ("host call", f))
+    for p in range(B - 1):
+        want = oracle.match_knn2(desc[p, :counts[p]], desc[p + 1, :counts[p + 1]])
+        assert knn[p, :counts[p]].tobytes() == want.tobytes(), p
+    assert np.all(knn[0, :counts[0]]["dist0"] == 0)  # identical frames
+    ex.set_stream(None)
+    ctx.set_stream(None)
