@@ -174,6 +174,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
     ap.add_argument("--chunks", type=int, default=8, help="e2e path: chunks per step")
     ap.add_argument("--lanes", type=int, default=4, help="e2e path: streams/handles the chunks alternate over")
     args = ap.parse_args()
@@ -359,6 +360,53 @@ def main():
     n_kp_step = int(cnt_host.sum())
     n_match_step = int(nm.sum().item())
 
+    # ---- side measurement, not part of `value`: MiniBow2::transform of every image of the step on the
+    # extractor's device results, ORBvoc-shaped synthetic vocabulary (k=10, L=6), levelsup 4 as Frame::computeBoW uses
+    next_rows = None
+    if rank == 0 and not args.no_next:
+        from snakeorb import synthetic as S
+
+        arr = S.vocabulary_arrays_bfs(7, 10, 6)
+        voc = snakeorb.Vocabulary(arrays=arr, device=local_rank)
+        b_ids = torch.empty((NI, stride), dtype=torch.int32, device="cuda")
+        b_val = torch.empty((NI, stride), dtype=torch.float32, device="cuda")
+        f_nod = torch.empty((NI, stride), dtype=torch.int32, device="cuda")
+        f_off = torch.empty((NI, stride + 1), dtype=torch.int32, device="cuda")
+        f_idx = torch.empty((NI, stride), dtype=torch.int32, device="cuda")
+        o_cnt = torch.empty((NI, 2), dtype=torch.int32, device="cuda")
+
+        def step_bow():
+            ctx.bow_transform_batch_device(voc, desc_ptr, cnt_ptr, NI, stride, 4, b_ids.data_ptr(), b_val.data_ptr(),
+                                           f_nod.data_ptr(), f_off.data_ptr(), f_idx.data_ptr(), o_cnt.data_ptr())
+
+        for _ in range(3):
+            step_bow()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0.record()
+        for _ in range(args.steps):
+            step_bow()
+        b1.record()
+        torch.cuda.synchronize()
+        bow_ms = b0.elapsed_time(b1) / args.steps
+        next_rows = {"bow_transform": {"frames_per_s": NI / (bow_ms * 1e-3), "ms_per_step": bow_ms, "frames_per_step": NI,
+                                       "vocabulary": "synthetic, ORBvoc shape k=10 L=6 (1 111 111 nodes), levelsup 4",
+                                       "words_per_frame": float(o_cnt[:, 0].float().mean().item())}}
+        if not args.no_cpu:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import oracle_py  # cpu_baseline leg only: the checker timed as the CPU port
+
+            vo = oracle_py.Vocabulary(arrays=arr)
+            dh = np.zeros((4, stride, 4), np.uint64)
+            cudart.cudaMemcpy(C.c_void_p(dh.ctypes.data), C.c_void_p(desc_ptr), C.c_size_t(dh.nbytes), 2)
+            t0 = time.time()
+            reps = 0
+            while time.time() - t0 < 1.0:
+                for f in range(4):
+                    vo.transform(dh[f, :cnt_host[f]], 4)
+                reps += 4
+            next_rows["bow_transform"]["cpu_port_frames_per_s_1_thread"] = reps / (time.time() - t0)
+        del voc
+
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
@@ -425,6 +473,8 @@ def main():
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
                            "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap)"}
+        if next_rows is not None:
+            line["next_rows"] = next_rows
         if not args.no_cpu:
             try:
                 popc = ctx.hamming_peak()
