@@ -294,6 +294,8 @@ typedef struct snk_frame_view
     double pose_q[4];                /* Frame::Pose() unit quaternion x,y,z,w */
     double pose_t[3];
     snk_grid_view grid;
+    const float* depth;              /* Features::depth (hasDepth(i) == depth[i] > 0); read by snk_fuse_search only,
+                                        may be NULL elsewhere */
 } snk_frame_view;
 
 /* Snake::FineTrackingPoint (Snake/Map/LocalMap.h:32-55) */
@@ -380,6 +382,71 @@ typedef struct snk_featvec_view
 SNK_API int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, int n2,
                           const snk_featvec_view* fv1, const snk_featvec_view* fv2, const uint8_t* valid1,
                           const uint8_t* valid2, int th, float ratio, int32_t* match12, int* n_matches);
+
+/* ---- local-mapping and loop-closing searches -------------------------------------------------
+ * All of them are independent per point / feature in the reference (its tmp_flags are never set), so the device
+ * evaluates every point at once and the results are listed in the reference's iteration order. */
+
+/* Snake::FusionPoint (Snake/Map/LocalMap.h:57-79) */
+typedef struct snk_point_fusion
+{
+    uint64_t desc[4];
+    double pos[3];
+    double normal[3];
+    float ref_depth;
+    int32_t ref_level;
+    int32_t observations;
+    int32_t id;
+} snk_point_fusion;
+
+/* MappingORBMatcher::Fuse(kf, pose, point_mask, LocalMap<FusionPoint>, fuseCandidates, th, obs_factor, feature_th)
+ * (Snake/LocalMapping/MappingORBMatcher.cpp:359-482, built with MATCHING_MIN_MAX_DISTANCE2 and
+ * MATCHING_CHECK_SCALE_CONSISTENCY2, SnakeGlobal.h:168-169). kf->pose_q/pose_t is the `pose` argument, kf->depth is
+ * required, point_mask may be NULL. fuseCandidates = (cand_kp[j], cand_id[j]), j < *n_candidates, in point order;
+ * both arrays need n_points entries. */
+SNK_API int snk_fuse_search(snk_ctx* c, const snk_frame_view* kf, const uint8_t* point_mask,
+                            const snk_point_fusion* points, int n_points, const snk_camera* cam,
+                            const snk_scale_pyramid* pyr, float th, float obs_factor, int feature_th, int32_t* cand_kp,
+                            int32_t* cand_id, int* n_candidates);
+
+/* The search of LoopORBmatcher::Fuse (Snake/LoopClosing/LoopORBMatcher.cpp:13-72): skip[i] = mp->isBad() ||
+ * mp->IsInKeyFrame(pKF) evaluated by the caller; best_idx[i] / best_dist[i] = the most similar keypoint within `th`
+ * pixels of the projection (-1 / 256 when the point is skipped, culled or has no candidate). The caller then applies
+ * :75-93 in point order to the points with best_dist <= TH_LOW (the map edits there do not feed back into the
+ * search: a replaced point is bad and was in the keyframe). ref_depth / ref_level / observations are not read. */
+SNK_API int snk_fuse_search_loop(snk_ctx* c, const snk_frame_view* kf, const uint8_t* skip,
+                                 const snk_point_fusion* points, int n_points, const snk_camera* cam, float th,
+                                 int32_t* best_idx, int32_t* best_dist);
+
+/* MappingORBMatcher::SearchForTriangulation2 (MappingORBMatcher.cpp:14-101): for every feature of kf1 without a map
+ * point, the best feature of kf2 under the same FeatureVector node (no map point, distance <= featureDistance and
+ * <= the running best starting at TH_LOW = 50 — the LAST minimum wins — and squared epipolar distance below
+ * (2*epipolarDistance/fx)^2; Saiga::EpipolarDistanceSquared, saiga/vision/reconstruction/Epipolar.cpp:47-56).
+ * kfX->kp_to_point[i] >= 0 stands for GetMapPoint(i) != null; npX = normalized_points (2 doubles per feature);
+ * E row-major. pairs = (idx1, idx2) in the reference's order, room for 2*kf1->n ints. Only n, desc, kp_to_point of
+ * the frame views are read. */
+SNK_API int snk_search_triangulation_bow(snk_ctx* c, const snk_frame_view* kf1, const double* np1,
+                                         const snk_featvec_view* fv1, const snk_frame_view* kf2, const double* np2,
+                                         const snk_featvec_view* fv2, const double* E, const snk_camera* cam,
+                                         float epipolar_distance, int feature_distance, int32_t* pairs, int* n_pairs);
+
+/* MappingORBMatcher::SearchForTriangulationProject (MappingORBMatcher.cpp:167-247): every feature of kf1 without a
+ * map point is unprojected with the depth of its coarse grid cell (depth_grid(cell.y/4, cell.x/4), row-major
+ * grid_rows x grid_cols), moved into kf2 (kf1->pose inverted, kf2->pose) and searched within 20 px (epipolar gate
+ * (epipolarDistance/fx)^2, then distance, last minimum wins). kf1->grid supplies featureGridBounds. */
+SNK_API int snk_search_triangulation_project(snk_ctx* c, const snk_frame_view* kf1, const double* np1,
+                                             const snk_frame_view* kf2, const double* np2, const double* depth_grid,
+                                             int grid_rows, int grid_cols, const double* E12, const snk_camera* cam,
+                                             float epipolar_distance, int feature_distance, int32_t* pairs,
+                                             int* n_pairs);
+
+/* MonoInitializer::ComputeMatchesPrediction (Snake/Tracking/Initialization/MonoInitializer.cpp:619-697): feature i
+ * of the left frame searches the right frame within `radius` (50) of last_positions[i]; first minimum wins; a match
+ * needs distance < feature_error (50). matches[i] = index in the right frame or -1; last_positions[i] is moved onto
+ * the matched keypoint. Only grid, kp_un and desc of `right` are read. */
+SNK_API int snk_match_prediction(snk_ctx* c, const uint64_t* desc_left, int n_left, double* last_positions,
+                                 const snk_frame_view* right, float radius, int feature_error, int32_t* matches,
+                                 int* n_matches);
 
 /* MiniBow2::TemplatedVocabulary (saiga/vision/slam/MiniBow2.h): the vocabulary tree on the device.
  * snk_voc_load_raw reads the file format of loadRaw/saveRaw (:1020-1075: k, L, two unused ints, u64 node count,

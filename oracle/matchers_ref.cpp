@@ -780,4 +780,253 @@ int match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_
     if (pair_ops) *pair_ops = ops;
     return nmatches;
 }
+// ---------------------------------------------------------------------------------------------
+// Local mapping / loop closing searches. The Snake classes around them (Keyframe, MapPoint, Map)
+// cannot be compiled outside the full application, so these follow the source text; the pieces they call that CAN
+// be compiled from the reference (ScalePyramid, EpipolarDistanceSquared, distance) are pinned in tests/.
+// ---------------------------------------------------------------------------------------------
+// Saiga::EpipolarDistanceSquared (saiga/vision/reconstruction/Epipolar.cpp:47-56). F * (x, y, 1) as Eigen evaluates a
+// fixed 3x3 * 3x1 product with its default SSE2 packets: rows 0 and 1 accumulate left to right, the scalar tail row
+// sums as t0 + (t1 + t2) (checked against the compiled reference function in tests/test_mapping_cpu.py).
+double epipolar_distance_squared(const double* p1, const double* p2, const double* F /* row-major */)
+{
+    const double l0 = (F[0] * p1[0] + F[1] * p1[1]) + F[2] * 1.0;
+    const double l1 = (F[3] * p1[0] + F[4] * p1[1]) + F[5] * 1.0;
+    const double l2 = F[6] * p1[0] + (F[7] * p1[1] + F[8] * 1.0);
+    const double d       = (p2[0] * l0 + p2[1] * l1) + 1.0 * l2;
+    const double lengSqr = l0 * l0 + l1 * l1;
+    return d * d / lengSqr;
+}
+
+// MappingORBMatcher::Fuse, LocalMap<FusionPoint> overload (Snake/LocalMapping/MappingORBMatcher.cpp:359-482)
+int fuse_search(const snk_frame_view* kf, const uint8_t* point_mask, const snk_point_fusion* pts, int n,
+                const snk_camera* K, const snk_scale_pyramid* sp, float th, float obs_factor, int feature_th,
+                int32_t* cand_kp, int32_t* cand_id, long long* pair_ops)
+{
+    const float th_squared = th * th;
+    const V3 cam           = camera_position(kf->pose_q, kf->pose_t);
+    const double logsf     = std::log(sp->scale_factor);
+    int fused              = 0;
+    long long ops          = 0;
+    for (int i = 0; i < n; ++i)
+    {
+        const snk_point_fusion& lmp = pts[i];
+        if (point_mask && !point_mask[i]) continue;
+        V3 wp{lmp.pos[0], lmp.pos[1], lmp.pos[2]};
+        V3 np = se3_apply(kf->pose_q, kf->pose_t, wp);
+        if (np.z <= 0) continue;
+        double u, v;
+        project(K, np, u, v);
+        if (!in_image(kf->grid, u, v)) continue;
+        V3 PO{cam.x - wp.x, cam.y - wp.y, cam.z - wp.z};
+        const double dist = std::sqrt(PO.x * PO.x + PO.y * PO.y + PO.z * PO.z);
+        // EstimateMinMaxDistance (ScalePyramid.h:26-41)
+        double max_d = (double)lmp.ref_depth * sp->scale[lmp.ref_level];
+        double min_d = max_d / sp->scale[sp->nlevels - 1];
+        min_d /= sp->scale_factor;
+        max_d *= sp->scale_factor;
+        if (dist < min_d || dist > max_d) continue;
+        if (PO.x * lmp.normal[0] + PO.y * lmp.normal[1] + PO.z * lmp.normal[2] < 0.5 * dist) continue;
+        float observationFactor = 1.0;
+        if (lmp.observations <= 2) observationFactor = obs_factor;
+        const float radius = observationFactor * th;
+        // PredictScaleLevel (ScalePyramid.h:44-56)
+        const double pmax       = (double)lmp.ref_depth * sp->scale[lmp.ref_level];
+        const double prediction = std::log(pmax / dist) / logsf;
+        const double r = radius, r2 = r * r;
+        int bestDist = 256, bestIdx = -1;
+        bool any = false;
+        // the stereo prediction (projectStereo, Intrinsics4.h:221-230) does not depend on the candidate
+        const double invz = 1.0 / np.z;
+        const double sx = K->fx * (np.x * invz) + K->cx, sy = K->fy * (np.y * invz) + K->cy;
+        const double sr = sx - K->bf * invz;
+        for_candidates(kf, u, v, radius, r2, [&](int pid, bool inside) {
+            const snk_keypoint_f64& kp = kf->kp_un[pid];
+            const double pe            = prediction - kp.octave;  // PredictionConsistent (ScalePyramid.h:58-64)
+            if (!(pe * pe < 1.2 * 1.2)) return;
+            if (!inside) return;
+            any = true;
+            double e2;
+            if (kf->depth[pid] > 0)
+            {
+                const double d0 = sx - kp.x, d1 = sy - kp.y, d2 = sr - (double)kf->right_points[pid];
+                e2 = d0 * d0 + d1 * d1 + d2 * d2;
+            }
+            else
+            {
+                const double d0 = u - kp.x, d1 = v - kp.y;
+                e2 = d0 * d0 + d1 * d1;
+            }
+            if (e2 > th_squared * observationFactor) return;
+            ++ops;
+            const int d = hamming(lmp.desc, kf->desc + 4 * (size_t)pid);
+            if (d < bestDist) bestDist = d, bestIdx = pid;
+        });
+        if (!any) continue;
+        if (bestDist <= feature_th)
+        {
+            cand_kp[fused] = bestIdx;
+            cand_id[fused] = lmp.id;
+            ++fused;
+        }
+    }
+    if (pair_ops) *pair_ops = ops;
+    return fused;
+}
+
+// LoopORBmatcher::Fuse, the search (Snake/LoopClosing/LoopORBMatcher.cpp:13-72)
+void fuse_search_loop(const snk_frame_view* kf, const uint8_t* skip, const snk_point_fusion* pts, int n,
+                      const snk_camera* K, float th, int32_t* best_idx, int32_t* best_dist)
+{
+    const V3 cam = camera_position(kf->pose_q, kf->pose_t);
+    for (int i = 0; i < n; ++i)
+    {
+        best_idx[i]  = -1;
+        best_dist[i] = 256;
+        if (skip && skip[i]) continue;
+        const snk_point_fusion& mp = pts[i];
+        V3 wp{mp.pos[0], mp.pos[1], mp.pos[2]};
+        V3 np = se3_apply(kf->pose_q, kf->pose_t, wp);
+        if (np.z <= 0) continue;
+        double u, v;
+        project(K, np, u, v);
+        if (!in_image(kf->grid, u, v)) continue;
+        V3 PO{cam.x - wp.x, cam.y - wp.y, cam.z - wp.z};
+        const double dist3D = std::sqrt(PO.x * PO.x + PO.y * PO.y + PO.z * PO.z);
+        if (PO.x * mp.normal[0] + PO.y * mp.normal[1] + PO.z * mp.normal[2] < 0.5 * dist3D) continue;
+        const float radius = th * 1;
+        const float r2     = radius * radius;  // GetFeaturesInArea(…, float r): r*r in float (Features.cpp:17)
+        int bestDist = 256, bestIdx = -1;
+        for_candidates(kf, u, v, radius, (double)r2, [&](int pid, bool inside) {
+            if (!inside) return;
+            const int d = hamming(mp.desc, kf->desc + 4 * (size_t)pid);
+            if (d < bestDist) bestDist = d, bestIdx = pid;
+        });
+        best_idx[i]  = bestIdx;
+        best_dist[i] = bestDist;
+    }
+}
+
+// MappingORBMatcher::SearchForTriangulation2 (Snake/LocalMapping/MappingORBMatcher.cpp:14-101)
+int search_triangulation_bow(const snk_frame_view* kf1, const double* np1, const snk_featvec_view* fv1,
+                             const snk_frame_view* kf2, const double* np2, const snk_featvec_view* fv2, const double* E,
+                             const snk_camera* K, float epipolarDistance, int featureDistance, int32_t* pairs,
+                             long long* pair_ops)
+{
+    const double th_chi1 = epipolarDistance * 2 / K->fx;  // float * int in float, then / double
+    const double th_chi2 = th_chi1 * th_chi1;
+    int nmatches = 0, a = 0, b = 0;
+    long long ops = 0;
+    while (a < fv1->n_nodes && b < fv2->n_nodes)
+    {
+        if (fv1->node_ids[a] == fv2->node_ids[b])
+        {
+            for (int ia = fv1->offsets[a]; ia < fv1->offsets[a + 1]; ++ia)
+            {
+                const int idx1 = fv1->indices[ia];
+                if (kf1->kp_to_point[idx1] >= 0) continue;
+                int bestDist = 50, bestIdx2 = -1;  // TH_LOW
+                for (int ib = fv2->offsets[b]; ib < fv2->offsets[b + 1]; ++ib)
+                {
+                    const int idx2 = fv2->indices[ib];
+                    if (kf2->kp_to_point[idx2] >= 0) continue;
+                    ++ops;
+                    const int dist = hamming(kf1->desc + 4 * (size_t)idx1, kf2->desc + 4 * (size_t)idx2);
+                    if (dist > featureDistance || dist > bestDist) continue;
+                    if (epipolar_distance_squared(np1 + 2 * idx1, np2 + 2 * idx2, E) < th_chi2) bestIdx2 = idx2, bestDist = dist;
+                }
+                if (bestIdx2 >= 0)
+                {
+                    pairs[2 * nmatches]     = idx1;
+                    pairs[2 * nmatches + 1] = bestIdx2;
+                    ++nmatches;
+                }
+            }
+            ++a, ++b;
+        }
+        else if (fv1->node_ids[a] < fv2->node_ids[b])
+            a = (int)(std::lower_bound(fv1->node_ids + a, fv1->node_ids + fv1->n_nodes, fv2->node_ids[b]) - fv1->node_ids);
+        else
+            b = (int)(std::lower_bound(fv2->node_ids + b, fv2->node_ids + fv2->n_nodes, fv1->node_ids[a]) - fv2->node_ids);
+    }
+    if (pair_ops) *pair_ops = ops;
+    return nmatches;
+}
+
+// MappingORBMatcher::SearchForTriangulationProject (Snake/LocalMapping/MappingORBMatcher.cpp:167-247)
+int search_triangulation_project(const snk_frame_view* kf1, const double* np1, const snk_frame_view* kf2,
+                                 const double* np2, const double* grid, int grid_rows, int grid_cols, const double* E12,
+                                 const snk_camera* K, float epipolarDistance, int featureDistance, int32_t* pairs,
+                                 long long* pair_ops)
+{
+    (void)grid_rows;
+    const double th_chi1 = epipolarDistance / K->fx;
+    const double th_chi2 = th_chi1 * th_chi1;
+    // Sophus SE3::inverse(): (q^-1, q^-1 * (t * -1))
+    const double qi[4] = {-kf1->pose_q[0], -kf1->pose_q[1], -kf1->pose_q[2], kf1->pose_q[3]};
+    const V3 ti        = camera_position(kf1->pose_q, kf1->pose_t);
+    const double tinv[3] = {ti.x, ti.y, ti.z};
+    int nmatches = 0;
+    long long ops = 0;
+    for (int idx1 = 0; idx1 < kf1->n; ++idx1)
+    {
+        if (kf1->kp_to_point[idx1] >= 0) continue;
+        const snk_keypoint_f64& kp1 = kf1->kp_un[idx1];
+        const Cell cell = cell_clamped(kf1->grid, kp1.x, kp1.y);
+        const double z  = grid[(size_t)(cell.cy / 4) * grid_cols + cell.cx / 4];
+        // K.unproject(ip, z) (Intrinsics4.h:70-74)
+        V3 p{(kp1.x - K->cx) / K->fx, (kp1.y - K->cy) / K->fy, 1.0};
+        p = V3{p.x * z, p.y * z, p.z * z};
+        const V3 wp = se3_apply(qi, tinv, p);
+        const V3 c2 = se3_apply(kf2->pose_q, kf2->pose_t, wp);
+        double u, v;
+        project(K, c2, u, v);
+        if (!in_image(kf1->grid, u, v)) continue;
+        int bestDist = 50, bestIdx2 = -1;
+        for_candidates(kf2, u, v, 20.f, 400.0, [&](int idx2, bool inside) {
+            if (!inside) return;
+            if (kf2->kp_to_point[idx2] >= 0) return;
+            if (epipolar_distance_squared(np1 + 2 * idx1, np2 + 2 * idx2, E12) > th_chi2) return;
+            ++ops;
+            const int dist = hamming(kf1->desc + 4 * (size_t)idx1, kf2->desc + 4 * (size_t)idx2);
+            if (dist > featureDistance || dist > bestDist) return;
+            bestIdx2 = idx2, bestDist = dist;
+        });
+        if (bestIdx2 >= 0)
+        {
+            pairs[2 * nmatches]     = idx1;
+            pairs[2 * nmatches + 1] = bestIdx2;
+            ++nmatches;
+        }
+    }
+    if (pair_ops) *pair_ops = ops;
+    return nmatches;
+}
+
+// MonoInitializer::ComputeMatchesPrediction (Snake/Tracking/Initialization/MonoInitializer.cpp:619-697)
+int match_prediction(const uint64_t* desc_left, int n_left, double* last_positions, const snk_frame_view* right,
+                     float radius, int featureError, int32_t* matches)
+{
+    int count = 0;
+    const float r2 = radius * radius;
+    for (int i = 0; i < n_left; ++i)
+    {
+        int bestDist = 256, bestIdx2 = -1;
+        for_candidates(right, last_positions[2 * i], last_positions[2 * i + 1], radius, (double)r2, [&](int i2, bool inside) {
+            if (!inside) return;
+            const int d = hamming(desc_left + 4 * (size_t)i, right->desc + 4 * (size_t)i2);
+            if (d < bestDist) bestDist = d, bestIdx2 = i2;
+        });
+        if (bestDist < featureError)
+        {
+            last_positions[2 * i]     = right->kp_un[bestIdx2].x;
+            last_positions[2 * i + 1] = right->kp_un[bestIdx2].y;
+            matches[i]                = bestIdx2;
+            ++count;
+        }
+        else
+            matches[i] = -1;
+    }
+    return count;
+}
 }  // namespace orbref

@@ -26,4 +26,20 @@ int search_projection_frame_to_kf(const snk_frame_view* f, const snk_point_kf* p
 int match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_featvec_view* fv1,
               const snk_featvec_view* fv2, const uint8_t* valid1, const uint8_t* valid2, int th, float ratio,
               int32_t* match12, long long* pair_ops);
+double epipolar_distance_squared(const double* p1, const double* p2, const double* F);
+int fuse_search(const snk_frame_view* kf, const uint8_t* point_mask, const snk_point_fusion* pts, int n,
+                const snk_camera* K, const snk_scale_pyramid* sp, float th, float obs_factor, int feature_th,
+                int32_t* cand_kp, int32_t* cand_id, long long* pair_ops);
+void fuse_search_loop(const snk_frame_view* kf, const uint8_t* skip, const snk_point_fusion* pts, int n,
+                      const snk_camera* K, float th, int32_t* best_idx, int32_t* best_dist);
+int search_triangulation_bow(const snk_frame_view* kf1, const double* np1, const snk_featvec_view* fv1,
+                             const snk_frame_view* kf2, const double* np2, const snk_featvec_view* fv2, const double* E,
+                             const snk_camera* K, float epipolarDistance, int featureDistance, int32_t* pairs,
+                             long long* pair_ops);
+int search_triangulation_project(const snk_frame_view* kf1, const double* np1, const snk_frame_view* kf2,
+                                 const double* np2, const double* grid, int grid_rows, int grid_cols, const double* E12,
+                                 const snk_camera* K, float epipolarDistance, int featureDistance, int32_t* pairs,
+                                 long long* pair_ops);
+int match_prediction(const uint64_t* desc_left, int n_left, double* last_positions, const snk_frame_view* right,
+                     float radius, int featureError, int32_t* matches);
 }  // namespace orbref

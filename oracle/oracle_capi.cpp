@@ -229,4 +229,38 @@ ORC_API float orc_bow_score(const int32_t* ids1, const float* v1, int n1, const 
 {
     return bowref::score(ids1, v1, n1, ids2, v2, n2);
 }
+// ---- local mapping / loop closing searches ----
+ORC_API double orc_epipolar_distance_squared(const double* p1, const double* p2, const double* F)
+{
+    return epipolar_distance_squared(p1, p2, F);
+}
+ORC_API int orc_fuse_search(const snk_frame_view* kf, const uint8_t* mask, const snk_point_fusion* pts, int n,
+                            const snk_camera* K, const snk_scale_pyramid* sp, float th, float obs_factor, int feature_th,
+                            int32_t* cand_kp, int32_t* cand_id, long long* ops)
+{
+    return fuse_search(kf, mask, pts, n, K, sp, th, obs_factor, feature_th, cand_kp, cand_id, ops);
+}
+ORC_API void orc_fuse_search_loop(const snk_frame_view* kf, const uint8_t* skip, const snk_point_fusion* pts, int n,
+                                  const snk_camera* K, float th, int32_t* best_idx, int32_t* best_dist)
+{
+    fuse_search_loop(kf, skip, pts, n, K, th, best_idx, best_dist);
+}
+ORC_API int orc_search_triangulation_bow(const snk_frame_view* kf1, const double* np1, const snk_featvec_view* fv1,
+                                         const snk_frame_view* kf2, const double* np2, const snk_featvec_view* fv2,
+                                         const double* E, const snk_camera* K, float epi, int fd, int32_t* pairs,
+                                         long long* ops)
+{
+    return search_triangulation_bow(kf1, np1, fv1, kf2, np2, fv2, E, K, epi, fd, pairs, ops);
+}
+ORC_API int orc_search_triangulation_project(const snk_frame_view* kf1, const double* np1, const snk_frame_view* kf2,
+                                             const double* np2, const double* grid, int gr, int gc, const double* E,
+                                             const snk_camera* K, float epi, int fd, int32_t* pairs, long long* ops)
+{
+    return search_triangulation_project(kf1, np1, kf2, np2, grid, gr, gc, E, K, epi, fd, pairs, ops);
+}
+ORC_API int orc_match_prediction(const uint64_t* dl, int n, double* pos, const snk_frame_view* right, float radius, int fe,
+                                 int32_t* matches)
+{
+    return match_prediction(dl, n, pos, right, radius, fe, matches);
+}
 }  // extern "C"

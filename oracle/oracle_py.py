@@ -326,3 +326,57 @@ def bow_score(ids1, v1, ids2, v2):
     ids1, ids2 = np.ascontiguousarray(ids1, np.int32), np.ascontiguousarray(ids2, np.int32)
     v1, v2 = np.ascontiguousarray(v1, np.float32), np.ascontiguousarray(v2, np.float32)
     return float(lib().orc_bow_score(_p(ids1), _p(v1), len(ids1), _p(ids2), _p(v2), len(ids2)))
+
+
+# ---- local mapping / loop closing searches ----
+def epipolar_distance_squared(p1, p2, F):
+    lib().orc_epipolar_distance_squared.restype = C.c_double
+    p1, p2, F = (np.ascontiguousarray(a, np.float64) for a in (p1, p2, F))
+    return float(lib().orc_epipolar_distance_squared(_p(p1), _p(p2), _p(F)))
+
+
+def fuse_search(kf, mask, points, cam, pyr, th, obs_factor, feature_th):
+    pts = np.ascontiguousarray(points)
+    n = len(pts)
+    ck, ci = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+    ops = C.c_longlong(0)
+    m = lib().orc_fuse_search(C.byref(kf), _p(mask) if mask is not None else None, _p(pts), n, C.byref(cam), C.byref(pyr),
+                              C.c_float(th), C.c_float(obs_factor), feature_th, _p(ck), _p(ci), C.byref(ops))
+    return ck[:m].copy(), ci[:m].copy(), ops.value
+
+
+def fuse_search_loop(kf, skip, points, cam, th):
+    pts = np.ascontiguousarray(points)
+    n = len(pts)
+    bi, bd = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+    lib().orc_fuse_search_loop(C.byref(kf), _p(skip) if skip is not None else None, _p(pts), n, C.byref(cam),
+                               C.c_float(th), _p(bi), _p(bd))
+    return bi[:n], bd[:n]
+
+
+def search_triangulation_bow(kf1, np1, fv1, kf2, np2, fv2, E, cam, epi, fd):
+    pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+    ops = C.c_longlong(0)
+    E = np.ascontiguousarray(E, np.float64)
+    m = lib().orc_search_triangulation_bow(C.byref(kf1), _p(np1), C.byref(fv1), C.byref(kf2), _p(np2), C.byref(fv2), _p(E),
+                                           C.byref(cam), C.c_float(epi), fd, _p(pairs), C.byref(ops))
+    return pairs[:m].copy(), ops.value
+
+
+def search_triangulation_project(kf1, np1, kf2, np2, grid, E, cam, epi, fd):
+    pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+    ops = C.c_longlong(0)
+    E = np.ascontiguousarray(E, np.float64)
+    grid = np.ascontiguousarray(grid, np.float64)
+    m = lib().orc_search_triangulation_project(C.byref(kf1), _p(np1), C.byref(kf2), _p(np2), _p(grid), grid.shape[0],
+                                               grid.shape[1], _p(E), C.byref(cam), C.c_float(epi), fd, _p(pairs),
+                                               C.byref(ops))
+    return pairs[:m].copy(), ops.value
+
+
+def match_prediction(desc_left, positions, right, radius, feature_error):
+    d = np.ascontiguousarray(desc_left, np.uint64).reshape(-1, 4)
+    pos = np.array(positions, np.float64, copy=True)
+    matches = np.zeros(max(len(d), 1), np.int32)
+    m = lib().orc_match_prediction(_p(d), len(d), _p(pos), C.byref(right), C.c_float(radius), feature_error, _p(matches))
+    return m, matches[:len(d)], pos

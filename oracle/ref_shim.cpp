@@ -220,3 +220,14 @@ REF_API float ref_bow_score(const int* ids1, const float* v1, int n1, const int*
     for (int i = 0; i < n2; ++i) b.push_back({ids2[i], v2[i]});
     return MiniBow2::FeatureVector::score(a, b);
 }
+
+
+// ---- Saiga::EpipolarDistanceSquared from the reference's own translation unit (Epipolar.cpp, see Makefile) -------
+#include "saiga/vision/reconstruction/Epipolar.h"
+REF_API double ref_epipolar_distance_squared(const double* p1, const double* p2, const double* F_rowmajor)
+{
+    Mat3 F;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) F(r, c) = F_rowmajor[3 * r + c];
+    return EpipolarDistanceSquared(Vec2(p1[0], p1[1]), Vec2(p2[0], p2[1]), F);
+}

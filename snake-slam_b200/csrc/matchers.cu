@@ -3,8 +3,10 @@
 #include "project_kernels.cuh"
 #include "image_kernels.cuh"
 #include "bow_kernels.cuh"
+#include "mapping_kernels.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -485,3 +487,4 @@ extern "C" int snk_match_knn2_noalloc(int device, void* cuda_stream, const uint6
 
 #include "project_host.inl"
 #include "bow_host.inl"
+#include "mapping_host.inl"

@@ -18,6 +18,8 @@ POINT_FINE = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("normal", "<f8", 
                        ("ref_level", "<i4"), ("valid", "<i4"), ("id", "<i4")])
 POINT_COARSE = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("normal", "<f8", 3), ("octave", "<i4"),
                          ("angle", "<f4"), ("id", "<i4"), ("_pad", "<i4")])
+POINT_FUSION = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("normal", "<f8", 3), ("ref_depth", "<f4"),
+                         ("ref_level", "<i4"), ("observations", "<i4"), ("id", "<i4")])
 POINT_KF = np.dtype([("desc", "<u8", 4), ("pos", "<f8", 3), ("id", "<i4"), ("_pad", "<i4")])
 assert KP32.itemsize == 24 and KP64.itemsize == 48 and POINT_FINE.itemsize == 96 and POINT_COARSE.itemsize == 96
 assert POINT_KF.itemsize == 64
@@ -75,7 +77,7 @@ class GridView(C.Structure):
 class FrameView(C.Structure):
     _fields_ = [("n", C.c_int32), ("kp_un", C.c_void_p), ("desc", C.c_void_p), ("right_points", C.c_void_p),
                 ("kp_to_point", C.c_void_p), ("pose_q", C.c_double * 4), ("pose_t", C.c_double * 3),
-                ("grid", GridView)]
+                ("grid", GridView), ("depth", C.c_void_p)]
 
 
 class ScalePyramidC(C.Structure):
@@ -321,6 +323,58 @@ class Context:
                                                     stride, levelsup, C.c_void_p(bow_ids), C.c_void_p(bow_vals),
                                                     C.c_void_p(fv_nodes), C.c_void_p(fv_offsets), C.c_void_p(fv_indices),
                                                     C.c_void_p(out_counts)))
+
+    # ---- local mapping / loop closing searches ----
+    def Fuse(self, kf, point_mask, points, cam, pyr, th, obs_factor, feature_th):
+        """MappingORBMatcher::Fuse (LocalMap<FusionPoint> overload) -> fuseCandidates as (kp index, point id) arrays."""
+        pts = np.ascontiguousarray(points, POINT_FUSION)
+        n = len(pts)
+        ck, ci = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+        m = C.c_int()
+        mask = None if point_mask is None else np.ascontiguousarray(point_mask, np.uint8)
+        _check(lib().snk_fuse_search(self.c, C.byref(kf), _p(mask) if mask is not None else None, _p(pts), n, C.byref(cam),
+                                     C.byref(pyr), C.c_float(th), C.c_float(obs_factor), feature_th, _p(ck), _p(ci),
+                                     C.byref(m)))
+        return ck[:m.value].copy(), ci[:m.value].copy()
+
+    def FuseLoopSearch(self, kf, skip, points, cam, th):
+        """The search of LoopORBmatcher::Fuse -> best_idx, best_dist per point."""
+        pts = np.ascontiguousarray(points, POINT_FUSION)
+        n = len(pts)
+        bi, bd = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+        skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+        _check(lib().snk_fuse_search_loop(self.c, C.byref(kf), _p(skip) if skip is not None else None, _p(pts), n,
+                                          C.byref(cam), C.c_float(th), _p(bi), _p(bd)))
+        return bi[:n], bd[:n]
+
+    def SearchForTriangulation2(self, kf1, np1, fv1, kf2, np2, fv2, E, cam, epipolar_distance, feature_distance):
+        pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+        E = np.ascontiguousarray(E, np.float64)
+        m = C.c_int()
+        _check(lib().snk_search_triangulation_bow(self.c, C.byref(kf1), _p(np1), C.byref(fv1), C.byref(kf2), _p(np2),
+                                                  C.byref(fv2), _p(E), C.byref(cam), C.c_float(epipolar_distance),
+                                                  feature_distance, _p(pairs), C.byref(m)))
+        return pairs[:m.value].copy()
+
+    def SearchForTriangulationProject(self, kf1, np1, kf2, np2, grid, E, cam, epipolar_distance, feature_distance):
+        pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+        E = np.ascontiguousarray(E, np.float64)
+        grid = np.ascontiguousarray(grid, np.float64)
+        m = C.c_int()
+        _check(lib().snk_search_triangulation_project(self.c, C.byref(kf1), _p(np1), C.byref(kf2), _p(np2), _p(grid),
+                                                      grid.shape[0], grid.shape[1], _p(E), C.byref(cam),
+                                                      C.c_float(epipolar_distance), feature_distance, _p(pairs),
+                                                      C.byref(m)))
+        return pairs[:m.value].copy()
+
+    def ComputeMatchesPrediction(self, desc_left, positions, right, radius=50.0, feature_error=50):
+        d = np.ascontiguousarray(desc_left, np.uint64).reshape(-1, 4)
+        pos = np.array(positions, np.float64, copy=True)
+        matches = np.zeros(max(len(d), 1), np.int32)
+        m = C.c_int()
+        _check(lib().snk_match_prediction(self.c, _p(d), len(d), _p(pos), C.byref(right), C.c_float(radius),
+                                          feature_error, _p(matches), C.byref(m)))
+        return m.value, matches[:len(d)], pos
 
     def stereo_orb_device(self, orb, n_pairs, params, rp_ptr, depth_ptr, nm_ptr):
         _check(lib().snk_stereo_match_orb_device(self.c, orb.h, n_pairs, C.byref(params), C.c_void_p(rp_ptr),

@@ -19,11 +19,14 @@ def make_frame(kps32, desc, w, h, rng, pose_q, pose_t, prematched_frac=0.15, rig
     f.kp = np.ascontiguousarray(k64)
     f.desc = np.ascontiguousarray(desc)
     f.right = np.where(rng.random(n) < right_frac, f.kp["x"] - bf / rng.uniform(3, 60, n), -1000.0).astype(np.float32)
+    f.depth = np.where(f.right > 0, bf / np.maximum(f.kp["x"] - f.right, 1e-3), -1.0).astype(np.float32)
+    f.right = np.where(f.depth > 0, f.right, -1.0).astype(np.float32)  # right_points and depth are set together
     f.k2p = np.where(rng.random(n) < prematched_frac, rng.integers(100000, 200000, n), -1).astype(np.int32)
     f.cells = np.ascontiguousarray(cells)
     v = snakeorb.FrameView()
     v.n = n
     v.kp_un, v.desc, v.right_points, v.kp_to_point = f.kp.ctypes.data, f.desc.ctypes.data, f.right.ctypes.data, f.k2p.ctypes.data
+    v.depth = f.depth.ctypes.data
     for i in range(4):
         v.pose_q[i] = pose_q[i]
     for i in range(3):
@@ -76,3 +79,29 @@ def featvec(desc, rng, n_nodes=100):
     fv.node_ids, fv.offsets, fv.indices = ids.ctypes.data, off.ctypes.data, idx.ctypes.data
     fv._keep = (ids, off, idx)
     return fv
+
+
+def fusion_points(mp, rng):
+    p = np.zeros(len(mp["pos"]), snakeorb.POINT_FUSION)
+    p["desc"], p["pos"], p["normal"] = mp["desc"], mp["pos"], mp["normal"]
+    p["ref_depth"], p["ref_level"] = mp["ref_depth"], mp["ref_level"]
+    p["observations"] = rng.integers(1, 7, len(p))
+    p["id"] = np.arange(len(p), dtype=np.int32) * 3 + 5
+    return p
+
+
+def normalized_points(frame, K):
+    fx, fy, cx, cy = K
+    return np.ascontiguousarray(np.stack([(frame.kp["x"] - cx) / fx, (frame.kp["y"] - cy) / fy], 1))
+
+
+def stereo_keyframes(feats, rng, K, w, h, baseline):
+    """Two keyframes looking at the synthetic stereo pair: kf1 at the identity, kf2 translated by `baseline` along x
+    (camera-frame translation -baseline), E = [t]x for t = (1, 0, 0): epipolar lines are image rows."""
+    kl, dl = feats["l"]
+    kr, dr = feats["r"]
+    q = np.array([0.0, 0.0, 0.0, 1.0])
+    f1 = make_frame(kl, dl, w, h, rng, q, np.zeros(3), prematched_frac=0.2)
+    f2 = make_frame(kr, dr, w, h, rng, q, np.array([-baseline, 0.0, 0.0]), prematched_frac=0.2)
+    E = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+    return f1, f2, normalized_points(f1, K), normalized_points(f2, K), E
