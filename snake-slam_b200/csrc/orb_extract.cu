@@ -109,8 +109,7 @@ struct snk_orb
     uint8_t* d_gauss = nullptr;
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
     ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
-    int* d_yofs[SNK_MAX_LEVELS]{};
-    short* d_yb[SNK_MAX_LEVELS]{};
+    ResizeRow* d_rows[SNK_MAX_LEVELS]{};
     float2* d_pattern_t = nullptr;  // rBRIEF pattern as float2, transposed to [point-in-byte][lane]
     CellDev* d_cells = nullptr;
     TileDev* d_tiles = nullptr;
@@ -139,7 +138,7 @@ struct snk_orb
         };
         F(d_pyr), F(d_gauss), F(d_cells), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
             F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
-        for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_yofs[l]), F(d_yb[l]);
+        for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_rows[l]);
         rows = cols = 0;
     }
 };
@@ -325,12 +324,22 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             q.sel = 0;
             for (int k = 0; k < 8; ++k) q.sel |= nib[k] << (4 * k);
         }
+        // per-row table: both source rows clamped as cv::resize's vertical pass clamps them, coefficients << 16
+        const int sh = P.lv[l - 1].h, dh = P.lv[l].h;
+        std::vector<ResizeRow> rows(dh);
+        for (int y = 0; y < dh; ++y)
+        {
+            SNK_REQUIRE(yb[2 * y] >= 0 && yb[2 * y] <= 2048 && yb[2 * y + 1] >= 0 && yb[2 * y + 1] <= 2048,
+                        "vertical coefficient outside [0, 2048]");
+            rows[y].sy0 = std::min(std::max(yo[y], 0), sh - 1);
+            rows[y].sy1 = std::min(std::max(yo[y] + 1, 0), sh - 1);
+            rows[y].b0  = (unsigned)yb[2 * y] << 16;
+            rows[y].b1  = (unsigned)yb[2 * y + 1] << 16;
+        }
         SNK_CUDA(cudaMalloc(&h->d_quads[l], quads.size() * sizeof(ResizeQuad)));
-        SNK_CUDA(cudaMalloc(&h->d_yofs[l], yo.size() * sizeof(int)));
-        SNK_CUDA(cudaMalloc(&h->d_yb[l], yb.size() * sizeof(short)));
+        SNK_CUDA(cudaMalloc(&h->d_rows[l], rows.size() * sizeof(ResizeRow)));
         SNK_CUDA(cudaMemcpy(h->d_quads[l], quads.data(), quads.size() * sizeof(ResizeQuad), cudaMemcpyHostToDevice));
-        SNK_CUDA(cudaMemcpy(h->d_yofs[l], yo.data(), yo.size() * sizeof(int), cudaMemcpyHostToDevice));
-        SNK_CUDA(cudaMemcpy(h->d_yb[l], yb.data(), yb.size() * sizeof(short), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMemcpy(h->d_rows[l], rows.data(), rows.size() * sizeof(ResizeRow), cudaMemcpyHostToDevice));
     }
     h->fast_rows = align_up(h->fast_rows, 4);  // keeps every tile buffer 128-byte aligned (4 rows x 96 bytes = 3 x 128)
     h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
@@ -581,7 +590,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         const int rps = px >= (40ll << 20) ? RS_ROWS : (px >= (10ll << 20) ? RS_ROWS / 2 : RS_ROWS / 4);
         dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + rps - 1) / rps + 3) / 4, n_imgs);
         k_resize<<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
-                                       h->d_quads[l], h->d_yofs[l], h->d_yb[l], rps);
+                                       h->d_quads[l], h->d_rows[l], rps);
         ++nl[1];
     }
     if (prof) cudaEventRecord(ev[2], st);

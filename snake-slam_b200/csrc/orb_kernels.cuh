@@ -92,10 +92,24 @@ struct ResizeQuad  // 32 bytes per 4 output pixels
     unsigned coef[4];    // ialpha pair per pixel: a0 | a1 << 16
 };
 
+struct ResizeRow  // 16 bytes per output row
+{
+    int sy0, sy1;      // the two source rows, already clamped to the image
+    unsigned b0, b1;   // vertical coefficients << 16 (0..2048: linear interpolation never produces negative ones)
+};
+
+// hi32(a * b) + c in one IMAD.HI
+__device__ __forceinline__ unsigned mad_hi(unsigned a, unsigned b, unsigned c)
+{
+    unsigned d;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src, size_t src_stride, int spitch, int sh,
                                                 uint8_t* __restrict__ dst, size_t dst_stride, int dpitch, int dw, int dh,
-                                                const ResizeQuad* __restrict__ quads, const int* __restrict__ yofs,
-                                                const short* __restrict__ yb, int rows_per_strip)
+                                                const ResizeQuad* __restrict__ quads, const ResizeRow* __restrict__ rows,
+                                                int rows_per_strip)
 {
     const int lane  = threadIdx.x & 31;
     const int strip = blockIdx.y * 4 + (threadIdx.x >> 5);
@@ -103,29 +117,33 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
     const int y0    = strip * rows_per_strip;  // shorter strips on small levels: the rows of a strip are a serial chain
     if (y0 >= dh || x >= dw) return;  // no warp-wide primitives below
     const uint8_t* S = src + (size_t)blockIdx.z * src_stride;
-    uint8_t* D       = dst + (size_t)blockIdx.z * dst_stride;
+    uint8_t* D       = dst + (size_t)blockIdx.z * dst_stride + (size_t)y0 * dpitch + x;
     const ResizeQuad q = quads[x >> 2];
     const int wlast = (spitch >> 2) - 1;
     const int i0 = min(q.word, wlast), i1 = min(q.word + 1, wlast), i2 = min(q.word + 2, wlast);
     const unsigned sel01 = q.sel & 0xffffu, sel23 = q.sel >> 16;
+    const bool full = x + 4 <= dw;
 
+    // horizontal pass of one source row: the four sums, already >> 4 as the vertical pass consumes them
     auto hrow = [&](int sy, unsigned (&h)[4]) {
         const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)sy * spitch);
         const unsigned w0 = __ldg(row + i0), w1 = __ldg(row + i1), w2 = __ldg(row + i2);
         const unsigned v0 = __funnelshift_r(w0, w1, q.shift_bits), v1 = __funnelshift_r(w1, w2, q.shift_bits);
         const unsigned r01 = __byte_perm(v0, v1, sel01), r23 = __byte_perm(v0, v1, sel23);
-        h[0] = __dp2a_lo(q.coef[0], r01, 0u);
-        h[1] = __dp2a_hi(q.coef[1], r01, 0u);
-        h[2] = __dp2a_lo(q.coef[2], r23, 0u);
-        h[3] = __dp2a_hi(q.coef[3], r23, 0u);
+        h[0] = __dp2a_lo(q.coef[0], r01, 0u) >> 4;
+        h[1] = __dp2a_hi(q.coef[1], r01, 0u) >> 4;
+        h[2] = __dp2a_lo(q.coef[2], r23, 0u) >> 4;
+        h[3] = __dp2a_hi(q.coef[3], r23, 0u) >> 4;
     };
 
     unsigned ha[4], hb[4];
     int held = -1;  // source row whose sums are in hb
     const int y1 = min(y0 + rows_per_strip, dh);
-    for (int y = y0; y < y1; ++y)
+    for (int y = y0; y < y1; ++y, D += dpitch)
     {
-        const int sy0 = min(max(yofs[y], 0), sh - 1), sy1 = min(max(yofs[y] + 1, 0), sh - 1);
+        const int4 rt = __ldg(reinterpret_cast<const int4*>(rows) + y);  // same address in every lane: one broadcast load
+        const int sy0 = rt.x, sy1 = rt.y;
+        const unsigned b0 = (unsigned)rt.z, b1 = (unsigned)rt.w;
         if (sy0 == held)
         {
 #pragma unroll
@@ -141,20 +159,17 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
             for (int j = 0; j < 4; ++j) hb[j] = ha[j];
         }
         held = sy1;
-        const int b0 = yb[2 * y], b1 = yb[2 * y + 1];
-        unsigned packed = 0;
+        // cv's vertical pass: uchar((((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2) — each product is
+        // truncated on its own, which is hi32((S >> 4) * (b << 16)): two IMAD.HI per pixel. The sum never exceeds 1022,
+        // and the reference narrows with a plain cast, so the low byte is the result.
+        unsigned v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-        {
-            int v = (((b0 * (int)(ha[j] >> 4)) >> 16) + ((b1 * (int)(hb[j] >> 4)) >> 16) + 2) >> 2;
-            v     = min(max(v, 0), 255);
-            packed |= (unsigned)v << (8 * j);
-        }
-        uint8_t* drow = D + (size_t)y * dpitch + x;
-        if (x + 4 <= dw)
-            *reinterpret_cast<uint32_t*>(drow) = packed;  // dpitch and x are multiples of 4
+        for (int j = 0; j < 4; ++j) v[j] = mad_hi(hb[j], b1, mad_hi(ha[j], b0, 2u)) >> 2;
+        const unsigned packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+        if (full)
+            *reinterpret_cast<uint32_t*>(D) = packed;  // dpitch and x are multiples of 4
         else
-            for (int j = 0; j < 4 && x + j < dw; ++j) drow[j] = (uint8_t)(packed >> (8 * j));
+            for (int j = 0; j < 4 && x + j < dw; ++j) D[j] = (uint8_t)(packed >> (8 * j));
     }
 }
 
