@@ -282,12 +282,14 @@ def main():
 
     NCH = args.chunks if (NI % (2 * args.chunks) == 0) else 1
     CI, CP = NI // NCH, P // NCH
-    h_kps = torch.empty((NI, cap, 24), dtype=torch.uint8, pin_memory=True)
-    h_desc = torch.empty((NI, cap, 4), dtype=torch.int64, pin_memory=True)
-    h_cnt = torch.empty((NI,), dtype=torch.int32, pin_memory=True)
-    h_rp = torch.empty((P, cap), dtype=torch.float32, pin_memory=True)
-    h_dp = torch.empty((P, cap), dtype=torch.float32, pin_memory=True)
-    h_nm = torch.empty((P,), dtype=torch.int32, pin_memory=True)
+    # two sets of pinned result buffers: step s+1 is enqueued while the results of step s are still arriving (a streaming
+    # consumer reads set s % 2 while set (s + 1) % 2 is being filled)
+    h_kps = torch.empty((2, NI, cap, 24), dtype=torch.uint8, pin_memory=True)
+    h_desc = torch.empty((2, NI, cap, 4), dtype=torch.int64, pin_memory=True)
+    h_cnt = torch.empty((2, NI), dtype=torch.int32, pin_memory=True)
+    h_rp = torch.empty((2, P, cap), dtype=torch.float32, pin_memory=True)
+    h_dp = torch.empty((2, P, cap), dtype=torch.float32, pin_memory=True)
+    h_nm = torch.empty((2, P), dtype=torch.int32, pin_memory=True)
     e2e_lanes = []
     if not args.no_e2e:
         for _ in range(min(args.lanes, NCH)):
@@ -300,28 +302,37 @@ def main():
                               torch.empty((CP, cap), dtype=torch.float32, device="cuda"),
                               torch.empty((CP,), dtype=torch.int32, device="cuda")))
 
-    def e2e_enqueue(k):
+    def e2e_enqueue(k, par):
         st, exc, cxc, rpc, dpc, nmc = e2e_lanes[k % len(e2e_lanes)]
         exc.enqueue_ptr(host.data_ptr() + k * CI * W * H, CI, H, W, W, W * H, False)
         cxc.stereo_orb_device(exc, CP, sp, rpc.data_ptr(), dpc.data_ptr(), nmc.data_ptr())
         with torch.cuda.stream(st):
-            h_rp[k * CP:(k + 1) * CP].copy_(rpc, non_blocking=True)
-            h_dp[k * CP:(k + 1) * CP].copy_(dpc, non_blocking=True)
-            h_nm[k * CP:(k + 1) * CP].copy_(nmc, non_blocking=True)
+            h_rp[par, k * CP:(k + 1) * CP].copy_(rpc, non_blocking=True)
+            h_dp[par, k * CP:(k + 1) * CP].copy_(dpc, non_blocking=True)
+            h_nm[par, k * CP:(k + 1) * CP].copy_(nmc, non_blocking=True)
 
-    def e2e_fetch(k):
+    def e2e_fetch(k, par):
         _, exc, _, _, _, _ = e2e_lanes[k % len(e2e_lanes)]
-        snakeorb._check(snakeorb.lib().snk_orb_fetch_async(exc.h, C.c_void_p(h_kps.data_ptr() + k * CI * cap * 24),
-                                                           C.c_void_p(h_desc.data_ptr() + k * CI * cap * 32), cap,
-                                                           C.c_void_p(h_cnt.data_ptr() + k * CI * 4)))
+        snakeorb._check(snakeorb.lib().snk_orb_fetch_async(exc.h, C.c_void_p(h_kps[par].data_ptr() + k * CI * cap * 24),
+                                                           C.c_void_p(h_desc[par].data_ptr() + k * CI * cap * 32), cap,
+                                                           C.c_void_p(h_cnt[par].data_ptr() + k * CI * 4)))
 
-    def step_e2e():
-        # every chunk: H2D, kernels, D2H on its lane's stream, no host wait in between; one sync per step
+    e2e_done = [[], []]  # per result set: one event per lane, recorded behind the set's last copy
+
+    def step_e2e(s):
+        # every chunk: H2D, kernels, D2H on its lane's stream, no host wait in between. The host then waits for the
+        # PREVIOUS step's results (set (s - 1) % 2), so the copies of consecutive steps overlap like a stream of frames.
+        par = s & 1
         for k in range(NCH):
-            e2e_enqueue(k)
-            e2e_fetch(k)
+            e2e_enqueue(k, par)
+            e2e_fetch(k, par)
+        e2e_done[par] = []
         for st, *_ in e2e_lanes:
-            st.synchronize()
+            ev = torch.cuda.Event()
+            ev.record(st)
+            e2e_done[par].append(ev)
+        for ev in e2e_done[par ^ 1]:
+            ev.synchronize()
 
     # ---- device-resident timing --------------------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
@@ -410,17 +421,18 @@ def main():
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        for _ in range(2):
-            step_e2e()
+        for i in range(2):
+            step_e2e(i)
         barrier()
         tw0 = time.perf_counter()
-        for _ in range(args.steps):
-            step_e2e()
+        for i in range(args.steps):
+            step_e2e(i)
         torch.cuda.synchronize()
         e2e = (time.perf_counter() - tw0) * 1e3  # host wall clock: the last fetch returns when the results are in host memory
         barrier()
         # the end-to-end path must deliver the same results as the device-resident one
-        assert int(h_cnt.sum()) == n_kp_step and int(h_nm.sum()) == n_match_step, "e2e results differ from the device path"
+        for par in range(2):
+            assert int(h_cnt[par].sum()) == n_kp_step and int(h_nm[par].sum()) == n_match_step, "e2e results differ from the device path"
 
     t = torch.tensor([ms, e2e if e2e is not None else 0.0], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -472,7 +484,7 @@ def main():
             d2h = NI * cap * (24 + 32) + NI * 4 + P * cap * 8 + P * 4 + 4
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
-                           "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap)"}
+                           "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
         if next_rows is not None:
             line["next_rows"] = next_rows
         if not args.no_cpu:
