@@ -268,6 +268,7 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
     __syncthreads();
     CellDev c = cells[cell0];
     if (tid == 0) issue(c, 0);
+    for (int i = tid; i < tile_bytes >> 4; i += FAST_NT) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
 
 #pragma unroll 1
     for (int kc = 0; kc < ncell; ++kc)
@@ -285,7 +286,7 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
     // while the copies are in flight: reset the per-cell state, clear the score tile (16-byte stores) and the bitmaps
     if (tid == 0) s_n1 = s_n2 = s_ini = 0;
     for (int i = tid; i < 2 * FAST_BMW; i += FAST_NT) (&bm[0][0])[i] = 0;
-    for (int i = tid; i < (h * FAST_PITCH) >> 4; i += FAST_NT) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+    // the score tile is all zero here: cleared once before the first cell, and every cell resets the entries it wrote
     {
         // bounded wait: a copy that never completes (bad descriptor) must not hang the device; it is reported instead
         const unsigned bar = bar_addr0 + 8u * buf, parity = (unsigned)((kc >> 1) & 1);
@@ -407,11 +408,13 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
         const int y = list2[k] >> 8, x = list2[k] & 255;
         const int i = (y - 3) * zw + (x - 3);
         const uint32_t word = B[i >> 5], bit = 1u << (i & 31);
+        const int sc = score[y][x + a];
+        score[y][x + a] = 0;  // list2 holds every entry phase B wrote: the tile is zero again for the next cell
         if (word & bit)
         {
             const int pos = pre[i >> 5] + __popc(word & (bit - 1));
             if (pos < P.cell_cap)
-                out[pos] = (uint32_t)(x + c.off_x) | ((uint32_t)(y + c.off_y) << 12) | ((uint32_t)(score[y][x + a] - 1) << 24);
+                out[pos] = (uint32_t)(x + c.off_x) | ((uint32_t)(y + c.off_y) << 12) | ((uint32_t)(sc - 1) << 24);
         }
     }
     if (tid == 0) cell_count[slot] = pre[FAST_BMW];
