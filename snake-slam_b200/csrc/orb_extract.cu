@@ -110,6 +110,7 @@ struct snk_orb
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
     ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
     ResizeRow* d_rows[SNK_MAX_LEVELS]{};
+    uint2* d_moment_tab = nullptr;  // ComputeAngle disc as per-word dp4a weights (orb_kernels.cuh: DS_MOM_TABLE)
     float2* d_pattern_t = nullptr;  // rBRIEF pattern as float2, transposed to [point-in-byte][lane]
     CellDev* d_cells = nullptr;
     TileDev* d_tiles = nullptr;
@@ -451,6 +452,34 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
         snk_orb_destroy(h);
         return SNK_ERR_CUDA;
     }
+    // word-wise moment weights: window byte p = 4 * w + b sits at column offset u = p - al - 15
+    {
+        std::vector<uint2> mt(DS_MOM_TABLE);
+        for (int al = 0; al < 4; ++al)
+            for (int r = 0; r < 31; ++r)
+                for (int w = 0; w < DS_MOM_WORDS; ++w)
+                {
+                    const int v = r - 15, lim = umax[v < 0 ? -v : v];
+                    uint2 e = make_uint2(0u, 0u);
+                    for (int b = 0; b < 4; ++b)
+                    {
+                        const int u = 4 * w + b - al - 15;
+                        if (u >= -lim && u <= lim)
+                        {
+                            e.x |= (unsigned)(unsigned char)(signed char)u << (8 * b);
+                            e.y |= 1u << (8 * b);
+                        }
+                    }
+                    mt[(al * 31 + r) * DS_MOM_WORDS + w] = e;
+                }
+        if (cudaMalloc(&h->d_moment_tab, mt.size() * sizeof(uint2)) != cudaSuccess ||
+            cudaMemcpy(h->d_moment_tab, mt.data(), mt.size() * sizeof(uint2), cudaMemcpyHostToDevice) != cudaSuccess)
+        {
+            set_error("moment table upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+            snk_orb_destroy(h);
+            return SNK_ERR_CUDA;
+        }
+    }
     *out = h;
     return SNK_OK;
 }
@@ -462,6 +491,7 @@ void snk_orb_destroy(snk_orb* h)
     cudaStreamSynchronize(h->stream);
     h->free_buffers();
     if (h->d_pattern_t) cudaFree(h->d_pattern_t);
+    if (h->d_moment_tab) cudaFree(h->d_moment_tab);
     if (h->d_rgba) cudaFree(h->d_rgba);
     if (h->h_counts) cudaFreeHost(h->h_counts);
     if (h->h_err) cudaFreeHost(h->h_err);
@@ -631,7 +661,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
 
     // stage 5: orientation + descriptors + output records
     k_describe<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, 0, st>>>(
-        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t);
+        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t, h->d_moment_tab);
     ++nl[5];
     if (prof)
     {

@@ -954,12 +954,27 @@ __global__ void __launch_bounds__(256) k_blur(PyrDev P, const TileDev* __restric
 
 constexpr int DS_WARPS = 8;
 constexpr int DS_KP_PER_WARP = 8;  // keypoints per warp: the CTA prologue (pattern, level prefix) is paid once per 64
+// Moment table of ORB::ComputeAngle for word-wise evaluation: entry [al][row][w] (al = (x - 15) & 3, row = v + 15,
+// w = aligned word 0..8 of the 36-byte window that starts at the aligned column below x - 15) holds
+//   .x  the four column offsets u of the word's bytes as signed bytes, 0 outside the disc  (m10 += dp4a(word, .x))
+//   .y  1 per byte inside the disc                                          (m01 += v * dp4a(word, .y))
+constexpr int DS_MOM_WORDS = 9, DS_MOM_TASKS = 31 * DS_MOM_WORDS;  // 279 word tasks per keypoint
+constexpr int DS_MOM_TABLE = 4 * DS_MOM_TASKS;                     // uint2 entries
+
+// sum of (unsigned byte of a) * (signed byte of b) + c
+__device__ __forceinline__ int dp4a_u8s8(unsigned a, unsigned b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint32_t* __restrict__ sel,
                                                             const int* __restrict__ sel_count,
                                                             snk_keypoint_f32* __restrict__ kps,
                                                             uint64_t* __restrict__ desc, int* __restrict__ counts,
-                                                            const float2* __restrict__ pattern_t)
+                                                            const float2* __restrict__ pattern_t,
+                                                            const uint2* __restrict__ moment_tab)
 {
     __shared__ float2 pat[16][32];  // pat[j][lane] = point 16*lane + j as floats (conflict-free: lanes are consecutive)
     __shared__ int s_pref[SNK_MAX_LEVELS + 1];
@@ -980,54 +995,78 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     }
     __syncthreads();
     const int total = min(s_pref[P.nlevels], P.kp_stride);
-#pragma unroll 1
-    for (int kk = 0; kk < DS_KP_PER_WARP; ++kk)
+    // the warp's keypoints: g(kk) = (blockIdx.x * DS_KP_PER_WARP + kk) * DS_WARPS + wid, kk < nk
+    const int g0 = blockIdx.x * DS_KP_PER_WARP * DS_WARPS + wid;
+    if (g0 >= total) return;
+    const int nk = min(DS_KP_PER_WARP, (total - g0 + DS_WARPS - 1) / DS_WARPS);
+
+    // ---- per keypoint (lane kk owns keypoint kk): level and packed position ----
+    int my_level = 0;
+    uint32_t my_p = 0;
+    if (lane < nk)
     {
-    const int g     = (blockIdx.x * DS_KP_PER_WARP + kk) * DS_WARPS + wid;
-    if (g >= total) return;
-    int level = 0;
-    while (level + 1 < P.nlevels && g >= s_pref[level + 1]) ++level;
-    const LevelDev& L = P.lv[level];
-    const uint32_t p  = sel[(size_t)img * P.sel_per_img + L.sel_base + (g - s_pref[level])];
-    // kp.point += (minBorderX, minBorderY)   ORBExtractor.cpp:165-166
-    const int x = (int)(p & 0xfffu) + 16, y = (int)((p >> 12) & 0xfffu) + 16;
-    const float resp = (float)(p >> 24);
+        const int g = g0 + lane * DS_WARPS;
+        while (my_level + 1 < P.nlevels && g >= s_pref[my_level + 1]) ++my_level;
+        my_p = sel[(size_t)img * P.sel_per_img + P.lv[my_level].sel_base + (g - s_pref[my_level])];
+    }
 
     // ---- ORB::ComputeAngle: integer moments over the radius-15 disc of the un-blurred level ----
-    // offsets inside one level image fit 32 bits (levels are at most 4000 x 4000)
-    const int pitch    = L.pitch;
-    const uint8_t* raw = L.img + (size_t)img * L.img_stride + (y * pitch + x);
-    const int u        = lane - 15;  // lane 31 idles
-    int m10 = 0, m01 = 0;
-    if (lane < 31)
+    // word-wise: 279 aligned words cover the 31 x 31 patch; lane takes tasks lane, lane + 32, ... (9 per lane)
+    int my_m10 = 0, my_m01 = 0;
+#pragma unroll 1
+    for (int kk = 0; kk < nk; ++kk)
     {
-        // u_max (ORBPattern::AngleUmax) as compile-time constants so the 31 row loads are independent and issue
-        // back to back; snk_orb_create checks the table against the host computation
-        constexpr int UMAX[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-        const int au = abs(u);
-        int rowsum = 0;  // sum over v of v * I(v,u) for my column
-        int colsum = 0;  // sum over v of I(v,u)
-        const uint8_t* col = raw + u;
+        const int level   = __shfl_sync(0xffffffffu, my_level, kk);
+        const uint32_t p  = __shfl_sync(0xffffffffu, my_p, kk);
+        const LevelDev& L = P.lv[level];
+        // kp.point += (minBorderX, minBorderY)   ORBExtractor.cpp:165-166
+        const int x = (int)(p & 0xfffu) + 16, y = (int)((p >> 12) & 0xfffu) + 16;
+        const int pitch = L.pitch;
+        const int al    = (x - 15) & 3;
+        // offsets inside one level image fit 32 bits (levels are at most 4000 x 4000)
+        const uint8_t* base = L.img + (size_t)img * L.img_stride + ((y - 15) * pitch + (x - 15 - al));
+        const uint2* tab    = moment_tab + al * DS_MOM_TASKS;
+        int m10 = 0, m01 = 0;
 #pragma unroll
-        for (int v = -15; v <= 15; ++v)
+        for (int it = 0; it < (DS_MOM_TASKS + 31) / 32; ++it)
         {
-            const int val = (au <= UMAX[v < 0 ? -v : v]) ? (int)col[v * pitch] : 0;
-            colsum += val;
-            rowsum += v * val;
+            const int t = lane + 32 * it;
+            if (t < DS_MOM_TASKS)
+            {
+                const int r = (t * 7282) >> 16;  // t / 9 for t < 279
+                const int w = t - 9 * r;
+                const unsigned word = __ldg(reinterpret_cast<const unsigned*>(base + r * pitch) + w);
+                const uint2 e       = __ldg(tab + t);
+                m10 = dp4a_u8s8(word, e.x, m10);                         // u8 pixels x s8 column offsets
+                m01 += (r - 15) * (int)__dp4a(word, e.y, 0u);            // v * sum of the row's pixels inside the disc
+            }
         }
-        m10 = u * colsum;
-        m01 = rowsum;
+        m10 = warp_sum(m10);
+        m01 = warp_sum(m01);
+        if (lane == kk) my_m10 = m10, my_m01 = m01;
     }
-    m10 = warp_sum(m10);
-    m01 = warp_sum(m01);
+
+    // ---- angle, sine and cosine of all keypoints of the warp at once (lane kk computes keypoint kk) ----
     // degrees(atan2f(m01, m10)): a * 180.f / pi_f, then wrap negatives by +360 (OrbDescriptors.cpp:52-53)
-    float angle = snkmath::atan2f_fdlibm((float)m01, (float)m10);
-    angle       = __fdiv_rn(__fmul_rn(angle, 180.0f), 3.14159265358979323846f);
-    angle       = __fadd_rn((angle < 0.f) ? 360.f : 0.f, angle);
+    float my_angle = snkmath::atan2f_fdlibm((float)my_m01, (float)my_m10);
+    my_angle       = __fdiv_rn(__fmul_rn(my_angle, 180.0f), 3.14159265358979323846f);
+    my_angle       = __fadd_rn((my_angle < 0.f) ? 360.f : 0.f, my_angle);
+    const float my_rad = __fmul_rn(__fdiv_rn(my_angle, 180.0f), 3.14159265358979323846f);
+    const float my_a = snkmath::cosf_glibc(my_rad), my_b = snkmath::sinf_glibc(my_rad);
 
     // ---- ORB::ComputeDescriptor on the blurred level; lane i produces byte i ----
-    const float rad = __fmul_rn(__fdiv_rn(angle, 180.0f), 3.14159265358979323846f);
-    const float a = snkmath::cosf_glibc(rad), b = snkmath::sinf_glibc(rad);
+#pragma unroll 1
+    for (int kk = 0; kk < nk; ++kk)
+    {
+    const int g       = g0 + kk * DS_WARPS;
+    const int level   = __shfl_sync(0xffffffffu, my_level, kk);
+    const uint32_t p  = __shfl_sync(0xffffffffu, my_p, kk);
+    const float angle = __shfl_sync(0xffffffffu, my_angle, kk);
+    const float a     = __shfl_sync(0xffffffffu, my_a, kk);
+    const float b     = __shfl_sync(0xffffffffu, my_b, kk);
+    const LevelDev& L = P.lv[level];
+    const int x = (int)(p & 0xfffu) + 16, y = (int)((p >> 12) & 0xfffu) + 16;
+    const float resp = (float)(p >> 24);
     const int gpitch  = L.gauss_pitch;
     const uint8_t* gs = L.gauss + (size_t)img * L.gauss_stride;
     const float px = (float)x, py = (float)y;
