@@ -643,7 +643,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     if (prof) cudaEventRecord(ev[3], st);
 
     // stage 3: quadtree distribution per (level, image)
-    k_distribute<<<dim3(P.nlevels, n_imgs), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
+    k_distribute<<<dim3(n_imgs, P.nlevels), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
                                                                      h->d_workA, h->d_workB, h->d_sel, h->d_sel_count,
                                                                      h->node_cap, QT_KP_SMEM, h->d_err);
     ++nl[3];

@@ -455,7 +455,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     int2* cpos      = reinterpret_cast<int2*>(ccnt_big + 4 * node_cap);  // (leaf position, next position) of node i
     __shared__ int s_warp[QT_NT / 32], s_ctrl[10];
 
-    const int level = blockIdx.x, img = blockIdx.y;
+    const int level = blockIdx.y, img = blockIdx.x;  // all level-0 blocks (the longest) are dispatched first
     const LevelDev& L = P.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const size_t wbase = (size_t)img * P.cand_per_img + L.cand_base;
