@@ -150,14 +150,14 @@ int bow_smem_attr(int device)
     std::lock_guard<std::mutex> lock(attr_mutex);
     if (device < 64 && !attr_set[device])
     {
-        SNK_CUDA(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, BOW_MAX_FEATURES * 12));
+        SNK_CUDA(cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, BOW_MAX_FEATURES * 16));
         attr_set[device] = true;
     }
     return SNK_OK;
 }
 int pow2_at_least(int n)
 {
-    int p = 32;
+    int p = 64;  // matches k_bow_assemble
     while (p < n) p <<= 1;
     return p;
 }
@@ -192,7 +192,7 @@ int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* desc, int 
     if ((rc = bow_smem_attr(c->device))) return rc;
     SNK_CUDA(cudaMemcpyAsync(dd, desc, 32 * (size_t)n, cudaMemcpyHostToDevice, st));
     k_bow_descend<<<(n + 15) / 16, 256, 0, st>>>(voc->dev(), reinterpret_cast<const uint4*>(dd), nullptr, n, n, levelsup, dw, df);
-    k_bow_assemble<<<1, BOW_NT, (size_t)pow2_at_least(n) * 12, st>>>(dw, df, nullptr, n, n, dbi, dbv, dfn, dfo, dfi, dcnt);
+    k_bow_assemble<<<1, BOW_NT, (size_t)pow2_at_least(n) * 16, st>>>(dw, df, nullptr, n, n, dbi, dbv, dfn, dfo, dfi, dcnt);
     SNK_CUDA(cudaGetLastError());
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 8, dcnt, 8, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(bow_ids, dbi, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
@@ -227,7 +227,7 @@ int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const uint64_
     cudaStream_t st = c->stream;
     k_bow_descend<<<dim3((stride + 15) / 16, n_frames), 256, 0, st>>>(voc->dev(), reinterpret_cast<const uint4*>(desc_dev),
                                                                       counts_dev, 0, stride, levelsup, dw, df);
-    k_bow_assemble<<<n_frames, BOW_NT, (size_t)pow2_at_least(stride) * 12, st>>>(
+    k_bow_assemble<<<n_frames, BOW_NT, (size_t)pow2_at_least(stride) * 16, st>>>(
         dw, df, counts_dev, 0, stride, bow_ids_dev, bow_vals_dev, fv_node_ids_dev, fv_offsets_dev, fv_indices_dev, out_counts_dev);
     SNK_CUDA(cudaGetLastError());
     return SNK_OK;

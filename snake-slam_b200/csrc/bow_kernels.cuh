@@ -6,19 +6,11 @@
 // The reference sorts the (node id, feature index) pairs with std::sort on the node id alone; std::sort is unstable
 // and the node ids repeat heavily, so the order of the features inside a node — which later decides the candidate
 // order of the BoW matchers — is whatever libstdc++'s introsort leaves behind. That permutation is reproduced
-// exactly, in parallel:
-//   * introsort's partition phase only depends on comparison outcomes. The sub-ranges of one recursion level are
-//     disjoint, so they are partitioned concurrently, one warp per range, level by level (the depth budget that
-//     triggers the heapsort fallback travels with each range).
-//   * one unguarded Hoare partition is data parallel once written on the ORIGINAL range: with l_1 < l_2 < ... the
-//     positions whose value is not before the pivot and r_1 > r_2 > ... those the pivot is not before, the serial
-//     loop swaps (l_t, r_t) for t = 1..T, T = #{t : l_t < r_t}, and returns min(l_{T+1}, r_T) (l_1 if T = 0).
-//   * the closing insertion pass is a stable sort by node id: a bitonic sort on (node id, position after the
-//     partition phase).
+// exactly and in parallel by gnusort::cta_sort (gnu_sort_cta.cuh).
 // tests/test_gpu_bow.py compares against std::sort through the oracle on tie-heavy inputs of every size class.
 #pragma once
 #include "common.cuh"
-#include "gnu_sort.cuh"
+#include "gnu_sort_cta.cuh"
 
 namespace snk
 {
@@ -87,66 +79,6 @@ __global__ void __launch_bounds__(256) k_bow_descend(VocDev V, const uint4* __re
     }
 }
 
-// ---- one exact libstdc++ partition step by a warp ------------------------------------------------------------
-// v[first, last) with last - first > 16; returns the cut of std::__unguarded_partition_pivot. Lp / Rq: scratch with
-// one u16 per element of the range (indexed like v).
-template <class C>
-__device__ int warp_partition_pivot(unsigned long long* v, int first, int last, uint16_t* Lp, uint16_t* Rq, int lane)
-{
-    if (lane == 0) gnusort::median_to_first<unsigned long long, C>(v, first, first + 1, first + (last - first) / 2, last - 1);
-    __syncwarp();
-    const unsigned long long P = v[first];
-    const int s = first + 1, e = last;
-    const unsigned lt = (1u << lane) - 1u;
-    int nL = 0, nR = 0;
-    for (int base = s; base < e; base += 32)
-    {
-        const int i      = base + lane;
-        const bool valid = i < e;
-        const unsigned long long x = valid ? v[i] : 0ull;
-        const bool isL = valid && !C::before(x, P), isR = valid && !C::before(P, x);
-        const unsigned mL = __ballot_sync(0xffffffffu, isL), mR = __ballot_sync(0xffffffffu, isR);
-        if (isL) Lp[s + nL + __popc(mL & lt)] = (uint16_t)i;
-        if (isR) Rq[s + nR + __popc(mR & lt)] = (uint16_t)i;
-        nL += __popc(mL);
-        nR += __popc(mR);
-    }
-    __syncwarp();
-    // T = number of leading t with l_t < r_t (monotone: l increases, r decreases)
-    const int m = min(nL, nR);
-    int T = 0;
-    for (int base = 0; base < m; base += 32)
-    {
-        const int t   = base + lane;
-        const bool ok = t < m && Lp[s + t] < Rq[s + nR - 1 - t];
-        const unsigned bm = __ballot_sync(0xffffffffu, ok);
-        if (bm == 0xffffffffu)
-            T += 32;
-        else
-        {
-            T += __ffs(~bm) - 1;
-            break;
-        }
-    }
-    for (int t = lane; t < T; t += 32)
-    {
-        const int a = Lp[s + t], b = Rq[s + nR - 1 - t];
-        const unsigned long long x = v[a];
-        v[a] = v[b];
-        v[b] = x;
-    }
-    int cut;
-    if (T == 0)
-        cut = Lp[s];
-    else
-    {
-        const int rT = Rq[s + nR - T];
-        cut          = (T < nL && Lp[s + T] < rT) ? (int)Lp[s + T] : rT;
-    }
-    __syncwarp();
-    return cut;
-}
-
 // bitonic sort of np2 (power of two) 64-bit keys in shared memory by the whole CTA
 __device__ __forceinline__ void cta_bitonic_u64(unsigned long long* key, int np2, int tid, int nt)
 {
@@ -172,7 +104,6 @@ __device__ __forceinline__ void cta_bitonic_u64(unsigned long long* key, int np2
 }
 
 constexpr int BOW_NT = 256;
-constexpr int BOW_SEG_MAX = 512;  // ranges of more than 16 elements in an array of <= 8192
 
 // exclusive rank of `flag` among the threads of the CTA for one 256-wide chunk; total returned in *total
 __device__ __forceinline__ int cta_rank(bool flag, int tid, int* s_warp, int* total)
@@ -194,7 +125,7 @@ __device__ __forceinline__ int cta_rank(bool flag, int tid, int* s_warp, int* to
     return before + __popc(m & ((1u << lane) - 1u));
 }
 
-// dynamic shared memory: key[np2] u64 | Lp[np2] u16 | Rq[np2] u16 (the two u16 arrays are reused as np2 floats)
+// dynamic shared memory: key[np2] u64 | 8 * np2 bytes of sort scratch (reused as np2 floats)
 // Batched like k_bow_descend: blockIdx.x = frame, outputs of frame f at f*stride (fv_offsets: f*(stride+1), counts: 2f).
 __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long long* __restrict__ words,
                                                           const unsigned long long* __restrict__ feats,
@@ -204,7 +135,7 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long lon
                                                           int* __restrict__ fv_indices, int* __restrict__ counts)
 {
     const int n = in_counts ? min(in_counts[blockIdx.x], stride) : n_fixed;
-    int np2     = 32;
+    int np2     = 64;  // >= 64 keeps 8 * np2 >= gnusort::cta_sort_scratch_bytes(n)
     while (np2 < n) np2 <<= 1;
     {
         const size_t f = blockIdx.x;
@@ -213,76 +144,21 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long lon
     }
     extern __shared__ __align__(16) unsigned char bow_smem[];
     unsigned long long* key = reinterpret_cast<unsigned long long*>(bow_smem);
-    uint16_t* Lp            = reinterpret_cast<uint16_t*>(key + np2);
-    uint16_t* Rq            = Lp + np2;
-    float* vals             = reinterpret_cast<float*>(Lp);
-    __shared__ uint2 segs[2][BOW_SEG_MAX];
-    __shared__ int nseg[2];
+    unsigned char* scratch  = reinterpret_cast<unsigned char*>(key + np2);  // 8 * np2 bytes
+    float* vals             = reinterpret_cast<float*>(scratch);
     __shared__ int s_warp[BOW_NT / 32];
     __shared__ int s_n;
     __shared__ float s_norm;
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    using Cmp = gnusort::AscHigh32;
+    const int tid = threadIdx.x, lane = tid & 31;
 
     // ================= FeatureVector::setFeatures (MiniBow2.h:101-126) =================
     for (int i = tid; i < n; i += BOW_NT) key[i] = feats[i];
-    if (tid == 0)
-    {
-        int lg = 0;
-        while ((n >> (lg + 1)) != 0) ++lg;
-        nseg[0] = nseg[1] = 0;
-        if (n > 16)
-        {
-            segs[0][0] = make_uint2((unsigned)n << 16, (unsigned)(2 * lg));  // first = 0 | last << 16, depth budget
-            nseg[0]    = 1;
-        }
-    }
     __syncthreads();
-    // introsort's partition phase, one recursion level per round
-    for (int cur = 0; nseg[cur] > 0; cur ^= 1)
+    gnusort::cta_sort<unsigned long long, gnusort::AscHigh32, BOW_NT>(key, n, scratch, tid);
     {
-        const int ns = nseg[cur];
-        for (int sidx = wid; sidx < ns; sidx += BOW_NT / 32)
-        {
-            const uint2 sg  = segs[cur][sidx];
-            const int first = (int)(sg.x & 0xffffu), last = (int)(sg.x >> 16);
-            int depth       = (int)sg.y;
-            if (depth == 0)
-            {
-                if (lane == 0) gnusort::heap_sort<unsigned long long, Cmp>(key, first, last);  // __partial_sort(first, last, last)
-                __syncwarp();
-                continue;
-            }
-            --depth;
-            const int cut = warp_partition_pivot<Cmp>(key, first, last, Lp, Rq, lane);
-            if (lane == 0)
-            {
-                if (last - cut > 16) segs[cur ^ 1][atomicAdd(&nseg[cur ^ 1], 1)] = make_uint2((unsigned)cut | ((unsigned)last << 16), depth);
-                if (cut - first > 16) segs[cur ^ 1][atomicAdd(&nseg[cur ^ 1], 1)] = make_uint2((unsigned)first | ((unsigned)cut << 16), depth);
-            }
-        }
-        __syncthreads();
-        if (tid == 0) nseg[cur] = 0;
-        __syncthreads();
-    }
-    // the insertion pass is a stable sort by node id: (node id + 1) << 26 | position << 13 | feature index
-    for (int i = tid; i < np2; i += BOW_NT)
-    {
-        unsigned long long k2 = ~0ull;
-        if (i < n)
-        {
-            const unsigned long long k1 = key[i];
-            const unsigned long long id1 = (unsigned long long)((long long)(int)(k1 >> 32) + 1);
-            k2 = (id1 << 26) | ((unsigned long long)i << 13) | (k1 & 0x1fffull);
-        }
-        key[i] = k2;  // slot i is read and written by this thread only
-    }
-    __syncthreads();
-    cta_bitonic_u64(key, np2, tid, BOW_NT);
-    {
-        // entries of zero-weight words (id -1 -> 0) sort first and are skipped (:111)
+        // entries of zero-weight words (node id -1) sort first and are skipped (:111)
         int skip_local = 0;
-        for (int i = tid; i < n; i += BOW_NT) skip_local += ((key[i] >> 26) == 0ull);
+        for (int i = tid; i < n; i += BOW_NT) skip_local += ((int)(key[i] >> 32) == -1);
         skip_local = warp_sum(skip_local);
         if (tid == 0) s_n = 0;
         __syncthreads();
@@ -298,9 +174,9 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long lon
             int id = 0;
             if (i < n && i >= skip)
             {
-                id   = (int)(key[i] >> 26) - 1;
-                head = (i == skip) || ((int)(key[i - 1] >> 26) - 1 != id);
-                fv_indices[i - skip] = (int)(key[i] & 0x1fffull);
+                id   = (int)(key[i] >> 32);
+                head = (i == skip) || ((int)(key[i - 1] >> 32) != id);
+                fv_indices[i - skip] = (int)(unsigned)key[i];
             }
             int total;
             const int r = cta_rank(head, tid, s_warp, &total);

@@ -11,7 +11,7 @@
 #pragma once
 #include "common.cuh"
 #include "glibc_math.cuh"
-#include "gnu_sort.cuh"
+#include "gnu_sort_cta.cuh"
 
 #include <cuda.h>  // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint, no link dependency)
 
@@ -558,9 +558,11 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         // std::sort by NumKeypoints descending (FeatureDistribution.cpp:124) — libstdc++ permutation
         for (int i = tid; i < m; i += QT_NT) keys[i] = ((uint32_t)(inner[i].to - inner[i].from) << gnusort::SHIFT) | (uint32_t)i;
         __syncthreads();
+        // the whole block sorts (same permutation as the serial code, gnu_sort_cta.cuh); its scratch lives in the
+        // child-count / position arrays, which are only written after the sort
+        gnusort::cta_sort<uint32_t, gnusort::DescCount, QT_NT>(keys, m, reinterpret_cast<unsigned char*>(ccnt_big), tid);
         if (tid == 0)
         {
-            gnusort::sort(keys, m);
             // nodes are now ordered by size: [0, nbig) are handled by a warp each, the rest by a thread each
             int lo = 0, hi = m;
             while (lo < hi)
