@@ -13,6 +13,8 @@
 #include <array>
 #include <cstdio>
 #include <cstdlib>
+#include <string>
+#include <utility>
 #include <vector>
 
 #ifdef SNAKEORB_WITH_SAIGA
@@ -197,6 +199,64 @@ inline int StereoMatchingB200(snk_ctx* c, double bf, bool relaxed, const std::ve
                            depth.data(), &n),
           "snk_stereo_match");
     return n;
+}
+
+// MiniBow2::TemplatedVocabulary<DescriptorORB> (saiga/vision/slam/MiniBow2.h:173-460): the members Snake calls.
+// BowVector / FeatureVector are the plain containers MiniBow2 derives its classes from (:43, :98).
+using BowVectorB200     = std::vector<std::pair<int, float>>;
+using FeatureVectorB200 = std::vector<std::pair<int, std::vector<int>>>;
+class VocabularyB200
+{
+   public:
+    // TemplatedVocabulary(const std::string& filename) -> loadRaw (:190, :1020)
+    VocabularyB200(const std::string& filename, snk_ctx* ctx, int device = 0) : ctx_(ctx)
+    {
+        check(snk_voc_load_raw(device, filename.c_str(), &voc_), "snk_voc_load_raw");
+        check(snk_voc_info(voc_, &k_, &L_, nullptr, &words_), "snk_voc_info");
+    }
+    ~VocabularyB200() { snk_voc_destroy(voc_); }
+    VocabularyB200(const VocabularyB200&)            = delete;
+    VocabularyB200& operator=(const VocabularyB200&) = delete;
+    unsigned int size() const { return (unsigned int)words_; }
+    bool empty() const { return words_ == 0; }
+    int getBranchingFactor() const { return k_; }
+    int getDepthLevels() const { return L_; }
+    // transform(features, v, fv, levelsup, num_threads) (:883-931); num_threads is meaningless here
+    void transform(const std::vector<DescriptorORB>& features, BowVectorB200& v, FeatureVectorB200& fv, int levelsup,
+                   int /*num_threads*/ = 1) const
+    {
+        const int n = (int)features.size();
+        std::vector<int32_t> ids(n + 1), nodes(n + 1), offs(n + 2), idx(n + 1);
+        std::vector<float> vals(n + 1);
+        int nb = 0, nf = 0;
+        check(snk_bow_transform(ctx_, voc_, reinterpret_cast<const uint64_t*>(features.data()), n, levelsup, ids.data(),
+                                vals.data(), &nb, nodes.data(), offs.data(), idx.data(), &nf),
+              "snk_bow_transform");
+        v.clear();
+        fv.clear();
+        v.reserve(nb);
+        fv.reserve(nf);
+        for (int i = 0; i < nb; ++i) v.emplace_back(ids[i], vals[i]);
+        for (int i = 0; i < nf; ++i) fv.emplace_back(nodes[i], std::vector<int>(idx.begin() + offs[i], idx.begin() + offs[i + 1]));
+    }
+    const snk_voc* handle() const { return voc_; }
+
+   private:
+    snk_ctx* ctx_  = nullptr;
+    snk_voc* voc_  = nullptr;
+    int k_ = 0, L_ = 0, words_ = 0;
+};
+
+// Preprocess::undistortKeypoints (Snake/Preprocess/Preprocess.cpp:55-77). rect: K_src fx fy cx cy | D_src.Coeffs() |
+// R.coeffs() (x y z w) | K_dst fx fy cx cy s — the fields of Saiga::Rectification, see snk_rectify.
+inline void undistortKeypointsB200(snk_ctx* c, const snk_rectify& rect, const std::vector<KeyPointD>& keypoints,
+                                   std::vector<KeyPointD>& undistorted_keypoints, std::vector<double>& normalized_points_xy)
+{
+    undistorted_keypoints.resize(keypoints.size());
+    normalized_points_xy.resize(2 * keypoints.size());
+    check(snk_undistort_keypoints(c, &rect, reinterpret_cast<const snk_keypoint_f64*>(keypoints.data()), (int)keypoints.size(),
+                                  reinterpret_cast<snk_keypoint_f64*>(undistorted_keypoints.data()), normalized_points_xy.data()),
+          "snk_undistort_keypoints");
 }
 }  // namespace snkadapter
 
