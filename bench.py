@@ -239,6 +239,17 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (libsnakeorb has no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    # keep this rank's host threads and its pinned buffers (first touch) on the NUMA node of its GPU: with several ranks
+    # per box the host-to-device copies otherwise cross the socket interconnect
+    numa = "unset"
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        numa = "cpu affinity of GPU %d (%d cpus)" % (local_rank, len(os.sched_getaffinity(0)))
+    except Exception as exc:  # noqa: BLE001
+        numa = "unset (%s)" % type(exc).__name__
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -484,7 +495,7 @@ def main():
             d2h = NI * cap * (24 + 32) + NI * 4 + P * cap * 8 + P * 4 + 4
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
-                           "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
+                           "host_affinity": numa, "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
         if next_rows is not None:
             line["next_rows"] = next_rows
         if not args.no_cpu:
