@@ -265,6 +265,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
     }
     P.cells_per_img = (int)h->cells.size();
+    cell_cap        = align_up(cell_cap, 4);  // every cell list starts 16-byte aligned (k_distribute gathers with uint4 loads)
     P.cell_cap      = cell_cap;
     SNK_REQUIRE((size_t)P.cells_per_img * cell_cap < (1u << 30), "image too large for the candidate arrays");
     P.cand_per_img = P.cells_per_img * cell_cap;

@@ -500,8 +500,17 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     for (int cidx = tid; cidx < L.n_cells; cidx += QT_NT)
     {
         const int cnt = min(cc[cidx], P.cell_cap), off = co[cidx];
-        const uint32_t* s = cand + ((size_t)img * P.cells_per_img + L.cell_base + cidx) * P.cell_cap;
-        for (int k = 0; k < cnt; ++k) A[off + k] = s[k];
+        // cell lists are 16-byte aligned and cell_cap is a multiple of 4: four candidates per load, all loads of a cell
+        // independent of each other
+        const uint4* s = reinterpret_cast<const uint4*>(cand + ((size_t)img * P.cells_per_img + L.cell_base + cidx) * P.cell_cap);
+        for (int k = 0; k < cnt; k += 4)
+        {
+            const uint4 v = __ldg(s + (k >> 2));
+            A[off + k] = v.x;
+            if (k + 1 < cnt) A[off + k + 1] = v.y;
+            if (k + 2 < cnt) A[off + k + 2] = v.z;
+            if (k + 3 < cnt) A[off + k + 3] = v.w;
+        }
     }
     __syncthreads();
 
