@@ -111,8 +111,11 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
     float* rp             = right_points + (size_t)pair * stride;
     float* dp             = depth + (size_t)pair * stride;
     const int tid         = threadIdx.x;
+    // gridDim.y blocks share one pair: block `part` owns the left keypoints of every gridDim.y-th group of ST_NT (each
+    // block sorts the right image's rows for itself — a few microseconds — so the blocks stay independent)
+    const int part = blockIdx.y, step = ST_NT * gridDim.y;
     if (tid == 0) s_matches = 0;
-    for (int i = tid; i < nl; i += ST_NT) rp[i] = dp[i] = -1000.f;  // Frame::allocateTmp (Snake/Map/Frame.cpp:25-26)
+    for (int i = part * ST_NT + tid; i < nl; i += step) rp[i] = dp[i] = -1000.f;  // Frame::allocateTmp (Snake/Map/Frame.cpp:25-26)
     if (nr > sort_cap)
     {
         if (tid == 0) atomicExch(err, 1);
@@ -158,7 +161,7 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
     const double ratio   = prm.relaxed ? 0.9 : 0.7;
     const float th_rot   = prm.relaxed ? 25.f : 5.f;
     int local = 0;
-    for (int i = tid; i < nl; i += ST_NT)
+    for (int i = part * ST_NT + tid; i < nl; i += step)
     {
         const double lx = (double)L[i].x;
         const int oct   = L[i].octave;
@@ -216,7 +219,7 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
     local = warp_sum(local);
     if ((tid & 31) == 0 && local) atomicAdd(&s_matches, local);
     __syncthreads();
-    if (tid == 0) n_matches[pair] = s_matches;
+    if (tid == 0 && s_matches) atomicAdd(&n_matches[pair], s_matches);  // n_matches is zeroed by the launcher
 }
 
 // --------------------------------------------------------------------------------------------------------------

@@ -220,8 +220,9 @@ int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_
     int cap = 1;
     while (cap < nr) cap <<= 1;
     SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
-    k_stereo<snk_keypoint_f64><<<1, ST_NT, stereo_smem(cap), st>>>(dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn,
-                                                                  c->d_err);
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
+    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap), st>>>(
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err);
     SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
@@ -246,14 +247,17 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     int cap = 1;
     while (cap < stride) cap <<= 1;
     SNK_REQUIRE(cap <= 16384, "more than 16384 keypoints per image");
-    static bool attr_set = false;
-    if (!attr_set)
+    static bool attr_set[64] = {};  // the attribute belongs to the device
+    if (c->device >= 64 || !attr_set[c->device])
     {
         SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
-        attr_set = true;
+        if (c->device < 64) attr_set[c->device] = true;
     }
-    k_stereo<snk_keypoint_f32><<<n_pairs, ST_NT, stereo_smem(cap), c->stream>>>(kps, desc, counts, stride, 0, 0, *p, cap,
-                                                                               right_points, depth, n_matches, c->d_err);
+    // enough blocks to fill the machine: several blocks per pair when the batch is small
+    const int parts = std::max(1, std::min((stride + ST_NT - 1) / ST_NT, 1024 / std::max(n_pairs, 1)));
+    SNK_CUDA(cudaMemsetAsync(n_matches, 0, 4 * (size_t)n_pairs, c->stream));
+    k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, stereo_smem(cap), c->stream>>>(
+        kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err);
     SNK_CUDA(cudaGetLastError());
     return SNK_OK;
 }
