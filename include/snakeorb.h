@@ -484,6 +484,7 @@ SNK_API int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const
  * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of
  * saiga/data/vision/{0,50}.features. */
 SNK_API int snk_features_write(const char* path, const snk_keypoint_f64* kps, const uint64_t* desc, int n);
+/* snk_features_read returns SNK_ERR_CAPACITY (and the file's feature count in *n_out) when capacity is too small. */
 SNK_API int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64_t* desc, int capacity, int* n_out);
 /* KeyPoint<float>::cast<double>() as FeatureDetector.cpp:129-132 applies it to the extractor's output. */
 SNK_API int snk_keypoints_widen(const snk_keypoint_f32* in, int n, snk_keypoint_f64* out);

@@ -404,7 +404,11 @@ extern "C" int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64
     else if (nd && std::fread(desc, 32, nd, f) != nd)
         rc = SNK_ERR_INVALID;
     std::fclose(f);
-    if (rc == SNK_ERR_CAPACITY) set_error("%s holds %llu features, capacity is %d", path, (unsigned long long)nk, capacity);
+    if (rc == SNK_ERR_CAPACITY)
+    {
+        set_error("%s holds %llu features, capacity is %d", path, (unsigned long long)nk, capacity);
+        *n_out = (int)std::min<uint64_t>(nk, 0x7fffffffu);  // lets the caller size its arrays and read again
+    }
     if (rc == SNK_ERR_INVALID) set_error("%s is not a feature cache file", path);
     if (rc) return rc;
     *n_out = (int)nk;

@@ -201,6 +201,66 @@ inline int StereoMatchingB200(snk_ctx* c, double bf, bool relaxed, const std::ve
     return n;
 }
 
+// FeatureDetector::Detect (Snake/Preprocess/FeatureDetector.cpp:86-175) for one frame: per image the `.features`
+// cache is read when settings.fd_bufferToFile is on and the file exists (:94-111), otherwise the image is extracted,
+// the keypoints are widened to double (:129-132) and the cache file is written (:134-139). File names as at :91-92.
+// Returns how many of the two images were actually extracted (0 when both came from the cache).
+struct FrameFeaturesB200
+{
+    std::vector<KeyPointD> keypoints, keypoints_right;
+    std::vector<DescriptorORB> descriptors, descriptors_right;
+};
+inline bool file_exists_b200(const std::string& path)
+{
+    if (FILE* f = std::fopen(path.c_str(), "rb"))
+    {
+        std::fclose(f);
+        return true;
+    }
+    return false;
+}
+inline bool read_features_b200(const std::string& path, std::vector<KeyPointD>& kps, std::vector<DescriptorORB>& desc)
+{
+    int n = 0;
+    // first call with capacity 0 reports the count (SNK_ERR_CAPACITY), like sizing a vector before `bf >> vector`
+    snk_features_read(path.c_str(), nullptr, nullptr, 0, &n);
+    kps.resize(n);
+    desc.resize(n);
+    return snk_features_read(path.c_str(), reinterpret_cast<snk_keypoint_f64*>(kps.data()),
+                             reinterpret_cast<uint64_t*>(desc.data()), n, &n) == SNK_OK;
+}
+inline int DetectFrameB200(ORBExtractorB200& extractor, bool fd_bufferToFile, const std::string& tmpDir, int file_id,
+                           ImageView<unsigned char> image, const ImageView<unsigned char>* right_image,
+                           FrameFeaturesB200& frame)
+{
+    bool compute_left = true, compute_right = right_image != nullptr;
+    const std::string feature_file       = tmpDir + "/" + std::to_string(file_id) + ".features";
+    const std::string feature_file_right = tmpDir + "/" + std::to_string(file_id) + "_right.features";
+    if (fd_bufferToFile)
+    {
+        if (compute_left && file_exists_b200(feature_file))
+            compute_left = !read_features_b200(feature_file, frame.keypoints, frame.descriptors);
+        if (compute_right && file_exists_b200(feature_file_right))
+            compute_right = !read_features_b200(feature_file_right, frame.keypoints_right, frame.descriptors_right);
+    }
+    auto run = [&](ImageView<unsigned char> img, std::vector<KeyPointD>& kps, std::vector<DescriptorORB>& desc,
+                   const std::string& file) {
+        std::vector<KeyPointF> mvKeys;
+        extractor.Detect(img, mvKeys, desc);
+        kps.resize(mvKeys.size());
+        check(snk_keypoints_widen(reinterpret_cast<const snk_keypoint_f32*>(mvKeys.data()), (int)mvKeys.size(),
+                                  reinterpret_cast<snk_keypoint_f64*>(kps.data())),
+              "snk_keypoints_widen");
+        if (fd_bufferToFile)
+            check(snk_features_write(file.c_str(), reinterpret_cast<const snk_keypoint_f64*>(kps.data()),
+                                     reinterpret_cast<const uint64_t*>(desc.data()), (int)kps.size()),
+                  "snk_features_write");
+    };
+    if (compute_left) run(image, frame.keypoints, frame.descriptors, feature_file);
+    if (compute_right) run(*right_image, frame.keypoints_right, frame.descriptors_right, feature_file_right);
+    return (int)compute_left + (int)compute_right;
+}
+
 // MiniBow2::TemplatedVocabulary<DescriptorORB> (saiga/vision/slam/MiniBow2.h:173-460): the members Snake calls.
 // BowVector / FeatureVector are the plain containers MiniBow2 derives its classes from (:43, :98).
 using BowVectorB200     = std::vector<std::pair<int, float>>;
