@@ -1013,7 +1013,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     // ---- ORB::ComputeAngle: integer moments over the radius-15 disc of the un-blurred level ----
     // word-wise: 279 aligned words cover the 31 x 31 patch; lane takes tasks lane, lane + 32, ... (9 per lane)
     int my_m10 = 0, my_m01 = 0;
-#pragma unroll 1
+#pragma unroll 2
     for (int kk = 0; kk < nk; ++kk)
     {
         const int level   = __shfl_sync(0xffffffffu, my_level, kk);
