@@ -113,6 +113,11 @@ struct snk_orb
     uint2* d_moment_tab = nullptr;  // ComputeAngle disc as per-word dp4a weights (orb_kernels.cuh: DS_MOM_TABLE)
     float2* d_pattern_t = nullptr;  // rBRIEF pattern as float2, transposed to [point-in-byte][lane]
     CellDev* d_cells = nullptr;
+    GroupDev* d_groups = nullptr;  // k_fast_group: runs of up to FASTG_CELLS neighbouring cells
+    std::vector<GroupDev> groups;
+    int fastg_list = 0;
+    size_t fastg_smem = 0;
+    bool per_cell_fast = false;    // SNK_FAST_PER_CELL=1 selects the one-cell-at-a-time kernel (A/B comparisons)
     TileDev* d_tiles = nullptr;
     uint32_t *d_cand = nullptr, *d_workA = nullptr, *d_workB = nullptr, *d_sel = nullptr;
     int *d_cell_count = nullptr, *d_cell_off = nullptr, *d_sel_count = nullptr, *d_counts = nullptr, *d_err = nullptr;
@@ -137,7 +142,7 @@ struct snk_orb
             if (p) cudaFree(p);
             p = nullptr;
         };
-        F(d_pyr), F(d_gauss), F(d_cells), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
+        F(d_pyr), F(d_gauss), F(d_cells), F(d_groups), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
             F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
         for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_rows[l]);
         rows = cols = 0;
@@ -163,7 +168,7 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
     SNK_REQUIRE(((uintptr_t)base % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
     const cuuint64_t dims[3]    = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)h->prm.max_batch};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
-    const cuuint32_t box[3]     = {(cuuint32_t)FAST_PITCH, (cuuint32_t)h->box_h[l], 1};
+    const cuuint32_t box[3]     = {(cuuint32_t)(h->per_cell_fast ? FAST_PITCH : FASTG_PITCH), (cuuint32_t)h->box_h[l], 1};
     const cuuint32_t estr[3]    = {1, 1, 1};
     CUresult r = fn(&h->maps.level[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
@@ -176,6 +181,10 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
 {
     if (h->rows == rows && h->cols == cols) return SNK_OK;
     h->free_buffers();
+    {
+        const char* e = getenv("SNK_FAST_PER_CELL");  // decides the TMA box width, so it is read before the maps are built
+        h->per_cell_fast = e && e[0] == '1';
+    }
     const int L = h->prm.nlevels, B = h->prm.max_batch;
     SNK_REQUIRE(rows <= 4000 && cols <= 4000, "image %dx%d too large (max 4000x4000)", cols, rows);
     PyrDev& P = h->P;
@@ -344,9 +353,58 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         SNK_CUDA(cudaMemcpy(h->d_quads[l], quads.data(), quads.size() * sizeof(ResizeQuad), cudaMemcpyHostToDevice));
         SNK_CUDA(cudaMemcpy(h->d_rows[l], rows.data(), rows.size() * sizeof(ResizeRow), cudaMemcpyHostToDevice));
     }
-    h->fast_rows = align_up(h->fast_rows, 4);  // keeps every tile buffer 128-byte aligned (4 rows x 96 bytes = 3 x 128)
+    h->fast_rows = align_up(h->fast_rows, 8);  // keeps every tile buffer 128-byte aligned (8 rows x 96 or 176 bytes)
     h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
     SNK_CUDA(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fast_smem, 48 * 1024)));
+    // groups of horizontally adjacent cells (fast_group.cuh): same level and cell row, contiguous zones, at most
+    // FASTG_CELLS cells and FASTG_GW ROI columns
+    h->groups.clear();
+    h->fastg_list = 8;
+    for (size_t ci = 0; ci < h->cells.size();)
+    {
+        const CellDev& f = h->cells[ci];
+        GroupDev g{};
+        g.level = f.level, g.x0 = f.x0, g.y0 = f.y0, g.h = f.h, g.box_h = (short)f.box_h, g.off_x = f.off_x, g.off_y = f.off_y;
+        g.cell0 = (int)ci;  // index in the image's cell list
+        for (int k = 0; k <= FASTG_CELLS; ++k) g.zb[k] = 32767;
+        int n = 0;
+        while (ci + n < h->cells.size() && n < FASTG_CELLS)
+        {
+            const CellDev& c = h->cells[ci + n];
+            if (c.level != f.level || c.y0 != f.y0 || c.h != f.h) break;
+            const int rel = c.x0 - f.x0;
+            if (n > 0 && rel + 3 != g.zb[n]) break;          // zones must touch
+            if (rel + c.w > FASTG_GW) break;
+            if (c.w < 7) break;                               // degenerate cell: keep it alone
+            g.zb[n]     = (short)(rel + 3);
+            g.zb[n + 1] = (short)(rel + c.w - 3);
+            ++n;
+        }
+        if (n == 0)
+        {  // a cell that cannot start a run (no zone): a group of its own with an empty zone
+            n       = 1;
+            g.zb[0] = 3, g.zb[1] = (short)std::max(3, f.w - 3);
+        }
+        g.ncell = (short)n;
+        g.zend  = g.zb[n];
+        const short zend = g.zend;
+        for (int k = n + 1; k <= FASTG_CELLS; ++k) g.zb[k] = 32767;
+        g.zb[n] = zend;
+        {
+            const int a = f.x0 & 15, c0 = a + g.zb[0], c1 = a + zend;
+            const int nwz = std::max(((c1 + 3) >> 2) - (c0 >> 2), 1);
+            g.zn_word0 = (unsigned short)(c0 >> 2), g.zn_words = (unsigned short)nwz, g.zn_inv = (1u << 20) / nwz + 1;
+            SNK_REQUIRE(a + (zend + 3) <= FASTG_PITCH, "internal: cell group wider than the FAST tile");
+        }
+        h->fastg_list = std::max(h->fastg_list, (std::max(zend - g.zb[0], 0) * std::max(f.h - 6, 0) + 7) & ~7);
+        h->groups.push_back(g);
+        ci += n;
+    }
+    h->fastg_smem = 3 * (size_t)h->fast_rows * FASTG_PITCH + 4 * (size_t)h->fastg_list;
+    SNK_REQUIRE(h->fastg_smem <= 200 * 1024, "internal: FAST group tile too large");
+    SNK_CUDA(cudaFuncSetAttribute(k_fast_group, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fastg_smem, 48 * 1024)));
+    SNK_CUDA(cudaMalloc(&h->d_groups, h->groups.size() * sizeof(GroupDev)));
+    SNK_CUDA(cudaMemcpy(h->d_groups, h->groups.data(), h->groups.size() * sizeof(GroupDev), cudaMemcpyHostToDevice));
     SNK_CUDA(cudaMalloc(&h->d_cells, h->cells.size() * sizeof(CellDev)));
     SNK_CUDA(cudaMemcpy(h->d_cells, h->cells.data(), h->cells.size() * sizeof(CellDev), cudaMemcpyHostToDevice));
     SNK_CUDA(cudaMalloc(&h->d_tiles, h->tiles.size() * sizeof(TileDev)));
@@ -639,8 +697,12 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
 
     // stage 2: FAST over every cell of every level
-    k_fast<<<dim3((P.cells_per_img + FAST_CPB - 1) / FAST_CPB, n_imgs), FAST_NT, h->fast_smem, st>>>(
-        P, h->maps, h->d_cells, h->d_cand, h->d_cell_count, h->d_err, h->fast_rows, h->fast_list);
+    if (h->per_cell_fast)
+        k_fast<<<dim3((P.cells_per_img + FAST_CPB - 1) / FAST_CPB, n_imgs), FAST_NT, h->fast_smem, st>>>(
+            P, h->maps, h->d_cells, h->d_cand, h->d_cell_count, h->d_err, h->fast_rows, h->fast_list);
+    else
+        k_fast_group<<<dim3(((int)h->groups.size() + FASTG_GPB - 1) / FASTG_GPB, n_imgs), FASTG_NT, h->fastg_smem, st>>>(
+            P, h->maps, h->d_groups, (int)h->groups.size(), h->d_cand, h->d_cell_count, h->d_err, h->fast_rows, h->fastg_list);
     ++nl[2];
     if (prof) cudaEventRecord(ev[3], st);
 

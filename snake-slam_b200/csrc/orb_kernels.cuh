@@ -177,7 +177,8 @@ constexpr int FAST_BMW = (FAST_ZMAX + 31) / 32;
 // Window of 9 = min3 of three windows of 3. (An earlier signed 32-bit formulation was mis-narrowed by nvcc 12.9 to
 // min.u16/max.u16 and returned wrong scores on sm_100a; everything here is explicitly unsigned and non-negative, and
 // tools/dev_check.cu checks the function on the device against brute force.)
-__device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[FAST_PITCH], int y, int x)
+template <int PITCH>
+__device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[PITCH], int y, int x)
 {
     const unsigned v = 256u + t[y][x];
     unsigned e[16];
@@ -412,6 +413,10 @@ __global__ void __launch_bounds__(FAST_NT) k_fast(PyrDev P, const __grid_constan
     }  // cells of this CTA
 }
 
+}  // namespace snk
+#include "fast_group.cuh"
+namespace snk
+{
 // --------------------------------------------------------------------------------------------------------------
 // Quadtree distribution
 // --------------------------------------------------------------------------------------------------------------
