@@ -203,3 +203,23 @@ def test_rgba_input(so, oracle):
     # and against the oracle's extraction of the converted image
     ko, do = oracle.Extractor(1000, 1.2, 8, 20, 7, 1).detect(conv[1])
     assert np.array_equal(a[1][1], do) and np.array_equal(a[1][0]["x"], ko["x"])
+
+
+@pytest.mark.parametrize("w,h,nf,scale,nl,kind", [
+    (1920, 1080, 3000, 1.2, 8, "image"),    # full HD: wide cell rows, many 4-cell groups plus ragged ends
+    (640, 480, 1500, 1.3, 5, "image"),      # largest supported scale step
+    (1241, 376, 2000, 1.1, 10, "image"),    # small scale step, 10 levels
+    (1241, 376, 2000, 1.2, 8, "noise"),     # every pixel a FAST candidate: list capacities of the cell groups
+    (333, 257, 400, 1.2, 4, "image"),       # odd sizes, few cells per row (groups shorter than 4)
+    (97, 230, 100, 1.2, 2, "noise"),        # a single cell column
+])
+def test_varied_geometries(so, oracle, w, h, nf, scale, nl, kind):
+    """Cell grids, group shapes and pyramid tables away from the BASELINE shapes, end to end against the oracle."""
+    from snakeorb import synthetic as S
+
+    img = S.image(4242 + w, w, h) if kind == "image" else S.adversarial("noise", w, h, 7 + h)
+    ex = so.ORBExtractor(nf, scale, nl, 20, 7)
+    k, d = ex.Detect(img)
+    k2, d2 = oracle.Extractor(nf, scale, nl, 20, 7, 4).detect(img)
+    assert len(k2) > 20
+    assert_same_features(k, d, k2, d2)
