@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(KNN_NT) k_knn2(const uint64_t* __restrict__ d1
 // left keypoint binary-searches its first row and walks the sorted run — same candidates, same order.
 // --------------------------------------------------------------------------------------------------------------
 constexpr int ST_NT = 256;
+constexpr int ST_ROW_BINS = 4096;  // image rows the counting sort of k_stereo covers (levels are at most 4000 rows)
 
 __device__ __forceinline__ int iround_f(float v) { return (int)__fadd_rn(v, v >= 0.f ? 0.5f : -0.5f); }
 
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
                                                   float* __restrict__ depth, int* __restrict__ n_matches,
                                                   int* __restrict__ err)
 {
-    extern __shared__ uint32_t keys[];  // sort_cap entries: (iRound(y) + 32768) << 16 | index
+    extern __shared__ uint32_t keys[];  // sort_cap entries: (iRound(y) + 32768) << 16 | index, then ST_ROW_BINS + 1 row counters
     __shared__ int s_matches;
     const int pair = blockIdx.x;
     // layout: left image = entry 2*pair, right image = entry 2*pair+1 of [..][stride] arrays
@@ -121,39 +122,106 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
         if (tid == 0) atomicExch(err, 1);
         return;
     }
-    int np2 = 1;
-    while (np2 < nr) np2 <<= 1;
-    for (int i = tid; i < np2; i += ST_NT)
+    // ---- right keypoints ordered by (iRound(y), index) ----
+    // Rows inside [0, ST_ROW_BINS): counting sort (histogram, scan, scatter, then every row orders its handful of
+    // entries by index) — a few passes over the keys. Any row outside that range: the general bitonic sort.
+    int* bins = reinterpret_cast<int*>(keys + sort_cap);  // ST_ROW_BINS + 1 counters
+    __shared__ int s_wide;
+    if (tid == 0) s_wide = 0;
+    for (int i = tid; i <= ST_ROW_BINS; i += ST_NT) bins[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < nr; i += ST_NT)
     {
-        uint32_t k = 0xffffffffu;
-        if (i < nr)
-        {
-            const int row = iround_f((float)R[i].y);
-            if (row < -32768 || row > 32766) atomicExch(err, 2);
-            k = ((uint32_t)(row + 32768) << 16) | (uint32_t)i;
-        }
-        keys[i] = k;
+        const int row = iround_f((float)R[i].y);
+        if (row < -32768 || row > 32766) atomicExch(err, 2);
+        if (row < 0 || row >= ST_ROW_BINS)
+            s_wide = 1;
+        else
+            atomicAdd(&bins[row], 1);
     }
     __syncthreads();
-    for (int k = 2; k <= np2; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1)
+    if (!s_wide)
+    {
+        // exclusive scan of the row counts: every thread owns ST_ROW_BINS / ST_NT consecutive bins
+        constexpr int PER = ST_ROW_BINS / ST_NT;
+        int local[PER], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) local[k] = bins[tid * PER + k], sum += local[k];
+        const int lane = tid & 31, wid = tid >> 5;
+        const int inc  = warp_incl_scan(sum, lane);
+        __shared__ int s_wsum[ST_NT / 32];
+        if (lane == 31) s_wsum[wid] = inc;
+        __syncthreads();
+        int base = inc - sum;
+#pragma unroll
+        for (int k = 0; k < ST_NT / 32; ++k)
+            if (k < wid) base += s_wsum[k];
+        // bins[r] = first slot of row r; it doubles as the scatter cursor and ends up at the first slot of row r + 1
+#pragma unroll
+        for (int k = 0; k < PER; ++k)
         {
-            for (int i = tid; i < np2; i += ST_NT)
+            bins[tid * PER + k] = base;
+            base += local[k];
+        }
+        if (tid == ST_NT - 1) bins[ST_ROW_BINS] = base;
+        __syncthreads();
+        // scatter (order inside a row arbitrary for now); the cursor of row r ends at the start of row r + 1
+        for (int i = tid; i < nr; i += ST_NT)
+        {
+            const int row = iround_f((float)R[i].y);
+            const int pos = atomicAdd(&bins[row], 1);
+            keys[pos]     = ((uint32_t)(row + 32768) << 16) | (uint32_t)i;
+        }
+        __syncthreads();
+        // row r now occupies [end of row r-1, bins[r]): order its entries by index (insertion sort, rows are short)
+        for (int r = tid; r < ST_ROW_BINS; r += ST_NT)
+        {
+            const int e = bins[r], b0 = (r == 0) ? 0 : bins[r - 1];
+            for (int i = b0 + 1; i < e; ++i)
             {
-                const int ixj = i ^ j;
-                if (ixj > i)
+                const uint32_t v = keys[i];
+                int j = i - 1;
+                while (j >= b0 && keys[j] > v)
                 {
-                    const uint32_t a = keys[i], b = keys[ixj];
-                    const bool up = (i & k) == 0;
-                    if ((a > b) == up)
+                    keys[j + 1] = keys[j];
+                    --j;
+                }
+                keys[j + 1] = v;
+            }
+        }
+        __syncthreads();
+    }
+    else
+    {
+        int np2 = 1;
+        while (np2 < nr) np2 <<= 1;
+        for (int i = tid; i < np2; i += ST_NT)
+        {
+            uint32_t k = 0xffffffffu;
+            if (i < nr) k = ((uint32_t)(iround_f((float)R[i].y) + 32768) << 16) | (uint32_t)i;
+            keys[i] = k;
+        }
+        __syncthreads();
+        for (int k = 2; k <= np2; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1)
+            {
+                for (int i = tid; i < np2; i += ST_NT)
+                {
+                    const int ixj = i ^ j;
+                    if (ixj > i)
                     {
-                        keys[i]   = b;
-                        keys[ixj] = a;
+                        const uint32_t a = keys[i], b = keys[ixj];
+                        const bool up = (i & k) == 0;
+                        if ((a > b) == up)
+                        {
+                            keys[i]   = b;
+                            keys[ixj] = a;
+                        }
                     }
                 }
+                __syncthreads();
             }
-            __syncthreads();
-        }
+    }
 
     const float min_disp = 0.f;
     const float max_disp = (float)(prm.bf * 0.5);

@@ -182,7 +182,7 @@ int snk_filter_matches(const snk_knn2* k, int n, int threshold, float ratio, int
     return SNK_OK;
 }
 
-static int stereo_smem(int sort_cap) { return sort_cap * 4; }
+static int stereo_smem(int sort_cap) { return sort_cap * 4 + (ST_ROW_BINS + 4) * 4; }
 
 int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
                      const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points, float* depth,

@@ -65,6 +65,17 @@ def test_stereo_row_search(so, ctx, oracle, feats, relaxed, bf):
                                             oracle.kp32_to_kp64(kr), dr)
     assert n == n2 and n > 0 and ops > 0
     assert rp.tobytes() == rp2.tobytes() and dp.tobytes() == dp2.tobytes()
+    # rows outside the counting sort's range (rectified coordinates can leave the image): the general sort path,
+    # and many keypoints on one row (long in-row insertion)
+    for dy, squash in ((5000.0, False), (-300.0, False), (0.0, True)):
+        a, b = so.kp32_to_kp64(kl), so.kp32_to_kp64(kr)
+        if squash:
+            a["y"], b["y"] = np.round(a["y"] / 40.0) * 40.0, np.round(b["y"] / 40.0) * 40.0
+        a["y"] += dy
+        b["y"] += dy
+        n3, rp3, dp3 = ctx.StereoMatching(p, a, dl, b, dr)
+        n4, rp4, dp4, _ = oracle.stereo_match(oracle.stereo_params(bf, relaxed, feats["scales"]), a, dl, b, dr)
+        assert n3 == n4 and n3 > 0 and rp3.tobytes() == rp4.tobytes() and dp3.tobytes() == dp4.tobytes(), (dy, squash)
     # empty sides
     n, rp, dp = ctx.StereoMatching(p, so.kp32_to_kp64(kl), dl, so.kp32_to_kp64(kr[:0]), dr[:0])
     assert n == 0 and np.all(rp == -1000) and np.all(dp == -1000)
