@@ -425,7 +425,7 @@ struct QNode
     float cx, cy, sx, sy;  // corner, size
     int from, to;
 };
-constexpr int QT_NT = 128;
+constexpr int QT_NT = 256;
 
 __device__ __forceinline__ float kp_x(uint32_t p) { return (float)(p & 0xfffu); }
 __device__ __forceinline__ float kp_y(uint32_t p) { return (float)((p >> 12) & 0xfffu); }
