@@ -1029,4 +1029,15 @@ int match_prediction(const uint64_t* desc_left, int n_left, double* last_positio
     }
     return count;
 }
+
+// Features::GetFeaturesInArea (Snake/Map/Features.cpp:13-30) as every search above enumerates its candidates
+int features_in_area(const snk_frame_view* f, double px, double py, float r, int32_t* out)
+{
+    int c = 0;
+    const float r2 = r * r;
+    for_candidates(f, px, py, r, (double)r2, [&](int pid, bool inside) {
+        if (inside) out[c++] = pid;
+    });
+    return c;
+}
 }  // namespace orbref

@@ -263,4 +263,8 @@ ORC_API int orc_match_prediction(const uint64_t* dl, int n, double* pos, const s
 {
     return match_prediction(dl, n, pos, right, radius, fe, matches);
 }
+ORC_API int orc_features_in_area(const snk_frame_view* f, double px, double py, float r, int32_t* out)
+{
+    return features_in_area(f, px, py, r, out);
+}
 }  // extern "C"

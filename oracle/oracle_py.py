@@ -380,3 +380,9 @@ def match_prediction(desc_left, positions, right, radius, feature_error):
     matches = np.zeros(max(len(d), 1), np.int32)
     m = lib().orc_match_prediction(_p(d), len(d), _p(pos), C.byref(right), C.c_float(radius), feature_error, _p(matches))
     return m, matches[:len(d)], pos
+
+
+def features_in_area(frame, px, py, r):
+    out = np.zeros(max(frame.n, 1), np.int32)
+    c = lib().orc_features_in_area(C.byref(frame), C.c_double(px), C.c_double(py), C.c_float(r), _p(out))
+    return out[:c].copy()

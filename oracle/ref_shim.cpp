@@ -231,3 +231,33 @@ REF_API double ref_epipolar_distance_squared(const double* p1, const double* p2,
         for (int c = 0; c < 3; ++c) F(r, c) = F_rowmajor[3 * r + c];
     return EpipolarDistanceSquared(Vec2(p1[0], p1[1]), Vec2(p2[0], p2[1]), F);
 }
+
+// ---- candidate enumeration of Features::GetFeaturesInArea (Snake/Map/Features.cpp:13-30) on the reference's own grid
+// classes: FeatureGridBounds2::minMaxCellWithRadius / cellClamped and FeatureGrid2::create / cellIt are the
+// reference's; the three nested loops and the distance test follow Features.cpp (that file needs the whole Snake map
+// to compile). kps must already be grid-ordered (ref_feature_grid's permutation applied). Returns the count.
+REF_API int ref_features_in_area(double bminx, double bminy, double bmaxx, double bmaxy, int rows, int cols,
+                                 const KeyPoint<double>* kps, int n, double px, double py, float r, int* out)
+{
+    FeatureGridBounds2<double, 20> b;
+    b.bmin        = Vec2(bminx, bminy);
+    b.bmax        = Vec2(bmaxx, bmaxy);
+    b.cellSize    = Vec2(20, 20);
+    b.cellSizeInv = b.cellSize.array().inverse();
+    b.Rows        = rows;
+    b.Cols        = cols;
+    std::vector<KeyPoint<double>> v(kps, kps + n);
+    FeatureGrid2 g;
+    auto perm = g.create(b, v);
+    for (int i = 0; i < n; ++i)
+        if (perm[i] != i) return -1;  // the caller did not pass grid-ordered keypoints
+    const Vec2 position(px, py);
+    auto [cellMin, cellMax] = b.minMaxCellWithRadius(position, r);
+    auto r2                 = r * r;
+    int c                   = 0;
+    for (auto cx : Range(cellMin.first, cellMax.first + 1))
+        for (auto cy : Range(cellMin.second, cellMax.second + 1))
+            for (auto pid : g.cellIt({cx, cy}))
+                if ((v[pid].point - position).squaredNorm() < r2) out[c++] = pid;
+    return c;
+}

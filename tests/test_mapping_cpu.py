@@ -76,3 +76,23 @@ def test_prediction_and_loop_fuse_vs_bruteforce(oracle):
         else:
             assert matches[i] == -1 and np.array_equal(newpos[i], pos[i])
     assert m == (matches >= 0).sum() and m > 100
+
+
+def test_candidate_enumeration_vs_reference_grid_classes(oracle, refso):
+    """Features::GetFeaturesInArea, the candidate order of every projection / fuse / prediction search: the oracle's
+    enumeration against the reference's own FeatureGridBounds2 / FeatureGrid2 objects (cell ranges with the float
+    radius, clamping at the borders, cx-outer / cy-inner / index order, float r*r distance gate)."""
+    rng, (f1, f2, np1, np2, E) = _frames(oracle, 3)
+    g = f1.view.grid
+    out = np.zeros(f1.view.n, np.int32)
+    total = 0
+    for _ in range(400):
+        px, py = rng.uniform(g.bmin_x - 30, g.bmax_x + 30), rng.uniform(g.bmin_y - 30, g.bmax_y + 30)
+        r = float(np.float32(rng.choice([2.5, 7.0, 20.0, 50.0, 133.3])))
+        c = refso.ref_features_in_area(C.c_double(g.bmin_x), C.c_double(g.bmin_y), C.c_double(g.bmax_x), C.c_double(g.bmax_y),
+                                       g.rows, g.cols, C.c_void_p(f1.kp.ctypes.data), f1.view.n, C.c_double(px),
+                                       C.c_double(py), C.c_float(r), C.c_void_p(out.ctypes.data))
+        assert c >= 0, "keypoints not in grid order"
+        assert np.array_equal(oracle.features_in_area(f1.view, px, py, r), out[:c])
+        total += c
+    assert total > 2000
