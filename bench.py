@@ -474,7 +474,8 @@ def main():
         achieved = bytes_launch / dur / 1e9
         e2e_bytes = sum(algorithmic_bytes(n_kp_step / NI, n_cand_img)[k] for k in ("pyramid", "fast", "blur", "describe"))
         extraction_ms = sum(stage.values())
-        roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        kname = {"fast": "k_fast_group", "pyramid": "k_resize"}.get(dom, "k_" + dom)
+        roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                     "algorithmic_bytes_per_image": ab[dom], "images_per_launch": NI / max(launches[dom], 1),
                     "stage_ms_per_step": stage, "stage_timing_pass_ms_per_step": ms_profiled / args.steps,
