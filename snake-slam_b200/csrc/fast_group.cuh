@@ -18,7 +18,7 @@ constexpr int FASTG_CELLS = 4;    // cells per group
 constexpr int FASTG_GW    = 160;  // largest ROI width of a group
 constexpr int FASTG_PITCH = 176;  // tile row pitch == TMA box width: group ROI + up to 15 bytes of alignment
 constexpr int FASTG_NT    = 256;
-constexpr int FASTG_GPB   = 2;    // groups per CTA
+constexpr int FASTG_GPB   = 4;    // groups per CTA
 
 struct GroupDev  // 48 bytes
 {
