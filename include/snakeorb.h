@@ -330,6 +330,12 @@ typedef struct snk_scale_pyramid
     double scale[16];
 } snk_scale_pyramid;
 
+/* FeatureGridBounds2<double,20>::computeFromIntrinsicsDist (saiga/vision/util/FeatureGrid2.h:63-104), called once
+ * at start-up (Snake/Preprocess/Input.cpp:93): the bounding box of the undistorted image border (resolution + 1
+ * points per side, undistortAll of Distortion.h:326-338), widened by 0.1, and the 20-px cell grid over it. Fills every
+ * field of *out except `cells`. Host-side helper, no GPU involved; dist = k1 k2 k3 k4 k5 k6 p1 p2. */
+SNK_API int snk_grid_bounds(int w, int h, const snk_camera* K, const double* dist, int resolution, snk_grid_view* out);
+
 /* Preprocess::computeFeatureGrid (Snake/Preprocess/Preprocess.cpp:244-266) == FeatureGrid2::create
  * (saiga/vision/util/FeatureGrid2.h:130-192): counting sort of the undistorted keypoints into the 20-px cells of
  * `bounds` (its `cells` member is ignored). permutation[i] = new index of keypoint i (keypoints outside the bounds

@@ -1040,4 +1040,37 @@ int features_in_area(const snk_frame_view* f, double px, double py, float r, int
     });
     return c;
 }
+
+// FeatureGridBounds2<double,20>::computeFromIntrinsicsDist (saiga/vision/util/FeatureGrid2.h:63-104) with
+// undistortAll (Distortion.h:326-338): the undistorted image border decides the grid the searches run on
+void grid_bounds(int w, int h, const double* K /* fx fy cx cy s */, const double* dist, int resolution, snk_grid_view* out)
+{
+    std::vector<double> px, py;
+    for (int i = 0; i < resolution + 1; ++i)
+    {
+        const float alpha = float(i) / resolution * w;
+        px.push_back(alpha), py.push_back(0);
+        px.push_back(alpha), py.push_back(h - 1);
+        const float beta = float(i) / resolution * h;
+        px.push_back(0), py.push_back(beta);
+        px.push_back(w - 1), py.push_back(beta);
+    }
+    double bminx = 0, bminy = 0, bmaxx = 0, bmaxy = 0;
+    for (size_t k = 0; k < px.size(); ++k)
+    {
+        const double nx0 = (px[k] - K[2]) / K[0], ny0 = (py[k] - K[3]) / K[1];  // unproject2
+        double nx, ny;
+        undistort_gn(dist, nx0, ny0, nx, ny);
+        const double ux = K[0] * nx + K[4] * ny + K[2], uy = K[1] * ny + K[3];  // normalizedToImage
+        if (k == 0) bminx = bmaxx = ux, bminy = bmaxy = uy;
+        bminx = std::min(ux, bminx), bminy = std::min(uy, bminy);
+        bmaxx = std::max(ux, bmaxx), bmaxy = std::max(uy, bmaxy);
+    }
+    bminx -= 0.1, bminy -= 0.1, bmaxx += 0.1, bmaxy += 0.1;
+    out->bmin_x = bminx, out->bmin_y = bminy, out->bmax_x = bmaxx, out->bmax_y = bmaxy;
+    out->cell_size_inv_x = out->cell_size_inv_y = 1.0 / 20.0;
+    out->rows  = (int)std::ceil((bmaxy - bminy) / 20.0);
+    out->cols  = (int)std::ceil((bmaxx - bminx) / 20.0);
+    out->cells = nullptr;
+}
 }  // namespace orbref

@@ -43,4 +43,5 @@ int search_triangulation_project(const snk_frame_view* kf1, const double* np1, c
 int match_prediction(const uint64_t* desc_left, int n_left, double* last_positions, const snk_frame_view* right,
                      float radius, int featureError, int32_t* matches);
 int features_in_area(const snk_frame_view* f, double px, double py, float r, int32_t* out);
+void grid_bounds(int w, int h, const double* K, const double* dist, int resolution, snk_grid_view* out);
 }  // namespace orbref

@@ -267,4 +267,8 @@ ORC_API int orc_features_in_area(const snk_frame_view* f, double px, double py, 
 {
     return features_in_area(f, px, py, r, out);
 }
+ORC_API void orc_grid_bounds(int w, int h, const double* K, const double* dist, int resolution, snk_grid_view* out)
+{
+    grid_bounds(w, h, K, dist, resolution, out);
+}
 }  // extern "C"

@@ -261,3 +261,16 @@ REF_API int ref_features_in_area(double bminx, double bminy, double bmaxx, doubl
                 if ((v[pid].point - position).squaredNorm() < r2) out[c++] = pid;
     return c;
 }
+
+// ---- FeatureGridBounds2<double,20>::computeFromIntrinsicsDist (FeatureGrid2.h:63-104), the reference's own ------
+// K: fx fy cx cy s, dist: k1..k6 p1 p2; out: bmin.x bmin.y bmax.x bmax.y cellSizeInv.x cellSizeInv.y; rows_cols[2]
+REF_API void ref_grid_bounds(int w, int h, const double* K, const double* dist, int resolution, double* out6, int* rows_cols)
+{
+    FeatureGridBounds2<double, 20> b;
+    Eigen::Matrix<double, 8, 1> c;
+    for (int i = 0; i < 8; ++i) c(i) = dist[i];
+    b.computeFromIntrinsicsDist(w, h, IntrinsicsPinholed(K[0], K[1], K[2], K[3], K[4]), Distortion(c), resolution);
+    out6[0] = b.bmin(0), out6[1] = b.bmin(1), out6[2] = b.bmax(0), out6[3] = b.bmax(1);
+    out6[4] = b.cellSizeInv(0), out6[5] = b.cellSizeInv(1);
+    rows_cols[0] = b.Rows, rows_cols[1] = b.Cols;
+}

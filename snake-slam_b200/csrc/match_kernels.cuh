@@ -300,7 +300,7 @@ struct DistortEval
     double xd, yd, j00, j01, j10, j11;
 };
 template <bool WITH_J>
-__device__ __forceinline__ DistortEval distort_point(const double* __restrict__ D, double x, double y)
+__host__ __device__ __forceinline__ DistortEval distort_point(const double* __restrict__ D, double x, double y)
 {
     DistortEval e;
     const double k1 = D[0], k2 = D[1], k3 = D[2], k4 = D[3], k5 = D[4], k6 = D[5], p1 = D[6], p2 = D[7];
@@ -342,18 +342,15 @@ __device__ __forceinline__ DistortEval distort_point(const double* __restrict__ 
     return e;
 }
 
-__global__ void k_undistort(snk_rectify r, const snk_keypoint_f64* __restrict__ kps, int n,
-                            snk_keypoint_f64* __restrict__ kp_un, double* __restrict__ normalized)
+// undistortPointGN (Distortion.h:241-285) with the point as its own start value. Host and device: the host uses it
+// for the feature-grid bounds (snk_grid_bounds), the device for the keypoints.
+__host__ __device__ inline void undistort_gn_hd(const double* __restrict__ D, double px, double py, double& ox, double& oy)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    snk_keypoint_f64 k = kps[i];
-    const double px = (k.x - r.cx) / r.fx, py = (k.y - r.cy) / r.fy;
     double x = px, y = py, lx = px, ly = py;
-    double last_chi2 = __longlong_as_double(0x7ff0000000000000ll);  // +inf
+    double last_chi2 = (double)INFINITY;
     for (int it = 0; it < 5; ++it)
     {
-        const DistortEval e = distort_point<true>(r.dist, x, y);
+        const DistortEval e = distort_point<true>(D, x, y);
         const double r0 = e.xd - px, r1 = e.yd - py;
         const double chi2 = r0 * r0 + r1 * r1;
         if (chi2 > last_chi2)
@@ -390,7 +387,7 @@ __global__ void k_undistort(snk_rectify r, const snk_keypoint_f64* __restrict__ 
         y += s1;
     }
     {
-        const DistortEval e = distort_point<false>(r.dist, x, y);
+        const DistortEval e = distort_point<false>(D, x, y);
         const double r0 = e.xd - px, r1 = e.yd - py;
         if (r0 * r0 + r1 * r1 > last_chi2)
         {
@@ -398,6 +395,19 @@ __global__ void k_undistort(snk_rectify r, const snk_keypoint_f64* __restrict__ 
             y = ly;
         }
     }
+    ox = x;
+    oy = y;
+}
+
+__global__ void k_undistort(snk_rectify r, const snk_keypoint_f64* __restrict__ kps, int n,
+                            snk_keypoint_f64* __restrict__ kp_un, double* __restrict__ normalized)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    snk_keypoint_f64 k = kps[i];
+    const double px = (k.x - r.cx) / r.fx, py = (k.y - r.cy) / r.fy;
+    double x, y;
+    undistort_gn_hd(r.dist, px, py, x, y);
     // Quaternion * Vector3 as Eigen evaluates it: uv = 2 (q.vec x v); v + w uv + q.vec x uv
     const double qx = r.quat[0], qy = r.quat[1], qz = r.quat[2], qw = r.quat[3];
     double u0 = qy * 1.0 - qz * y, u1 = qz * x - qx * 1.0, u2 = qx * y - qy * x;

@@ -339,6 +339,41 @@ int snk_rgba_to_gray(snk_ctx* c, const uint8_t* rgba, int rows, int cols, size_t
     return SNK_OK;
 }
 
+int snk_grid_bounds(int w, int h, const snk_camera* K, const double* dist, int resolution, snk_grid_view* out)
+{
+    SNK_REQUIRE(K && dist && out && w > 0 && h > 0 && resolution >= 1, "bad argument");
+    SNK_REQUIRE(K->fx != 0 && K->fy != 0, "zero focal length");
+    // host arithmetic in the reference's order; this translation unit's host code is built without FMA contraction
+    // targets (plain x86-64), so it rounds like the reference's -O2 build
+    double bminx = 0, bminy = 0, bmaxx = 0, bmaxy = 0;
+    bool first = true;
+    auto visit = [&](double px, double py) {
+        const double nx0 = (px - K->cx) / K->fx, ny0 = (py - K->cy) / K->fy;  // unproject2
+        double nx, ny;
+        undistort_gn_hd(dist, nx0, ny0, nx, ny);
+        const double ux = K->fx * nx + K->s * ny + K->cx, uy = K->fy * ny + K->cy;  // normalizedToImage
+        if (first) bminx = bmaxx = ux, bminy = bmaxy = uy, first = false;
+        bminx = std::min(ux, bminx), bminy = std::min(uy, bminy);
+        bmaxx = std::max(ux, bmaxx), bmaxy = std::max(uy, bmaxy);
+    };
+    for (int i = 0; i < resolution + 1; ++i)
+    {
+        const float alpha = float(i) / resolution * w;  // float, as FeatureGrid2.h:70
+        visit(alpha, 0);
+        visit(alpha, h - 1);
+        const float beta = float(i) / resolution * h;
+        visit(0, beta);
+        visit(w - 1, beta);
+    }
+    bminx -= 0.1, bminy -= 0.1, bmaxx += 0.1, bmaxy += 0.1;
+    out->bmin_x = bminx, out->bmin_y = bminy, out->bmax_x = bmaxx, out->bmax_y = bmaxy;
+    out->cell_size_inv_x = out->cell_size_inv_y = 1.0 / 20.0;
+    out->rows  = (int)std::ceil((bmaxy - bminy) / 20.0);
+    out->cols  = (int)std::ceil((bmaxx - bminx) / 20.0);
+    out->cells = nullptr;
+    return SNK_OK;
+}
+
 int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s)
 {
     SNK_REQUIRE(c && pair_ops_per_s, "bad argument");

@@ -149,6 +149,9 @@ struct snk_orb
     }
 };
 
+// dynamic shared memory opt-in of k_fast / k_fast_group / k_distribute: one ceiling for every handle of the process
+static constexpr int SMEM_CEILING = 200 * 1024;
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no libcuda link dependency)
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -288,8 +291,10 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
     h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES + 2 * (size_t)QT_KP_SMEM * 4;
     SNK_REQUIRE(24 * h->node_cap >= gnusort::cta_sort_scratch_bytes(h->node_cap), "internal: sort scratch does not fit");
-    SNK_REQUIRE(h->qt_smem <= 200 * 1024, "nfeatures too large for the distribution kernel's shared memory");
-    SNK_CUDA(cudaFuncSetAttribute(k_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
+    SNK_REQUIRE(h->qt_smem <= (size_t)SMEM_CEILING, "nfeatures too large for the distribution kernel's shared memory");
+    // the attribute belongs to the kernel, not to this handle: every handle sets the same ceiling, so handles with
+    // different image sizes (or threads creating handles at the same time) cannot lower it under each other
+    SNK_CUDA(cudaFuncSetAttribute(k_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_CEILING));
 
     // + slack: the kernels read whole aligned words / short row segments that may extend a few bytes past a row's end
     SNK_CUDA(cudaMalloc(&h->d_pyr, pyr_bytes + 256));
@@ -355,7 +360,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     }
     h->fast_rows = align_up(h->fast_rows, 8);  // keeps every tile buffer 128-byte aligned (8 rows x 96 or 176 bytes)
     h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
-    SNK_CUDA(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fast_smem, 48 * 1024)));
+    SNK_REQUIRE(h->fast_smem <= (size_t)SMEM_CEILING, "internal: FAST tile too large");
+    SNK_CUDA(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_CEILING));
     // groups of horizontally adjacent cells (fast_group.cuh): same level and cell row, contiguous zones, at most
     // FASTG_CELLS cells and FASTG_GW ROI columns
     h->groups.clear();
@@ -401,8 +407,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         ci += n;
     }
     h->fastg_smem = 3 * (size_t)h->fast_rows * FASTG_PITCH + 4 * (size_t)h->fastg_list;
-    SNK_REQUIRE(h->fastg_smem <= 200 * 1024, "internal: FAST group tile too large");
-    SNK_CUDA(cudaFuncSetAttribute(k_fast_group, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fastg_smem, 48 * 1024)));
+    SNK_REQUIRE(h->fastg_smem <= (size_t)SMEM_CEILING, "internal: FAST group tile too large");
+    SNK_CUDA(cudaFuncSetAttribute(k_fast_group, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_CEILING));
     SNK_CUDA(cudaMalloc(&h->d_groups, h->groups.size() * sizeof(GroupDev)));
     SNK_CUDA(cudaMemcpy(h->d_groups, h->groups.data(), h->groups.size() * sizeof(GroupDev), cudaMemcpyHostToDevice));
     SNK_CUDA(cudaMalloc(&h->d_cells, h->cells.size() * sizeof(CellDev)));

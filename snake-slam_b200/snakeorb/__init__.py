@@ -471,6 +471,15 @@ class Vocabulary:
         return ids[:nb.value], vals[:nb.value], fn[:nf.value], fo[:nf.value + 1], fi[:fo[nf.value]]
 
 
+def grid_bounds(w, h, cam, dist, resolution=20):
+    """FeatureGridBounds2::computeFromIntrinsicsDist -> GridView without cells (host-side helper, no GPU)."""
+    d = np.ascontiguousarray(dist, np.float64)
+    assert len(d) == 8
+    g = GridView()
+    _check(lib().snk_grid_bounds(w, h, C.byref(cam), _p(d), resolution, C.byref(g)))
+    return g
+
+
 def kp32_to_kp64(k):
     o = np.zeros(len(k), KP64)
     for f in ("x", "y", "size", "angle", "response", "octave"):

@@ -223,3 +223,65 @@ def test_varied_geometries(so, oracle, w, h, nf, scale, nl, kind):
     k2, d2 = oracle.Extractor(nf, scale, nl, 20, 7, 4).detect(img)
     assert len(k2) > 20
     assert_same_features(k, d, k2, d2)
+
+
+def test_two_threads_two_handles(so, oracle):
+    """INTEGRATION.md promises a re-entrant library with one handle per thread (Snake's Preprocess, Tracking and
+    LoopClosing threads each own theirs): two host threads drive their own extractor and matcher context at the same
+    time, on different image sizes, and get exactly the single-threaded results."""
+    import threading
+
+    from snakeorb import synthetic as S
+
+    jobs = [(np.stack([S.image(300 + i, 752, 480) for i in range(4)]), 1200), (np.stack([S.image(400 + i, 640, 480) for i in range(4)]), 1000)]
+    want = []
+    for imgs, nf in jobs:
+        ex = so.ORBExtractor(nf, 1.2, 8, 20, 7, max_batch=4)
+        want.append(ex.DetectBatch(imgs))
+    got = [None, None]
+    errors = []
+
+    def work(slot):
+        try:
+            imgs, nf = jobs[slot]
+            ex = so.ORBExtractor(nf, 1.2, 8, 20, 7, max_batch=4)
+            ctx = so.Context()
+            for _ in range(6):
+                res = ex.DetectBatch(imgs)
+                knn = ctx.matchKnn2(res[0][1], res[1][1])
+            got[slot] = (res, knn)
+        except Exception as exc:  # noqa: BLE001
+            errors.append(exc)
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for slot in range(2):
+        res, knn = got[slot]
+        for (k, d), (k2, d2) in zip(res, want[slot]):
+            assert k.tobytes() == k2.tobytes() and d.tobytes() == d2.tobytes()
+        assert knn.tobytes() == oracle.match_knn2(want[slot][0][1], want[slot][1][1]).tobytes()
+
+
+def test_handles_of_different_sizes_interleaved(so, oracle):
+    """Several extractor handles alive at once, with different image sizes and feature counts, used alternately: the
+    kernels' shared-memory opt-in is per kernel, not per handle, so a later handle must not shrink it under an
+    earlier one (regression: the second handle's set-up made the first handle's launches fail)."""
+    from snakeorb import synthetic as S
+
+    big = S.image(61, 1241, 376)
+    small = S.image(62, 333, 257)
+    a = so.ORBExtractor(2000, 1.2, 8, 20, 7)
+    ka, da = a.Detect(big)
+    b = so.ORBExtractor(300, 1.2, 4, 20, 7)
+    kb, db = b.Detect(small)
+    for _ in range(3):
+        k, d = a.Detect(big)
+        assert k.tobytes() == ka.tobytes() and d.tobytes() == da.tobytes()
+        k, d = b.Detect(small)
+        assert k.tobytes() == kb.tobytes() and d.tobytes() == db.tobytes()
+    assert_same_features(ka, da, *oracle.Extractor(2000, 1.2, 8, 20, 7, 2).detect(big))
+    assert_same_features(kb, db, *oracle.Extractor(300, 1.2, 4, 20, 7, 1).detect(small))

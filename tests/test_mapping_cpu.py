@@ -96,3 +96,28 @@ def test_candidate_enumeration_vs_reference_grid_classes(oracle, refso):
         assert np.array_equal(oracle.features_in_area(f1.view, px, py, r), out[:c])
         total += c
     assert total > 2000
+
+
+def test_grid_bounds_product_oracle_reference(oracle, refso):
+    """FeatureGridBounds2::computeFromIntrinsicsDist: the library's host helper (no GPU involved), the oracle and the
+    reference's own class compiled into oracle/_ref agree to the last bit."""
+    import snakeorb as so
+
+    cases = [(752, 480, [458.654, 457.296, 367.215, 248.375, 0.0], [-0.28340811, 0.07395907, 0, 0, 0, 0, 0.00019359, 1.76187114e-05]),
+             (640, 480, [517.3, 516.5, 318.6, 255.3, 0.0], [0.2624, -0.9531, 1.1633, 0, 0, 0, -0.0054, 0.0026]),
+             (1241, 376, [718.856, 718.856, 607.19, 185.22, 0.0], [0.0] * 8),
+             (1280, 720, [700.0, 705.0, 620.0, 350.0, 0.5], [-0.2, 0.05, 0.01, 0.02, -0.01, 0.003, 0.001, -0.002])]
+    for w, h, K, D in cases:
+        for res in (20, 7):
+            Ka, Da = np.array(K), np.array(D, np.float64)
+            o6, rc = np.zeros(6), np.zeros(2, np.int32)
+            refso.ref_grid_bounds(w, h, C.c_void_p(Ka.ctypes.data), C.c_void_p(Da.ctypes.data), res, C.c_void_p(o6.ctypes.data),
+                                  C.c_void_p(rc.ctypes.data))
+            go = so.GridView()
+            oracle.lib().orc_grid_bounds(w, h, C.c_void_p(Ka.ctypes.data), C.c_void_p(Da.ctypes.data), res, C.byref(go))
+            cam = M.camera(K[0], K[1], K[2], K[3], 0.0)
+            cam.s = K[4]
+            gp = so.grid_bounds(w, h, cam, Da, res)
+            for g in (go, gp):
+                got = np.array([g.bmin_x, g.bmin_y, g.bmax_x, g.bmax_y, g.cell_size_inv_x, g.cell_size_inv_y])
+                assert got.tobytes() == o6.tobytes() and (g.rows, g.cols) == tuple(rc), (w, h, res)
