@@ -285,3 +285,43 @@ def test_handles_of_different_sizes_interleaved(so, oracle):
         assert k.tobytes() == kb.tobytes() and d.tobytes() == db.tobytes()
     assert_same_features(ka, da, *oracle.Extractor(2000, 1.2, 8, 20, 7, 2).detect(big))
     assert_same_features(kb, db, *oracle.Extractor(300, 1.2, 4, 20, 7, 1).detect(small))
+
+
+def test_no_device_memory_leak_over_handle_lifetimes(so):
+    """Handles, contexts and vocabularies give back everything they allocated: free device memory after 25 create /
+    use / destroy cycles (two image sizes, so the buffers are re-allocated inside a handle as well) is what it was."""
+    import ctypes as C
+
+    from snakeorb import synthetic as S
+
+    rt = C.CDLL("libcudart.so")
+
+    def free_bytes():
+        f, t = C.c_size_t(), C.c_size_t()
+        assert rt.cudaMemGetInfo(C.byref(f), C.byref(t)) == 0
+        return f.value
+
+    a, b = S.image(1, 752, 480), S.image(2, 640, 400)
+    d = np.random.default_rng(0).integers(0, 2**63, (500, 4)).astype(np.uint64)
+
+    def cycle():
+        ex = so.ORBExtractor(1000, 1.2, 8, 20, 7, max_batch=2)
+        ex.Detect(a)
+        ex.Detect(b)
+        ctx = so.Context()
+        ctx.matchKnn2(d, d)
+        ex.close() if hasattr(ex, "close") else None
+        ctx.close()
+        del ex, ctx
+
+    for _ in range(3):
+        cycle()  # first cycles: module load, lazily created library state
+    import gc
+
+    gc.collect()
+    before = free_bytes()
+    for _ in range(25):
+        cycle()
+    gc.collect()
+    after = free_bytes()
+    assert abs(before - after) <= 8 << 20, (before, after)
