@@ -325,3 +325,30 @@ def test_no_device_memory_leak_over_handle_lifetimes(so):
     gc.collect()
     after = free_bytes()
     assert abs(before - after) <= 8 << 20, (before, after)
+
+
+def test_random_geometries_fuzz(so, oracle):
+    """Seeded sweep over image sizes, feature counts, level counts, scale factors and thresholds (cell grids with
+    ragged last columns / rows, groups of 1-4 cells, tiny top levels): every case bit-exact against the oracle."""
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(2024)
+    done = 0
+    for case in range(40):
+        w, h = int(rng.integers(96, 1000)), int(rng.integers(96, 700))
+        nl = int(rng.integers(1, 9))
+        scale = float(np.float32(rng.choice([1.1, 1.15, 1.2, 1.25, 1.3])))
+        nf = int(rng.integers(50, 2500))
+        th = int(rng.integers(8, 30))
+        thmin = int(rng.integers(3, th + 1))
+        # every level needs at least one FAST cell row and column (the reference divides by zero otherwise)
+        if min(w, h) / scale ** (nl - 1) < 70:
+            continue
+        kind = "noise" if case % 5 == 4 else "image"
+        img = S.image(7000 + case, w, h) if kind == "image" else S.adversarial("noise", w, h, case)
+        ex = so.ORBExtractor(nf, scale, nl, th, thmin)
+        k, d = ex.Detect(img)
+        k2, d2 = oracle.Extractor(nf, scale, nl, th, thmin, 2).detect(img)
+        assert_same_features(k, d, k2, d2)
+        done += 1
+    assert done >= 25
