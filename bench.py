@@ -428,6 +428,53 @@ def main():
                 reps += 4
             next_rows["bow_transform"]["cpu_port_frames_per_s_1_thread"] = reps / (time.time() - t0)
         del voc
+        # C3: SearchByProjection2 of 20 000 local-map points into one KITTI-shaped frame (host structs in, host results
+        # out, as Tracking calls it); C4: BoW-candidate matching of two TUM-shaped keyframes. Side measurements.
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import matchdata as MD
+
+            rngn = np.random.default_rng(5)
+            exk = snakeorb.ORBExtractor(2000, SCALE, NLEVELS, TH, THMIN, device=local_rank)
+            kk, dk = exk.Detect(S.image(3000, 1241, 376))
+            sc_k, _ = exk.getPyramid()
+            Kk = (718.856, 718.856, 607.19, 185.22)
+            fr = MD.make_frame(kk, dk, 1241, 376, rngn, S.quat_from_axis_angle(rngn.normal(size=3), 0.004), rngn.uniform(-0.05, 0.05, 3))
+            mp = S.map_points_from_keypoints(fr.kp, fr.desc, Kk, rngn, 20000, sc_k)
+            pts = MD.fine_points(mp, rngn)
+            camk, pyrk = MD.camera(*Kk, 386.1), snakeorb.scale_pyramid_c(1.2, sc_k)
+            ctxn = snakeorb.Context(device=local_rank)
+            for _ in range(3):
+                mres = ctxn.SearchByProjection2(fr.view, pts, camk, pyrk, 4.0, 0.8)
+            t0 = time.perf_counter()
+            for _ in range(20):
+                ctxn.SearchByProjection2(fr.view, pts, camk, pyrk, 4.0, 0.8)
+            gpu_ms = (time.perf_counter() - t0) / 20 * 1e3
+            next_rows["search_projection_c3"] = {"ms_per_call": gpu_ms, "map_points": 20000, "frame_keypoints": int(fr.view.n),
+                                                 "matches": int(mres[0]), "path": "host structs in, host results out"}
+            d1 = dk[:1000]
+            d2 = np.concatenate([S.flip_bits(d1[rngn.permutation(1000)[:600]], rngn, 12), dk[1000:1400]])
+            fv1, fv2 = MD.featvec(d1, rngn), MD.featvec(d2, rngn)
+            v1 = np.ones(len(d1), np.uint8)
+            v2 = np.ones(len(d2), np.uint8)
+            for _ in range(3):
+                mb = ctxn.MatchBoW(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+            t0 = time.perf_counter()
+            for _ in range(50):
+                ctxn.MatchBoW(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+            next_rows["match_bow_c4"] = {"ms_per_call": (time.perf_counter() - t0) / 50 * 1e3, "features": [len(d1), len(d2)],
+                                         "matches": int(mb[0]), "path": "host arrays in, host results out"}
+            if not args.no_cpu:
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    oracle_py.search_projection_fine(fr.view, pts, camk, pyrk, 4.0, 0.8)
+                next_rows["search_projection_c3"]["cpu_port_ms_per_call_1_thread"] = (time.perf_counter() - t0) / 3 * 1e3
+                t0 = time.perf_counter()
+                for _ in range(10):
+                    oracle_py.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+                next_rows["match_bow_c4"]["cpu_port_ms_per_call_1_thread"] = (time.perf_counter() - t0) / 10 * 1e3
+        except Exception as exc:  # noqa: BLE001 — side measurements must never take the bench line down
+            next_rows["side_measurement_error"] = repr(exc)[:200]
 
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
     e2e = None
