@@ -485,6 +485,13 @@ SNK_API int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const
                                            int32_t* bow_ids_dev, float* bow_vals_dev, int32_t* fv_node_ids_dev,
                                            int32_t* fv_offsets_dev, int32_t* fv_indices_dev, int32_t* out_counts_dev);
 
+/* FeatureVector::score (MiniBow2.h:134-170; TemplatedVocabulary::score, :283): the L1 similarity of one query
+ * BowVector against n_cand others (keyframe-database queries of loop detection and relocalisation). Candidates are
+ * concatenated: candidate k owns cand_ids / cand_vals [cand_offsets[k], cand_offsets[k+1]); ids ascending inside
+ * every vector, as snk_bow_transform produces them. scores[k] has the reference's float rounding. */
+SNK_API int snk_bow_score_batch(snk_ctx* c, const int32_t* q_ids, const float* q_vals, int nq, const int32_t* cand_ids,
+                                const float* cand_vals, const int32_t* cand_offsets, int n_cand, float* scores);
+
 /* The reference's feature cache (Snake/Preprocess/FeatureDetector.cpp:97-111 read, :134-139 write; settings
  * fd_bufferToFile), a saiga BinaryFile dump (saiga/core/util/BinaryFile.h:30-78): u64 n, n x KeyPoint<double>
  * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of

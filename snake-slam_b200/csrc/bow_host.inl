@@ -232,3 +232,41 @@ int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const uint64_
     SNK_CUDA(cudaGetLastError());
     return SNK_OK;
 }
+
+int snk_bow_score_batch(snk_ctx* c, const int32_t* q_ids, const float* q_vals, int nq, const int32_t* cand_ids,
+                        const float* cand_vals, const int32_t* cand_offsets, int n_cand, float* scores)
+{
+    SNK_REQUIRE(c && nq >= 0 && n_cand >= 0, "bad argument");
+    if (n_cand == 0) return SNK_OK;
+    SNK_REQUIRE(cand_offsets && scores && (nq == 0 || (q_ids && q_vals)), "null arrays");
+    const int total = cand_offsets[n_cand];
+    SNK_REQUIRE(cand_offsets[0] == 0 && total >= 0 && (total == 0 || (cand_ids && cand_vals)), "bad candidate arrays");
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, 2 * padded<int>(std::max(nq, 1)) + 2 * padded<int>(std::max(total, 1)) + padded<int>(n_cand + 1) +
+                                padded<float>(n_cand));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    int* dqi   = cv.take<int>(std::max(nq, 1));
+    float* dqv = cv.take<float>(std::max(nq, 1));
+    int* dci   = cv.take<int>(std::max(total, 1));
+    float* dcv = cv.take<float>(std::max(total, 1));
+    int* dco   = cv.take<int>(n_cand + 1);
+    float* ds  = cv.take<float>(n_cand);
+    cudaStream_t st = c->stream;
+    if (nq)
+    {
+        SNK_CUDA(cudaMemcpyAsync(dqi, q_ids, 4 * (size_t)nq, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(dqv, q_vals, 4 * (size_t)nq, cudaMemcpyHostToDevice, st));
+    }
+    if (total)
+    {
+        SNK_CUDA(cudaMemcpyAsync(dci, cand_ids, 4 * (size_t)total, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(dcv, cand_vals, 4 * (size_t)total, cudaMemcpyHostToDevice, st));
+    }
+    SNK_CUDA(cudaMemcpyAsync(dco, cand_offsets, 4 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, st));
+    k_bow_score<<<(n_cand + 127) / 128, 128, 0, st>>>(dqi, dqv, nq, dci, dcv, dco, n_cand, ds);
+    SNK_CUDA(cudaGetLastError());
+    SNK_CUDA(cudaMemcpyAsync(scores, ds, 4 * (size_t)n_cand, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    return SNK_OK;
+}

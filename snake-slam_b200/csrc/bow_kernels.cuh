@@ -245,4 +245,33 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const unsigned long lon
     const float norm = s_norm;
     for (int i = tid; i < words_before; i += BOW_NT) bow_vals[i] = (norm > 0.f) ? vals[i] / norm : vals[i];
 }
+
+// FeatureVector::score (MiniBow2.h:134-170): L1 score of one query BowVector against many, one thread per candidate.
+// The reference adds the terms of the common words in ascending word order in float: the merge stays serial per pair
+// (its lower_bound jumps only skip non-common words, a plain two-pointer walk visits the same matches in the same order).
+__global__ void k_bow_score(const int* __restrict__ q_ids, const float* __restrict__ q_vals, int nq,
+                            const int* __restrict__ c_ids, const float* __restrict__ c_vals,
+                            const int* __restrict__ c_offsets, int n_cand, float* __restrict__ scores)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_cand) return;
+    int i = 0, j = c_offsets[c];
+    const int je = c_offsets[c + 1];
+    float score = 0.f;
+    while (i < nq && j < je)
+    {
+        const int a = q_ids[i], b = c_ids[j];
+        if (a == b)
+        {
+            const float vi = q_vals[i], wi = c_vals[j];
+            score = __fadd_rn(score, __fsub_rn(__fsub_rn(fabsf(__fsub_rn(vi, wi)), fabsf(vi)), fabsf(wi)));
+            ++i, ++j;
+        }
+        else if (a < b)
+            ++i;
+        else
+            ++j;
+    }
+    scores[c] = __fmul_rn(score, -0.5f);
+}
 }  // namespace snk

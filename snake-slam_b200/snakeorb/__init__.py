@@ -376,6 +376,18 @@ class Context:
                                           feature_error, _p(matches), C.byref(m)))
         return m.value, matches[:len(d)], pos
 
+    def bow_scores(self, q_ids, q_vals, cands):
+        """FeatureVector::score of (q_ids, q_vals) against every (ids, vals) pair of `cands` -> float32 array."""
+        q_ids, q_vals = np.ascontiguousarray(q_ids, np.int32), np.ascontiguousarray(q_vals, np.float32)
+        off = np.zeros(len(cands) + 1, np.int32)
+        for k, (i, _) in enumerate(cands):
+            off[k + 1] = off[k] + len(i)
+        ci = np.ascontiguousarray(np.concatenate([np.asarray(i, np.int32) for i, _ in cands]) if cands else np.zeros(0, np.int32))
+        cvv = np.ascontiguousarray(np.concatenate([np.asarray(v, np.float32) for _, v in cands]) if cands else np.zeros(0, np.float32))
+        out = np.zeros(max(len(cands), 1), np.float32)
+        _check(lib().snk_bow_score_batch(self.c, _p(q_ids), _p(q_vals), len(q_ids), _p(ci), _p(cvv), _p(off), len(cands), _p(out)))
+        return out[:len(cands)]
+
     def stereo_orb_device(self, orb, n_pairs, params, rp_ptr, depth_ptr, nm_ptr):
         _check(lib().snk_stereo_match_orb_device(self.c, orb.h, n_pairs, C.byref(params), C.c_void_p(rp_ptr),
                                                  C.c_void_p(depth_ptr), C.c_void_p(nm_ptr)))

@@ -77,3 +77,17 @@ def test_transform_vs_compiled_reference_random(oracle, refso, golden):
         assert np.array_equal(got[0], ids[:nb.value]) and got[1].tobytes() == vals[:nb.value].tobytes()
         assert np.array_equal(got[2], fn[:nf.value]) and np.array_equal(got[3], fo[:nf.value + 1])
         assert np.array_equal(got[4], fi[:fo[nf.value]])
+
+
+def test_score_vs_compiled_reference(oracle, refso, golden):
+    """FeatureVector::score: the oracle's merge against the reference's compiled function on real BowVectors."""
+    refso.ref_bow_score.restype = C.c_float
+    v = oracle.Vocabulary(VOC)
+    vecs = [v.transform(golden[f"bow_{name}_desc"], 1)[:2] for name in SETS]
+    for i1, v1 in vecs:
+        for i2, v2 in vecs:
+            a1, a2 = np.ascontiguousarray(i1, np.int32), np.ascontiguousarray(i2, np.int32)
+            b1, b2 = np.ascontiguousarray(v1, np.float32), np.ascontiguousarray(v2, np.float32)
+            want = refso.ref_bow_score(C.c_void_p(a1.ctypes.data), C.c_void_p(b1.ctypes.data), len(a1), C.c_void_p(a2.ctypes.data),
+                                       C.c_void_p(b2.ctypes.data), len(a2))
+            assert np.float32(oracle.bow_score(a1, b1, a2, b2)).tobytes() == np.float32(want).tobytes()

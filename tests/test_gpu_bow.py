@@ -145,3 +145,27 @@ def test_device_chain_extract_bow_knn2(so, ctx, oracle):
     assert np.all(knn[0, :counts[0]]["dist0"] == 0)  # identical frames
     ex.set_stream(None)
     ctx.set_stream(None)
+
+
+def test_bow_score_batch(so, ctx, oracle, refso=None):
+    """FeatureVector::score of one frame against many: float bits equal to the oracle's serial merge (itself equal to
+    the reference's compiled score on the same vectors, tests/test_bow_cpu.py)."""
+    from snakeorb import synthetic as S
+
+    arr = S.vocabulary_arrays(21, 10, 4)
+    vo = oracle.Vocabulary(arrays=arr)
+    rng = np.random.default_rng(2)
+    nodes = arr[5]
+    vecs = []
+    for k in range(60):
+        n = int(rng.integers(1, 1500))
+        d = S.flip_bits(nodes[rng.integers(1, len(nodes), n)], rng, 6)
+        ids, vals, *_ = vo.transform(d, 2)
+        vecs.append((ids, vals))
+    vecs.append((np.zeros(0, np.int32), np.zeros(0, np.float32)))  # a frame without words
+    q = vecs[7]
+    got = ctx.bow_scores(q[0], q[1], vecs)
+    want = np.array([oracle.bow_score(q[0], q[1], i, v) for i, v in vecs], np.float32)
+    assert got.tobytes() == want.tobytes()
+    assert abs(got[7] - 1.0) < 1e-5 and got[-1] == 0.0 and np.all(got[:-1] >= 0)
+    assert len(ctx.bow_scores(q[0], q[1], [])) == 0
