@@ -169,3 +169,41 @@ def test_bow_score_batch(so, ctx, oracle, refso=None):
     assert got.tobytes() == want.tobytes()
     assert abs(got[7] - 1.0) < 1e-5 and got[-1] == 0.0 and np.all(got[:-1] >= 0)
     assert len(ctx.bow_scores(q[0], q[1], [])) == 0
+
+
+def test_c4_chain_transform_then_match_bow(so, ctx, oracle):
+    """Config C4 as SURVEY 8(d) words it: two TUM-shaped keyframes, their FeatureVectors from the vocabulary transform
+    (levelsup as Frame::computeBoW passes it — the intra-node order is the std::sort-dependent one), validity masks
+    70 % true, MatchBoW(th = 50, ratio = 0.75); plus the relocalisation form matchKnn2 + filterMatches(60, 0.8).
+    The whole device chain equals the whole oracle chain."""
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(44)
+    ex = so.ORBExtractor(1000, 1.2, 8, 20, 7)
+    k1, d1 = ex.Detect(S.image(4000, 640, 480))
+    # second keyframe: the same scene shifted by a few pixels plus a different frame's features
+    img2 = np.roll(S.image(4000, 640, 480), (3, 5), (0, 1))
+    k2, d2 = ex.Detect(img2)
+    v, vo = so.Vocabulary(VOC), oracle.Vocabulary(VOC)
+
+    def fv_view(nodes, offs, idx):
+        fv = so.FeatVecView()
+        nodes, offs, idx = (np.ascontiguousarray(a, np.int32) for a in (nodes, offs, idx))
+        fv.n_nodes, fv.node_ids, fv.offsets, fv.indices = len(nodes), nodes.ctypes.data, offs.ctypes.data, idx.ctypes.data
+        fv._keep = (nodes, offs, idx)
+        return fv
+
+    v1 = (rng.random(len(d1)) < 0.7).astype(np.uint8)
+    v2 = (rng.random(len(d2)) < 0.7).astype(np.uint8)
+    for levelsup in (1, 2):  # the test vocabulary has L = 3 (ORBvoc: L = 6, levelsup = 4): same node depths above the words
+        g1, g2 = v.transform(ctx, d1, levelsup), v.transform(ctx, d2, levelsup)
+        o1, o2 = vo.transform(d1, levelsup), vo.transform(d2, levelsup)
+        same(g1, o1, "kf1"), same(g2, o2, "kf2")
+        m, m12 = ctx.MatchBoW(d1, d2, fv_view(*g1[2:]), fv_view(*g2[2:]), v1, v2, 50, 0.75)
+        mo, m12o, ops = oracle.match_bow(d1, d2, fv_view(*o1[2:]), fv_view(*o2[2:]), v1, v2, 50, 0.75)
+        assert m == mo and np.array_equal(m12, m12o) and m > 50
+        # BoW similarity of the two keyframes, as the loop detector would rank them
+        assert ctx.bow_scores(g1[0], g1[1], [(g2[0], g2[1])])[0] == np.float32(oracle.bow_score(o1[0], o1[1], o2[0], o2[1]))
+    knn = ctx.matchKnn2(d1, d2)
+    assert knn.tobytes() == oracle.match_knn2(d1, d2).tobytes()
+    assert np.array_equal(ctx.filterMatches(knn, 60, 0.8), oracle.filter_matches(oracle.match_knn2(d1, d2), 60, 0.8))
