@@ -473,6 +473,24 @@ def main():
                 for _ in range(10):
                     oracle_py.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
                 next_rows["match_bow_c4"]["cpu_port_ms_per_call_1_thread"] = (time.perf_counter() - t0) / 10 * 1e3
+            # C1 latency: one 752x480 frame, host image in, host keypoints + descriptors out, stream-synchronous call
+            # (median of 200 after 20 warm-ups) — what a live camera loop sees
+            ex1 = snakeorb.ORBExtractor(1000, SCALE, NLEVELS, TH, THMIN, device=local_rank)
+            img1 = S.image(1000, W, H)
+            lat = []
+            for i in range(220):
+                t0 = time.perf_counter()
+                k1, _ = ex1.Detect(img1)
+                lat.append((time.perf_counter() - t0) * 1e3)
+            lat = sorted(lat[20:])
+            next_rows["single_frame_latency_c1"] = {"median_ms": lat[len(lat) // 2], "p95_ms": lat[int(len(lat) * 0.95)],
+                                                    "keypoints": int(len(k1)), "path": "host image in, host results out, synchronous"}
+            if not args.no_cpu:
+                oe = oracle_py.Extractor(1000, SCALE, NLEVELS, TH, THMIN, 2)
+                t0 = time.perf_counter()
+                for _ in range(10):
+                    oe.detect(img1)
+                next_rows["single_frame_latency_c1"]["cpu_port_ms_2_threads"] = (time.perf_counter() - t0) / 10 * 1e3
         except Exception as exc:  # noqa: BLE001 — side measurements must never take the bench line down
             next_rows["side_measurement_error"] = repr(exc)[:200]
 
