@@ -540,8 +540,23 @@ def main():
         e2e_bytes = sum(algorithmic_bytes(n_kp_step / NI, n_cand_img)[k] for k in ("pyramid", "fast", "blur", "describe"))
         extraction_ms = sum(stage.values())
         kname = {"fast": "k_fast_group", "pyramid": "k_resize"}.get(dom, "k_" + dom)
+        # DRAM traffic of that kernel: dram__bytes_read + dram__bytes_write of the committed `ncu --set full` capture
+        # (profiles/*_ncu_summary.csv, a 128-image launch of this same command), scaled to this launch's image count
+        traffic, traffic_src = None, None
+        try:
+            import csv
+            import glob
+
+            newest = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_summary.csv")))[-1]
+            rows_ = [r for r in csv.reader(open(newest)) if r and r[0] == kname]
+            if rows_:
+                per_img = (sum(float(r[2]) + float(r[3]) for r in rows_) * 1e6) / 128.0  # Mbyte columns, 128 images per capture
+                traffic = per_img * NI / max(launches[dom], 1)
+                traffic_src = os.path.relpath(newest, ROOT) + " (128-image capture, scaled per image)"
+        except Exception:  # noqa: BLE001
+            traffic = None
         roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                     "algorithmic_bytes_per_image": ab[dom], "images_per_launch": NI / max(launches[dom], 1),
                     "stage_ms_per_step": stage, "stage_timing_pass_ms_per_step": ms_profiled / args.steps,
                     "stage_timing": "separate pass of the same K steps with cudaEvents between the kernels (blur serialised "
