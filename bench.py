@@ -175,7 +175,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
-    ap.add_argument("--chunks", type=int, default=8, help="e2e path: chunks per step")
+    ap.add_argument("--chunks", type=int, default=4, help="e2e path: chunks per step (sweep on B200: 2/2 61.6k, 4/4 61.7k, 8/4 55.5k, 8/8 60.6k, 16/8 58.9k pairs/s)")
     ap.add_argument("--lanes", type=int, default=4, help="e2e path: streams/handles the chunks alternate over")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
