@@ -266,6 +266,15 @@ typedef struct snk_rectify
 SNK_API int snk_undistort_keypoints(snk_ctx* c, const snk_rectify* r, const snk_keypoint_f64* kps, int n,
                                     snk_keypoint_f64* kp_un, double* normalized_points /* 2n */);
 
+/* The whole of Preprocess::StereoMatching (Snake/Preprocess/Preprocess.cpp:122-242) including its two
+ * Rectification::Forward loops (saiga/vision/cameraModel/Rectify.cpp:18-25: unproject, undistortPointGN, rotate,
+ * project with K_dst — the per-point math of snk_undistort_keypoints) for the RAW left / right keypoints; everything
+ * stays on the device between the steps. snk_rectify as in snk_undistort_keypoints, one per camera. */
+SNK_API int snk_stereo_matching(snk_ctx* c, const snk_rectify* rect_left, const snk_rectify* rect_right,
+                                const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
+                                const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points,
+                                float* depth, int* n_matches);
+
 /* Camera, grid and frame views used by the projection searches. */
 typedef struct snk_camera
 {

@@ -232,6 +232,59 @@ int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_
     return SNK_OK;
 }
 
+int snk_stereo_matching(snk_ctx* c, const snk_rectify* rect_left, const snk_rectify* rect_right, const snk_stereo_params* p,
+                        const snk_keypoint_f64* left, const uint64_t* dl, int nl, const snk_keypoint_f64* right,
+                        const uint64_t* dr, int nr, float* right_points, float* depth, int* n_matches)
+{
+    SNK_REQUIRE(c && rect_left && rect_right && p && n_matches && nl >= 0 && nr >= 0, "bad argument");
+    SNK_REQUIRE(nl == 0 || (left && dl && right_points && depth), "null left arrays");
+    SNK_REQUIRE(nr == 0 || (right && dr), "null right arrays");
+    SNK_REQUIRE(p->nlevels >= 1 && p->nlevels <= 16, "bad nlevels");
+    *n_matches = 0;
+    if (nl == 0) return SNK_OK;
+    if (nr == 0)
+    {
+        for (int i = 0; i < nl; ++i) right_points[i] = depth[i] = -1000.f;
+        return SNK_OK;
+    }
+    for (int i = 0; i < nl; ++i) SNK_REQUIRE(left[i].octave >= 0 && left[i].octave < p->nlevels, "octave out of range");
+    SNK_REQUIRE(nr <= 16384, "more than 16384 right keypoints");
+    SNK_CUDA(cudaSetDevice(c->device));
+    const int stride = std::max(nl, nr);
+    int rc = ctx_reserve(c, 2 * padded<snk_keypoint_f64>(2 * (size_t)stride) + padded<uint64_t>(8 * (size_t)stride) +
+                                2 * padded<float>(stride) + padded<double>(2 * (size_t)stride) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    snk_keypoint_f64* raw = cv.take<snk_keypoint_f64>(2 * (size_t)stride);
+    snk_keypoint_f64* dk  = cv.take<snk_keypoint_f64>(2 * (size_t)stride);
+    uint64_t* dd          = cv.take<uint64_t>(8 * (size_t)stride);
+    float* drp            = cv.take<float>(stride);
+    float* ddp            = cv.take<float>(stride);
+    double* dnorm         = cv.take<double>(2 * (size_t)stride);  // normalized points: produced by the kernel, not needed here
+    int* dn               = cv.take<int>(4);
+    cudaStream_t st       = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(raw, left, sizeof(snk_keypoint_f64) * (size_t)nl, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(raw + stride, right, sizeof(snk_keypoint_f64) * (size_t)nr, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(dd, dl, 32 * (size_t)nl, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemcpyAsync(dd + 4 * (size_t)stride, dr, 32 * (size_t)nr, cudaMemcpyHostToDevice, st));
+    // the two Rectification::Forward loops (Preprocess.cpp:141-151): same per-point math as undistortKeypoints
+    k_undistort<<<(nl + 127) / 128, 128, 0, st>>>(*rect_left, raw, nl, dk, dnorm);
+    k_undistort<<<(nr + 127) / 128, 128, 0, st>>>(*rect_right, raw + stride, nr, dk + stride, dnorm);
+    int cap = 1;
+    while (cap < nr) cap <<= 1;
+    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
+    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap), st>>>(
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err);
+    SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    rc = check_err(c, "stereo_matching");
+    if (rc) return rc;
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
 int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_stereo_params* p, float* right_points,
                                 float* depth, int32_t* n_matches)
 {

@@ -302,6 +302,17 @@ class Context:
                                       _p(out), C.c_size_t(out.strides[0] if out.size else 0)))
         return out
 
+    def StereoMatchingRaw(self, rect_left, rect_right, params, left, dl, right, dr):
+        """The whole Preprocess::StereoMatching incl. Rectification::Forward of the raw keypoints."""
+        left, right = np.ascontiguousarray(left, KP64), np.ascontiguousarray(right, KP64)
+        dl, dr = np.ascontiguousarray(dl, np.uint64), np.ascontiguousarray(dr, np.uint64)
+        rp = np.zeros(max(len(left), 1), np.float32)
+        dp = np.zeros(max(len(left), 1), np.float32)
+        n = C.c_int()
+        _check(lib().snk_stereo_matching(self.c, C.byref(rect_left), C.byref(rect_right), C.byref(params), _p(left), _p(dl),
+                                         len(left), _p(right), _p(dr), len(right), _p(rp), _p(dp), C.byref(n)))
+        return n.value, rp[:len(left)], dp[:len(left)]
+
     def ComputeStereoFromRGBD(self, params, kp_un, depth_img):
         """Preprocess::ComputeStereoFromRGBD -> (matches, right_points, depth)."""
         kp_un = np.ascontiguousarray(kp_un, KP64)

@@ -265,3 +265,33 @@ def test_undistort_keypoints(so, ctx, oracle):
         assert un.tobytes() == un2.tobytes() and nrm.tobytes() == nrm2.tobytes(), case
     un, nrm = ctx.undistortKeypoints(rect, np.zeros(0, so.KP64))
     assert len(un) == 0
+
+
+def test_stereo_matching_with_rectification(so, ctx, oracle, feats):
+    """The whole Preprocess::StereoMatching: Rectification::Forward of the raw left / right keypoints (distorted
+    cameras, a small rectifying rotation each) and the row search, in one call — equal to the oracle's two steps."""
+    kl, dl = feats["l"]
+    kr, dr = feats["r"]
+    K = [718.856, 718.856, 607.19, 185.22, 0.0]
+    dist = [-0.12, 0.03, 0, 0, 0, 0, 0.0004, -0.0002]
+
+    def rect(q):
+        q = np.array(q, np.float64)
+        q /= np.sqrt((q * q).sum())
+        return so.Rectify.from_vector(np.array(K + dist + list(q) + K, np.float64))
+
+    rl, rr = rect([0.001, -0.002, 0.0005, 1.0]), rect([-0.0015, 0.001, -0.0005, 1.0])
+    p = so.stereo_params(386.1, True, feats["scales"])
+    a, b = so.kp32_to_kp64(kl), so.kp32_to_kp64(kr)
+    n, rp, dp = ctx.StereoMatchingRaw(rl, rr, p, a, dl, b, dr)
+    ua, _ = oracle.undistort_keypoints(rl, a)
+    ub, _ = oracle.undistort_keypoints(rr, b)
+    n2, rp2, dp2, _ = oracle.stereo_match(oracle.stereo_params(386.1, True, feats["scales"]), ua, dl, ub, dr)
+    assert n == n2 and n > 100 and rp.tobytes() == rp2.tobytes() and dp.tobytes() == dp2.tobytes()
+    # identity rectification: the plain entry point
+    ident = so.Rectify.from_vector(np.array(K + [0.0] * 8 + [0, 0, 0, 1.0] + K, np.float64))
+    n3, rp3, dp3 = ctx.StereoMatchingRaw(ident, ident, p, a, dl, b, dr)
+    ui, _ = oracle.undistort_keypoints(ident, a)
+    uj, _ = oracle.undistort_keypoints(ident, b)
+    n4, rp4, dp4, _ = oracle.stereo_match(oracle.stereo_params(386.1, True, feats["scales"]), ui, dl, uj, dr)
+    assert n3 == n4 and rp3.tobytes() == rp4.tobytes() and dp3.tobytes() == dp4.tobytes()
