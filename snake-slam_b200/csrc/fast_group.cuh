@@ -123,19 +123,25 @@ __global__ void __launch_bounds__(FASTG_NT) k_fast_group(PyrDev P, const __grid_
         const int c0 = a + zx0, c1 = a + zx1;  // zone columns [c0, c1) in tile coordinates
         const int wz0 = g.zn_word0, nwz = g.zn_words, ntask = zh * nwz;
         const unsigned addc = (unsigned)(127 - min(t, 127)) * 0x01010101u;
+        // bytes of the first / last word of the span that lie inside the zone columns (all bytes of the words between)
+        const int wl = wz0 + nwz - 1;
+        const unsigned mfirst = (4 * wz0 < c0) ? (0x80808080u << (8 * (c0 - 4 * wz0))) : 0x80808080u;
+        const unsigned mlast  = (4 * wl + 4 > c1) ? (0x80808080u >> (8 * (4 * wl + 4 - c1))) : 0x80808080u;
+        const uint32_t* tw = reinterpret_cast<const uint32_t*>(&tile[3][0]) + wz0;
         for (int task = tid; task < ntask; task += FASTG_NT)
         {
             const int ry = (int)(((unsigned)task * g.zn_inv) >> 20);  // task / nwz
-            const int wx = wz0 + task - ry * nwz;
+            const int wr = task - ry * nwz;
+            const int wx = wz0 + wr;
             const int y  = 3 + ry;
-            unsigned zmask = 0x80808080u;  // bytes of the word that lie inside the zone columns
-            if (4 * wx < c0) zmask &= 0xffffffffu << (8 * (c0 - 4 * wx));
-            if (4 * wx + 4 > c1) zmask &= 0xffffffffu >> (8 * (4 * wx + 4 - c1));
-            const uint32_t* rc = reinterpret_cast<const uint32_t*>(&tile[y][0]);
-            const unsigned v  = rc[wx];
-            const unsigned pS = rc[wx + 3 * (FASTG_PITCH / 4)], pN = rc[wx - 3 * (FASTG_PITCH / 4)];
-            const unsigned pE = __funnelshift_r(v, rc[min(wx + 1, FASTG_PITCH / 4 - 1)], 24);  // bytes x+3
-            const unsigned pW = __funnelshift_r(rc[max(wx - 1, 0)], v, 8);                     // bytes x-3
+            const unsigned zmask = (wr == 0 ? mfirst : 0x80808080u) & (wr == nwz - 1 ? mlast : 0x80808080u);
+            // the words left / right of the row are read unclamped: they lie inside the tile (rows 3.. of it), and a
+            // zone pixel's x-3 / x+3 never leave the ROI, so foreign bytes only reach pixels the zone mask drops
+            const uint32_t* rc = tw + ry * (FASTG_PITCH / 4) + wr;
+            const unsigned v  = rc[0];
+            const unsigned pS = rc[3 * (FASTG_PITCH / 4)], pN = rc[-3 * (FASTG_PITCH / 4)];
+            const unsigned pE = __funnelshift_r(v, rc[1], 24);   // bytes x+3
+            const unsigned pW = __funnelshift_r(rc[-1], v, 8);   // bytes x-3
             const unsigned dS = __vabsdiffu4(pS, v), dN = __vabsdiffu4(pN, v), dE = __vabsdiffu4(pE, v), dW = __vabsdiffu4(pW, v);
             const unsigned fS = ((dS & 0x7f7f7f7fu) + addc) | dS, fN = ((dN & 0x7f7f7f7fu) + addc) | dN;
             const unsigned fE = ((dE & 0x7f7f7f7fu) + addc) | dE, fW = ((dW & 0x7f7f7f7fu) + addc) | dW;

@@ -180,9 +180,10 @@ constexpr int FAST_BMW = (FAST_ZMAX + 31) / 32;
 template <int PITCH>
 __device__ __forceinline__ int fast_arc_score(const uint8_t (*t)[PITCH], int y, int x)
 {
-    const unsigned v = 256u + t[y][x];
+    // d = 256 + centre - ring pixel; e = d | (1023 - d) << 16 = (256 + centre) * 0xFFFF0001 + 0x03FF0000 + pixel * 0xFFFF
+    const unsigned v = (256u + t[y][x]) * 0xFFFF0001u + 0x03FF0000u;
     unsigned e[16];
-#define SNK_E(k, yy, xx) e[k] = (v - t[yy][xx]) * 0xFFFF0001u + 0x03FF0000u;  // d | (1023 - d) << 16
+#define SNK_E(k, yy, xx) e[k] = t[yy][xx] * 0x0000FFFFu + v;
     SNK_E(0, y + 3, x) SNK_E(1, y + 3, x + 1) SNK_E(2, y + 2, x + 2) SNK_E(3, y + 1, x + 3)
     SNK_E(4, y, x + 3) SNK_E(5, y - 1, x + 3) SNK_E(6, y - 2, x + 2) SNK_E(7, y - 3, x + 1)
     SNK_E(8, y - 3, x) SNK_E(9, y - 3, x - 1) SNK_E(10, y - 2, x - 2) SNK_E(11, y - 1, x - 3)
