@@ -175,8 +175,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
-    ap.add_argument("--chunks", type=int, default=4, help="e2e path: chunks per step (sweep on B200: 2/2 61.6k, 4/4 61.7k, 8/4 55.5k, 8/8 60.6k, 16/8 58.9k pairs/s)")
-    ap.add_argument("--lanes", type=int, default=4, help="e2e path: streams/handles the chunks alternate over")
+    ap.add_argument("--chunks", type=int, default=2, help="e2e path: chunks per step (sweep on B200, 55 GB/s link, chunks/lanes: 1/2 64.3k, 2/3 73.0k, 2/6 72.9k, 4/4 66.4k, 4/6 66.8k, 8/8 62.3k pairs/s)")
+    ap.add_argument("--lanes", type=int, default=3, help="e2e path: streams/handles the stream of chunks goes round robin over")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -303,7 +303,7 @@ def main():
     h_nm = torch.empty((2, P), dtype=torch.int32, pin_memory=True)
     e2e_lanes = []
     if not args.no_e2e:
-        for _ in range(min(args.lanes, NCH)):
+        for _ in range(args.lanes):
             st = torch.cuda.Stream()
             exc = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=CI, device=local_rank)
             cxc = snakeorb.Context(device=local_rank)
@@ -313,8 +313,8 @@ def main():
                               torch.empty((CP, cap), dtype=torch.float32, device="cuda"),
                               torch.empty((CP,), dtype=torch.int32, device="cuda")))
 
-    def e2e_enqueue(k, par):
-        st, exc, cxc, rpc, dpc, nmc = e2e_lanes[k % len(e2e_lanes)]
+    def e2e_enqueue(k, par, lane):
+        st, exc, cxc, rpc, dpc, nmc = e2e_lanes[lane]
         exc.enqueue_ptr(host.data_ptr() + k * CI * W * H, CI, H, W, W, W * H, False)
         cxc.stereo_orb_device(exc, CP, sp, rpc.data_ptr(), dpc.data_ptr(), nmc.data_ptr())
         with torch.cuda.stream(st):
@@ -322,8 +322,8 @@ def main():
             h_dp[par, k * CP:(k + 1) * CP].copy_(dpc, non_blocking=True)
             h_nm[par, k * CP:(k + 1) * CP].copy_(nmc, non_blocking=True)
 
-    def e2e_fetch(k, par):
-        _, exc, _, _, _, _ = e2e_lanes[k % len(e2e_lanes)]
+    def e2e_fetch(k, par, lane):
+        _, exc, _, _, _, _ = e2e_lanes[lane]
         snakeorb._check(snakeorb.lib().snk_orb_fetch_async(exc.h, C.c_void_p(h_kps[par].data_ptr() + k * CI * cap * 24),
                                                            C.c_void_p(h_desc[par].data_ptr() + k * CI * cap * 32), cap,
                                                            C.c_void_p(h_cnt[par].data_ptr() + k * CI * 4)))
@@ -335,8 +335,11 @@ def main():
         # PREVIOUS step's results (set (s - 1) % 2), so the copies of consecutive steps overlap like a stream of frames.
         par = s & 1
         for k in range(NCH):
-            e2e_enqueue(k, par)
-            e2e_fetch(k, par)
+            # lanes are taken round robin over the stream of chunks: with more lanes than chunks a chunk's upload
+            # does not queue behind the same lane's previous step
+            lane = (s * NCH + k) % len(e2e_lanes)
+            e2e_enqueue(k, par, lane)
+            e2e_fetch(k, par, lane)
         e2e_done[par] = []
         for st, *_ in e2e_lanes:
             ev = torch.cuda.Event()
@@ -497,11 +500,12 @@ def main():
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        for i in range(2):
+        n_warm = 2 * max(1, -(-len(e2e_lanes) // NCH))  # every lane used once, an even count keeps the result-set parity
+        for i in range(n_warm):
             step_e2e(i)
         barrier()
         tw0 = time.perf_counter()
-        for i in range(args.steps):
+        for i in range(n_warm, n_warm + args.steps):
             step_e2e(i)
         torch.cuda.synchronize()
         e2e = (time.perf_counter() - tw0) * 1e3  # host wall clock: the last fetch returns when the results are in host memory
@@ -576,7 +580,7 @@ def main():
             d2h = NI * cap * (24 + 32) + NI * 4 + P * cap * 8 + P * 4 + 4
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
-                           "host_affinity": numa, "pipeline": f"{NCH} chunks alternating over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
+                           "host_affinity": numa, "pipeline": f"{NCH} chunks per step, the stream of chunks round robin over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
         if next_rows is not None:
             line["next_rows"] = next_rows
         if not args.no_cpu:

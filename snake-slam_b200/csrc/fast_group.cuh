@@ -149,12 +149,11 @@ __global__ void __launch_bounds__(FASTG_NT) k_fast_group(PyrDev P, const __grid_
             if (m4)
             {
                 int off = atomicAdd(&s_n1, __popc(m4));  // list order is irrelevant (ranks come from the bitmaps)
-                do
-                {
-                    const int j = (__ffs(m4) - 1) >> 3;
-                    m4 &= m4 - 1;
-                    list1[off++] = (uint16_t)((y << 8) | (4 * wx + j - a));
-                } while (m4);
+                const int e0 = (y << 8) | (4 * wx - a);  // four predicated stores beat a loop over the set bits
+                if (m4 & 0x00000080u) list1[off++] = (uint16_t)e0;
+                if (m4 & 0x00008000u) list1[off++] = (uint16_t)(e0 + 1);
+                if (m4 & 0x00800000u) list1[off++] = (uint16_t)(e0 + 2);
+                if (m4 & 0x80000000u) list1[off] = (uint16_t)(e0 + 3);
             }
         }
     }
