@@ -176,6 +176,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
     ap.add_argument("--chunks", type=int, default=2, help="e2e path: chunks per step (sweep on B200, 55 GB/s link, chunks/lanes: 1/2 64.3k, 2/3 73.0k, 2/6 72.9k, 4/4 66.4k, 4/6 66.8k, 8/8 62.3k pairs/s)")
+    ap.add_argument("--depth", type=int, default=2, help="e2e path: steps in flight (pinned result sets); the host waits for step s-depth+1")
     ap.add_argument("--lanes", type=int, default=3, help="e2e path: streams/handles the stream of chunks goes round robin over")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -293,14 +294,15 @@ def main():
 
     NCH = args.chunks if (NI % (2 * args.chunks) == 0) else 1
     CI, CP = NI // NCH, P // NCH
-    # two sets of pinned result buffers: step s+1 is enqueued while the results of step s are still arriving (a streaming
+    DEPTH = max(2, args.depth)
+    # DEPTH sets of pinned result buffers: step s+1 is enqueued while the results of step s are still arriving (a streaming
     # consumer reads set s % 2 while set (s + 1) % 2 is being filled)
-    h_kps = torch.empty((2, NI, cap, 24), dtype=torch.uint8, pin_memory=True)
-    h_desc = torch.empty((2, NI, cap, 4), dtype=torch.int64, pin_memory=True)
-    h_cnt = torch.empty((2, NI), dtype=torch.int32, pin_memory=True)
-    h_rp = torch.empty((2, P, cap), dtype=torch.float32, pin_memory=True)
-    h_dp = torch.empty((2, P, cap), dtype=torch.float32, pin_memory=True)
-    h_nm = torch.empty((2, P), dtype=torch.int32, pin_memory=True)
+    h_kps = torch.empty((DEPTH, NI, cap, 24), dtype=torch.uint8, pin_memory=True)
+    h_desc = torch.empty((DEPTH, NI, cap, 4), dtype=torch.int64, pin_memory=True)
+    h_cnt = torch.empty((DEPTH, NI), dtype=torch.int32, pin_memory=True)
+    h_rp = torch.empty((DEPTH, P, cap), dtype=torch.float32, pin_memory=True)
+    h_dp = torch.empty((DEPTH, P, cap), dtype=torch.float32, pin_memory=True)
+    h_nm = torch.empty((DEPTH, P), dtype=torch.int32, pin_memory=True)
     e2e_lanes = []
     if not args.no_e2e:
         for _ in range(args.lanes):
@@ -328,12 +330,12 @@ def main():
                                                            C.c_void_p(h_desc[par].data_ptr() + k * CI * cap * 32), cap,
                                                            C.c_void_p(h_cnt[par].data_ptr() + k * CI * 4)))
 
-    e2e_done = [[], []]  # per result set: one event per lane, recorded behind the set's last copy
+    e2e_done = [[] for _ in range(DEPTH)]  # per result set: one event per lane, recorded behind the set's last copy
 
     def step_e2e(s):
         # every chunk: H2D, kernels, D2H on its lane's stream, no host wait in between. The host then waits for the
         # PREVIOUS step's results (set (s - 1) % 2), so the copies of consecutive steps overlap like a stream of frames.
-        par = s & 1
+        par = s % DEPTH
         for k in range(NCH):
             # lanes are taken round robin over the stream of chunks: with more lanes than chunks a chunk's upload
             # does not queue behind the same lane's previous step
@@ -345,7 +347,7 @@ def main():
             ev = torch.cuda.Event()
             ev.record(st)
             e2e_done[par].append(ev)
-        for ev in e2e_done[par ^ 1]:
+        for ev in e2e_done[(s + 1) % DEPTH]:  # the oldest step still in flight
             ev.synchronize()
 
     # ---- device-resident timing --------------------------------------------------------------------------------
@@ -500,7 +502,7 @@ def main():
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        n_warm = 2 * max(1, -(-len(e2e_lanes) // NCH))  # every lane used once, an even count keeps the result-set parity
+        n_warm = DEPTH * max(1, -(-len(e2e_lanes) // NCH))  # every lane and every result set used at least once
         for i in range(n_warm):
             step_e2e(i)
         barrier()
@@ -511,7 +513,7 @@ def main():
         e2e = (time.perf_counter() - tw0) * 1e3  # host wall clock: the last fetch returns when the results are in host memory
         barrier()
         # the end-to-end path must deliver the same results as the device-resident one
-        for par in range(2):
+        for par in range(DEPTH):
             assert int(h_cnt[par].sum()) == n_kp_step and int(h_nm[par].sum()) == n_match_step, "e2e results differ from the device path"
 
     t = torch.tensor([ms, e2e if e2e is not None else 0.0], dtype=torch.float64, device="cuda")
