@@ -176,6 +176,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
     ap.add_argument("--chunks", type=int, default=2, help="e2e path: chunks per step (sweep on B200, 55 GB/s link, chunks/lanes: 1/2 64.3k, 2/3 73.0k, 2/6 72.9k, 4/4 66.4k, 4/6 66.8k, 8/8 62.3k pairs/s)")
+    ap.add_argument("--device-lanes", type=int, default=1, help="device-resident path: the step's batch cut into this many parts, each on its own handle and stream, all in flight together (measured: 1: 3.33 ms/step, 2: 4.02, 4: 4.03, 8: 4.07 - kernels with different shared-memory carve-outs do not share an SM, parts that start together only get in each other's way)")
     ap.add_argument("--depth", type=int, default=2, help="e2e path: steps in flight (pinned result sets); the host waits for step s-depth+1")
     ap.add_argument("--lanes", type=int, default=3, help="e2e path: streams/handles the stream of chunks goes round robin over")
     args = ap.parse_args()
@@ -283,9 +284,31 @@ def main():
     dp = torch.empty((P, cap), dtype=torch.float32, device="cuda")
     nm = torch.empty((P,), dtype=torch.int32, device="cuda")
 
-    def step_device():
-        ex.enqueue_ptr(dev.data_ptr(), NI, H, W, W, W * H, True)
-        ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+    # the whole batch on one handle (also the path of the per-stage timing pass), or cut into DL parts on DL handles and
+    # streams that run concurrently: the thin kernels of one part (quadtree, stereo, the small pyramid levels) then
+    # share the SMs with the wide ones of another
+    DL = args.device_lanes if (args.device_lanes > 1 and P % args.device_lanes == 0) else 1
+    dev_lanes = []
+    for _ in range(DL if DL > 1 else 0):
+        st = torch.cuda.Stream()
+        exk = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=NI // DL, device=local_rank)
+        cxk = snakeorb.Context(device=local_rank)
+        exk.set_stream(st.cuda_stream)
+        cxk.set_stream(st.cuda_stream)
+        dev_lanes.append((st, exk, cxk))
+
+    def step_device(single=False):
+        if DL == 1 or single:
+            ex.enqueue_ptr(dev.data_ptr(), NI, H, W, W, W * H, True)
+            ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+            return
+        ci, cp = NI // DL, P // DL
+        for k, (st, exk, cxk) in enumerate(dev_lanes):
+            st.wait_stream(tstream)
+            exk.enqueue_ptr(dev.data_ptr() + k * ci * W * H, ci, H, W, W, W * H, True)
+            cxk.stereo_orb_device(exk, cp, sp, rp.data_ptr() + 4 * k * cp * cap, dp.data_ptr() + 4 * k * cp * cap, nm.data_ptr() + 4 * k * cp)
+        for st, _, _ in dev_lanes:
+            tstream.wait_stream(st)
 
     # ---- end-to-end path: host (pinned) buffers in and out, the batch cut into chunks that alternate between two
     # extractor handles on two streams so that the H2D copy of chunk k+1 and the D2H of chunk k-1 overlap chunk k's
@@ -374,7 +397,7 @@ def main():
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     p0.record()
     for _ in range(args.steps):
-        step_device()
+        step_device(single=True)
     p1.record()
     barrier()
     ms_profiled = p0.elapsed_time(p1)
