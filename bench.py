@@ -571,7 +571,7 @@ def main():
         kname = {"fast": "k_fast_group", "pyramid": "k_resize"}.get(dom, "k_" + dom)
         # DRAM traffic of that kernel: dram__bytes_read + dram__bytes_write of the committed `ncu --set full` capture
         # (profiles/*_ncu_summary.csv, a 128-image launch of this same command), scaled to this launch's image count
-        traffic, traffic_src = None, None
+        traffic, traffic_src, limiter = None, None, None
         try:
             import csv
             import glob
@@ -582,10 +582,15 @@ def main():
                 per_img = (sum(float(r[2]) + float(r[3]) for r in rows_) * 1e6) / 128.0  # Mbyte columns, 128 images per capture
                 traffic = per_img * NI / max(launches[dom], 1)
                 traffic_src = os.path.relpath(newest, ROOT) + " (128-image capture, scaled per image)"
+                # what the kernel is bound by when it is not the memory system: share of the issue slots it uses (same capture)
+                limiter = {"what": "instruction issue (integer byte-SIMD, shared-memory lists), not DRAM",
+                           "issue_active_pct": sum(float(r[6]) for r in rows_) / len(rows_),
+                           "dram_pct_of_peak": sum(float(r[4]) for r in rows_) / len(rows_),
+                           "warp_instructions_per_image": sum(float(r[9]) for r in rows_) / 128.0}
         except Exception:  # noqa: BLE001
             traffic = None
         roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                    "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "limiter": limiter, "peak_source": peak_src,
                     "algorithmic_bytes_per_image": ab[dom], "images_per_launch": NI / max(launches[dom], 1),
                     "stage_ms_per_step": stage, "stage_timing_pass_ms_per_step": ms_profiled / args.steps,
                     "stage_timing": "separate pass of the same K steps with cudaEvents between the kernels (blur serialised "
