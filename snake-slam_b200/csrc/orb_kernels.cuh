@@ -625,34 +625,44 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         }
         __syncthreads();
 
-        // serial bookkeeping of the split loop (:127-159): where each node's children land and where it stops
-        if (tid == 0)
+        // bookkeeping of the split loop (:127-159): where each node's children land and where it stops. The serial
+        // loop's running counts are prefix sums, its break is the first node that satisfies the finish rule: one warp
+        // scans 32 nodes at a time (leaf count in the low, inner count in the high half of one word)
+        if (wid == 0)
         {
-            int nl = n_leaves, nn = 0, processed = m, fin = 0, lpi = -1;
-            for (int i = 0; i < m; ++i)
+            int nl = n_leaves, nn = 0, lpi = -1;
+            for (int base = 0; base < m && lpi < 0; base += 32)
             {
-                cpos[i] = make_int2(nl, nn);
+                const int i = base + lane;
+                int d = 0;
+                if (i < m)
+                {
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-                {
-                    const int c = ccnt_big[4 * i + q];
-                    nl += (c == 1);
-                    nn += (c > 1);
+                    for (int q = 0; q < 4; ++q)
+                    {
+                        const int c = ccnt_big[4 * i + q];
+                        d += (c == 1) + ((c > 1) << 16);
+                    }
                 }
-                if (nl + nn + (m - i - 1) >= target)
-                {
-                    lpi       = i;
-                    fin       = 1;
-                    processed = i + 1;
-                    break;
-                }
+                const int inc = warp_incl_scan(d, lane);
+                const int il = inc & 0xffff, in = inc >> 16;
+                if (i < m) cpos[i] = make_int2(nl + il - (d & 0xffff), nn + in - (d >> 16));
+                const bool hit    = (i < m) && (nl + il + nn + in + (m - i - 1) >= target);
+                const unsigned hm = __ballot_sync(0xffffffffu, hit);
+                const int f       = hm ? (__ffs(hm) - 1) : 31;  // the node the serial loop stops at, else the chunk's last
+                if (hm) lpi = base + f;
+                nl += __shfl_sync(0xffffffffu, il, f);
+                nn += __shfl_sync(0xffffffffu, in, f);
             }
-            if (nl > node_cap || nn > node_cap) atomicExch(err, 2);
-            s_ctrl[0] = nn;
-            s_ctrl[1] = nl;
-            s_ctrl[4] = fin;
-            if (fin) s_ctrl[3] = lpi;
-            s_ctrl[7] = processed;
+            if (lane == 0)
+            {
+                if (nl > node_cap || nn > node_cap) atomicExch(err, 2);
+                s_ctrl[0] = nn;
+                s_ctrl[1] = nl;
+                s_ctrl[4] = (lpi >= 0);
+                if (lpi >= 0) s_ctrl[3] = lpi;
+                s_ctrl[7] = (lpi >= 0) ? lpi + 1 : m;
+            }
         }
         __syncthreads();
         const int processed = s_ctrl[7];
