@@ -290,7 +290,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->node_cap = align_up(max_quota + 8, 4);  // multiple of 4 keeps the int2 array of the kernel 8-byte aligned
     SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
     h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES + 2 * (size_t)QT_KP_SMEM * 4;
-    SNK_REQUIRE(24 * h->node_cap >= gnusort::cta_sort_scratch_bytes(h->node_cap), "internal: sort scratch does not fit");
+    SNK_REQUIRE(20 * h->node_cap >= gnusort::cta_sort_scratch_bytes(h->node_cap), "internal: sort scratch does not fit");
     SNK_REQUIRE(h->qt_smem <= (size_t)SMEM_CEILING, "nfeatures too large for the distribution kernel's shared memory");
     // the attribute belongs to the kernel, not to this handle: every handle sets the same ceiling, so handles with
     // different image sizes (or threads creating handles at the same time) cannot lower it under each other

@@ -431,8 +431,10 @@ constexpr int QT_NT = 256;
 __device__ __forceinline__ float kp_x(uint32_t p) { return (float)(p & 0xfffu); }
 __device__ __forceinline__ float kp_y(uint32_t p) { return (float)((p >> 12) & 0xfffu); }
 
-// dynamic shared memory: 3 node lists + sort keys + per-node child counts/positions = QT_NODE_BYTES per node
-constexpr int QT_NODE_BYTES = 3 * 24 + 4 + 16 + 8;
+// dynamic shared memory: 2 node lists + leaf positions + sort keys + per-node child counts / positions = QT_NODE_BYTES
+// per node (a leaf holds one keypoint: only its position in the keypoint array is kept). 76 bytes per node and 2 x 2048
+// keypoints let six blocks share an SM at the BASELINE quotas.
+constexpr int QT_NODE_BYTES = 2 * 24 + 4 + 4 + 16 + 4;
 constexpr int QT_SMALL = 24;      // nodes up to this many keypoints are processed by a single thread
 constexpr int QT_KP_SMEM = 2048;  // keypoints per (level, image) kept in shared memory (x2: array + partition buffer)
 __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* __restrict__ cand,
@@ -444,10 +446,10 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     extern __shared__ __align__(16) unsigned char smem[];
     QNode* listA    = reinterpret_cast<QNode*>(smem);
     QNode* listB    = listA + node_cap;
-    QNode* leaves   = listB + node_cap;
-    uint32_t* keys  = reinterpret_cast<uint32_t*>(leaves + node_cap);
+    uint32_t* leaves = reinterpret_cast<uint32_t*>(listB + node_cap);  // position of the leaf's keypoint
+    uint32_t* keys  = leaves + node_cap;
     int* ccnt_big   = reinterpret_cast<int*>(keys + node_cap);           // child sizes of sorted node i (4 per node)
-    int2* cpos      = reinterpret_cast<int2*>(ccnt_big + 4 * node_cap);  // (leaf position, next position) of node i
+    short2* cpos    = reinterpret_cast<short2*>(ccnt_big + 4 * node_cap);  // (leaf position, next position) of node i (<= node_cap + 4 each)
     __shared__ int s_warp[QT_NT / 32], s_ctrl[10];
 
     const int level = blockIdx.y, img = blockIdx.x;  // all level-0 blocks (the longest) are dispatched first
@@ -646,7 +648,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
                 }
                 const int inc = warp_incl_scan(d, lane);
                 const int il = inc & 0xffff, in = inc >> 16;
-                if (i < m) cpos[i] = make_int2(nl + il - (d & 0xffff), nn + in - (d >> 16));
+                if (i < m) cpos[i] = make_short2((short)min(nl + il - (d & 0xffff), 32767), (short)min(nn + in - (d >> 16), 32767));
                 const bool hit    = (i < m) && (nl + il + nn + in + (m - i - 1) >= target);
                 const unsigned hm = __ballot_sync(0xffffffffu, hit);
                 const int f       = hm ? (__ffs(hm) - 1) : 31;  // the node the serial loop stops at, else the chunk's last
@@ -685,7 +687,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
                 B[dst]           = p;
             }
             for (int k = nd.from; k < nd.to; ++k) A[k] = B[k];
-            int2 pos = cpos[i];
+            int2 pos = make_int2(cpos[i].x, cpos[i].y);
             int from = nd.from;
 #pragma unroll
             for (int q = 0; q < 4; ++q)
@@ -701,7 +703,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
                 from += c;
                 if (c == 1)
                 {
-                    if (pos.x < node_cap) leaves[pos.x] = ch;
+                    if (pos.x < node_cap) leaves[pos.x] = (uint32_t)ch.from;
                     ++pos.x;
                 }
                 else if (c > 1)
@@ -745,7 +747,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
             for (int k = nd.from + lane; k < nd.to; k += 32) A[k] = B[k];
             if (lane == 0)
             {
-                int2 pos = cpos[i];
+                int2 pos = make_int2(cpos[i].x, cpos[i].y);
                 int from = nd.from;
                 const int cs[4] = {c0, c1, c2, c3};
 #pragma unroll
@@ -762,7 +764,7 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
                     from += c;
                     if (c == 1)
                     {
-                        if (pos.x < node_cap) leaves[pos.x] = ch;
+                        if (pos.x < node_cap) leaves[pos.x] = (uint32_t)ch.from;
                         ++pos.x;
                     }
                     else if (c > 1)
@@ -787,7 +789,10 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
     {
         QNode nd;
         if (o < n_leaves)
-            nd = leaves[o];
+        {
+            if (o < out_cap) out[o] = A[leaves[o]];
+            continue;
+        }
         else if (o < n_leaves + n_next)
             nd = next[o - n_leaves];
         else
