@@ -84,3 +84,49 @@ def test_two_gloo_ranks_equal_single_process(tmp_path, oracle):
     assert got.shape == (2, n_frames)
     assert list(got[0]) == want_c and list(got[1]) == want_d
     assert float(np.load(tmp_path / "tmax.npy")[0]) == 11.0
+
+
+CONTRACT_KEYS = ["metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                 "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches"]
+
+
+def test_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference: the reference side of the driver's ratio runs without a GPU (it is the CPU path), prints
+    ONE JSON line with the contract's keys, impl = reference, a cpu_baseline describing the run and an e2e equal to it."""
+    import json
+    import subprocess
+    import sys
+
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--pairs", "2"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for k in CONTRACT_KEYS + ["impl", "cpu_baseline"]:
+        assert k in d, k
+    assert d["impl"] == "reference" and d["gpu_launches"] == 0 and d["vs_baseline"] is None and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert "workload" in d["config"] and "model" not in d["config"]
+
+
+def test_committed_bench_line_has_every_contract_key():
+    """The newest bench line under profiles/ (written on a B200) carries the contract's keys plus roofline, cpu_baseline,
+    clocks; guards bench.py's JSON assembly against silently dropping one."""
+    import glob
+    import json
+
+    newest = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_bench.json")))[-1]
+    d = json.loads(open(newest).read().strip().splitlines()[-1])
+    for k in CONTRACT_KEYS + ["roofline", "cpu_baseline", "clocks"]:
+        assert k in d, (newest, k)
+    for k in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+        assert k in d["roofline"], k
+    assert d["roofline"]["bound"] in ("hbm", "tensor") and abs(d["roofline"]["frac"] - d["roofline"]["achieved"] / d["roofline"]["peak"]) < 1e-9
+    for k in ("value", "unit", "cores", "kind", "sample"):
+        assert k in d["cpu_baseline"], k
+    for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"):
+        assert k in d["e2e"], k
+    assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["gpu_launches"] > 0 and d["e2e"]["value"] != d["value"]
+    assert d["clocks"]["reasons"] == [] or all("thermal" not in r and "hw_slowdown" not in r for r in d["clocks"]["reasons"])
