@@ -806,6 +806,7 @@ int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacit
     SNK_REQUIRE(h && n_out, "null argument");
     const int n = h->last_n;
     if (n == 0) return SNK_OK;
+    SNK_REQUIRE(kps && desc && capacity >= 0, "null result arrays");
     SNK_CUDA(cudaSetDevice(h->prm.device));
     cudaStream_t st = h->stream;
     const int ks    = h->P.kp_stride;
@@ -880,7 +881,7 @@ int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, 
                          size_t img_stride, int on_device, snk_keypoint_f32* kps, uint64_t* desc, int capacity,
                          int* n_out)
 {
-    SNK_REQUIRE(h && n_out, "null argument");
+    SNK_REQUIRE(h && n_out && kps && desc && capacity >= 0, "null argument");  // before any work is queued
     for (int i = 0; i < n_imgs; ++i) n_out[i] = 0;
     int rc = snk_orb_enqueue(h, imgs, n_imgs, rows, cols, pitch, img_stride, on_device);
     if (rc) return rc;
