@@ -97,8 +97,10 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
                                                   const int* __restrict__ counts, int stride, int nl_fixed, int nr_fixed,
                                                   snk_stereo_params prm, int sort_cap, float* __restrict__ right_points,
                                                   float* __restrict__ depth, int* __restrict__ n_matches,
-                                                  int* __restrict__ err)
+                                                  int* __restrict__ err, int nbins)
 {
+    // nbins: rows the counting sort covers, a multiple of ST_NT, <= ST_ROW_BINS (the image height rounded up when the
+    // caller knows it: clearing, scanning and ordering 4096 rows for a 480-row image was most of the sort)
     extern __shared__ uint32_t keys[];  // sort_cap entries: (iRound(y) + 32768) << 16 | index, then ST_ROW_BINS + 1 row counters
     __shared__ int s_matches;
     const int pair = blockIdx.x;
@@ -128,13 +130,13 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
     int* bins = reinterpret_cast<int*>(keys + sort_cap);  // ST_ROW_BINS + 1 counters
     __shared__ int s_wide;
     if (tid == 0) s_wide = 0;
-    for (int i = tid; i <= ST_ROW_BINS; i += ST_NT) bins[i] = 0;
+    for (int i = tid; i <= nbins; i += ST_NT) bins[i] = 0;
     __syncthreads();
     for (int i = tid; i < nr; i += ST_NT)
     {
         const int row = iround_f((float)R[i].y);
         if (row < -32768 || row > 32766) atomicExch(err, 2);
-        if (row < 0 || row >= ST_ROW_BINS)
+        if (row < 0 || row >= nbins)
             s_wide = 1;
         else
             atomicAdd(&bins[row], 1);
@@ -142,11 +144,10 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
     __syncthreads();
     if (!s_wide)
     {
-        // exclusive scan of the row counts: every thread owns ST_ROW_BINS / ST_NT consecutive bins
-        constexpr int PER = ST_ROW_BINS / ST_NT;
-        int local[PER], sum = 0;
-#pragma unroll
-        for (int k = 0; k < PER; ++k) local[k] = bins[tid * PER + k], sum += local[k];
+        // exclusive scan of the row counts: every thread owns nbins / ST_NT consecutive bins
+        const int PER = nbins / ST_NT;
+        int sum = 0;
+        for (int k = 0; k < PER; ++k) sum += bins[tid * PER + k];
         const int lane = tid & 31, wid = tid >> 5;
         const int inc  = warp_incl_scan(sum, lane);
         __shared__ int s_wsum[ST_NT / 32];
@@ -157,13 +158,13 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
         for (int k = 0; k < ST_NT / 32; ++k)
             if (k < wid) base += s_wsum[k];
         // bins[r] = first slot of row r; it doubles as the scatter cursor and ends up at the first slot of row r + 1
-#pragma unroll
         for (int k = 0; k < PER; ++k)
         {
+            const int cnt       = bins[tid * PER + k];
             bins[tid * PER + k] = base;
-            base += local[k];
+            base += cnt;
         }
-        if (tid == ST_NT - 1) bins[ST_ROW_BINS] = base;
+        if (tid == ST_NT - 1) bins[nbins] = base;
         __syncthreads();
         // scatter (order inside a row arbitrary for now); the cursor of row r ends at the start of row r + 1
         for (int i = tid; i < nr; i += ST_NT)
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
         }
         __syncthreads();
         // row r now occupies [end of row r-1, bins[r]): order its entries by index (insertion sort, rows are short)
-        for (int r = tid; r < ST_ROW_BINS; r += ST_NT)
+        for (int r = tid; r < nbins; r += ST_NT)
         {
             const int e = bins[r], b0 = (r == 0) ? 0 : bins[r - 1];
             for (int i = b0 + 1; i < e; ++i)

@@ -182,7 +182,9 @@ int snk_filter_matches(const snk_knn2* k, int n, int threshold, float ratio, int
     return SNK_OK;
 }
 
-static int stereo_smem(int sort_cap) { return sort_cap * 4 + (ST_ROW_BINS + 4) * 4; }
+static int stereo_smem(int sort_cap, int nbins = ST_ROW_BINS) { return sort_cap * 4 + (nbins + 4) * 4; }
+// rows the counting sort of k_stereo has to cover for keypoints of an image with `rows` rows: a multiple of ST_NT
+static int stereo_bins(int rows) { return std::min(ST_ROW_BINS, std::max(ST_NT, (rows + ST_NT) / ST_NT * ST_NT)); }
 
 int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl, int nl,
                      const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points, float* depth,
@@ -221,8 +223,11 @@ int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_
     while (cap < nr) cap <<= 1;
     SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
     SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
-    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap), st>>>(
-        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err);
+    double ymax = 0;  // the right keypoints are host data here: the sort only has to cover the rows they use
+    for (int i = 0; i < nr; ++i) ymax = (right[i].y > ymax) ? right[i].y : ymax;
+    const int nbins = stereo_bins(ymax < 4096.0 ? (int)ymax + 1 : ST_ROW_BINS);
+    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap, nbins), st>>>(
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, nbins);
     SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
@@ -275,7 +280,7 @@ int snk_stereo_matching(snk_ctx* c, const snk_rectify* rect_left, const snk_rect
     SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
     SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
     k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap), st>>>(
-        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err);
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, ST_ROW_BINS);
     SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
@@ -309,8 +314,11 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     // enough blocks to fill the machine: several blocks per pair when the batch is small
     const int parts = std::max(1, std::min((stride + ST_NT - 1) / ST_NT, 1024 / std::max(n_pairs, 1)));
     SNK_CUDA(cudaMemsetAsync(n_matches, 0, 4 * (size_t)n_pairs, c->stream));
-    k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, stereo_smem(cap), c->stream>>>(
-        kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err);
+    int rows0 = ST_ROW_BINS;  // keypoint rows are level-0 rows: the image height bounds them
+    if (snk_orb_get_level(h, 0, 0, 0, nullptr, &rows0, nullptr, nullptr) != SNK_OK) rows0 = ST_ROW_BINS;
+    const int nbins = stereo_bins(rows0 + 1);
+    k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, stereo_smem(cap, nbins), c->stream>>>(
+        kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err, nbins);
     SNK_CUDA(cudaGetLastError());
     return SNK_OK;
 }
