@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
                                                   const int* __restrict__ counts, int stride, int nl_fixed, int nr_fixed,
                                                   snk_stereo_params prm, int sort_cap, float* __restrict__ right_points,
                                                   float* __restrict__ depth, int* __restrict__ n_matches,
-                                                  int* __restrict__ err, int nbins)
+                                                  int* __restrict__ err, int nbins, int staged)
 {
     // nbins: rows the counting sort covers, a multiple of ST_NT, <= ST_ROW_BINS (the image height rounded up when the
     // caller knows it: clearing, scanning and ordering 4096 rows for a 480-row image was most of the sort)
@@ -224,6 +224,22 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
             }
     }
 
+    // staged != 0: x and octave of the right keypoints in sorted order behind the counters, so that the candidate walk
+    // below touches shared memory only (its loop is a serial chain per thread; global loads in it cost a round trip each)
+    using XT = decltype(KP::x);
+    XT* sx   = reinterpret_cast<XT*>(reinterpret_cast<unsigned char*>(keys) + (((size_t)(sort_cap + nbins + 4) * 4 + 7) & ~(size_t)7));
+    int* so  = reinterpret_cast<int*>(sx + sort_cap);
+    if (staged)
+    {
+        for (int k = tid; k < nr; k += ST_NT)
+        {
+            const int o = (int)(keys[k] & 0xffffu);
+            sx[k] = R[o].x;
+            so[k] = R[o].octave;
+        }
+        __syncthreads();
+    }
+
     const float min_disp = 0.f;
     const float max_disp = (float)(prm.bf * 0.5);
     const int th_dist    = prm.relaxed ? 75 : 40;
@@ -255,9 +271,9 @@ __global__ void __launch_bounds__(ST_NT) k_stereo(const KP* __restrict__ kps, co
             const uint32_t key = keys[k];
             if ((int)(key >> 16) - 32768 > row_hi) break;
             const int o = (int)(key & 0xffffu);
-            const double disparity = lx - (double)R[o].x;
+            const double disparity = lx - (double)(staged ? sx[k] : R[o].x);
             if (disparity < min_disp || disparity > max_disp) continue;
-            if (abs(oct - R[o].octave) > 1) continue;
+            if (abs(oct - (staged ? so[k] : R[o].octave)) > 1) continue;
             const int d = hamming(q, load_desc(DR + 4 * (size_t)o));
             if (d < best)
             {

@@ -183,6 +183,13 @@ int snk_filter_matches(const snk_knn2* k, int n, int threshold, float ratio, int
 }
 
 static int stereo_smem(int sort_cap, int nbins = ST_ROW_BINS) { return sort_cap * 4 + (nbins + 4) * 4; }
+constexpr int ST_SMEM_CEILING = 200 * 1024;
+// with the right keypoints' x (xt_bytes each) and octaves staged behind the counters; 0 if that does not fit
+static int stereo_smem_staged(int sort_cap, int nbins, int xt_bytes)
+{
+    const size_t b = (((size_t)(sort_cap + nbins + 4) * 4 + 7) & ~(size_t)7) + (size_t)sort_cap * (xt_bytes + 4);
+    return b <= (size_t)ST_SMEM_CEILING ? (int)b : 0;
+}
 // rows the counting sort of k_stereo has to cover for keypoints of an image with `rows` rows: a multiple of ST_NT
 static int stereo_bins(int rows) { return std::min(ST_ROW_BINS, std::max(ST_NT, (rows + ST_NT) / ST_NT * ST_NT)); }
 
@@ -221,13 +228,14 @@ int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_
     SNK_CUDA(cudaMemcpyAsync(dd + 4 * (size_t)stride, dr, 32 * (size_t)nr, cudaMemcpyHostToDevice, st));
     int cap = 1;
     while (cap < nr) cap <<= 1;
-    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_CEILING));
     SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
     double ymax = 0;  // the right keypoints are host data here: the sort only has to cover the rows they use
     for (int i = 0; i < nr; ++i) ymax = (right[i].y > ymax) ? right[i].y : ymax;
     const int nbins = stereo_bins(ymax < 4096.0 ? (int)ymax + 1 : ST_ROW_BINS);
-    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap, nbins), st>>>(
-        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, nbins);
+    const int staged = stereo_smem_staged(cap, nbins, 8);
+    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, staged ? staged : stereo_smem(cap, nbins), st>>>(
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, nbins, staged);
     SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
@@ -277,10 +285,11 @@ int snk_stereo_matching(snk_ctx* c, const snk_rectify* rect_left, const snk_rect
     k_undistort<<<(nr + 127) / 128, 128, 0, st>>>(*rect_right, raw + stride, nr, dk + stride, dnorm);
     int cap = 1;
     while (cap < nr) cap <<= 1;
-    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+    SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f64>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_CEILING));
     SNK_CUDA(cudaMemsetAsync(dn, 0, 4, st));
-    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, stereo_smem(cap), st>>>(
-        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, ST_ROW_BINS);
+    const int staged = stereo_smem_staged(cap, ST_ROW_BINS, 8);
+    k_stereo<snk_keypoint_f64><<<dim3(1, std::min(8, (nl + ST_NT - 1) / ST_NT)), ST_NT, staged ? staged : stereo_smem(cap), st>>>(
+        dk, dd, nullptr, stride, nl, nr, *p, cap, drp, ddp, dn, c->d_err, ST_ROW_BINS, staged);
     SNK_CUDA(cudaMemcpyAsync(right_points, drp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(depth, ddp, 4 * (size_t)nl, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
@@ -308,7 +317,7 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     static bool attr_set[64] = {};  // the attribute belongs to the device
     if (c->device >= 64 || !attr_set[c->device])
     {
-        SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, stereo_smem(16384)));
+        SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_CEILING));
         if (c->device < 64) attr_set[c->device] = true;
     }
     // enough blocks to fill the machine: several blocks per pair when the batch is small
@@ -317,8 +326,9 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     int rows0 = ST_ROW_BINS;  // keypoint rows are level-0 rows: the image height bounds them
     if (snk_orb_get_level(h, 0, 0, 0, nullptr, &rows0, nullptr, nullptr) != SNK_OK) rows0 = ST_ROW_BINS;
     const int nbins = stereo_bins(rows0 + 1);
-    k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, stereo_smem(cap, nbins), c->stream>>>(
-        kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err, nbins);
+    const int staged = stereo_smem_staged(cap, nbins, 4);
+    k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, staged ? staged : stereo_smem(cap, nbins), c->stream>>>(
+        kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err, nbins, staged);
     SNK_CUDA(cudaGetLastError());
     return SNK_OK;
 }
