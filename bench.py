@@ -167,8 +167,8 @@ def cpu_pairs_per_s(distinct, threads, budget_s, stereo_params_fn):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--pairs", type=int, default=256, help="stereo pairs per step per GPU")
     ap.add_argument("--impl", default="snakeorb", choices=["snakeorb", "reference"])
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
