@@ -35,7 +35,8 @@ typedef enum snk_status
     SNK_ERR_UNSUPPORTED = -4
 } snk_status;
 
-/* Text of the last error raised on the calling thread (never NULL). */
+/* Text of the last error raised on the calling thread (never NULL). No reference counterpart: the reference aborts
+ * through SAIGA_ASSERT (saiga/core/util/assert.h) where this library returns a status. snk_version likewise. */
 SNK_API const char* snk_last_error(void);
 SNK_API const char* snk_version(void);
 
@@ -90,7 +91,9 @@ typedef struct snk_orb_params
 SNK_API int snk_orb_create(const snk_orb_params* params, snk_orb** out);
 SNK_API void snk_orb_destroy(snk_orb* h);
 
-/* Run all work of this handle on `cuda_stream` (a cudaStream_t; NULL = the handle's own stream). */
+/* Run all work of this handle on `cuda_stream` (a cudaStream_t; NULL = the handle's own stream). The reference's GPU
+ * extractor owns its streams (ORBExtractorGPU.h:81,103-105); here the caller may supply one to order the extractor
+ * against its own copies and matchers. */
 SNK_API int snk_orb_set_stream(snk_orb* h, void* cuda_stream);
 
 /* ORBExtractor::Detect (ORBExtractor.cpp:178-233): one image, results in host memory. `img` is rows x cols u8 with
@@ -106,7 +109,8 @@ SNK_API int snk_orb_detect_batch(snk_orb* h, const uint8_t* imgs, int n_imgs, in
                                  size_t img_stride, int imgs_are_device, snk_keypoint_f32* kps, uint64_t* desc,
                                  int capacity, int* n_out);
 
-/* Asynchronous halves of the call above, for pipelines that keep results on the device:
+/* Asynchronous halves of the call above, for pipelines that keep results on the device (the upload + kernels /
+ * download split of ORBExtractorGPU::Detect, saiga/cuda/imageProcessing/ORBExtractorGPU.cu:100-192):
  * enqueue = copy-in (if host) + all kernels on the handle's stream; no host synchronisation. */
 SNK_API int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int cols, size_t pitch,
                             size_t img_stride, int imgs_are_device);
@@ -115,11 +119,13 @@ SNK_API int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int row
  * is written straight into the level-0 buffer: gray = (R*9798 + G*19235 + B*3735 + 16384) >> 15, alpha ignored. */
 SNK_API int snk_orb_enqueue_rgba(snk_orb* h, const uint8_t* rgba, int n_imgs, int rows, int cols, size_t pitch,
                                  size_t img_stride, int imgs_are_device);
-/* Device-resident results of the last enqueue: keypoints [max_batch][stride] (24-byte records), descriptors
+/* No reference counterpart (its extractors only return host vectors, ORBExtractor.cpp:223-232): device-resident
+ * results of the last enqueue for the matchers that consume them in place: keypoints [max_batch][stride] (24-byte records), descriptors
  * [max_batch][stride][4] u64, counts [max_batch] i32. Valid until the next enqueue on this handle. */
 SNK_API int snk_orb_device_results(snk_orb* h, const snk_keypoint_f32** kps_dev, const uint64_t** desc_dev,
                                    const int32_t** counts_dev, int* stride);
-/* Copy the results of the last enqueue to the host (synchronises the stream). */
+/* Copy the results of the last enqueue to the host (synchronises the stream): the output half of
+ * ORBExtractor::Detect (ORBExtractor.cpp:223-232: keypoints and descriptors appended level by level). */
 SNK_API int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
 
 /* Same copies as snk_orb_fetch, enqueued on the handle's stream without waiting for them: keypoints, descriptors and
@@ -129,7 +135,8 @@ SNK_API int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int
  * capacity must be >= snk_orb_max_keypoints(). */
 SNK_API int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
 
-/* Upper bound of keypoints per image for this handle (sum over levels of quota+3). */
+/* Upper bound of keypoints per image for this handle (sum over levels of quota+3): what a caller
+ * sizes its arrays with, where the reference lets std::vector grow (ORBExtractor.cpp:219-221 reserve, :223 insert). */
 SNK_API int snk_orb_max_keypoints(const snk_orb* h);
 
 /* ORBExtractor::getPyramid (ORBExtractor.h:61) / ScalePyramid accessors (saiga/vision/util/ScalePyramid.h:78-84):
@@ -140,7 +147,8 @@ SNK_API int snk_orb_pyramid(const snk_orb* h, double* scale, int32_t* features);
  * batch (blurred = 0) or to its Gaussian-blurred copy (blurred = 1). Valid until the next enqueue. */
 SNK_API int snk_orb_get_level(snk_orb* h, int img, int level, int blurred, const uint8_t** dev_ptr, int* rows,
                               int* cols, size_t* pitch);
-/* Same, copied to host memory with `dst_pitch` bytes per row (test/debug helper). */
+/* Same, copied to host memory with `dst_pitch` bytes per row (test/debug helper; the reference's GetImage returns
+ * a host ImageView directly, ORBExtractor.h:55-59). */
 SNK_API int snk_orb_read_level(snk_orb* h, int img, int level, int blurred, uint8_t* dst, size_t dst_pitch);
 /* Raw FAST candidates of one level before distribution (ORBExtractor.cpp:133-155 order), as x | y<<12 | score<<24
  * with coordinates relative to (16,16). Test/debug helper. */
@@ -149,13 +157,16 @@ SNK_API int snk_orb_read_candidates(snk_orb* h, int img, int level, uint32_t* pa
 /* Per-stage device time accumulated since the last reset, in milliseconds (cudaEvents on the handle's stream).
  * stage: 0 copy-in, 1 pyramid, 2 FAST, 3 distribute, 4 blur, 5 orientation + descriptors + output records,
  * 6 reserved, 7 total.
- * Profiling costs two event records per stage; it is off by default. */
+ * Profiling costs two event records per stage; it is off by default. Counterpart of the per-module timers the
+ * reference prints at exit (Snake/System/Module.cpp:78-100, FeatureDetector.cpp:75,81), per kernel stage here. */
 #define SNK_ORB_NUM_STAGES 8
 SNK_API int snk_orb_set_profiling(snk_orb* h, int enabled);
 SNK_API int snk_orb_stage_ms(snk_orb* h, float* ms /*[SNK_ORB_NUM_STAGES]*/, int* launches /*[SNK_ORB_NUM_STAGES]*/, int reset);
 
 /* ------------------------------------------------------------------------------------------------------------
- * Matching context (device, stream, growable scratch) shared by all matchers below.
+ * Matching context (device, stream, growable scratch) shared by all matchers below. No reference counterpart: the
+ * reference's matchers are stateless objects on the host (Features.h:299, SnakeORBMatcher.h); a GPU library needs
+ * a place for its device scratch and its stream.
  * ---------------------------------------------------------------------------------------------------------- */
 typedef struct snk_ctx snk_ctx;
 SNK_API int snk_ctx_create(int device, snk_ctx** out);
@@ -174,7 +185,9 @@ typedef struct snk_knn2
     int32_t dist0, idx0, dist1, idx1;
 } snk_knn2;
 SNK_API int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t* d2, int m, snk_knn2* out);
-/* Batched form on device memory: problem p matches d1 + 4*p*stride1 (n[p] rows) against d2 + 4*p*stride2 (m[p]);
+/* Batched form of the same matchKnn2 (Features.h:323-388) on device memory, one problem per keyframe pair (the
+ * loops over candidate keyframes at Snake/LoopClosing/LoopORBMatcher.cpp:104-106 and
+ * Initialization/MonoInitializer.cpp:587-590 call it once per pair): problem p matches d1 + 4*p*stride1 (n[p] rows) against d2 + 4*p*stride2 (m[p]);
  * n, m are device int arrays; out is device [n_problems][stride1]. Asynchronous on the context stream. */
 SNK_API int snk_match_knn2_batch_device(snk_ctx* c, const uint64_t* d1_dev, const int32_t* n_dev, int stride1,
                                         const uint64_t* d2_dev, const int32_t* m_dev, int stride2, int n_problems,
@@ -227,7 +240,8 @@ typedef struct snk_stereo_params
 SNK_API int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_keypoint_f64* left, const uint64_t* dl,
                              int nl, const snk_keypoint_f64* right, const uint64_t* dr, int nr, float* right_points,
                              float* depth, int* n_matches);
-/* Batched, device-resident form fed directly by an extractor handle: images 2p and 2p+1 of the last enqueue are the
+/* Batched, device-resident form of the same Preprocess::StereoMatching body (Preprocess.cpp:152-239), fed directly by
+ * an extractor handle: images 2p and 2p+1 of the last enqueue are the
  * left / right image of stereo pair p (identity rectification, i.e. EuRoC/KITTI rectified input). Outputs are device
  * arrays [n_pairs][stride] (stride from snk_orb_device_results) and n_matches_dev[n_pairs]. Asynchronous on the
  * extractor's stream. */
@@ -485,8 +499,9 @@ SNK_API int snk_bow_transform(snk_ctx* c, const snk_voc* voc, const uint64_t* de
                               int32_t* bow_ids, float* bow_vals, int* n_bow, int32_t* fv_node_ids,
                               int32_t* fv_offsets, int32_t* fv_indices, int* n_fv_nodes);
 
-/* Batched, device-resident form (e.g. straight from snk_orb_device_results: desc_dev [n_frames][stride][4],
- * counts_dev [n_frames], stride <= 8192). Outputs are device arrays: bow_ids / bow_vals / fv_node_ids / fv_indices
+/* Batched, device-resident form of the same transform (MiniBow2.h:883-931; Frame::computeBoW, Snake/Map/Frame.cpp:36-42,
+ * once per frame) — e.g. straight from snk_orb_device_results: desc_dev [n_frames][stride][4],
+ * counts_dev [n_frames], stride <= 8192. Outputs are device arrays: bow_ids / bow_vals / fv_node_ids / fv_indices
  * [n_frames][stride], fv_offsets [n_frames][stride + 1], out_counts [n_frames][2] = (words, nodes). Asynchronous on
  * the context's stream. */
 SNK_API int snk_bow_transform_batch_device(snk_ctx* c, const snk_voc* voc, const uint64_t* desc_dev,
@@ -506,17 +521,19 @@ SNK_API int snk_bow_score_batch(snk_ctx* c, const int32_t* q_ids, const float* q
  * (48-byte records), u64 n, n x DescriptorORB (32 bytes). Host-side helpers, no GPU involved. Also the format of
  * saiga/data/vision/{0,50}.features. */
 SNK_API int snk_features_write(const char* path, const snk_keypoint_f64* kps, const uint64_t* desc, int n);
-/* snk_features_read returns SNK_ERR_CAPACITY (and the file's feature count in *n_out) when capacity is too small. */
+/* The read side (FeatureDetector.cpp:101-102, `bf >> frame.keypoints >> frame.descriptors`). Returns
+ * SNK_ERR_CAPACITY (and the file's feature count in *n_out) when capacity is too small. */
 SNK_API int snk_features_read(const char* path, snk_keypoint_f64* kps, uint64_t* desc, int capacity, int* n_out);
 /* KeyPoint<float>::cast<double>() as FeatureDetector.cpp:129-132 applies it to the extractor's output. */
 SNK_API int snk_keypoints_widen(const snk_keypoint_f32* in, int n, snk_keypoint_f64* out);
 
-/* Input::computeGrayscaleImage alone (host RGBA in, host grey out), for callers that keep the grey image. */
+/* Input::computeGrayscaleImage (Snake/Preprocess/Input.cpp:394-413) alone (host RGBA in, host grey out), for callers
+ * that keep the grey image. */
 SNK_API int snk_rgba_to_gray(snk_ctx* c, const uint8_t* rgba, int rows, int cols, size_t pitch, uint8_t* gray,
                              size_t gray_pitch);
 
 /* Register-resident popc microbenchmark: measured 256-bit Hamming distances per second of this device, the
- * denominator of the matcher roofline. */
+ * denominator of the matcher roofline. Measurement helper, no reference counterpart. */
 SNK_API int snk_hamming_peak_selftest(snk_ctx* c, double* pair_ops_per_s);
 
 #ifdef __cplusplus
