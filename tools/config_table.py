@@ -112,9 +112,30 @@ def main():
         n_cand = sum(len(ex.candidates(l, 0)) for l in range(NLEVELS))
         ab = algorithmic_bytes(w, h, n_kp, n_cand)
         cpu = cpu_images_per_s(distinct, nf, args.threads, args.cpu_budget)
+        # latency: one image, host in, host out, synchronous Detect; median of 200 after 20 warm-ups
+        ex1 = snakeorb.ORBExtractor(nf, SCALE, NLEVELS, TH, THMIN, max_batch=1)
+        for _ in range(20):
+            ex1.Detect(distinct[0])
+        lat = []
+        for i in range(200):
+            t0 = time.perf_counter()
+            ex1.Detect(distinct[i % 8])
+            lat.append(time.perf_counter() - t0)
+        # the reference's own threading: one extractor, fd_threads = 2 (Settings.h:90)
+        import oracle_py
+
+        oe = oracle_py.Extractor(nf, SCALE, NLEVELS, TH, THMIN, 2)
+        oe.detect(distinct[0])
+        t0 = time.perf_counter()
+        for i in range(10):
+            oe.detect(distinct[i % 8])
+        cpu2_ms = (time.perf_counter() - t0) / 10 * 1e3
+        del ex1
         rows[name] = {"batch": B, "ms_per_batch": ms, "images_per_s": B / (ms * 1e-3), "keypoints_per_s": B * n_kp / (ms * 1e-3),
                       "keypoints_per_image": n_kp, "raw_candidates_per_image": n_cand, "extraction_bytes_per_image": ab,
-                      "hbm_frac": ab * B / (ms * 1e-3) / 1e9 / hbm, "cpu_port_images_per_s": cpu, "cpu_threads": args.threads}
+                      "hbm_frac": ab * B / (ms * 1e-3) / 1e9 / hbm, "cpu_port_images_per_s": cpu, "cpu_threads": args.threads,
+                      "latency_ms_median": float(np.median(lat)) * 1e3, "latency_ms_p95": float(np.percentile(lat, 95)) * 1e3,
+                      "cpu_port_ms_per_image_fd_threads_2": cpu2_ms}
         del ex, dev
 
     # ---- matcher kernels on the C2 shape: Hamming pair evaluations per second against the measured popc issue peak
@@ -184,6 +205,22 @@ def main():
     knn_ops = float((cnt[0::2].astype(np.int64) * cnt[1::2]).sum())
     matchers["knn2_batch"] = {"problems": P, "ms": ms_knn, "pair_ops": knn_ops, "pair_ops_per_s": knn_ops / (ms_knn * 1e-3),
                               "popc_frac": knn_ops / (ms_knn * 1e-3) / peak}
+    # relocalisation form of C4: matchKnn2 1000 x 1000 + filterMatches(60, 0.8), one call, host arrays in and out
+    kq, dq = orc.detect(pairs[0])
+    kt, dt = orc.detect(pairs[2])
+    dq, dt = dq[:1000], dt[:1000]
+    for _ in range(5):
+        ctx.matchKnn2(dq, dt)
+    ts = []
+    for _ in range(50):
+        t0 = time.perf_counter()
+        k2 = ctx.matchKnn2(dq, dt)
+        snakeorb.Context.filterMatches(k2, 60, 0.8)
+        ts.append(time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        oracle_py.filter_matches(oracle_py.match_knn2(dq, dt), 60, 0.8)
+    matchers["knn2_1000x1000_single_call"] = {"ms_median": float(np.median(ts)) * 1e3, "cpu_port_ms_1_thread": (time.perf_counter() - t0) / 3 * 1e3}
     print(json.dumps({"hbm_peak_gbs": hbm, "extraction": rows, "matchers": matchers}))
 
 
