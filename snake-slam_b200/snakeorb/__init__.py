@@ -143,8 +143,8 @@ class ORBExtractor:
         self.cap = lib().snk_orb_max_keypoints(self.h)
 
     def close(self):
-        if getattr(self, "h", None):
-            lib().snk_orb_destroy(self.h)
+        if getattr(self, "h", None) and lib is not None and _lib is not None:  # module globals are gone at interpreter exit
+            _lib.snk_orb_destroy(self.h)
             self.h = None
 
     __del__ = close
@@ -241,8 +241,8 @@ class Context:
         _check(lib().snk_ctx_create(device, C.byref(self.c)))
 
     def close(self):
-        if getattr(self, "c", None):
-            lib().snk_ctx_destroy(self.c)
+        if getattr(self, "c", None) and lib is not None and _lib is not None:  # module globals are gone at interpreter exit
+            _lib.snk_ctx_destroy(self.c)
             self.c = None
 
     __del__ = close
@@ -476,8 +476,8 @@ class Vocabulary:
         self.k, self.L, self.n_nodes, self.n_words = k.value, L.value, nn.value, nw.value
 
     def close(self):
-        if getattr(self, "v", None):
-            lib().snk_voc_destroy(self.v)
+        if getattr(self, "v", None) and lib is not None and _lib is not None:  # module globals are gone at interpreter exit
+            _lib.snk_voc_destroy(self.v)
             self.v = None
 
     __del__ = close
