@@ -1,7 +1,8 @@
 // Device side of the ORB extractor: data layout descriptors and the kernels.
 //
 //   k_resize      level l from level l-1        cv::resize INTER_LINEAR fixed point    ORBExtractor.cpp:282
-//   k_fast        FAST-9/16 + NMS per cell      cv::FAST per cell, two thresholds      ORBExtractor.cpp:114-157
+//   k_fast_group  FAST-9/16 + NMS per cell,     cv::FAST per cell, two thresholds      ORBExtractor.cpp:114-157
+//                 4 neighbouring cells per CTA  (fast_group.cuh; k_fast = the earlier one-cell kernel, SNK_FAST_PER_CELL=1)
 //   k_distribute  quadtree selection per level  QuadtreeFeatureDistributor::Distribute FeatureDistribution.cpp:72-189
 //   k_blur        7x7 Gaussian, reflect-101     cv::GaussianBlur                       ORBExtractor.cpp:213
 //   k_describe    orientation + rBRIEF + pack   ORB::ComputeAngle / ComputeDescriptor  OrbDescriptors.cpp:26-125,
