@@ -134,6 +134,20 @@ SNK_API int snk_orb_fetch(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int
  * counterpart of the download step of ORBExtractorGPU::Detect (saiga/cuda/imageProcessing/ORBExtractorGPU.cu:178-192).
  * capacity must be >= snk_orb_max_keypoints(). */
 SNK_API int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int capacity, int* n_out);
+/* Error check for the asynchronous path (snk_orb_enqueue + snk_orb_fetch_async never look at the kernels' error flag:
+ * capacity guards of the FAST / quadtree kernels, the bounded wait on the tile loads). Synchronises the handle's stream,
+ * returns SNK_ERR_CAPACITY (and clears the flag) if any batch since the last check hit one, SNK_OK otherwise. The
+ * reference aborts through SAIGA_ASSERT at the equivalent places (ORBExtractor.cpp:184). */
+SNK_API int snk_orb_check(snk_orb* h);
+/* Number of images of the last enqueue (0 before the first one / after an empty one). No reference counterpart. */
+SNK_API int snk_orb_last_batch(const snk_orb* h);
+/* Stream ordering for consumers of snk_orb_device_results (no reference counterpart: its extractors are synchronous).
+ * snk_orb_order_stream_after: work queued on `cuda_stream` after this call starts only when everything queued on the
+ * handle's stream so far (the last enqueue) has finished. snk_orb_order_after_stream: the handle's NEXT enqueue starts
+ * only when everything queued on `cuda_stream` so far has finished (the consumer has read the results). Events only,
+ * the host does not wait. */
+SNK_API int snk_orb_order_stream_after(snk_orb* h, void* cuda_stream);
+SNK_API int snk_orb_order_after_stream(snk_orb* h, void* cuda_stream);
 
 /* Upper bound of keypoints per image for this handle (sum over levels of quota+3): what a caller
  * sizes its arrays with, where the reference lets std::vector grow (ORBExtractor.cpp:219-221 reserve, :223 insert). */
@@ -243,10 +257,22 @@ SNK_API int snk_stereo_match(snk_ctx* c, const snk_stereo_params* p, const snk_k
 /* Batched, device-resident form of the same Preprocess::StereoMatching body (Preprocess.cpp:152-239), fed directly by
  * an extractor handle: images 2p and 2p+1 of the last enqueue are the
  * left / right image of stereo pair p (identity rectification, i.e. EuRoC/KITTI rectified input). Outputs are device
- * arrays [n_pairs][stride] (stride from snk_orb_device_results) and n_matches_dev[n_pairs]. Asynchronous on the
- * extractor's stream. */
+ * arrays [n_pairs][stride] (stride from snk_orb_device_results) and n_matches_dev[n_pairs]; 2 * n_pairs must not
+ * exceed the image count of the last enqueue. Asynchronous: the kernel runs on the CONTEXT's stream, ordered by events
+ * after the extractor stream's last enqueue and before its next one (no host synchronisation); the outputs are valid
+ * once the context's stream has reached this point. Device-side faults show up in snk_ctx_check. */
 SNK_API int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_stereo_params* p,
                                         float* right_points_dev, float* depth_dev, int32_t* n_matches_dev);
+
+/* The same two orderings for a context's stream: call snk_ctx_wait_orb before handing snk_orb_device_results pointers
+ * to snk_match_knn2_batch_device / snk_bow_transform_batch_device / snk_bow_score_batch (they run on the context's
+ * stream and take raw pointers, so they cannot order themselves), and snk_orb_wait_ctx before the handle's next
+ * enqueue. Both are no-ops when the two handles share one stream (snk_orb_set_stream / snk_ctx_set_stream). */
+SNK_API int snk_ctx_wait_orb(snk_ctx* c, snk_orb* h);
+SNK_API int snk_orb_wait_ctx(snk_orb* h, snk_ctx* c);
+/* Synchronises the context's stream and reports (then clears) device-side faults of the asynchronous matcher entry
+ * points (SNK_ERR_CAPACITY), so that they do not surface in a later unrelated call. */
+SNK_API int snk_ctx_check(snk_ctx* c);
 
 /* Preprocess::ComputeStereoFromRGBD (Snake/Preprocess/Preprocess.cpp:79-120): per undistorted keypoint, re-distort
  * with the depth camera's model (saiga/vision/cameraModel/Distortion.h:128-170), look the depth up at the nearest

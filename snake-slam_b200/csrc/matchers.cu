@@ -310,16 +310,26 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     int stride;
     int rc = snk_orb_device_results(h, &kps, &desc, &counts, &stride);
     if (rc) return rc;
+    SNK_REQUIRE(2 * n_pairs <= snk_orb_last_batch(h), "n_pairs %d needs %d images, the last enqueue held %d", n_pairs,
+                2 * n_pairs, snk_orb_last_batch(h));
     SNK_CUDA(cudaSetDevice(c->device));
     int cap = 1;
     while (cap < stride) cap <<= 1;
     SNK_REQUIRE(cap <= 16384, "more than 16384 keypoints per image");
-    static bool attr_set[64] = {};  // the attribute belongs to the device
-    if (c->device >= 64 || !attr_set[c->device])
     {
-        SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_CEILING));
-        if (c->device < 64) attr_set[c->device] = true;
+        // the attribute belongs to the device; set once per device, under a lock (handles may be used from several threads)
+        static std::mutex mtx;
+        static bool attr_set[64] = {};
+        std::lock_guard<std::mutex> lock(mtx);
+        if (c->device >= 64 || !attr_set[c->device])
+        {
+            SNK_CUDA(cudaFuncSetAttribute(k_stereo<snk_keypoint_f32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_CEILING));
+            if (c->device < 64) attr_set[c->device] = true;
+        }
     }
+    // the kernel runs on the context's stream: it must start after the extraction that fills kps / desc / counts ...
+    rc = snk_orb_order_stream_after(h, c->stream);
+    if (rc) return rc;
     // enough blocks to fill the machine: several blocks per pair when the batch is small
     const int parts = std::max(1, std::min((stride + ST_NT - 1) / ST_NT, 1024 / std::max(n_pairs, 1)));
     SNK_CUDA(cudaMemsetAsync(n_matches, 0, 4 * (size_t)n_pairs, c->stream));
@@ -330,7 +340,27 @@ int snk_stereo_match_orb_device(snk_ctx* c, snk_orb* h, int n_pairs, const snk_s
     k_stereo<snk_keypoint_f32><<<dim3(n_pairs, parts), ST_NT, staged ? staged : stereo_smem(cap, nbins), c->stream>>>(
         kps, desc, counts, stride, 0, 0, *p, cap, right_points, depth, n_matches, c->d_err, nbins, staged);
     SNK_CUDA(cudaGetLastError());
-    return SNK_OK;
+    // ... and the handle's next enqueue must not overwrite them before this kernel has read them
+    return snk_orb_order_after_stream(h, c->stream);
+}
+
+int snk_ctx_wait_orb(snk_ctx* c, snk_orb* h)
+{
+    SNK_REQUIRE(c && h, "null argument");
+    return snk_orb_order_stream_after(h, c->stream);
+}
+
+int snk_orb_wait_ctx(snk_orb* h, snk_ctx* c)
+{
+    SNK_REQUIRE(c && h, "null argument");
+    return snk_orb_order_after_stream(h, c->stream);
+}
+
+int snk_ctx_check(snk_ctx* c)
+{
+    SNK_REQUIRE(c, "null context");
+    SNK_CUDA(cudaSetDevice(c->device));
+    return check_err(c, "matcher kernels");
 }
 
 int snk_stereo_from_rgbd(snk_ctx* c, const snk_rgbd_params* p, const snk_keypoint_f64* kp_un, int n,
@@ -548,12 +578,17 @@ constexpr int kMaxDevices = 64;
 std::mutex g_noalloc_mutex;
 unsigned char* g_noalloc_ptr[kMaxDevices] = {};  // device address of the scratch array, per device ordinal
 
-// One-time set-up for `device`, which must be the current device.
+// Makes `device` current; the first call for an ordinal also checks that it is an sm_100 part and looks up the
+// array's address there (both answers are kept, so later calls cost one cudaSetDevice).
 int noalloc_scratch(int device, unsigned char** out)
 {
     std::lock_guard<std::mutex> lock(g_noalloc_mutex);
-    if (!g_noalloc_ptr[device])
+    if (g_noalloc_ptr[device])
+        SNK_CUDA(cudaSetDevice(device));
+    else
     {
+        int rc = select_device(device);
+        if (rc) return rc;
         unsigned char* ptr = nullptr;
         cudaError_t e      = cudaGetSymbolAddress((void**)&ptr, g_knn2_noalloc_scratch);
         if (e != cudaSuccess || !ptr)
@@ -578,10 +613,8 @@ extern "C" int snk_match_knn2_noalloc(int device, void* cuda_stream, const uint6
                 "use snk_match_knn2 for larger sets",
                 SNK_KNN2_NOALLOC_MAX, n, m);
     if (n == 0) return SNK_OK;
-    int rc = select_device(device);  // makes `device` current and checks it is an sm_100 part
-    if (rc) return rc;
     unsigned char* base = nullptr;
-    rc                  = noalloc_scratch(device, &base);
+    int rc              = noalloc_scratch(device, &base);
     if (rc) return rc;
     // fixed carve-up of the array: [d1 | d2 | results]
     uint64_t* a = reinterpret_cast<uint64_t*>(base);

@@ -87,6 +87,7 @@ struct snk_orb
     // descriptor kernel (serialised on the main stream while per-stage profiling is on, so stage times stay separable)
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_sync = nullptr;  // orders another stream against this handle's stream (snk_orb_order_*)
     int rows = 0, cols = 0;  // geometry the buffers are sized for (0 = none yet)
     int last_n = 0;
 
@@ -479,13 +480,19 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
         return SNK_ERR_CUDA;
     }
     h->stream = h->own_stream;
-    cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking);
-    cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
-    cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault);
-    cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault);
-    for (auto& set : h->ev)
-        for (auto& e : set) cudaEventCreate(&e);
+    if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_sync, cudaEventDisableTiming) != cudaSuccess ||
+        cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault) != cudaSuccess ||
+        cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault) != cudaSuccess)
+    {
+        set_error("extractor setup failed (streams, events or %zu bytes of pinned memory): %s",
+                  sizeof(int) * (size_t)p->max_batch, cudaGetErrorString(cudaGetLastError()));
+        snk_orb_destroy(h);
+        return SNK_ERR_CUDA;
+    }
+    *h->h_err = 0;
     // constants of the descriptor kernel
     int umax[16];
     {
@@ -568,6 +575,7 @@ void snk_orb_destroy(snk_orb* h)
     if (h->side_stream) cudaStreamDestroy(h->side_stream);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->ev_sync) cudaEventDestroy(h->ev_sync);
     delete h;
 }
 
@@ -861,6 +869,8 @@ int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int c
     SNK_CUDA(cudaSetDevice(h->prm.device));
     cudaStream_t st = h->stream;
     SNK_CUDA(cudaMemcpyAsync(n_out, h->d_counts, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    // the kernels' error flag is sticky on the device: the latest copy also shows earlier batches' faults (snk_orb_check)
+    SNK_CUDA(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
     if (capacity == ks)
     {
         SNK_CUDA(cudaMemcpyAsync(kps, h->d_kps, (size_t)n * ks * sizeof(snk_keypoint_f32), cudaMemcpyDeviceToHost, st));
@@ -874,6 +884,45 @@ int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* desc, int c
         SNK_CUDA(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->d_desc, (size_t)ks * 32, (size_t)ks * 32, n,
                                    cudaMemcpyDeviceToHost, st));
     }
+    return SNK_OK;
+}
+
+int snk_orb_check(snk_orb* h)
+{
+    SNK_REQUIRE(h, "null handle");
+    if (!h->rows) return SNK_OK;  // nothing has run yet
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    SNK_CUDA(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    SNK_CUDA(cudaStreamSynchronize(h->stream));
+    if (*h->h_err)
+    {
+        set_error("internal capacity error %d in the extraction kernels", *h->h_err);
+        *h->h_err = 0;
+        SNK_CUDA(cudaMemsetAsync(h->d_err, 0, 4, h->stream));
+        return SNK_ERR_CAPACITY;
+    }
+    return SNK_OK;
+}
+
+int snk_orb_last_batch(const snk_orb* h) { return h ? h->last_n : 0; }
+
+int snk_orb_order_stream_after(snk_orb* h, void* stream)
+{
+    SNK_REQUIRE(h, "null handle");
+    if ((cudaStream_t)stream == h->stream) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    SNK_CUDA(cudaEventRecord(h->ev_sync, h->stream));
+    SNK_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_sync, 0));
+    return SNK_OK;
+}
+
+int snk_orb_order_after_stream(snk_orb* h, void* stream)
+{
+    SNK_REQUIRE(h, "null handle");
+    if ((cudaStream_t)stream == h->stream) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    SNK_CUDA(cudaEventRecord(h->ev_sync, (cudaStream_t)stream));
+    SNK_CUDA(cudaStreamWaitEvent(h->stream, h->ev_sync, 0));
     return SNK_OK;
 }
 
@@ -946,6 +995,12 @@ int snk_orb_set_profiling(snk_orb* h, int enabled)
 {
     SNK_REQUIRE(h, "null handle");
     collect_events(h);
+    if (enabled && !h->ev[0][0])
+    {
+        SNK_CUDA(cudaSetDevice(h->prm.device));
+        for (auto& set : h->ev)
+            for (auto& e : set) SNK_CUDA(cudaEventCreate(&e));
+    }
     h->profiling = enabled != 0;
     return SNK_OK;
 }

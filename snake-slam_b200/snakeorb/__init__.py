@@ -200,6 +200,16 @@ class ORBExtractor:
         _check(lib().snk_orb_fetch(self.h, _p(kps), _p(desc), self.cap, _p(counts)))
         return kps, desc, counts
 
+    def check(self):
+        """snk_orb_check: synchronise and raise if a kernel of the asynchronous path reported a fault."""
+        _check(lib().snk_orb_check(self.h))
+
+    def last_batch(self):
+        return lib().snk_orb_last_batch(self.h)
+
+    def wait_ctx(self, ctx):
+        _check(lib().snk_orb_wait_ctx(self.h, ctx.c))
+
     def device_results(self):
         k, d, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
         s = C.c_int()
@@ -249,6 +259,13 @@ class Context:
 
     def set_stream(self, cuda_stream):
         _check(lib().snk_ctx_set_stream(self.c, C.c_void_p(cuda_stream)))
+
+    def wait_orb(self, orb):
+        """Order this context's stream after the extractor's last enqueue (snk_ctx_wait_orb)."""
+        _check(lib().snk_ctx_wait_orb(self.c, orb.h))
+
+    def check(self):
+        _check(lib().snk_ctx_check(self.c))
 
     def distance(self, a, b):
         """Saiga::distance for n pairs."""

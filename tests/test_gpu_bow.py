@@ -114,9 +114,9 @@ def test_device_chain_extract_bow_knn2(so, ctx, oracle):
     B = 5
     imgs = np.stack([S.image(40 + i // 2 if i < 4 else 99, 752, 480) for i in range(B)])  # frames 0/1 and 2/3 equal
     ex = so.ORBExtractor(1200, 1.2, 8, 20, 7, max_batch=B)
-    ex.set_stream(0)
-    ctx.set_stream(0)
+    # default handles (each owns a stream): the raw-pointer consumers are ordered behind the extraction explicitly
     ex.enqueue_ptr(imgs.ctypes.data, B, 480, 752, 752, 752 * 480, False)
+    ctx.wait_orb(ex)
     kps_ptr, desc_ptr, cnt_ptr, stride = ex.device_results()
     v = so.Vocabulary(VOC)
     vo = oracle.Vocabulary(VOC)
@@ -143,8 +143,6 @@ def test_device_chain_extract_bow_knn2(so, ctx, oracle):
         want = oracle.match_knn2(desc[p, :counts[p]], desc[p + 1, :counts[p + 1]])
         assert knn[p, :counts[p]].tobytes() == want.tobytes(), p
     assert np.all(knn[0, :counts[0]]["dist0"] == 0)  # identical frames
-    ex.set_stream(None)
-    ctx.set_stream(None)
 
 
 def test_bow_score_batch(so, ctx, oracle, refso=None):

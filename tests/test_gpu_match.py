@@ -94,21 +94,28 @@ def test_stereo_device_path_equals_host_path(so, ctx, oracle):
         l = S.image(700 + i, 752, 480)
         pairs += [l, S.stereo_right(l, 800 + i, 4.0, 20.0)]
     imgs = np.stack(pairs)
+    # expected values come from a second extractor: the handle under test must not have seen these images before, so
+    # that results left over from an earlier run cannot stand in for an unordered read
+    res = so.ORBExtractor(1200, 1.2, 8, 20, 7, max_batch=6).DetectBatch(imgs)
     ex = so.ORBExtractor(1200, 1.2, 8, 20, 7, max_batch=6)
-    res = ex.DetectBatch(imgs)
     scales, _ = ex.getPyramid()
     p = so.stereo_params(47.9, True, scales)
-    # device outputs in a scratch buffer obtained through the hamming context's own allocator: use cudart directly
     cudart = C.CDLL("libcudart.so")
+    warm = np.stack([S.image(990 + i, 752, 480) for i in range(6)])
+    ex.enqueue_ptr(warm.ctypes.data, 6, 480, 752, 752, 752 * 480, False)  # sizes the buffers with other images
     stride = ex.device_results()[3]
     bufs = [C.c_void_p() for _ in range(3)]
     for b, nbytes in zip(bufs, (3 * stride * 4, 3 * stride * 4, 3 * 4)):
         assert cudart.cudaMalloc(C.byref(b), C.c_size_t(nbytes)) == 0
-    ex.enqueue_ptr(imgs.ctypes.data, 6, 480, 752, 752, 752 * 480, False)
-    ctx.set_stream(0)
-    ex.set_stream(0)
+    # default handles: the extractor and the context each own a stream; the call itself orders them
     ex.enqueue_ptr(imgs.ctypes.data, 6, 480, 752, 752, 752 * 480, False)
     ctx.stereo_orb_device(ex, 3, p, bufs[0].value, bufs[1].value, bufs[2].value)
+    with pytest.raises(so.SnakeOrbError):
+        ctx.stereo_orb_device(ex, 4, p, bufs[0].value, bufs[1].value, bufs[2].value)  # 8 images, 6 were enqueued
+    # the next enqueue is ordered behind the stereo kernel: it may overwrite the results only after they were read
+    ex.enqueue_ptr(warm.ctypes.data, 6, 480, 752, 752, 752 * 480, False)
+    ctx.check()
+    ex.check()
     rp = np.zeros((3, stride), np.float32)
     dp = np.zeros((3, stride), np.float32)
     nm = np.zeros(3, np.int32)
@@ -123,8 +130,6 @@ def test_stereo_device_path_equals_host_path(so, ctx, oracle):
         assert rp[i, :len(kl)].tobytes() == rp2.tobytes() and dp[i, :len(kl)].tobytes() == dp2.tobytes()
     for b in bufs:
         cudart.cudaFree(b)
-    ex.set_stream(None)
-    ctx.set_stream(None)
 
 
 def _c3(so, feats, seed, n_points):

@@ -1,6 +1,8 @@
 """GPU test of snk_match_knn2_noalloc, the kNN-2 entry point for callers that may not allocate device memory
 (see include/snakeorb.h). It is called through the C ABI and must return exactly what snk_match_knn2 returns
-(bit-equal records — the tolerance of every matcher test here is zero), on two calls in a row: the calls share one
+(bit-equal records — the tolerance of every matcher test here is zero) and what the CPU oracle's matchKnn2 returns
+(the two entry points share a kernel, so agreeing with each other alone would not catch a common fault), on two
+calls in a row: the calls share one
 fixed scratch array inside the library, so the second, smaller call runs on top of the first call's leftovers.
 
 The file name sorts last on purpose: with `pytest -x` every other test has already run when this one does."""
@@ -22,7 +24,10 @@ def _knn2_noalloc(so, d1, d2, device=0, stream=None):
 
 
 def test_knn2_noalloc_equals_knn2_on_two_calls_in_a_row():
+    import oracle_py as oracle
     import snakeorb as so
+
+    oracle.build()
 
     rng = np.random.default_rng(2024)
     ctx = so.Context()
@@ -37,6 +42,7 @@ def test_knn2_noalloc_equals_knn2_on_two_calls_in_a_row():
         assert rc == 0, so.lib().snk_last_error()
         want = ctx.matchKnn2(d1, d2)  # the existing, allocating entry point
         assert got.tobytes() == want.tobytes()
+        assert got.tobytes() == oracle.match_knn2(d1, d2).tobytes()  # BruteForceMatcher::matchKnn2 on the CPU
     # empty train set and single query behave like the existing entry point too
     rc, got = _knn2_noalloc(so, problems[0][0][:1], problems[0][1][:0])
     assert rc == 0 and got.tobytes() == ctx.matchKnn2(problems[0][0][:1], problems[0][1][:0]).tobytes()
