@@ -386,3 +386,141 @@ def features_in_area(frame, px, py, r):
     out = np.zeros(max(frame.n, 1), np.int32)
     c = lib().orc_features_in_area(C.byref(frame), C.c_double(px), C.c_double(py), C.c_float(r), _p(out))
     return out[:c].copy()
+
+
+# ---- the reference's own Snake matchers (oracle/_ref/libsnake_ref.so, built by the Makefile from the translation units
+# where they lie under /root/reference; see ref_snake_shim.cpp). Same arguments and results as the functions above. ----
+_snake = None
+
+
+def snake_ref():
+    """The compiled Snake matchers, or None when oracle/_ref/libsnake_ref.so was not built (no /root/reference)."""
+    global _snake
+    if _snake is None:
+        so = os.path.join(HERE, "_ref", "libsnake_ref.so")
+        if not os.path.exists(so):
+            return None
+        _snake = C.CDLL(so)
+    return _snake
+
+
+def ref_stereo_matching(rect_left, rect_right, bf, relaxed, levels, scale_factor, left, dl, right, dr):
+    """Preprocess::StereoMatching on raw keypoints (it rectifies them itself)."""
+    left = np.ascontiguousarray(left, KP64)
+    right = np.ascontiguousarray(right, KP64)
+    dl = np.ascontiguousarray(dl, np.uint64)
+    dr = np.ascontiguousarray(dr, np.uint64)
+    rp = np.zeros(len(left), np.float32)
+    dp = np.zeros(len(left), np.float32)
+    n = snake_ref().snkref_stereo_matching(C.byref(rect_left), C.byref(rect_right), C.c_double(bf), int(relaxed), levels,
+                                           C.c_double(scale_factor), _p(left), _p(dl), len(left), _p(right), _p(dr),
+                                           len(right), _p(rp), _p(dp))
+    return n, rp, dp
+
+
+def ref_stereo_from_rgbd(params, kp_un, depth_img):
+    kp_un = np.ascontiguousarray(kp_un, KP64)
+    rp = np.zeros(max(len(kp_un), 1), np.float32)
+    dp = np.zeros(max(len(kp_un), 1), np.float32)
+    n = snake_ref().snkref_stereo_from_rgbd(C.byref(params), _p(kp_un), len(kp_un), _p(depth_img), depth_img.shape[0],
+                                            depth_img.shape[1], C.c_size_t(depth_img.strides[0]), _p(rp), _p(dp))
+    return n, rp[:len(kp_un)], dp[:len(kp_un)]
+
+
+def ref_undistort_keypoints(rect, kps, rows, cols):
+    kps = np.ascontiguousarray(kps, KP64)
+    out = np.zeros(len(kps), KP64)
+    nrm = np.zeros((len(kps), 2), np.float64)
+    snake_ref().snkref_undistort_keypoints(C.byref(rect), _p(kps), len(kps), rows, cols, _p(out), _p(nrm))
+    return out, nrm
+
+
+def ref_search_projection_fine(frame, points, cam, pyr, th, ratio, threads=1):
+    pts = np.array(points, copy=True)
+    n = len(pts)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    bi = np.zeros(max(n, 1), np.int32)
+    bd = np.zeros(max(n, 1), np.int32)
+    vis = np.zeros(max(n, 1), np.uint8)
+    m = snake_ref().snkref_search_projection_fine(C.byref(frame), _p(pts), n, C.byref(cam), C.byref(pyr), C.c_float(th),
+                                                  C.c_float(ratio), _p(k2p), _p(bi), _p(bd), _p(vis), threads)
+    return m, k2p[:frame.n], bi[:n], bd[:n], vis[:n], pts
+
+
+def ref_search_projection_coarse(frame, points, cam, pyr, th, feature_error, motion, threads=1):
+    pts = np.ascontiguousarray(points)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    m = snake_ref().snkref_search_projection_coarse(C.byref(frame), _p(pts), len(pts), C.byref(cam), C.byref(pyr),
+                                                    C.c_float(th), feature_error, motion, _p(k2p), threads)
+    return m, k2p[:frame.n]
+
+
+def ref_search_projection_frame_to_kf(frame, points, cam, th, feature_error):
+    pts = np.ascontiguousarray(points)
+    k2p = np.zeros(max(frame.n, 1), np.int32)
+    m = snake_ref().snkref_search_projection_frame_to_kf(C.byref(frame), _p(pts), len(pts), C.byref(cam), C.c_float(th),
+                                                         feature_error, _p(k2p))
+    return m, k2p[:frame.n]
+
+
+def ref_match_bow(d1, d2, fv1, fv2, valid1, valid2, th, ratio):
+    d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+    d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+    m12 = np.zeros(max(len(d1), 1), np.int32)
+    m = snake_ref().snkref_match_bow(_p(d1), len(d1), _p(d2), len(d2), C.byref(fv1), C.byref(fv2), _p(valid1), _p(valid2),
+                                     th, C.c_float(ratio), _p(m12))
+    return m, m12[:len(d1)]
+
+
+def ref_fuse_search(kf, mask, points, cam, pyr, th, obs_factor, feature_th):
+    pts = np.ascontiguousarray(points)
+    n = len(pts)
+    ck, ci = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+    m = snake_ref().snkref_fuse_search(C.byref(kf), _p(mask) if mask is not None else None, _p(pts), n, C.byref(cam),
+                                       C.byref(pyr), C.c_float(th), C.c_float(obs_factor), feature_th, _p(ck), _p(ci))
+    return ck[:m].copy(), ci[:m].copy()
+
+
+def ref_fuse_loop(kf, skip, points, cam, th):
+    """LoopORBmatcher::Fuse, search and map edits: (nFused, feature index each point ends up observing or -1,
+    per keyframe feature 0 = its original point is still good / 1 = it went bad (replaced) / 2 = it had none)."""
+    pts = np.ascontiguousarray(points)
+    n = len(pts)
+    state = np.zeros(max(n, 1), np.int32)
+    bad = np.zeros(max(kf.n, 1), np.uint8)
+    m = snake_ref().snkref_fuse_loop(C.byref(kf), _p(skip) if skip is not None else None, _p(pts), n, C.byref(cam),
+                                     C.c_float(th), _p(state), _p(bad))
+    return m, state[:n], bad[:kf.n]
+
+
+def ref_search_triangulation_bow(kf1, np1, fv1, kf2, np2, fv2, E, cam, epi, fd):
+    pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+    E = np.ascontiguousarray(E, np.float64)
+    m = snake_ref().snkref_search_triangulation_bow(C.byref(kf1), _p(np1), C.byref(fv1), C.byref(kf2), _p(np2),
+                                                    C.byref(fv2), _p(E), C.byref(cam), C.c_float(epi), fd, _p(pairs))
+    return pairs[:m].copy()
+
+
+def ref_search_triangulation_project(kf1, np1, kf2, np2, grid, E, cam, epi, fd):
+    pairs = np.zeros((max(kf1.n, 1), 2), np.int32)
+    E = np.ascontiguousarray(E, np.float64)
+    grid = np.ascontiguousarray(grid, np.float64)
+    m = snake_ref().snkref_search_triangulation_project(C.byref(kf1), _p(np1), C.byref(kf2), _p(np2), _p(grid),
+                                                        grid.shape[0], grid.shape[1], _p(E), C.byref(cam),
+                                                        C.c_float(epi), fd, _p(pairs))
+    return pairs[:m].copy()
+
+
+def ref_match_prediction(desc_left, positions, right, radius, feature_error, threads=1):
+    d = np.ascontiguousarray(desc_left, np.uint64).reshape(-1, 4)
+    pos = np.array(positions, np.float64, copy=True)
+    matches = np.zeros(max(len(d), 1), np.int32)
+    m = snake_ref().snkref_match_prediction(_p(d), len(d), _p(pos), C.byref(right), C.c_float(radius), feature_error,
+                                            threads, _p(matches))
+    return m, matches[:len(d)], pos
+
+
+def ref_features_in_area(frame, px, py, r):
+    out = np.zeros(max(frame.n, 1), np.int32)
+    c = snake_ref().snkref_features_in_area(C.byref(frame), C.c_double(px), C.c_double(py), C.c_float(r), _p(out))
+    return out[:c].copy()
