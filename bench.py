@@ -164,6 +164,208 @@ def cpu_pairs_per_s(distinct, threads, budget_s, stereo_params_fn):
     return n / dt, n, kp / dt
 
 
+def pick_device(torch, dist, local_rank, world):
+    """Which GPU this rank drives. With as many visible GPUs as ranks (or one rank) it is LOCAL_RANK. With more visible
+    GPUs than ranks the box is probed first: on this pool's 8-GPU boxes the host-to-device rate differs between the two
+    halves of the box once several GPUs upload at the same time (tools/scratch/numa8.py), so the ranks try the low
+    block (rank r -> GPU r) and the high block (rank r -> GPU visible - world + r) with concurrent 64 MB uploads from
+    pinned memory and keep the block whose slowest link is faster. Returns (device index, probe record or None)."""
+    visible = torch.cuda.device_count()
+    if world == 1 or visible <= world:
+        return local_rank % max(visible, 1), None
+    import torch.distributed  # noqa: F401
+
+    rates = {}
+    for name, dev in (("low", local_rank), ("high", visible - world + local_rank)):
+        with torch.cuda.device(dev):
+            src = torch.empty(64 << 20, dtype=torch.uint8, pin_memory=True)
+            dst = torch.empty(64 << 20, dtype=torch.uint8, device=f"cuda:{dev}")
+            dst.copy_(src, non_blocking=True)
+            torch.cuda.synchronize(dev)
+            t = torch.zeros(1)
+            dist.all_reduce(t)  # gloo: all ranks start their uploads together
+            t0 = time.perf_counter()
+            for _ in range(8):
+                dst.copy_(src, non_blocking=True)
+            torch.cuda.synchronize(dev)
+            gbs = 8 * (64 << 20) / (time.perf_counter() - t0) / 1e9
+            allr = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
+            dist.all_gather(allr, torch.tensor([gbs], dtype=torch.float64))
+            rates[name] = [float(x) for x in allr]
+            del src, dst
+    pick = "high" if min(rates["high"]) > 1.05 * min(rates["low"]) else "low"
+    dev = local_rank if pick == "low" else visible - world + local_rank
+    return dev, {"visible_gpus": visible, "picked": pick, "h2d_gbs_per_gpu_low_block": rates["low"],
+                 "h2d_gbs_per_gpu_high_block": rates["high"]}
+
+
+class HostArray:
+    """Page-locked host array. One rank: plain pinned memory. Several ranks: one array in /dev/shm shared by all of
+    them (the sequence and its results exist once on the box, as they would for a real dataset), registered with the
+    CUDA driver in every process so copies to and from it are asynchronous."""
+
+    def __init__(self, torch, name, shape, np_dtype, world, rank, barrier):
+        import ctypes as C
+
+        self.nbytes = int(np.prod(shape)) * np.dtype(np_dtype).itemsize
+        self.path, self.rank, self._reg = None, rank, False
+        if world == 1:
+            self._t = torch.empty(self.nbytes, dtype=torch.uint8, pin_memory=True)
+            self.np = self._t.numpy().view(np_dtype).reshape(shape)
+        else:
+            self.path = f"/dev/shm/snkbench_{os.environ.get('MASTER_PORT', '0')}_{name}"
+            if rank == 0:
+                import shutil
+
+                if shutil.disk_usage("/dev/shm").free < self.nbytes + (1 << 28):
+                    raise SystemExit(f"/dev/shm has no room for {self.nbytes} bytes ({name})")
+                np.memmap(self.path, dtype=np.uint8, mode="w+", shape=(self.nbytes,)).flush()
+            barrier()
+            self.np = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(self.nbytes,)).view(np_dtype).reshape(shape)
+            self._cudart = C.CDLL("libcudart.so")
+            rc = self._cudart.cudaHostRegister(C.c_void_p(self.np.ctypes.data), C.c_size_t(self.nbytes), 1)  # portable
+            if rc != 0:
+                raise SystemExit(f"cudaHostRegister({name}, {self.nbytes} bytes) failed with {rc}")
+            self._reg = True
+        self.ptr = self.np.ctypes.data
+
+    def close(self, barrier):
+        import ctypes as C
+
+        if self._reg:
+            self._cudart.cudaHostUnregister(C.c_void_p(self.ptr))
+        if self.path:
+            barrier()
+            if self.rank == 0 and os.path.exists(self.path):
+                os.unlink(self.path)
+
+
+def c5_frame(distinct, f, out):
+    """Pair f of the C5 sequence: one of the distinct synthetic pairs, circularly shifted by a frame-dependent amount in
+    both axes (the same shift for left and right, so the stereo geometry is kept): every frame has different bytes."""
+    nd = len(distinct) // 2
+    src, rep = f % nd, f // nd
+    for e in range(2):
+        out[e] = np.roll(distinct[2 * src + e], (7 * rep, 3 * rep), axis=(0, 1))
+
+
+def run_c5(args, env):
+    """BASELINE.json configs[4]: the whole sequence, sharded by frame over the ranks through the shared chunk queue."""
+    import ctypes as C
+    import hashlib
+
+    torch, dist, snakeorb = env["torch"], env["dist"], env["snakeorb"]
+    rank, world, store, barrier, Lane, cap = env["rank"], env["world"], env["store"], env["barrier"], env["Lane"], env["cap"]
+    ChunkQueue, local_rank, numa, config = env["ChunkQueue"], env["local_rank"], env["numa"], dict(env["config"])
+    F, CPc = args.frames, args.c5_chunk
+    seq = HostArray(torch, "seq", (F, 2, H, W), np.uint8, world, rank, barrier)
+    o_kps = HostArray(torch, "kps", (2 * F, cap, 24), np.uint8, world, rank, barrier)
+    o_desc = HostArray(torch, "desc", (2 * F, cap, 4), np.uint64, world, rank, barrier)
+    o_cnt = HostArray(torch, "cnt", (2 * F,), np.int32, world, rank, barrier)
+    o_rp = HostArray(torch, "rp", (F, cap), np.float32, world, rank, barrier)
+    o_dp = HostArray(torch, "dp", (F, cap), np.float32, world, rank, barrier)
+    o_nm = HostArray(torch, "nm", (F,), np.int32, world, rank, barrier)
+    outs = (o_kps, o_desc, o_cnt, o_rp, o_dp, o_nm)
+    distinct = synth_pairs(16, seed0=10000)
+    for f in range(rank, F, world):  # every rank writes its share of the frames
+        c5_frame(distinct, f, seq.np[f])
+    barrier()
+    lanes = [Lane(CPc) for _ in range(args.lanes)]
+    dev_seq = torch.empty((F, 2, H, W), dtype=torch.uint8, device="cuda")  # 2.7 GB: the sequence resident in HBM
+    rc = C.CDLL("libcudart.so").cudaMemcpy(C.c_void_p(dev_seq.data_ptr()), C.c_void_p(seq.ptr), C.c_size_t(seq.nbytes), 1)
+    assert rc == 0
+
+    def one_pass(key, on_device):
+        for o in outs:
+            if rank == 0:
+                o.np.reshape(-1).view(np.uint8)[:] = 0xCD  # poison: a frame nobody processed shows in the digest
+        barrier()
+        q = ChunkQueue(F, CPc, store=store, key=key)
+        base = dev_seq.data_ptr() if on_device else seq.ptr
+        barrier()
+        t0 = time.perf_counter()
+        i = mine = 0
+        while True:
+            lanes[i % len(lanes)].wait()
+            c = q.pull()
+            if c is None:
+                break
+            lo, hi = q.frames(c)
+            lanes[i % len(lanes)].run(base + lo * 2 * W * H, on_device, hi - lo, o_kps.ptr + 2 * lo * cap * 24, o_desc.ptr + 2 * lo * cap * 32,
+                                      o_cnt.ptr + 2 * lo * 4, o_rp.ptr + lo * cap * 4, o_dp.ptr + lo * cap * 4, o_nm.ptr + lo * 4)
+            i += 1
+            mine += 1
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        barrier()
+        return dt, mine
+
+    def digest():
+        """sha256 over the per-frame results in frame order: keypoints and descriptors of both images trimmed to their
+        counts, right_points / depth of the left image's keypoints, the match count."""
+        h = hashlib.sha256()
+        cnt = o_cnt.np
+        for f in range(F):
+            for e in range(2):
+                n = int(cnt[2 * f + e])
+                h.update(o_kps.np[2 * f + e, :n].tobytes())
+                h.update(o_desc.np[2 * f + e, :n].tobytes())
+            n = int(cnt[2 * f])
+            h.update(o_rp.np[f, :n].tobytes())
+            h.update(o_dp.np[f, :n].tobytes())
+            h.update(o_nm.np[f:f + 1].tobytes())
+        return h.hexdigest(), int(cnt.sum()), int(o_nm.np.sum())
+
+    for w in range(max(args.warmup, 1)):
+        one_pass(f"c5_warm_{w}", False)
+    res = {}
+    for mode, on_device in (("host", False), ("device", True)):
+        times, chunks = [], None
+        for k in range(max(args.steps, 1)):
+            dt, mine = one_pass(f"c5_{mode}_{k}", on_device)
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            g = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dist.all_gather(g, torch.tensor([mine], dtype=torch.int64, device="cuda"))
+                chunks = [int(x) for x in g]
+            else:
+                chunks = [mine]
+            times.append(float(t))
+        res[mode] = (times, chunks, digest() if rank == 0 else None)
+    for ln in lanes:
+        ln.ex.check()
+        ln.cx.check()
+    if rank == 0:
+        (th, ch, (dg_h, nkp, nmatch)), (td, cd, (dg_d, _, _)) = res["host"], res["device"]
+        assert dg_h == dg_d, "host-fed and device-resident passes returned different results"
+        K = len(th)
+        config.update({"workload": f"C5 {F}-pair synthetic EuRoC-length stereo sequence (distinct frames), ORB extract x2 (1200 kp, 8 "
+                                   f"levels, 1.2, FAST 20/7) + stereo row search per pair; frames sharded over {world} GPU(s) in "
+                                   f"chunks of {CPc} pairs from a shared queue; results in host memory in frame order",
+                       "pairs_in_sequence": F, "chunk_pairs": CPc,
+                       "l2": f"{seq.nbytes / 1e9:.2f} GB of distinct input per pass (>> 126 MB L2)"})
+        config.pop("pairs_per_step_per_gpu", None), config.pop("images_per_step_per_gpu", None)
+        line = {"metric": METRIC, "value": F * K / sum(td), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": max(args.warmup, 1),
+                "ms_per_step": sum(td) / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
+                "data": "synthetic", "config": config, "sequence_wall_s_device_resident": td, "sequence_wall_s_host_fed": th,
+                "keypoints_per_sequence": nkp, "stereo_matches_per_sequence": nmatch, "results_sha256": dg_h,
+                "chunks_per_rank_device": cd,
+                "e2e": {"value": F * K / sum(th), "unit": "frames/s", "h2d_bytes_per_step": seq.nbytes,
+                        "d2h_bytes_per_step": sum(o.nbytes for o in outs), "ms_per_step": sum(th) / K * 1e3,
+                        "chunks_per_rank": ch, "host_affinity": numa, "device_choice": env["h2d_probe"],
+                        "pipeline": f"{len(lanes)} streams/handles per rank, chunks of {CPc} pairs from a queue shared by the ranks"},
+                # per chunk: 7 resize levels, FAST, quadtree, blur, describe, stereo
+                "gpu_launches": 12 * ((F + CPc - 1) // CPc) * 2 * K}
+        print(json.dumps(line))
+    for o in (seq,) + outs:
+        o.close(barrier)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -175,6 +377,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-next", action="store_true", help="skip the side measurements of the rows after the extractor")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
+                    help="c2 (default, the contract's line): one resident batch per step, weak scaling. c5: BASELINE.json "
+                         "configs[4] as written - a 3680-pair sequence of distinct frames in pinned host memory, sharded by "
+                         "frame over the ranks, results back in host memory in frame order, wall clock for the whole "
+                         "sequence (strong scaling); --steps / --warmup count passes over the sequence")
+    ap.add_argument("--frames", type=int, default=3680, help="c5: stereo pairs in the sequence")
+    ap.add_argument("--c5-chunk", type=int, default=128, help="c5: stereo pairs per chunk of the shared queue")
     ap.add_argument("--chunks", type=int, default=2, help="e2e path: chunks per step (sweep on B200, 55 GB/s link, chunks/lanes: 1/2 64.3k, 2/3 73.0k, 2/6 72.9k, 4/4 66.4k, 4/6 66.8k, 8/8 62.3k pairs/s)")
     ap.add_argument("--device-lanes", type=int, default=1, help="device-resident path: the step's batch cut into this many parts, each on its own handle and stream, all in flight together (measured: 1: 3.33 ms/step, 2: 4.02, 4: 4.03, 8: 4.07 - kernels with different shared-memory carve-outs do not share an SM, parts that start together only get in each other's way)")
     ap.add_argument("--depth", type=int, default=2, help="e2e path: steps in flight (pinned result sets); the host waits for step s-depth+1")
@@ -228,9 +437,10 @@ def main():
         v = per_step * K / dt
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": K,
                 "warmup": Wm, "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": dict(config, pairs_per_step=per_step),
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,  # the same keys as the CUDA arm
                 "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
-                                 "sample": f"{per_step} stereo pairs per step x {K} steps, one extractor per thread"},
+                                 "sample": f"a bounded sample of the step: {per_step} of its {args.pairs} stereo pairs per step "
+                                           f"x {K} steps, one extractor per thread"},
                 "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line))
@@ -243,7 +453,11 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (libsnakeorb has no CPU fallback)")
-    torch.cuda.set_device(local_rank)
+    if world > 1:
+        # gloo carries the control plane (device choice, chunk queue statistics), NCCL the timing barrier / reduction
+        dist.init_process_group("cpu:gloo,cuda:nccl")
+    device_index, h2d_probe = pick_device(torch, dist, local_rank, world)
+    torch.cuda.set_device(device_index)
     # keep this rank's host threads and its pinned buffers (first touch) on the NUMA node of its GPU: with several ranks
     # per box the host-to-device copies otherwise cross the socket interconnect
     numa = "unset"
@@ -251,16 +465,22 @@ def main():
         import pynvml
 
         pynvml.nvmlInit()
-        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
-        numa = "cpu affinity of GPU %d (%d cpus)" % (local_rank, len(os.sched_getaffinity(0)))
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(device_index))
+        numa = "cpu affinity of GPU %d (%d cpus)" % (device_index, len(os.sched_getaffinity(0)))
     except Exception as exc:  # noqa: BLE001
         numa = "unset (%s)" % type(exc).__name__
+    store = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from torch.distributed.distributed_c10d import _get_default_store
+
+        store = _get_default_store()
+    local_rank = device_index  # everything below addresses the chosen device
+
+    _bar = torch.zeros(1, device="cuda")
 
     def barrier():
         if world > 1:
-            dist.barrier()
+            dist.all_reduce(_bar)  # NCCL, on this rank's device
         torch.cuda.synchronize()
 
     P, NI = args.pairs, 2 * args.pairs
@@ -313,68 +533,69 @@ def main():
         for st, _, _ in dev_lanes:
             tstream.wait_stream(st)
 
-    # ---- end-to-end path: host (pinned) buffers in and out, the batch cut into chunks that alternate between two
-    # extractor handles on two streams so that the H2D copy of chunk k+1 and the D2H of chunk k-1 overlap chunk k's
-    # kernels (every byte still crosses PCIe inside the timed region)
+    # ---- end-to-end path: host (pinned) buffers in and out. The step's batch is cut into chunks; a chunk runs on one of
+    # `--lanes` extractor handles / streams (H2D, all kernels, D2H on that stream, no host wait in between), so the upload
+    # of one chunk, the kernels of another and the download of a third overlap; every byte still crosses PCIe inside
+    # the timed region. Which rank takes which chunk is decided by a queue shared by all ranks (snakeorb.sharding
+    # .ChunkQueue): a rank asks for the next chunk when one of its lanes is free, so GPUs behind a slower host link take
+    # fewer chunks instead of holding the whole job back.
     import ctypes as C
 
+    from snakeorb.sharding import ChunkQueue
+
+    cudart = C.CDLL("libcudart.so")
     NCH = args.chunks if (NI % (2 * args.chunks) == 0) else 1
     CI, CP = NI // NCH, P // NCH
     DEPTH = max(2, args.depth)
-    # DEPTH sets of pinned result buffers: step s+1 is enqueued while the results of step s are still arriving (a streaming
-    # consumer reads set s % 2 while set (s + 1) % 2 is being filled)
-    h_kps = torch.empty((DEPTH, NI, cap, 24), dtype=torch.uint8, pin_memory=True)
-    h_desc = torch.empty((DEPTH, NI, cap, 4), dtype=torch.int64, pin_memory=True)
-    h_cnt = torch.empty((DEPTH, NI), dtype=torch.int32, pin_memory=True)
-    h_rp = torch.empty((DEPTH, P, cap), dtype=torch.float32, pin_memory=True)
-    h_dp = torch.empty((DEPTH, P, cap), dtype=torch.float32, pin_memory=True)
-    h_nm = torch.empty((DEPTH, P), dtype=torch.int32, pin_memory=True)
-    e2e_lanes = []
-    if not args.no_e2e:
-        for _ in range(args.lanes):
-            st = torch.cuda.Stream()
-            exc = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=CI, device=local_rank)
-            cxc = snakeorb.Context(device=local_rank)
-            exc.set_stream(st.cuda_stream)
-            cxc.set_stream(st.cuda_stream)
-            e2e_lanes.append((st, exc, cxc, torch.empty((CP, cap), dtype=torch.float32, device="cuda"),
-                              torch.empty((CP, cap), dtype=torch.float32, device="cuda"),
-                              torch.empty((CP,), dtype=torch.int32, device="cuda")))
+    NSLOT = DEPTH * NCH  # pinned result slots of this rank, reused round robin (a streaming consumer reads slot i while i+1.. fill)
+    h_kps = torch.empty((NSLOT, CI, cap, 24), dtype=torch.uint8, pin_memory=True)
+    h_desc = torch.empty((NSLOT, CI, cap, 4), dtype=torch.int64, pin_memory=True)
+    h_cnt = torch.empty((NSLOT, CI), dtype=torch.int32, pin_memory=True)
+    h_rp = torch.empty((NSLOT, CP, cap), dtype=torch.float32, pin_memory=True)
+    h_dp = torch.empty((NSLOT, CP, cap), dtype=torch.float32, pin_memory=True)
+    h_nm = torch.empty((NSLOT, CP), dtype=torch.int32, pin_memory=True)
 
-    def e2e_enqueue(k, par, lane):
-        st, exc, cxc, rpc, dpc, nmc = e2e_lanes[lane]
-        exc.enqueue_ptr(host.data_ptr() + k * CI * W * H, CI, H, W, W, W * H, False)
-        cxc.stereo_orb_device(exc, CP, sp, rpc.data_ptr(), dpc.data_ptr(), nmc.data_ptr())
-        with torch.cuda.stream(st):
-            h_rp[par, k * CP:(k + 1) * CP].copy_(rpc, non_blocking=True)
-            h_dp[par, k * CP:(k + 1) * CP].copy_(dpc, non_blocking=True)
-            h_nm[par, k * CP:(k + 1) * CP].copy_(nmc, non_blocking=True)
+    class Lane:
+        def __init__(self, max_pairs):
+            self.st = torch.cuda.Stream()
+            self.ex = snakeorb.ORBExtractor(NFEAT, SCALE, NLEVELS, TH, THMIN, max_batch=2 * max_pairs, device=local_rank)
+            self.cx = snakeorb.Context(device=local_rank)
+            self.ex.set_stream(self.st.cuda_stream)
+            self.cx.set_stream(self.st.cuda_stream)
+            self.rp = torch.empty((max_pairs, cap), dtype=torch.float32, device="cuda")
+            self.dp = torch.empty((max_pairs, cap), dtype=torch.float32, device="cuda")
+            self.nm = torch.empty((max_pairs,), dtype=torch.int32, device="cuda")
+            self.ev = None
 
-    def e2e_fetch(k, par, lane):
-        _, exc, _, _, _, _ = e2e_lanes[lane]
-        snakeorb._check(snakeorb.lib().snk_orb_fetch_async(exc.h, C.c_void_p(h_kps[par].data_ptr() + k * CI * cap * 24),
-                                                           C.c_void_p(h_desc[par].data_ptr() + k * CI * cap * 32), cap,
-                                                           C.c_void_p(h_cnt[par].data_ptr() + k * CI * 4)))
+        def wait(self):
+            if self.ev is not None:
+                self.ev.synchronize()
 
-    e2e_done = [[] for _ in range(DEPTH)]  # per result set: one event per lane, recorded behind the set's last copy
+        def run(self, src_ptr, on_device, n_pairs, o_kps, o_desc, o_cnt, o_rp, o_dp, o_nm):
+            """One chunk: images at src_ptr -> keypoints, descriptors, counts, right_points, depth, match counts at
+            the given host addresses. Everything is queued on the lane's stream; self.ev marks the end."""
+            self.ex.enqueue_ptr(src_ptr, 2 * n_pairs, H, W, W, W * H, on_device)
+            self.cx.stereo_orb_device(self.ex, n_pairs, sp, self.rp.data_ptr(), self.dp.data_ptr(), self.nm.data_ptr())
+            snakeorb._check(snakeorb.lib().snk_orb_fetch_async(self.ex.h, C.c_void_p(o_kps), C.c_void_p(o_desc), cap, C.c_void_p(o_cnt)))
+            s_ = C.c_void_p(self.st.cuda_stream)
+            for dst, src, nb in ((o_rp, self.rp, 4 * n_pairs * cap), (o_dp, self.dp, 4 * n_pairs * cap), (o_nm, self.nm, 4 * n_pairs)):
+                rc = cudart.cudaMemcpyAsync(C.c_void_p(dst), C.c_void_p(src.data_ptr()), C.c_size_t(nb), 2, s_)
+                assert rc == 0, "cudaMemcpyAsync failed"
+            self.ev = torch.cuda.Event()
+            self.ev.record(self.st)
 
-    def step_e2e(s):
-        # every chunk: H2D, kernels, D2H on its lane's stream, no host wait in between. The host then waits for the
-        # PREVIOUS step's results (set (s - 1) % 2), so the copies of consecutive steps overlap like a stream of frames.
-        par = s % DEPTH
-        for k in range(NCH):
-            # lanes are taken round robin over the stream of chunks: with more lanes than chunks a chunk's upload
-            # does not queue behind the same lane's previous step
-            lane = (s * NCH + k) % len(e2e_lanes)
-            e2e_enqueue(k, par, lane)
-            e2e_fetch(k, par, lane)
-        e2e_done[par] = []
-        for st, *_ in e2e_lanes:
-            ev = torch.cuda.Event()
-            ev.record(st)
-            e2e_done[par].append(ev)
-        for ev in e2e_done[(s + 1) % DEPTH]:  # the oldest step still in flight
-            ev.synchronize()
+    e2e_lanes = [Lane(CP) for _ in range(args.lanes)] if not args.no_e2e else []
+    slot_slice = [-1] * NSLOT  # which slice of the batch each result slot holds (for the check after the run)
+
+    def e2e_chunk(i, k):
+        """Local chunk number i (lane and result slot round robin) processes slice k of this rank's pinned batch."""
+        lane, slot = e2e_lanes[i % len(e2e_lanes)], i % NSLOT
+        slot_slice[slot] = k
+        lane.run(host.data_ptr() + k * CI * W * H, False, CP, h_kps[slot].data_ptr(), h_desc[slot].data_ptr(), h_cnt[slot].data_ptr(),
+                 h_rp[slot].data_ptr(), h_dp[slot].data_ptr(), h_nm[slot].data_ptr())
+
+    if args.workload == "c5":
+        return run_c5(args, locals())
 
     # ---- device-resident timing --------------------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
@@ -526,25 +747,48 @@ def main():
             next_rows["side_measurement_error"] = repr(exc)[:200]
 
     # ---- end-to-end timing (host buffers) ---------------------------------------------------------------------------
-    e2e = None
+    e2e, my_chunks = None, 0
     if not args.no_e2e:
-        n_warm = DEPTH * max(1, -(-len(e2e_lanes) // NCH))  # every lane and every result set used at least once
-        for i in range(n_warm):
-            step_e2e(i)
+        i = 0
+        for _ in range(max(NSLOT, len(e2e_lanes), 3 * NCH)):  # warm-up: every lane and every result slot used at least once
+            e2e_lanes[i % len(e2e_lanes)].wait()
+            e2e_chunk(i, i % NCH)
+            i += 1
+        torch.cuda.synchronize()
+        # the timed job: K steps' worth of chunks for every rank, handed out by the shared queue
+        queue = ChunkQueue(world * args.steps * P, CP, store=store, key="snk_e2e_chunks")
         barrier()
         tw0 = time.perf_counter()
-        for i in range(n_warm, n_warm + args.steps):
-            step_e2e(i)
+        while True:
+            e2e_lanes[i % len(e2e_lanes)].wait()  # ask for work only when a lane is free
+            c = queue.pull()
+            if c is None:
+                break
+            e2e_chunk(i, c % NCH)
+            i += 1
+            my_chunks += 1
         torch.cuda.synchronize()
-        e2e = (time.perf_counter() - tw0) * 1e3  # host wall clock: the last fetch returns when the results are in host memory
+        e2e = (time.perf_counter() - tw0) * 1e3  # host wall clock: the results of this rank's last chunk are in host memory
         barrier()
         # the end-to-end path must deliver the same results as the device-resident one
-        for par in range(DEPTH):
-            assert int(h_cnt[par].sum()) == n_kp_step and int(h_nm[par].sum()) == n_match_step, "e2e results differ from the device path"
+        cnt_t, nm_t = torch.from_numpy(cnt_host), nm.cpu()
+        for slot in range(NSLOT):
+            k = slot_slice[slot]
+            if k < 0:
+                continue
+            assert int(h_cnt[slot].sum()) == int(cnt_t[k * CI:(k + 1) * CI].sum()) and \
+                int(h_nm[slot].sum()) == int(nm_t[k * CP:(k + 1) * CP].sum()), "e2e results differ from the device path"
+        for ln in e2e_lanes:
+            ln.ex.check()  # device-side fault flags of the asynchronous path
+            ln.cx.check()
 
     t = torch.tensor([ms, e2e if e2e is not None else 0.0], dtype=torch.float64, device="cuda")
+    chunks_per_rank = [my_chunks]
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        g = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+        dist.all_gather(g, torch.tensor([my_chunks], dtype=torch.int64, device="cuda"))
+        chunks_per_rank = [int(x) for x in g]
     ms_max, e2e_max = float(t[0]), float(t[1])
     value = world * P * args.steps / (ms_max * 1e-3)
     kp_per_s = world * n_kp_step * args.steps / (ms_max * 1e-3)
@@ -613,7 +857,8 @@ def main():
             d2h = NI * cap * (24 + 32) + NI * 4 + P * cap * 8 + P * 4 + 4
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
-                           "host_affinity": numa, "pipeline": f"{NCH} chunks per step, the stream of chunks round robin over {len(e2e_lanes)} streams/handles (copy-compute overlap); the host waits for step s-1 while step s is in flight (two pinned result sets)"}
+                           "host_affinity": numa, "chunks_per_rank": chunks_per_rank, "device_choice": h2d_probe,
+                           "pipeline": f"chunks of {CP} pairs ({NCH} per step), handed out to the ranks by a shared queue; on a rank the chunks go round robin over {len(e2e_lanes)} streams/handles (copy-compute overlap), a rank asks for the next chunk when a lane is free; {NSLOT} pinned result slots per rank"}
         if next_rows is not None:
             line["next_rows"] = next_rows
         if not args.no_cpu:

@@ -86,6 +86,53 @@ def test_two_gloo_ranks_equal_single_process(tmp_path, oracle):
     assert float(np.load(tmp_path / "tmax.npy")[0]) == 11.0
 
 
+def _queue_worker(rank, world, port, n_frames, chunk, out_dir):
+    for p in (ROOT, os.path.join(ROOT, "snake-slam_b200")):
+        sys.path.insert(0, p)
+    import time
+
+    import torch.distributed as dist
+    from torch.distributed.distributed_c10d import _get_default_store
+
+    from snakeorb.sharding import ChunkQueue
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    q = ChunkQueue(n_frames, chunk, store=_get_default_store(), key="test_queue")
+    mine = []
+    while True:
+        c = q.pull()
+        if c is None:
+            break
+        mine.append(c)
+        time.sleep(0.002 * (1 + 3 * rank))  # ranks of different speed: the faster one ends up with more chunks
+    np.save(os.path.join(out_dir, f"chunks_{rank}.npy"), np.array(mine, np.int64))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_chunk_queue_hands_out_every_chunk_once_across_ranks(tmp_path):
+    """The dynamic frame assignment of bench.py's end-to-end path: two gloo ranks of different speed pull chunks of a
+    3680-frame sequence from one store-backed counter; every chunk is taken exactly once, the faster rank takes more,
+    and the chunk -> frame range map covers the sequence in order."""
+    import torch.multiprocessing as mp
+
+    from snakeorb.sharding import ChunkQueue
+
+    n_frames, chunk, world, port = 3680, 128, 2, 31000 + os.getpid() % 2000
+    mp.spawn(_queue_worker, args=(world, port, n_frames, chunk, str(tmp_path)), nprocs=world, join=True)
+    got = [np.load(tmp_path / f"chunks_{r}.npy") for r in range(world)]
+    allc = np.sort(np.concatenate(got))
+    q = ChunkQueue(n_frames, chunk)
+    assert q.n_chunks == 29 and list(allc) == list(range(29))
+    assert len(got[0]) > len(got[1]) > 0
+    ranges = [q.frames(c) for c in range(q.n_chunks)]
+    assert ranges[0] == (0, 128) and ranges[-1] == (3584, 3680) and all(ranges[i][1] == ranges[i + 1][0] for i in range(28))
+    # one process, no store: a plain counter
+    assert [q.pull() for _ in range(31)] == list(range(29)) + [None, None]
+    with pytest.raises(ValueError):
+        ChunkQueue(10, 0)
+
+
 CONTRACT_KEYS = ["metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
                  "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches"]
 
