@@ -164,39 +164,45 @@ def cpu_pairs_per_s(distinct, threads, budget_s, stereo_params_fn):
     return n / dt, n, kp / dt
 
 
+def upload_probe(torch, dist, dev, world):
+    """GB/s of 8 x 64 MB pinned-host -> device copies on GPU `dev` while every other rank does the same on its GPU
+    (the ranks start together). Returns the list of all ranks' rates."""
+    with torch.cuda.device(dev):
+        src = torch.empty(64 << 20, dtype=torch.uint8, pin_memory=True)
+        dst = torch.empty(64 << 20, dtype=torch.uint8, device=f"cuda:{dev}")
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.all_reduce(torch.zeros(1))  # gloo: a common starting line
+        t0 = time.perf_counter()
+        for _ in range(8):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        gbs = 8 * (64 << 20) / (time.perf_counter() - t0) / 1e9
+    if world == 1:
+        return [gbs]
+    allr = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(allr, torch.tensor([gbs], dtype=torch.float64))
+    return [float(x) for x in allr]
+
+
 def pick_device(torch, dist, local_rank, world):
-    """Which GPU this rank drives. With as many visible GPUs as ranks (or one rank) it is LOCAL_RANK. With more visible
-    GPUs than ranks the box is probed first: on this pool's 8-GPU boxes the host-to-device rate differs between the two
-    halves of the box once several GPUs upload at the same time (tools/scratch/numa8.py), so the ranks try the low
-    block (rank r -> GPU r) and the high block (rank r -> GPU visible - world + r) with concurrent 64 MB uploads from
-    pinned memory and keep the block whose slowest link is faster. Returns (device index, probe record or None)."""
+    """Which GPU this rank drives, and how fast the ranks can upload when all of them do (the end-to-end ceiling of
+    the box). With as many visible GPUs as ranks (or one rank) the GPU is LOCAL_RANK. With more visible GPUs than ranks
+    the box is probed: on this pool's 8-GPU boxes the host-to-device rate differs between the two halves of the box once
+    several GPUs upload at the same time (tools/scratch/numa8.py), so the ranks try the low block (rank r -> GPU r) and
+    the high block (rank r -> GPU visible - world + r) and keep the block whose slowest link is faster.
+    Returns (device index, probe record)."""
     visible = torch.cuda.device_count()
     if world == 1 or visible <= world:
-        return local_rank % max(visible, 1), None
-    import torch.distributed  # noqa: F401
-
-    rates = {}
-    for name, dev in (("low", local_rank), ("high", visible - world + local_rank)):
-        with torch.cuda.device(dev):
-            src = torch.empty(64 << 20, dtype=torch.uint8, pin_memory=True)
-            dst = torch.empty(64 << 20, dtype=torch.uint8, device=f"cuda:{dev}")
-            dst.copy_(src, non_blocking=True)
-            torch.cuda.synchronize(dev)
-            t = torch.zeros(1)
-            dist.all_reduce(t)  # gloo: all ranks start their uploads together
-            t0 = time.perf_counter()
-            for _ in range(8):
-                dst.copy_(src, non_blocking=True)
-            torch.cuda.synchronize(dev)
-            gbs = 8 * (64 << 20) / (time.perf_counter() - t0) / 1e9
-            allr = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
-            dist.all_gather(allr, torch.tensor([gbs], dtype=torch.float64))
-            rates[name] = [float(x) for x in allr]
-            del src, dst
+        dev = local_rank % max(visible, 1)
+        return dev, {"visible_gpus": visible, "picked": "rank order", "h2d_gbs_per_gpu": upload_probe(torch, dist, dev, world)}
+    rates = {name: upload_probe(torch, dist, dev, world)
+             for name, dev in (("low", local_rank), ("high", visible - world + local_rank))}
     pick = "high" if min(rates["high"]) > 1.05 * min(rates["low"]) else "low"
     dev = local_rank if pick == "low" else visible - world + local_rank
-    return dev, {"visible_gpus": visible, "picked": pick, "h2d_gbs_per_gpu_low_block": rates["low"],
-                 "h2d_gbs_per_gpu_high_block": rates["high"]}
+    return dev, {"visible_gpus": visible, "picked": pick + " block", "h2d_gbs_per_gpu": rates[pick],
+                 "h2d_gbs_per_gpu_other_block": rates["high" if pick == "low" else "low"]}
 
 
 class HostArray:
@@ -270,28 +276,29 @@ def run_c5(args, env):
     for f in range(rank, F, world):  # every rank writes its share of the frames
         c5_frame(distinct, f, seq.np[f])
     barrier()
-    lanes = [Lane(CPc) for _ in range(args.lanes)]
+    DCH = max(CPc, 256)  # the device-resident pass has no upload to hide: larger chunks, two lanes
+    lanes = [Lane(DCH) for _ in range(args.lanes)]
     dev_seq = torch.empty((F, 2, H, W), dtype=torch.uint8, device="cuda")  # 2.7 GB: the sequence resident in HBM
     rc = C.CDLL("libcudart.so").cudaMemcpy(C.c_void_p(dev_seq.data_ptr()), C.c_void_p(seq.ptr), C.c_size_t(seq.nbytes), 1)
     assert rc == 0
 
-    def one_pass(key, on_device):
+    def one_pass(key, on_device, chunk, nlanes):
         for o in outs:
             if rank == 0:
                 o.np.reshape(-1).view(np.uint8)[:] = 0xCD  # poison: a frame nobody processed shows in the digest
         barrier()
-        q = ChunkQueue(F, CPc, store=store, key=key)
+        q = ChunkQueue(F, chunk, store=store, key=key)
         base = dev_seq.data_ptr() if on_device else seq.ptr
         barrier()
         t0 = time.perf_counter()
         i = mine = 0
         while True:
-            lanes[i % len(lanes)].wait()
+            lanes[i % nlanes].wait()
             c = q.pull()
             if c is None:
                 break
             lo, hi = q.frames(c)
-            lanes[i % len(lanes)].run(base + lo * 2 * W * H, on_device, hi - lo, o_kps.ptr + 2 * lo * cap * 24, o_desc.ptr + 2 * lo * cap * 32,
+            lanes[i % nlanes].run(base + lo * 2 * W * H, on_device, hi - lo, o_kps.ptr + 2 * lo * cap * 24, o_desc.ptr + 2 * lo * cap * 32,
                                       o_cnt.ptr + 2 * lo * 4, o_rp.ptr + lo * cap * 4, o_dp.ptr + lo * cap * 4, o_nm.ptr + lo * 4)
             i += 1
             mine += 1
@@ -317,12 +324,13 @@ def run_c5(args, env):
         return h.hexdigest(), int(cnt.sum()), int(o_nm.np.sum())
 
     for w in range(max(args.warmup, 1)):
-        one_pass(f"c5_warm_{w}", False)
+        one_pass(f"c5_warm_{w}", False, CPc, len(lanes))
+        one_pass(f"c5_warmd_{w}", True, DCH, min(2, len(lanes)))
     res = {}
     for mode, on_device in (("host", False), ("device", True)):
         times, chunks = [], None
         for k in range(max(args.steps, 1)):
-            dt, mine = one_pass(f"c5_{mode}_{k}", on_device)
+            dt, mine = one_pass(f"c5_{mode}_{k}", on_device, DCH if on_device else CPc, min(2, len(lanes)) if on_device else len(lanes))
             t = torch.tensor([dt], dtype=torch.float64, device="cuda")
             g = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
             if world > 1:
@@ -343,7 +351,7 @@ def run_c5(args, env):
         config.update({"workload": f"C5 {F}-pair synthetic EuRoC-length stereo sequence (distinct frames), ORB extract x2 (1200 kp, 8 "
                                    f"levels, 1.2, FAST 20/7) + stereo row search per pair; frames sharded over {world} GPU(s) in "
                                    f"chunks of {CPc} pairs from a shared queue; results in host memory in frame order",
-                       "pairs_in_sequence": F, "chunk_pairs": CPc,
+                       "pairs_in_sequence": F, "chunk_pairs": CPc, "chunk_pairs_device_resident": DCH,
                        "l2": f"{seq.nbytes / 1e9:.2f} GB of distinct input per pass (>> 126 MB L2)"})
         config.pop("pairs_per_step_per_gpu", None), config.pop("images_per_step_per_gpu", None)
         line = {"metric": METRIC, "value": F * K / sum(td), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": max(args.warmup, 1),
@@ -354,6 +362,7 @@ def run_c5(args, env):
                 "e2e": {"value": F * K / sum(th), "unit": "frames/s", "h2d_bytes_per_step": seq.nbytes,
                         "d2h_bytes_per_step": sum(o.nbytes for o in outs), "ms_per_step": sum(th) / K * 1e3,
                         "chunks_per_rank": ch, "host_affinity": numa, "device_choice": env["h2d_probe"],
+                        "upload_ceiling_frames_per_s": sum(env["h2d_probe"]["h2d_gbs_per_gpu"]) * 1e9 / (2 * W * H),
                         "pipeline": f"{len(lanes)} streams/handles per rank, chunks of {CPc} pairs from a queue shared by the ranks"},
                 # per chunk: 7 resize levels, FAST, quadtree, blur, describe, stereo
                 "gpu_launches": 12 * ((F + CPc - 1) // CPc) * 2 * K}
@@ -858,6 +867,9 @@ def main():
             line["e2e"] = {"value": world * P * args.steps / (e2e_max * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_max / args.steps,
                            "host_affinity": numa, "chunks_per_rank": chunks_per_rank, "device_choice": h2d_probe,
+                           # what the box's host side allows when every rank uploads at once (probe at start-up): the
+                           # step's input bytes at the sum of the measured per-GPU rates
+                           "upload_ceiling_frames_per_s": sum(h2d_probe["h2d_gbs_per_gpu"]) * 1e9 / (2 * W * H),
                            "pipeline": f"chunks of {CP} pairs ({NCH} per step), handed out to the ranks by a shared queue; on a rank the chunks go round robin over {len(e2e_lanes)} streams/handles (copy-compute overlap), a rank asks for the next chunk when a lane is free; {NSLOT} pinned result slots per rank"}
         if next_rows is not None:
             line["next_rows"] = next_rows

@@ -82,6 +82,76 @@ __global__ void __launch_bounds__(KNN_NT) k_knn2(const uint64_t* __restrict__ d1
 }
 
 // --------------------------------------------------------------------------------------------------------------
+// The same matchKnn2 for ONE problem that would not fill the machine with a thread per query (1000 x 1000 is 8 blocks
+// of k_knn2 on 148 SMs): the train set is split across warps instead. A warp keeps 32 train descriptors in registers
+// (one per lane) and walks a group of queries; per query every lane computes one distance and the warp reduces to the
+// two smallest keys with two REDUX min operations. A key is distance << 22 | train index, so the unsigned minimum is
+// the reference's choice: smallest distance, and among equals the first in train order (strict '<', Features.h:335-348);
+// the second key is the minimum over the remaining lanes — exactly the (best, second best) pair the serial loop leaves.
+// The partial pairs of all train chunks are merged by k_knn2_merge in the same key order.
+// --------------------------------------------------------------------------------------------------------------
+constexpr int KNS_WARPS = 4;                  // train chunks (of 32) per block
+constexpr unsigned KNS_NONE = 0xFFFFFFFFu;    // "no candidate" key
+constexpr int KNS_MAX_M = 1 << 22;            // train indices must fit the key
+
+__global__ void __launch_bounds__(KNS_WARPS * 32) k_knn2_split(const uint64_t* __restrict__ d1, int n, const uint64_t* __restrict__ d2,
+                                                               int m, int qgroup, uint2* __restrict__ partial)
+{
+    extern __shared__ uint4 kns_q[];  // the block's query group, 2 x uint4 per descriptor
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int q0 = blockIdx.y * qgroup, nq = min(qgroup, n - q0);
+    const int chunk = blockIdx.x * KNS_WARPS + wid;  // train descriptors [32 chunk, 32 chunk + 32)
+    const int j = chunk * 32 + lane;
+    for (int k = threadIdx.x; k < 2 * nq; k += KNS_WARPS * 32) kns_q[k] = reinterpret_cast<const uint4*>(d1 + 4 * (size_t)q0)[k];
+    Desc t{};
+    if (j < m) t = load_desc(d2 + 4 * (size_t)j);
+    const unsigned jkey = (j < m) ? (unsigned)j : KNS_NONE;
+    __syncthreads();
+    if (chunk * 32 >= m) return;
+    uint2* out = partial + (size_t)chunk * n + q0;
+    unsigned r1 = KNS_NONE, r2 = KNS_NONE;
+    for (int q = 0; q < nq; ++q)
+    {
+        const uint4 a = kns_q[2 * q], b = kns_q[2 * q + 1];
+        const int d = __popc(t.w[0] ^ a.x) + __popc(t.w[1] ^ a.y) + __popc(t.w[2] ^ a.z) + __popc(t.w[3] ^ a.w) +
+                      __popc(t.w[4] ^ b.x) + __popc(t.w[5] ^ b.y) + __popc(t.w[6] ^ b.z) + __popc(t.w[7] ^ b.w);
+        const unsigned key = (j < m) ? (((unsigned)d << 22) | jkey) : KNS_NONE;
+        const unsigned k1 = __reduce_min_sync(0xffffffffu, key);
+        const unsigned k2 = __reduce_min_sync(0xffffffffu, key == k1 ? KNS_NONE : key);  // keys of valid lanes are distinct
+        if (lane == (q & 31)) r1 = k1, r2 = k2;
+        if ((q & 31) == 31 || q == nq - 1)
+        {
+            const int qq = (q & ~31) + lane;  // lane l holds query (q & ~31) + l: one coalesced store per 32 queries
+            if (qq <= q) out[qq] = make_uint2(r1, r2);
+        }
+    }
+}
+
+__global__ void k_knn2_merge(const uint2* __restrict__ partial, int n, int n_chunks, snk_knn2* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned a = KNS_NONE, b = KNS_NONE;  // the two smallest keys so far, a < b (or both "none")
+    for (int c = 0; c < n_chunks; ++c)
+    {
+        const uint2 p = partial[(size_t)c * n + i];  // p.x < p.y
+        if (p.x < a)
+        {
+            b = min(a, p.y);
+            a = p.x;
+        }
+        else
+            b = min(b, p.x);
+    }
+    snk_knn2 r;
+    r.dist0 = (a == KNS_NONE) ? 1000 : (int)(a >> 22);
+    r.idx0  = (a == KNS_NONE) ? -1 : (int)(a & 0x3fffffu);
+    r.dist1 = (b == KNS_NONE) ? 1000 : (int)(b >> 22);
+    r.idx1  = (b == KNS_NONE) ? -1 : (int)(b & 0x3fffffu);
+    out[i]  = r;
+}
+
+// --------------------------------------------------------------------------------------------------------------
 // Preprocess::StereoMatching (Snake/Preprocess/Preprocess.cpp:152-239). One CTA per stereo pair.
 // The reference buckets right keypoints by iRound(y) and scans rows y-r..y+r, each bucket in ascending index: the
 // candidate order is (row, index). Here the right keypoints are sorted by that key in shared memory (bitonic), each

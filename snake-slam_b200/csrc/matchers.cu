@@ -145,12 +145,32 @@ int snk_match_knn2_batch_device(snk_ctx* c, const uint64_t* d1, const int32_t* n
     return SNK_OK;
 }
 
+// How one n x m problem is spread over the machine: with at least two full waves of query blocks the thread-per-query
+// kernel is used; below that the train set is split over warps (k_knn2_split + k_knn2_merge). qgroup = queries per block.
+static bool knn2_split_plan(int device, int n, int m, int* qgroup, int* n_chunks)
+{
+    static int sms[64] = {};
+    if (device < 64 && !sms[device]) cudaDeviceGetAttribute(&sms[device], cudaDevAttrMultiProcessorCount, device);
+    const int nsm = (device < 64 && sms[device] > 0) ? sms[device] : 148;
+    if (m <= 0 || m > KNS_MAX_M || (n + KNN_NT - 1) / KNN_NT >= 2 * nsm) return false;
+    const int tblocks = (m + 32 * KNS_WARPS - 1) / (32 * KNS_WARPS);
+    // about four blocks per SM, query groups in multiples of 32 (one coalesced partial store per 32 queries)
+    int g = (int)(((long long)n * tblocks + 4LL * nsm - 1) / (4LL * nsm));
+    g = std::min(256, std::max(32, (g + 31) / 32 * 32));
+    *qgroup   = g;
+    *n_chunks = (m + 31) / 32;
+    return (size_t)*n_chunks * n * sizeof(uint2) <= ((size_t)64 << 20);
+}
+
 int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t* d2, int m, snk_knn2* out)
 {
     SNK_REQUIRE(c && out && n >= 0 && m >= 0 && (n == 0 || d1) && (m == 0 || d2), "bad argument");
     if (n == 0) return SNK_OK;
     SNK_CUDA(cudaSetDevice(c->device));
-    int rc = ctx_reserve(c, padded<uint64_t>(4 * (size_t)n) + padded<uint64_t>(4 * (size_t)std::max(m, 1)) + padded<snk_knn2>(n));
+    int qgroup = 0, n_chunks = 0;
+    const bool split = knn2_split_plan(c->device, n, m, &qgroup, &n_chunks);
+    int rc = ctx_reserve(c, padded<uint64_t>(4 * (size_t)n) + padded<uint64_t>(4 * (size_t)std::max(m, 1)) + padded<snk_knn2>(n) +
+                                (split ? padded<uint2>((size_t)n_chunks * n) : 0));
     if (rc) return rc;
     Carver cv{c->d_buf};
     uint64_t* a = cv.take<uint64_t>(4 * (size_t)n);
@@ -158,7 +178,16 @@ int snk_match_knn2(snk_ctx* c, const uint64_t* d1, int n, const uint64_t* d2, in
     snk_knn2* o = cv.take<snk_knn2>(n);
     SNK_CUDA(cudaMemcpyAsync(a, d1, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
     if (m) SNK_CUDA(cudaMemcpyAsync(b, d2, 32 * (size_t)m, cudaMemcpyHostToDevice, c->stream));
-    k_knn2<<<dim3((n + KNN_NT - 1) / KNN_NT, 1), KNN_NT, 0, c->stream>>>(a, nullptr, n, n, b, nullptr, m, m, o);
+    if (split)
+    {
+        uint2* part = cv.take<uint2>((size_t)n_chunks * n);
+        k_knn2_split<<<dim3((n_chunks + KNS_WARPS - 1) / KNS_WARPS, (n + qgroup - 1) / qgroup), KNS_WARPS * 32, (size_t)qgroup * 32,
+                       c->stream>>>(a, n, b, m, qgroup, part);
+        k_knn2_merge<<<(n + 127) / 128, 128, 0, c->stream>>>(part, n, n_chunks, o);
+    }
+    else
+        k_knn2<<<dim3((n + KNN_NT - 1) / KNN_NT, 1), KNN_NT, 0, c->stream>>>(a, nullptr, n, n, b, nullptr, m, m, o);
+    SNK_CUDA(cudaGetLastError());
     SNK_CUDA(cudaMemcpyAsync(out, o, sizeof(snk_knn2) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
     SNK_CUDA(cudaStreamSynchronize(c->stream));
     return SNK_OK;

@@ -55,6 +55,21 @@ def test_distance_and_knn2(so, ctx, oracle, feats):
     assert np.array_equal(np.stack([k["dist0"], k["idx0"], k["dist1"], k["idx1"]], 1), g["knn_out"])
 
 
+@pytest.mark.parametrize("n,m", [(1000, 1000), (1, 1), (1, 2), (31, 33), (33, 31), (257, 129), (1000, 7), (5, 4096), (2000, 1999),
+                                 (40000, 64)])
+def test_knn2_split_train_path(so, ctx, oracle, n, m):
+    """One problem too small for a thread per query runs with the train set split over warps (k_knn2_split: lane per
+    train descriptor, REDUX min for best / second best, k_knn2_merge); n = 40000 takes the thread-per-query kernel.
+    Tie-heavy inputs: the train set holds many exact copies, so first-minimum and second-best order decide."""
+    rng = np.random.default_rng(n * 7919 + m)
+    pool = rng.integers(0, 2**63, (max(2, min(m, 40) // 3), 4)).astype(np.uint64)
+    d2 = pool[rng.integers(0, len(pool), m)].copy()
+    d2[rng.random(m) < 0.3] ^= np.uint64(1) << np.uint64(int(rng.integers(0, 63)))
+    d1 = pool[rng.integers(0, len(pool), n)] ^ (np.uint64(1) << rng.integers(0, 63, (n, 4)).astype(np.uint64))
+    got = ctx.matchKnn2(d1, d2)
+    assert got.tobytes() == oracle.match_knn2(d1, d2, threads=4).tobytes()
+
+
 @pytest.mark.parametrize("relaxed,bf", [(True, 386.1), (False, 386.1), (True, 47.9)])
 def test_stereo_row_search(so, ctx, oracle, feats, relaxed, bf):
     kl, dl = feats["l"]
