@@ -404,6 +404,19 @@ def snake_ref():
     return _snake
 
 
+def snake_adapter():
+    """oracle/_ref/libsnake_adapter.so: the same entry points as snake_ref(), but the real Snake objects are driven through
+    the drop-in classes of snake-slam_b200/host/snakeorb_snake_adapter.h (libsnakeorb.so, needs a GPU). None if not built."""
+    so = os.path.join(HERE, "_ref", "libsnake_adapter.so")
+    return C.CDLL(so) if os.path.exists(so) else None
+
+
+def set_snake_lib(lib):
+    """Route the ref_* wrappers below to `lib` (snake_adapter()) or back to the compiled reference (None)."""
+    global _snake
+    _snake = lib
+
+
 def ref_stereo_matching(rect_left, rect_right, bf, relaxed, levels, scale_factor, left, dl, right, dr):
     """Preprocess::StereoMatching on raw keypoints (it rectifies them itself)."""
     left = np.ascontiguousarray(left, KP64)

@@ -27,6 +27,17 @@
 
 #include "../include/snakeorb.h"
 
+// Built a second time with -DSNK_USE_ADAPTER (oracle/Makefile: _ref/libsnake_adapter.so): the same object builders, but
+// the calls go to the drop-in classes of snake-slam_b200/host/snakeorb_snake_adapter.h (libsnakeorb.so, the GPU) instead
+// of the reference's classes — the adapter is tested with real Snake objects against the reference's frozen outputs.
+#ifdef SNK_USE_ADAPTER
+#    define SNAKEORB_WITH_SAIGA
+#    include "../snake-slam_b200/host/snakeorb_snake_adapter.h"
+using ProjectionMatcherT = snkadapter::SnakeORBMatcherB200;
+#else
+using ProjectionMatcherT = Snake::SnakeORBMatcher;
+#endif
+
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -182,8 +193,13 @@ REF_API int snkref_stereo_matching(const snk_rectify* rl, const snk_rectify* rr,
     for (int i = 0; i < nr; ++i)
         fr.keypoints_right.push_back(to_kp(right[i])), fr.descriptors_right.push_back(to_desc(dr + 4 * (size_t)i));
     fr.allocateTmp();  // right_points / depth = -1000 (Frame.cpp:21-29)
+#ifdef SNK_USE_ADAPTER
+    snkadapter::PreprocessB200 pp;
+    int m = pp.StereoMatching(fr);
+#else
     alignas(Preprocess) static unsigned char raw[sizeof(Preprocess)];  // the method reads no member; the ctor would start a thread
     int m = reinterpret_cast<Preprocess*>(raw)->StereoMatching(fr);
+#endif
     for (int i = 0; i < nl; ++i) right_points[i] = fr.right_points[i], depth[i] = fr.depth[i];
     return m;
 }
@@ -205,8 +221,13 @@ REF_API int snkref_stereo_from_rgbd(const snk_rgbd_params* p, const snk_keypoint
     fr.depth_image.create(rows, cols);
     for (int y = 0; y < rows; ++y)
         std::memcpy(&fr.depth_image(y, 0), reinterpret_cast<const char*>(img) + (size_t)y * pitch, (size_t)cols * 4);
+#ifdef SNK_USE_ADAPTER
+    snkadapter::PreprocessB200 pp;
+    int m = pp.ComputeStereoFromRGBD(fr);
+#else
     alignas(Preprocess) static unsigned char raw[sizeof(Preprocess)];
     int m = reinterpret_cast<Preprocess*>(raw)->ComputeStereoFromRGBD(fr);
+#endif
     for (int i = 0; i < n; ++i) right_points[i] = fr.right_points[i], depth[i] = fr.depth[i];
     return m;
 }
@@ -221,8 +242,13 @@ REF_API void snkref_undistort_keypoints(const snk_rectify* r, const snk_keypoint
     for (int i = 0; i < n; ++i) fr.keypoints.push_back(to_kp(kps[i]));
     fr.image.create(img_rows, img_cols);  // only its size is read (an assert)
     fr.allocateTmp();
+#ifdef SNK_USE_ADAPTER
+    snkadapter::PreprocessB200 pp;
+    pp.undistortKeypoints(fr);
+#else
     alignas(Preprocess) static unsigned char raw[sizeof(Preprocess)];
     reinterpret_cast<Preprocess*>(raw)->undistortKeypoints(fr);
+#endif
     for (int i = 0; i < n; ++i)
     {
         kp_un[i]   = kps[i];
@@ -259,7 +285,7 @@ REF_API int snkref_search_projection_fine(const snk_frame_view* f, snk_point_fin
         ftp.valid = pts[i].valid != 0;
         lm.points.push_back(ftp);
     }
-    SnakeORBMatcher matcher;
+    ProjectionMatcherT matcher;
     int m = matcher.SearchByProjection2(*fr, lm, th, ratio, threads);
     for (int i = 0; i < n; ++i)
     {
@@ -300,7 +326,7 @@ REF_API int snkref_search_projection_coarse(const snk_frame_view* f, const snk_p
         ctp.angle      = pts[i].angle;
         lm.points.push_back(ctp);
     }
-    SnakeORBMatcher matcher;
+    ProjectionMatcherT matcher;
     int m = matcher.SearchByProjectionFrameFrame2(*fr, lm, th, feature_error, threads);
     copy_assignment(*fr, kp_to_point_out);
     return m;
@@ -327,7 +353,7 @@ REF_API int snkref_search_projection_frame_to_kf(const snk_frame_view* f, const 
         mp->position   = Vec3(pts[i].pos[0], pts[i].pos[1], pts[i].pos[2]);
         obs[i]         = mp;
     }
-    SnakeORBMatcher matcher;
+    ProjectionMatcherT matcher;
     int m = matcher.SearchByProjectionFrameToKeyframe(*fr, kf, th, feature_error);
     copy_assignment(*fr, kp_to_point_out);
     return m;
@@ -362,7 +388,12 @@ REF_API int snkref_match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int
     fill(kf1, d1, n1, fv1, valid1);
     fill(kf2, d2, n2, fv2, valid2);
     std::vector<MapPoint*> matches12;
+#ifdef SNK_USE_ADAPTER
+    snkadapter::LoopORBmatcherB200 lm;
+    int m = lm.MatchBoW(&kf1, &kf2, matches12, th, ratio);
+#else
     int m = LoopORBmatcher::MatchBoW(&kf1, &kf2, matches12, th, ratio);
+#endif
     for (int i = 0; i < n1; ++i) match12[i] = matches12[i] ? matches12[i]->id() : -1;
     return m;
 }

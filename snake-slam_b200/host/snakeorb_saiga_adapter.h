@@ -10,6 +10,7 @@
 #pragma once
 #include "../../include/snakeorb.h"
 
+#include <algorithm>
 #include <array>
 #include <cstdio>
 #include <cstdlib>
@@ -112,12 +113,44 @@ class ORBExtractorB200
         return n;
     }
 
-    // Left and right image of a stereo frame in one batched call (FeatureDetector.cpp:124 + :154 back to back).
+    // Left and right image of a stereo frame (FeatureDetector.cpp:124 + :154 back to back) in ONE batched launch sequence
+    // (the handle is created with max_batch = 2): both images are queued as a batch of two, results fetched once.
     void DetectStereo(ImageView<unsigned char> left, ImageView<unsigned char> right, std::vector<KeyPointF>& kl,
                       std::vector<DescriptorORB>& dl, std::vector<KeyPointF>& kr, std::vector<DescriptorORB>& dr)
     {
-        Detect(left, kl, dl);
-        Detect(right, kr, dr);
+        if (left.empty() || right.empty() || left.rows != right.rows || left.cols != right.cols || left.pitchBytes != right.pitchBytes)
+        {
+            Detect(left, kl, dl);  // shapes differ (or an image is missing): two independent calls, as the reference does
+            Detect(right, kr, dr);
+            return;
+        }
+#ifdef SNAKEORB_WITH_SAIGA
+        const unsigned char *pl = left.data8, *pr = right.data8;
+#else
+        const unsigned char *pl = left.data, *pr = right.data;
+#endif
+        const int cap = snk_orb_max_keypoints(h_);
+        const size_t img_bytes = left.pitchBytes * (size_t)left.rows;
+        std::vector<KeyPointF> k2(2 * (size_t)cap);
+        std::vector<DescriptorORB> d2(2 * (size_t)cap);
+        int n[2] = {0, 0};
+        // the batch entry point takes one base pointer and an image stride: stage the pair contiguously unless it already is
+        const unsigned char* base = pl;
+        size_t stride             = (size_t)(pr - pl);
+        if (pr < pl || stride < img_bytes || stride % 16 != 0)
+        {
+            stage_.resize(2 * img_bytes);
+            std::copy(pl, pl + img_bytes, stage_.begin());
+            std::copy(pr, pr + img_bytes, stage_.begin() + img_bytes);
+            base = stage_.data(), stride = img_bytes;
+        }
+        check(snk_orb_detect_batch(h_, base, 2, left.rows, left.cols, left.pitchBytes, stride, /*imgs_are_device=*/0,
+                                   reinterpret_cast<snk_keypoint_f32*>(k2.data()), reinterpret_cast<uint64_t*>(d2.data()), cap, n),
+              "snk_orb_detect_batch");
+        kl.assign(k2.begin(), k2.begin() + n[0]);
+        dl.assign(d2.begin(), d2.begin() + n[0]);
+        kr.assign(k2.begin() + cap, k2.begin() + cap + n[1]);
+        dr.assign(d2.begin() + cap, d2.begin() + cap + n[1]);
     }
 
     // ScalePyramid accessors used by the matchers (ScalePyramid.h:78-84)
@@ -138,6 +171,7 @@ class ORBExtractorB200
    private:
     snk_orb* h_     = nullptr;
     int num_levels_ = 0;
+    std::vector<unsigned char> stage_;  // DetectStereo: the pair side by side when the caller's images are not
 };
 
 // Drop-in for Saiga::BruteForceMatcher<DescriptorORB> (Features.h:299-423): same public members.
