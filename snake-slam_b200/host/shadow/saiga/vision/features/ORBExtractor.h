@@ -42,7 +42,7 @@ class ORBExtractor
             int rows = 0, cols = 0;
             snkadapter::check(snk_orb_get_level(impl.handle(), 0, level, 0, nullptr, &rows, &cols, nullptr), "snk_orb_get_level");
             m.image.create(rows, cols);
-            snkadapter::check(snk_orb_read_level(impl.handle(), 0, level, 0, m.image.data8, m.image.pitchBytes), "snk_orb_read_level");
+            snkadapter::check(snk_orb_read_level(impl.handle(), 0, level, 0, m.image.data8(), m.image.pitchBytes), "snk_orb_read_level");
             m.valid = true;
         }
         return m.image.getImageView();
