@@ -189,20 +189,25 @@ def upload_probe(torch, dist, dev, world):
 def pick_device(torch, dist, local_rank, world):
     """Which GPU this rank drives, and how fast the ranks can upload when all of them do (the end-to-end ceiling of
     the box). With as many visible GPUs as ranks (or one rank) the GPU is LOCAL_RANK. With more visible GPUs than ranks
-    the box is probed: on this pool's 8-GPU boxes the host-to-device rate differs between the two halves of the box once
-    several GPUs upload at the same time (tools/scratch/numa8.py), so the ranks try the low block (rank r -> GPU r) and
-    the high block (rank r -> GPU visible - world + r) and keep the block whose slowest link is faster.
+    the box is probed: on this pool's 8-GPU boxes GPUs 0-3 share one host path (about 100 GB/s in total: 51 GB/s each for
+    two of them, 24 GB/s each for four) and GPUs 4-7 another, faster one (tools/scratch/numa8.py, profiles/r2c_*), so the
+    ranks try three placements - the low block (rank r -> GPU r), the high block (rank r -> GPU visible - world + r) and
+    one that alternates between the two halves of the box - with concurrent uploads, and keep the one with the highest
+    total rate (the chunk queue of the end-to-end path balances unequal links, so the sum is what counts).
     Returns (device index, probe record)."""
     visible = torch.cuda.device_count()
     if world == 1 or visible <= world:
         dev = local_rank % max(visible, 1)
         return dev, {"visible_gpus": visible, "picked": "rank order", "h2d_gbs_per_gpu": upload_probe(torch, dist, dev, world)}
-    rates = {name: upload_probe(torch, dist, dev, world)
-             for name, dev in (("low", local_rank), ("high", visible - world + local_rank))}
-    pick = "high" if min(rates["high"]) > 1.05 * min(rates["low"]) else "low"
-    dev = local_rank if pick == "low" else visible - world + local_rank
-    return dev, {"visible_gpus": visible, "picked": pick + " block", "h2d_gbs_per_gpu": rates[pick],
-                 "h2d_gbs_per_gpu_other_block": rates["high" if pick == "low" else "low"]}
+    half = visible // 2
+    placements = {"low block": local_rank, "high block": visible - world + local_rank,
+                  "alternating halves": (local_rank % 2) * half + local_rank // 2}
+    rates = {name: upload_probe(torch, dist, dev, world) for name, dev in placements.items()}
+    pick = max(rates, key=lambda k: sum(rates[k]))
+    if sum(rates[pick]) < 1.05 * sum(rates["low block"]):
+        pick = "low block"
+    return placements[pick], {"visible_gpus": visible, "picked": pick, "h2d_gbs_per_gpu": rates[pick],
+                              "h2d_gbs_per_gpu_of_every_placement": rates}
 
 
 class HostArray:
