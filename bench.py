@@ -888,6 +888,19 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} stereo pairs of the same workload, one oracle extractor per thread, "
                                               f"{cores} threads", "keypoints_per_s": kps}
+            # two more CPU figures, informational: the port rebuilt -O3 -march=native on this host, and
+            # the reference's own kernels (cv2 4.13 SIMD + its compiled Saiga pieces) under a Python driver
+            anchors = {}
+            for variant in ("native", "hybrid"):
+                try:
+                    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cpu_anchor.py"), "--variant", variant,
+                                          "--threads", str(cores), "--budget", str(min(args.cpu_budget, 8.0))],
+                                         capture_output=True, text=True, timeout=240)
+                    anchors[variant] = json.loads(out.stdout.strip().splitlines()[-1]) if out.returncode == 0 else \
+                        {"unavailable": (out.stderr.strip().splitlines() or ["failed"])[-1][:200]}
+                except Exception as exc:  # noqa: BLE001
+                    anchors[variant] = {"unavailable": repr(exc)[:200]}
+            line["cpu_anchors"] = {"o3_march_native_port": anchors["native"], "cv2_simd_hybrid": anchors["hybrid"]}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

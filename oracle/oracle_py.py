@@ -29,7 +29,7 @@ _ref = None
 def lib():
     global _lib
     if _lib is None:
-        so = os.path.join(HERE, "liborb_oracle.so")
+        so = os.environ.get("SNK_ORACLE_SO") or os.path.join(HERE, "liborb_oracle.so")  # tools/cpu_anchor.py swaps the build
         if not os.path.exists(so):
             build()
         _lib = C.CDLL(so)
