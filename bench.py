@@ -694,6 +694,33 @@ def main():
                 reps += 4
             next_rows["bow_transform"]["cpu_port_frames_per_s_1_thread"] = reps / (time.time() - t0)
         del voc
+        # the same step on a NOISY variant of the batch (Gaussian sensor noise, sigma = 5 grey levels: 2.3x the raw FAST
+        # candidates, level 0 beyond the quadtree kernel's small shared-memory array): density regressions show up here
+        try:
+            rngz = np.random.default_rng(77)
+            noisy = np.clip(batch.astype(np.int16) + np.rint(rngz.normal(0, 5.0, (32,) + batch.shape[1:])).astype(np.int16)[np.arange(NI) % 32],
+                            0, 255).astype(np.uint8)
+            dev_noisy = torch.from_numpy(noisy).cuda()
+            for _ in range(3):
+                ex.enqueue_ptr(dev_noisy.data_ptr(), NI, H, W, W, W * H, True)
+                ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+            z0, z1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            z0.record()
+            for _ in range(args.steps):
+                ex.enqueue_ptr(dev_noisy.data_ptr(), NI, H, W, W, W * H, True)
+                ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+            z1.record()
+            torch.cuda.synchronize()
+            zms = z0.elapsed_time(z1) / args.steps
+            next_rows["noisy_sigma5_c2"] = {"frames_per_s": P / (zms * 1e-3), "ms_per_step": zms,
+                                            "raw_fast_candidates_per_image": sum(len(ex.candidates(l, 0)) for l in range(NLEVELS)),
+                                            "vs_clean_batch": (ms / args.steps) / zms}
+            del dev_noisy
+            ex.enqueue_ptr(dev.data_ptr(), NI, H, W, W, W * H, True)  # the clean batch's results are read again below
+            ctx.stereo_orb_device(ex, P, sp, rp.data_ptr(), dp.data_ptr(), nm.data_ptr())
+            torch.cuda.synchronize()
+        except Exception as exc:  # noqa: BLE001
+            next_rows["noisy_sigma5_c2"] = {"error": repr(exc)[:200]}
         # C3: SearchByProjection2 of 20 000 local-map points into one KITTI-shaped frame (host structs in, host results
         # out, as Tracking calls it); C4: BoW-candidate matching of two TUM-shaped keyframes. Side measurements.
         try:

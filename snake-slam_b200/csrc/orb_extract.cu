@@ -87,6 +87,8 @@ struct snk_orb
     // descriptor kernel (serialised on the main stream while per-stage profiling is on, so stage times stay separable)
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t dense_stream = nullptr;  // the dense pass of the quadtree distribution runs beside the ordinary one
+    cudaEvent_t ev_fork2 = nullptr, ev_join2 = nullptr;
     cudaEvent_t ev_sync = nullptr;  // orders another stream against this handle's stream (snk_orb_order_*)
     int rows = 0, cols = 0;  // geometry the buffers are sized for (0 = none yet)
     int last_n = 0;
@@ -103,6 +105,8 @@ struct snk_orb
     std::vector<TileDev> tiles;
     int node_cap = 0;
     size_t qt_smem = 0;
+    int qt_big_levels = 0, qt_big_cap = 0;  // levels [0, qt_big_levels) run in their own launch with qt_big_cap keypoints in smem
+    size_t qt_smem_big = 0;
 
     uint8_t* d_rgba = nullptr;   // staging for host RGBA input (snk_orb_enqueue_rgba), grown on demand
     size_t rgba_bytes = 0;
@@ -291,6 +295,20 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->node_cap = align_up(max_quota + 8, 4);  // multiple of 4 keeps the int2 array of the kernel 8-byte aligned
     SNK_REQUIRE(h->node_cap < (1 << gnusort::SHIFT), "nfeatures too large: %d nodes per level", h->node_cap);
     h->qt_smem = (size_t)h->node_cap * QT_NODE_BYTES + 2 * (size_t)QT_KP_SMEM * 4;
+    {
+        // the largest levels (those a noisy image can push beyond QT_KP_SMEM candidates) get a second launch with a larger
+        // shared-memory capacity that only picks up the dense problems; SNK_QT_BIG_CAP / SNK_QT_BIG_LEVELS override for A/B runs
+        const char* e1 = getenv("SNK_QT_BIG_CAP");
+        const char* e2 = getenv("SNK_QT_BIG_LEVELS");
+        h->qt_big_cap  = e1 ? atoi(e1) : QT_KP_SMEM_BIG;
+        int nbig = 0;
+        for (int l = 0; l < L; ++l)
+            if ((long long)P.lv[l].w * P.lv[l].h >= 200000) nbig = l + 1;  // 752x480: levels 0 and 1
+        h->qt_big_levels = e2 ? std::min(atoi(e2), L) : nbig;
+        if (h->qt_big_cap <= QT_KP_SMEM) h->qt_big_levels = 0;
+        h->qt_smem_big = (size_t)h->node_cap * QT_NODE_BYTES + 2 * (size_t)h->qt_big_cap * 4;
+        if (h->qt_smem_big > (size_t)SMEM_CEILING) h->qt_big_levels = 0;
+    }
     SNK_REQUIRE(20 * h->node_cap >= gnusort::cta_sort_scratch_bytes(h->node_cap), "internal: sort scratch does not fit");
     SNK_REQUIRE(h->qt_smem <= (size_t)SMEM_CEILING, "nfeatures too large for the distribution kernel's shared memory");
     // the attribute belongs to the kernel, not to this handle: every handle sets the same ceiling, so handles with
@@ -484,6 +502,9 @@ int snk_orb_create(const snk_orb_params* p, snk_orb** out)
         cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&h->ev_sync, cudaEventDisableTiming) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->dense_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_fork2, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
         cudaHostAlloc(&h->h_counts, sizeof(int) * p->max_batch, cudaHostAllocDefault) != cudaSuccess ||
         cudaHostAlloc(&h->h_err, sizeof(int), cudaHostAllocDefault) != cudaSuccess)
     {
@@ -576,6 +597,9 @@ void snk_orb_destroy(snk_orb* h)
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->ev_sync) cudaEventDestroy(h->ev_sync);
+    if (h->dense_stream) cudaStreamDestroy(h->dense_stream);
+    if (h->ev_fork2) cudaEventDestroy(h->ev_fork2);
+    if (h->ev_join2) cudaEventDestroy(h->ev_join2);
     delete h;
 }
 
@@ -721,10 +745,27 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     if (prof) cudaEventRecord(ev[3], st);
 
     // stage 3: quadtree distribution per (level, image)
-    k_distribute<<<dim3(n_imgs, P.nlevels), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off,
-                                                                     h->d_workA, h->d_workB, h->d_sel, h->d_sel_count,
-                                                                     h->node_cap, QT_KP_SMEM, h->d_err);
+    // the dense (level, image) problems run in their own launch (larger shared-memory array, fewer blocks per SM) on a
+    // second stream beside the ordinary ones; on ordinary images that launch's blocks return at once
+    if (h->qt_big_levels > 0)
+    {
+        cudaStream_t ds = prof ? st : h->dense_stream;
+        if (!prof)
+        {
+            SNK_CUDA(cudaEventRecord(h->ev_fork2, st));
+            SNK_CUDA(cudaStreamWaitEvent(ds, h->ev_fork2, 0));
+        }
+        k_distribute<<<dim3(n_imgs, h->qt_big_levels), QT_NT, h->qt_smem_big, ds>>>(
+            P, h->d_cand, h->d_cell_count, h->d_cell_off, h->d_workA, h->d_workB, h->d_sel, h->d_sel_count, h->node_cap, h->qt_big_cap,
+            h->d_err, 2, QT_KP_SMEM, h->qt_big_levels);
+        if (!prof) SNK_CUDA(cudaEventRecord(h->ev_join2, ds));
+        ++nl[3];
+    }
+    k_distribute<<<dim3(n_imgs, P.nlevels), QT_NT, h->qt_smem, st>>>(P, h->d_cand, h->d_cell_count, h->d_cell_off, h->d_workA,
+                                                                     h->d_workB, h->d_sel, h->d_sel_count, h->node_cap, QT_KP_SMEM,
+                                                                     h->d_err, h->qt_big_levels > 0 ? 1 : 0, QT_KP_SMEM, h->qt_big_levels);
     ++nl[3];
+    if (h->qt_big_levels > 0 && !prof) SNK_CUDA(cudaStreamWaitEvent(st, h->ev_join2, 0));
     if (prof) cudaEventRecord(ev[4], st);
 
     // stage 4: blur (serial variant) / join

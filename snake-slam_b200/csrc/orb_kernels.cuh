@@ -438,11 +438,14 @@ __device__ __forceinline__ float kp_y(uint32_t p) { return (float)((p >> 12) & 0
 constexpr int QT_NODE_BYTES = 2 * 24 + 4 + 4 + 16 + 4;
 constexpr int QT_SMALL = 24;      // nodes up to this many keypoints are processed by a single thread
 constexpr int QT_KP_SMEM = 2048;  // keypoints per (level, image) kept in shared memory (x2: array + partition buffer)
+// the largest levels get their own launch with a larger capacity: camera noise of a few grey levels lifts level 0 of a
+// 752x480 image above 2048 candidates, and the global-scratch path costs about 1.5x per candidate
+constexpr int QT_KP_SMEM_BIG = 8192;
 __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* __restrict__ cand,
                                                       const int* __restrict__ cell_count, int* __restrict__ cell_off,
                                                       uint32_t* __restrict__ workA, uint32_t* __restrict__ workB,
                                                       uint32_t* __restrict__ sel, int* __restrict__ sel_count,
-                                                      int node_cap, int kp_cap, int* __restrict__ err)
+                                                      int node_cap, int kp_cap, int* __restrict__ err, int pass, int small_cap, int big_levels)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     QNode* listA    = reinterpret_cast<QNode*>(smem);
@@ -489,6 +492,10 @@ __global__ void __launch_bounds__(QT_NT) k_distribute(PyrDev P, const uint32_t* 
         __syncthreads();
     }
     const int n = running;
+    // two launches share the (level, image) problems: pass 1 (shared memory for small_cap keypoints, six blocks per SM)
+    // takes those with at most small_cap candidates, pass 2 (a larger array, fewer blocks per SM) the dense rest — on
+    // ordinary images its blocks end here; pass 0 takes everything
+    if ((pass == 1 && level < big_levels && n > small_cap) || (pass == 2 && n <= small_cap)) return;
     if (n > kp_cap)
     {
         A = workA + wbase;
