@@ -403,6 +403,32 @@ SNK_API int snk_search_projection_fine(snk_ctx* c, const snk_frame_view* frame, 
                                        int32_t* kp_to_point_out, int32_t* best_idx, int32_t* best_dist,
                                        uint8_t* visible, int* n_matches);
 
+/* The same SearchByProjection2 (SnakeORBMatcher.cpp:365-526) on data that STAYS on the device between calls. In the
+ * reference the frame (Snake/Map/Frame.h) and the local map (LocalMap<FineTrackingPoint>, Snake/Map/LocalMap.h:83-186,
+ * rebuilt by TrackingFine::updateLocalMap once per frame) live in host memory and the search runs where they are; the
+ * host-struct entry point above uploads both on every call (1.9 MB for 20 000 points), which is most of its time.
+ *   snk_frame_dev_*  : a device copy of a frame view (keypoints, descriptors, right_points, assignments, grid); the pose
+ *                      can be changed (pose refinement runs between the coarse and the fine search), the assignments
+ *                      follow the searches (keep_assignment) or are set from the host.
+ *   snk_localmap_*   : capacity points on the device; snk_localmap_upload replaces points [first, first + n) and sets the
+ *                      number of points in use (new_size).
+ *   snk_search_projection_fine_resident: the search; lm point `valid` flags are updated on the device as the reference
+ *   updates lmp.valid. Host outputs (each may be NULL): kp_to_point_out[n keypoints], point_valid_out[n points] (int32),
+ *   visible_out[n points] (1 where the reference calls IncreaseVisible). Synchronous. */
+typedef struct snk_frame_dev snk_frame_dev;
+typedef struct snk_localmap snk_localmap;
+SNK_API int snk_frame_dev_create(snk_ctx* c, const snk_frame_view* host_view, snk_frame_dev** out);
+SNK_API void snk_frame_dev_destroy(snk_frame_dev* f);
+SNK_API int snk_frame_dev_set_pose(snk_frame_dev* f, const double* q_xyzw, const double* t);
+SNK_API int snk_frame_dev_set_assignment(snk_frame_dev* f, const int32_t* kp_to_point);
+SNK_API int snk_localmap_create(snk_ctx* c, int capacity, snk_localmap** out);
+SNK_API void snk_localmap_destroy(snk_localmap* lm);
+SNK_API int snk_localmap_upload(snk_localmap* lm, const snk_point_fine* points, int first, int n, int new_size);
+SNK_API int snk_search_projection_fine_resident(snk_ctx* c, snk_frame_dev* frame, snk_localmap* lm, const snk_camera* cam,
+                                                const snk_scale_pyramid* pyr, float th, float ratio, int keep_assignment,
+                                                int32_t* kp_to_point_out, int32_t* point_valid_out, uint8_t* visible_out,
+                                                int* n_matches);
+
 /* SnakeORBMatcher::SearchByProjectionFrameFrame2 (Snake/Tracking/SnakeORBMatcher.cpp:191-354).
  * motion: 0 neither, 1 bForward, 2 bBackward (the caller evaluates :209-212). */
 SNK_API int snk_search_projection_coarse(snk_ctx* c, const snk_frame_view* frame, const snk_point_coarse* points,

@@ -45,6 +45,12 @@ int upload_frame(snk_ctx* c, Carver& cv, const snk_frame_view* v, FrameUpload& u
     return SNK_OK;
 }
 
+__global__ void k_gather_valid(const snk_point_fine* p, int n, int* out)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = p[i].valid;
+}
+
 __global__ void k_fill_int(int* p, int n, int v)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -273,6 +279,177 @@ int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, in
     FeatVecDev f1{fv1->n_nodes, ids1, of1, in1}, f2{fv2->n_nodes, ids2, of2, in2};
     k_match_bow<<<(fv1->n_nodes + 3) / 4, 128, 0, st>>>(a, b, f1, f2, v1, v2, th, ratio, m12, m2, dn);
     SNK_CUDA(cudaMemcpyAsync(match12, m12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    *n_matches = c->h_pin[4];
+    return SNK_OK;
+}
+
+
+// ---- device-resident frame and local map (no reference counterpart: there both live in host memory, Snake/Map/Frame.h,
+// Snake/Map/LocalMap.h:83-186) -----------------------------------------------------------------------------------------
+struct snk_frame_dev
+{
+    snk_ctx* c = nullptr;
+    FrameDev f{};
+    int cap_n = 0, cap_cells = 0;
+    unsigned char* buf = nullptr;
+    int *k2p = nullptr, *k2p_out = nullptr, *winner = nullptr;
+};
+struct snk_localmap
+{
+    snk_ctx* c        = nullptr;
+    snk_point_fine* d = nullptr;
+    int *bi = nullptr, *bd = nullptr;
+    uint8_t* vis = nullptr;
+    int capacity = 0, n = 0;
+};
+
+int snk_frame_dev_create(snk_ctx* c, const snk_frame_view* v, snk_frame_dev** out)
+{
+    SNK_REQUIRE(c && out, "null argument");
+    int rc = check_frame(v);
+    if (rc) return rc;
+    SNK_CUDA(cudaSetDevice(c->device));
+    auto* fd = new snk_frame_dev;
+    fd->c    = c;
+    const size_t n = std::max(v->n, 1), cells = (size_t)v->grid.rows * v->grid.cols;
+    const size_t bytes = padded<snk_keypoint_f64>(n) + padded<uint64_t>(4 * n) + padded<float>(n) + 3 * padded<int>(n) + padded<int>(2 * cells);
+    if (cudaMalloc(&fd->buf, bytes) != cudaSuccess)
+    {
+        set_error("snk_frame_dev_create: cudaMalloc(%zu) failed", bytes);
+        delete fd;
+        return SNK_ERR_CUDA;
+    }
+    Carver cv{fd->buf};
+    auto* kp = cv.take<snk_keypoint_f64>(n);
+    auto* ds = cv.take<uint64_t>(4 * n);
+    auto* rp = cv.take<float>(n);
+    fd->k2p     = cv.take<int>(n);
+    fd->k2p_out = cv.take<int>(n);
+    fd->winner  = cv.take<int>(n);
+    auto* cl    = cv.take<int>(2 * cells);
+    cudaStream_t st = c->stream;
+    if (v->n)
+    {
+        SNK_CUDA(cudaMemcpyAsync(kp, v->kp_un, sizeof(snk_keypoint_f64) * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(ds, v->desc, 32 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(rp, v->right_points, 4 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+        SNK_CUDA(cudaMemcpyAsync(fd->k2p, v->kp_to_point, 4 * (size_t)v->n, cudaMemcpyHostToDevice, st));
+    }
+    SNK_CUDA(cudaMemcpyAsync(cl, v->grid.cells, 8 * cells, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaStreamSynchronize(st));  // the caller's arrays may go away after this call
+    FrameDev& f = fd->f;
+    f.n = v->n, f.kp_un = kp, f.desc = ds, f.right_points = rp, f.kp_to_point = fd->k2p;
+    for (int i = 0; i < 4; ++i) f.q[i] = v->pose_q[i];
+    for (int i = 0; i < 3; ++i) f.t[i] = v->pose_t[i];
+    f.bmin_x = v->grid.bmin_x, f.bmin_y = v->grid.bmin_y, f.bmax_x = v->grid.bmax_x, f.bmax_y = v->grid.bmax_y;
+    f.inv_x = v->grid.cell_size_inv_x, f.inv_y = v->grid.cell_size_inv_y;
+    f.rows = v->grid.rows, f.cols = v->grid.cols, f.cells = cl;
+    *out = fd;
+    return SNK_OK;
+}
+
+void snk_frame_dev_destroy(snk_frame_dev* f)
+{
+    if (!f) return;
+    cudaSetDevice(f->c->device);
+    cudaStreamSynchronize(f->c->stream);
+    if (f->buf) cudaFree(f->buf);
+    delete f;
+}
+
+int snk_frame_dev_set_pose(snk_frame_dev* f, const double* q_xyzw, const double* t)
+{
+    SNK_REQUIRE(f && q_xyzw && t, "null argument");
+    for (int i = 0; i < 4; ++i) f->f.q[i] = q_xyzw[i];
+    for (int i = 0; i < 3; ++i) f->f.t[i] = t[i];
+    return SNK_OK;
+}
+
+int snk_frame_dev_set_assignment(snk_frame_dev* f, const int32_t* kp_to_point)
+{
+    SNK_REQUIRE(f && (f->f.n == 0 || kp_to_point), "null argument");
+    if (f->f.n == 0) return SNK_OK;
+    SNK_CUDA(cudaSetDevice(f->c->device));
+    SNK_CUDA(cudaMemcpyAsync(f->k2p, kp_to_point, 4 * (size_t)f->f.n, cudaMemcpyHostToDevice, f->c->stream));
+    SNK_CUDA(cudaStreamSynchronize(f->c->stream));
+    return SNK_OK;
+}
+
+int snk_localmap_create(snk_ctx* c, int capacity, snk_localmap** out)
+{
+    SNK_REQUIRE(c && out && capacity >= 1, "bad argument");
+    SNK_CUDA(cudaSetDevice(c->device));
+    auto* lm     = new snk_localmap;
+    lm->c        = c;
+    lm->capacity = capacity;
+    if (cudaMalloc(&lm->d, sizeof(snk_point_fine) * (size_t)capacity) != cudaSuccess || cudaMalloc(&lm->bi, 4 * (size_t)capacity) != cudaSuccess ||
+        cudaMalloc(&lm->bd, 4 * (size_t)capacity) != cudaSuccess || cudaMalloc(&lm->vis, (size_t)capacity) != cudaSuccess)
+    {
+        set_error("snk_localmap_create: cudaMalloc failed for %d points", capacity);
+        cudaFree(lm->d), cudaFree(lm->bi), cudaFree(lm->bd), cudaFree(lm->vis);
+        delete lm;
+        return SNK_ERR_CUDA;
+    }
+    *out = lm;
+    return SNK_OK;
+}
+
+void snk_localmap_destroy(snk_localmap* lm)
+{
+    if (!lm) return;
+    cudaSetDevice(lm->c->device);
+    cudaStreamSynchronize(lm->c->stream);
+    cudaFree(lm->d), cudaFree(lm->bi), cudaFree(lm->bd), cudaFree(lm->vis);
+    delete lm;
+}
+
+int snk_localmap_upload(snk_localmap* lm, const snk_point_fine* points, int first, int n, int new_size)
+{
+    SNK_REQUIRE(lm && first >= 0 && n >= 0 && (n == 0 || points), "bad argument");
+    SNK_REQUIRE(first + n <= lm->capacity && new_size <= lm->capacity && new_size >= 0, "local map capacity %d exceeded", lm->capacity);
+    for (int i = 0; i < n; ++i) SNK_REQUIRE(points[i].ref_level >= 0 && points[i].ref_level < 16, "ref_level out of range");
+    SNK_CUDA(cudaSetDevice(lm->c->device));
+    if (n)
+    {
+        SNK_CUDA(cudaMemcpyAsync(lm->d + first, points, sizeof(snk_point_fine) * (size_t)n, cudaMemcpyHostToDevice, lm->c->stream));
+        SNK_CUDA(cudaStreamSynchronize(lm->c->stream));
+    }
+    lm->n = new_size;
+    return SNK_OK;
+}
+
+int snk_search_projection_fine_resident(snk_ctx* c, snk_frame_dev* fd, snk_localmap* lm, const snk_camera* cam,
+                                        const snk_scale_pyramid* pyr, float th, float ratio, int keep_assignment,
+                                        int32_t* kp_to_point_out, int32_t* point_valid_out, uint8_t* visible_out, int* n_matches)
+{
+    SNK_REQUIRE(c && fd && lm && cam && pyr && n_matches, "null argument");
+    SNK_REQUIRE(fd->c == c && lm->c == c, "frame and local map must belong to this context");
+    SNK_REQUIRE(pyr->nlevels >= 1 && pyr->nlevels <= 16, "bad pyramid");
+    SNK_CUDA(cudaSetDevice(c->device));
+    int rc = ctx_reserve(c, padded<int>(std::max(lm->n, 1)) + padded<int>(4));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    int* dvalid = cv.take<int>(std::max(lm->n, 1));
+    int* dn     = cv.take<int>(4);
+    cudaStream_t st = c->stream;
+    const int nk = fd->f.n, np = lm->n;
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 16, st));
+    if (nk) k_fill_int<<<(nk + 255) / 256, 256, 0, st>>>(fd->winner, nk, 0x7fffffff);
+    if (np)
+        k_proj_fine<<<(np + 127) / 128, 128, 0, st>>>(fd->f, lm->d, np, *cam, *pyr, th, ratio, std::log(pyr->scale_factor), lm->bi, lm->bd,
+                                                     lm->vis, fd->winner);
+    if (nk)
+        k_assign<snk_point_fine><<<(nk + 255) / 256, 256, 0, st>>>(fd->k2p, fd->winner, lm->d, nullptr, nk, fd->k2p_out, nullptr, dn);
+    if (np && point_valid_out)
+    {
+        k_gather_valid<<<(np + 255) / 256, 256, 0, st>>>(lm->d, np, dvalid);
+        SNK_CUDA(cudaMemcpyAsync(point_valid_out, dvalid, 4 * (size_t)np, cudaMemcpyDeviceToHost, st));
+    }
+    if (np && visible_out) SNK_CUDA(cudaMemcpyAsync(visible_out, lm->vis, (size_t)np, cudaMemcpyDeviceToHost, st));
+    if (nk && kp_to_point_out) SNK_CUDA(cudaMemcpyAsync(kp_to_point_out, fd->k2p_out, 4 * (size_t)nk, cudaMemcpyDeviceToHost, st));
+    if (nk && keep_assignment) SNK_CUDA(cudaMemcpyAsync(fd->k2p, fd->k2p_out, 4 * (size_t)nk, cudaMemcpyDeviceToDevice, st));
     SNK_CUDA(cudaMemcpyAsync(c->h_pin + 4, dn, 4, cudaMemcpyDeviceToHost, st));
     SNK_CUDA(cudaStreamSynchronize(st));
     *n_matches = c->h_pin[4];

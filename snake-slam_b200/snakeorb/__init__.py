@@ -243,6 +243,49 @@ class ORBExtractor:
         return ms, ln
 
 
+class FrameDev:
+    """snk_frame_dev: a frame view kept on the device between searches."""
+
+    def __init__(self, ctx, view):
+        self.h, self.ctx, self.n = C.c_void_p(), ctx, view.n
+        _check(lib().snk_frame_dev_create(ctx.c, C.byref(view), C.byref(self.h)))
+
+    def set_pose(self, q_xyzw, t):
+        q, t = np.ascontiguousarray(q_xyzw, np.float64), np.ascontiguousarray(t, np.float64)
+        _check(lib().snk_frame_dev_set_pose(self.h, _p(q), _p(t)))
+
+    def set_assignment(self, k2p):
+        k2p = np.ascontiguousarray(k2p, np.int32)
+        _check(lib().snk_frame_dev_set_assignment(self.h, _p(k2p)))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None and getattr(self.ctx, "c", None):
+            _lib.snk_frame_dev_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+class LocalMapDev:
+    """snk_localmap: LocalMap<FineTrackingPoint> kept on the device."""
+
+    def __init__(self, ctx, capacity):
+        self.h, self.ctx, self.n = C.c_void_p(), ctx, 0
+        _check(lib().snk_localmap_create(ctx.c, capacity, C.byref(self.h)))
+
+    def upload(self, points, first=0, new_size=None):
+        pts = np.ascontiguousarray(points, POINT_FINE)
+        self.n = first + len(pts) if new_size is None else new_size
+        _check(lib().snk_localmap_upload(self.h, _p(pts), first, len(pts), self.n))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None and getattr(self.ctx, "c", None):
+            _lib.snk_localmap_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
 class Context:
     """snk_ctx: device + stream + scratch for the matchers."""
 
@@ -432,6 +475,24 @@ class Context:
                                                 C.c_float(th), C.c_float(ratio), _p(k2p), _p(bi), _p(bd), _p(vis),
                                                 C.byref(m)))
         return m.value, k2p[:frame.n], bi[:n], bd[:n], vis[:n], pts
+
+    def frame_dev(self, view):
+        """Device copy of a frame view (snk_frame_dev_create); keep the returned object alive while it is used."""
+        return FrameDev(self, view)
+
+    def localmap(self, capacity):
+        return LocalMapDev(self, capacity)
+
+    def SearchByProjection2Resident(self, frame_dev, lm, cam, pyr, th, ratio, keep_assignment=True):
+        """SearchByProjection2 on a device-resident frame and local map -> (matches, kp_to_point, valid, visible)."""
+        k2p = np.zeros(max(frame_dev.n, 1), np.int32)
+        valid = np.zeros(max(lm.n, 1), np.int32)
+        vis = np.zeros(max(lm.n, 1), np.uint8)
+        m = C.c_int()
+        _check(lib().snk_search_projection_fine_resident(self.c, frame_dev.h, lm.h, C.byref(cam), C.byref(pyr), C.c_float(th),
+                                                         C.c_float(ratio), int(keep_assignment), _p(k2p), _p(valid), _p(vis),
+                                                         C.byref(m)))
+        return m.value, k2p[:frame_dev.n], valid[:lm.n], vis[:lm.n]
 
     def SearchByProjectionFrameFrame2(self, frame, points, cam, pyr, th, feature_error, motion):
         pts = np.ascontiguousarray(points, POINT_COARSE)

@@ -175,6 +175,51 @@ def test_search_by_projection_fine(so, ctx, oracle, feats, th, n_points):
         assert m > 100 and ops > 1000
 
 
+def test_search_by_projection_fine_resident(so, ctx, oracle, feats):
+    """Device-resident frame + local map (snk_frame_dev / snk_localmap): the search must return what the host-struct entry
+    point and the oracle return, a second search on the same frame must see the first one's assignments (the reference's
+    Frame::mvpMapPoints persists between searches), and a changed pose / a partly replaced local map must take effect."""
+    rng, frame, mp, cam, pyr = _c3(so, feats, 21, 20000)
+    pts = M.fine_points(mp, rng)
+    want = oracle.search_projection_fine(frame.view, pts, cam, pyr, 4.0, 0.8)
+    fd, lm = ctx.frame_dev(frame.view), ctx.localmap(25000)
+    lm.upload(pts)
+    m, k2p, valid, vis = ctx.SearchByProjection2Resident(fd, lm, cam, pyr, 4.0, 0.8)
+    assert m == want[0] and m > 500
+    assert np.array_equal(k2p, want[1]) and np.array_equal(vis, want[4]) and np.array_equal(valid, want[5]["valid"])
+    # second search, other points, tighter radius: the first search's assignments are taken (device side) and skipped
+    pts2 = M.fine_points(S_map(so, frame, feats, rng, 6000), rng)
+    pts2["id"] += 100000
+    frame2_k2p = want[1].copy()
+    frame.k2p[:] = frame2_k2p  # the host view for the oracle: assignments after search 1
+    want2 = oracle.search_projection_fine(frame.view, pts2, cam, pyr, 1.0, 0.7)
+    lm.upload(pts2)
+    m2, k2p2, valid2, vis2 = ctx.SearchByProjection2Resident(fd, lm, cam, pyr, 1.0, 0.7)
+    assert m2 == want2[0] and np.array_equal(k2p2, want2[1]) and np.array_equal(valid2, want2[5]["valid"])
+    # a new pose and a partial update of the local map
+    q = so.synthetic.quat_from_axis_angle(np.array([0.0, 1.0, 0.2]), 0.003)
+    t = np.array([0.02, -0.01, 0.03])
+    fd.set_pose(q, t)
+    fd.set_assignment(np.full(frame.view.n, -1, np.int32))
+    frame.k2p[:] = -1
+    for i in range(4):
+        frame.view.pose_q[i] = q[i]
+    for i in range(3):
+        frame.view.pose_t[i] = t[i]
+    pts3 = want2[5].copy()  # the local map as search 2 left it (valid flags cleared where the reference clears them)
+    pts3[1000:2000] = pts[1000:2000]
+    lm.upload(pts[1000:2000], first=1000, new_size=len(pts2))
+    want3 = oracle.search_projection_fine(frame.view, pts3, cam, pyr, 4.0, 0.8)
+    m3, k2p3, valid3, _ = ctx.SearchByProjection2Resident(fd, lm, cam, pyr, 4.0, 0.8, keep_assignment=False)
+    assert m3 == want3[0] and np.array_equal(k2p3, want3[1])
+
+
+def S_map(so, frame, feats, rng, n):
+    from snakeorb import synthetic as S
+
+    return S.map_points_from_keypoints(frame.kp, frame.desc, (718.856, 718.856, 607.19, 185.22), rng, n, feats["scales"])
+
+
 @pytest.mark.parametrize("motion", [0, 1, 2])
 def test_search_by_projection_coarse(so, ctx, oracle, feats, motion):
     rng, frame, mp, cam, pyr = _c3(so, feats, 12 + motion, 3000)
