@@ -745,6 +745,19 @@ def main():
             gpu_ms = (time.perf_counter() - t0) / 20 * 1e3
             next_rows["search_projection_c3"] = {"ms_per_call": gpu_ms, "map_points": 20000, "frame_keypoints": int(fr.view.n),
                                                  "matches": int(mres[0]), "path": "host structs in, host results out"}
+            # the same search with the frame and the local map resident on the device (snk_frame_dev / snk_localmap): what is
+            # left per call is the kernels and the download of the per-point flags and the assignment
+            fdv, lmv = ctxn.frame_dev(fr.view), ctxn.localmap(20000)
+            lmv.upload(pts)
+            for _ in range(3):
+                ctxn.SearchByProjection2Resident(fdv, lmv, camk, pyrk, 4.0, 0.8, keep_assignment=False)
+            lmv.upload(pts)
+            t0 = time.perf_counter()
+            for _ in range(20):
+                mres2 = ctxn.SearchByProjection2Resident(fdv, lmv, camk, pyrk, 4.0, 0.8, keep_assignment=False)
+            res_ms = (time.perf_counter() - t0) / 20 * 1e3
+            next_rows["search_projection_c3"].update({"resident_ms_per_call": res_ms, "resident_matches": int(mres2[0]),
+                                                      "resident_path": "frame and local map on the device, flags and assignment downloaded"})
             d1 = dk[:1000]
             d2 = np.concatenate([S.flip_bits(d1[rngn.permutation(1000)[:600]], rngn, 12), dk[1000:1400]])
             fv1, fv2 = MD.featvec(d1, rngn), MD.featvec(d2, rngn)
@@ -762,6 +775,12 @@ def main():
                 for _ in range(3):
                     oracle_py.search_projection_fine(fr.view, pts, camk, pyrk, 4.0, 0.8)
                 next_rows["search_projection_c3"]["cpu_port_ms_per_call_1_thread"] = (time.perf_counter() - t0) / 3 * 1e3
+                ops3 = oracle_py.search_projection_fine(fr.view, pts, camk, pyrk, 4.0, 0.8)[-1]  # distance() calls of the reference
+                next_rows["search_projection_c3"].update({"pair_ops_per_call": int(ops3),
+                                                          "pair_ops_per_s_resident": ops3 / (res_ms * 1e-3)})
+                opsb = oracle_py.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)[-1]
+                next_rows["match_bow_c4"].update({"pair_ops_per_call": int(opsb),
+                                                  "pair_ops_per_s": opsb / (next_rows["match_bow_c4"]["ms_per_call"] * 1e-3)})
                 t0 = time.perf_counter()
                 for _ in range(10):
                     oracle_py.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
