@@ -3,6 +3,8 @@
 #include "orb_kernels.cuh"
 #include "image_kernels.cuh"
 
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: ranges cost nothing unless a profiler is attached
+
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -674,6 +676,26 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         cudaEventRecord(ev[0], st);
     }
 
+    nvtxRangePushA("snk_orb_enqueue");
+    struct NvtxPop
+    {
+        ~NvtxPop() { nvtxRangePop(); }
+    } nvtx_pop_enqueue;
+    struct NvtxStage  // one open stage range at a time, closed on every return path
+    {
+        bool open = false;
+        void next(const char* name)
+        {
+            if (open) nvtxRangePop();
+            nvtxRangePushA(name);
+            open = true;
+        }
+        ~NvtxStage()
+        {
+            if (open) nvtxRangePop();
+        }
+    } nvtx_stage;
+    nvtx_stage.next("snk:level0");
     // stage 0: level 0. Device input is used in place (the reference copies it, ORBExtractor.cpp:269; nothing reads the
     // copy's apron, so aliasing is equivalent). Host input is copied straight into the level-0 buffer.
     // the kernels read rows as aligned 32-bit words and the FAST tiles through TMA (16-byte base / pitch / stride)
@@ -708,6 +730,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
     if (prof) cudaEventRecord(ev[1], st);
 
+    nvtx_stage.next("snk:pyramid");
     // stage 1: pyramid chain
     for (int l = 1; l < P.nlevels; ++l)
     {
@@ -723,6 +746,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
     if (prof) cudaEventRecord(ev[2], st);
 
+    nvtx_stage.next("snk:blur+fast");
     // blur of every level: on the side stream unless stages are being timed
     const bool overlap = !prof && h->side_stream && h->ev_fork && h->ev_join;
     if (overlap)
@@ -744,6 +768,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     ++nl[2];
     if (prof) cudaEventRecord(ev[3], st);
 
+    nvtx_stage.next("snk:distribute");
     // stage 3: quadtree distribution per (level, image)
     // the dense (level, image) problems run in their own launch (larger shared-memory array, fewer blocks per SM) on a
     // second stream beside the ordinary ones; on ordinary images that launch's blocks return at once
@@ -778,6 +803,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     }
     if (prof) cudaEventRecord(ev[5], st);
 
+    nvtx_stage.next("snk:describe");
     // stage 5: orientation + descriptors + output records
     k_describe<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, 0, st>>>(
         P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t, h->d_moment_tab);
