@@ -876,24 +876,24 @@ def main():
         e2e_bytes = sum(algorithmic_bytes(n_kp_step / NI, n_cand_img)[k] for k in ("pyramid", "fast", "blur", "describe"))
         extraction_ms = sum(stage.values())
         kname = {"fast": "k_fast_group", "pyramid": "k_resize"}.get(dom, "k_" + dom)
-        # DRAM traffic of that kernel: dram__bytes_read + dram__bytes_write of the committed `ncu --set full` capture
-        # (profiles/*_ncu_summary.csv, a 128-image launch of this same command), scaled to this launch's image count
+        # DRAM traffic of that kernel: dram__bytes_read + dram__bytes_write of the committed `ncu --set full` capture of THIS
+        # command at THIS launch shape (profiles/r2n_ncu_summary.csv: 512 images per launch, base units), per launch
         traffic, traffic_src, limiter = None, None, None
         try:
             import csv
-            import glob
 
-            newest = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_summary.csv")))[-1]
-            rows_ = [r for r in csv.reader(open(newest)) if r and r[0] == kname]
+            cap = os.path.join(ROOT, "profiles", "r2n_ncu_summary.csv")
+            cap_images = 512
+            rows_ = [r for r in csv.reader(open(cap)) if r and r[0] == kname and float(r[9]) > 5e6]  # skip launches whose blocks return at once
             if rows_:
-                per_img = (sum(float(r[2]) + float(r[3]) for r in rows_) * 1e6) / 128.0  # Mbyte columns, 128 images per capture
-                traffic = per_img * NI / max(launches[dom], 1)
-                traffic_src = os.path.relpath(newest, ROOT) + " (128-image capture, scaled per image)"
+                per_img = sum(float(r[2]) + float(r[3]) for r in rows_) / cap_images
+                traffic = per_img * NI / len(rows_)
+                traffic_src = os.path.relpath(cap, ROOT) + f" ({cap_images}-image launches, the bench's own shape)"
                 # what the kernel is bound by when it is not the memory system: share of the issue slots it uses (same capture)
                 limiter = {"what": "instruction issue (integer byte-SIMD, shared-memory lists), not DRAM",
                            "issue_active_pct": sum(float(r[6]) for r in rows_) / len(rows_),
                            "dram_pct_of_peak": sum(float(r[4]) for r in rows_) / len(rows_),
-                           "warp_instructions_per_image": sum(float(r[9]) for r in rows_) / 128.0}
+                           "warp_instructions_per_image": sum(float(r[9]) for r in rows_) / cap_images}
         except Exception:  # noqa: BLE001
             traffic = None
         roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",

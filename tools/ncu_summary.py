@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Reduce an `ncu --set full` report to the per-launch columns quoted in DESIGN.md / profiles/*_ncu_summary.csv.
+"""Reduce an `ncu --set full` report to the per-launch columns quoted in DESIGN.md / profiles/*_ncu_summary.csv
+(base units: bytes, ns, plain counts - bench.py reads the DRAM byte columns).
 
     python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/r1x_ncu_summary.csv
 """
@@ -28,7 +29,7 @@ COLS = [
 
 
 def main(rep, out):
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], check=True, capture_output=True,
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--print-units", "base"], check=True, capture_output=True,
                          text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     head, units, body = rows[0], rows[1], rows[2:]
