@@ -882,13 +882,13 @@ def main():
         try:
             import csv
 
-            cap = os.path.join(ROOT, "profiles", "r2n_ncu_summary.csv")
+            cap_csv = os.path.join(ROOT, "profiles", "r2n_ncu_summary.csv")
             cap_images = 512
-            rows_ = [r for r in csv.reader(open(cap)) if r and r[0] == kname and float(r[9]) > 5e6]  # skip launches whose blocks return at once
+            rows_ = [r for r in csv.reader(open(cap_csv)) if r and r[0] == kname and float(r[9]) > 5e6]  # skip launches whose blocks return at once
             if rows_:
                 per_img = sum(float(r[2]) + float(r[3]) for r in rows_) / cap_images
                 traffic = per_img * NI / len(rows_)
-                traffic_src = os.path.relpath(cap, ROOT) + f" ({cap_images}-image launches, the bench's own shape)"
+                traffic_src = os.path.relpath(cap_csv, ROOT) + f" ({cap_images}-image launches, the bench's own shape)"
                 # what the kernel is bound by when it is not the memory system: share of the issue slots it uses (same capture)
                 limiter = {"what": "instruction issue (integer byte-SIMD, shared-memory lists), not DRAM",
                            "issue_active_pct": sum(float(r[6]) for r in rows_) / len(rows_),
