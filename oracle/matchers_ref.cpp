@@ -1,7 +1,9 @@
 // TEST INFRASTRUCTURE ONLY — CPU oracle, never on the product path.
 //
-// Restatements of the reference's Hamming matchers on the plain structs of include/snakeorb.h (the originals are
-// entangled with Snake::Frame / Map / globals and do not compile standalone). Paths relative to /root/reference/.
+// Restatements of the reference's Hamming matchers on the plain structs of include/snakeorb.h. PINNED: the originals
+// (which work on Snake::Frame / Map / globals) are compiled unmodified into oracle/_ref/libsnake_ref.so
+// (ref_snake_shim.cpp) and tests/test_oracle_snake_live.py requires identical results on 1000 seeded cases per function;
+// their outputs are frozen in tests/golden/golden_snake.npz. Paths relative to /root/reference/.
 // Built with -ffp-contract=off: the double geometry is evaluated unfused, in the reference's operation order.
 #include "matchers_ref.h"
 
@@ -781,9 +783,8 @@ int match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int n2, const snk_
     return nmatches;
 }
 // ---------------------------------------------------------------------------------------------
-// Local mapping / loop closing searches. The Snake classes around them (Keyframe, MapPoint, Map)
-// cannot be compiled outside the full application, so these follow the source text; the pieces they call that CAN
-// be compiled from the reference (ScalePyramid, EpipolarDistanceSquared, distance) are pinned in tests/.
+// Local mapping / loop closing searches, pinned like the rest of this file on the reference's own
+// compiled MappingORBMatcher.cpp / LoopORBMatcher.cpp / MonoInitializer.cpp (oracle/_ref/libsnake_ref.so).
 // ---------------------------------------------------------------------------------------------
 // Saiga::EpipolarDistanceSquared (saiga/vision/reconstruction/Epipolar.cpp:47-56). F * (x, y, 1) as Eigen evaluates a
 // fixed 3x3 * 3x1 product with its default SSE2 packets: rows 0 and 1 accumulate left to right, the scalar tail row
