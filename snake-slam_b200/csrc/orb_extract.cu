@@ -105,6 +105,9 @@ struct snk_orb
     int map0_pitch = 0;
     size_t map0_stride = 0;
     std::vector<TileDev> tiles;
+    std::vector<BlurTask> blur_tasks;  // k_blur_mma: (level, 24-column strip, 128-row band)
+    BlurTask* d_blur_tasks = nullptr;
+    bool blur_mma = true;              // SNK_BLUR_MMA=0 selects the dp4a kernel k_blur (A/B comparisons)
     int node_cap = 0;
     size_t qt_smem = 0;
     int qt_big_levels = 0, qt_big_cap = 0;  // levels [0, qt_big_levels) run in their own launch with qt_big_cap keypoints in smem
@@ -149,7 +152,7 @@ struct snk_orb
             if (p) cudaFree(p);
             p = nullptr;
         };
-        F(d_pyr), F(d_gauss), F(d_cells), F(d_groups), F(d_tiles), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
+        F(d_pyr), F(d_gauss), F(d_cells), F(d_groups), F(d_tiles), F(d_blur_tasks), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
             F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
         for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_rows[l]);
         rows = cols = 0;
@@ -187,6 +190,16 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
     return SNK_OK;
 }
 
+// cv::GaussianBlur of every level (ORBExtractor.cpp:213): the tensor-core kernel, or the dp4a one for A/B runs
+static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
+{
+    if (h->blur_mma)
+        k_blur_mma<<<dim3((unsigned)(h->blur_tasks.size() + BM_WARPS - 1) / BM_WARPS, n_imgs), BM_WARPS * 32, 0, st>>>(
+            P, h->d_blur_tasks, (int)h->blur_tasks.size());
+    else
+        k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
+}
+
 static int orb_allocate(snk_orb* h, int rows, int cols)
 {
     if (h->rows == rows && h->cols == cols) return SNK_OK;
@@ -207,6 +220,11 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->cells.clear();
     h->fast_rows = h->fast_list = 0;
     h->tiles.clear();
+    h->blur_tasks.clear();
+    {
+        const char* e = getenv("SNK_BLUR_MMA");
+        h->blur_mma   = !(e && e[0] == '0');
+    }
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
     int cell_cap = 1, sel_acc = 0;
@@ -282,6 +300,9 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         sel_acc += lv.quota + 4;
         for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
+        for (int band = 0; band < (lv.h + BM_BAND - 1) / BM_BAND; ++band)
+            for (int strip = 0; strip < (lv.w + BM_COLS - 1) / BM_COLS; ++strip)
+                h->blur_tasks.push_back(BlurTask{(short)l, (short)strip, (short)band, 0});
     }
     P.cells_per_img = (int)h->cells.size();
     cell_cap        = align_up(cell_cap, 4);  // every cell list starts 16-byte aligned (k_distribute gathers with uint4 loads)
@@ -436,6 +457,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     SNK_CUDA(cudaMemcpy(h->d_cells, h->cells.data(), h->cells.size() * sizeof(CellDev), cudaMemcpyHostToDevice));
     SNK_CUDA(cudaMalloc(&h->d_tiles, h->tiles.size() * sizeof(TileDev)));
     SNK_CUDA(cudaMemcpy(h->d_tiles, h->tiles.data(), h->tiles.size() * sizeof(TileDev), cudaMemcpyHostToDevice));
+    SNK_CUDA(cudaMalloc(&h->d_blur_tasks, h->blur_tasks.size() * sizeof(BlurTask)));
+    SNK_CUDA(cudaMemcpy(h->d_blur_tasks, h->blur_tasks.data(), h->blur_tasks.size() * sizeof(BlurTask), cudaMemcpyHostToDevice));
     const size_t cand_n = (size_t)B * P.cand_per_img;
     SNK_CUDA(cudaMalloc(&h->d_cand, cand_n * 4));
     SNK_CUDA(cudaMalloc(&h->d_workA, cand_n * 4));
@@ -753,7 +776,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
     {
         SNK_CUDA(cudaEventRecord(h->ev_fork, st));
         SNK_CUDA(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
-        k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, h->side_stream>>>(P, h->d_tiles, (int)h->tiles.size());
+        launch_blur(h, P, n_imgs, h->side_stream);
         SNK_CUDA(cudaEventRecord(h->ev_join, h->side_stream));
         ++nl[4];
     }
@@ -798,7 +821,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         SNK_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     else
     {
-        k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
+        launch_blur(h, P, n_imgs, st);
         ++nl[4];
     }
     if (prof) cudaEventRecord(ev[5], st);

@@ -1147,3 +1147,5 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
     }  // keypoints of this warp
 }
 }  // namespace snk
+
+#include "blur_mma.cuh"
