@@ -1,29 +1,37 @@
-// 7x7 Gaussian blur as two exact integer banded contractions on the tensor cores (included by orb_kernels.cuh).
+// 7x7 Gaussian blur as two exact banded contractions on the tensor cores (included by orb_kernels.cuh).
 //
 // cv::GaussianBlur(level, 7x7, sigma 2, REFLECT_101) on 8-bit data is exact integer arithmetic: a row
 // pass with the 8-bit kernel w = {18,34,48,56,48,34,18} (sum 256) giving 16-bit values, a column pass with the same
 // kernel giving 24.16 fixed point, one rounding at the end: out = (sum_ij w_i w_j in[r+i-3][c+j-3] + 32768) >> 16.
-// Both passes are multiplications with banded matrices, so they run as mma.sync.m16n8k32 (u8 x u8 -> s32):
-//   row pass     D1[16 rows x 8 cols]  = In[16 rows x 32 cols] (A, row-major: 4 consecutive pixels per register, as they
-//                                         lie in memory)  x  Bh[32 x 8] (B: the band, constants in registers)
-//   column pass  Out[16 rows x 8 cols] = Bv[16 x 32 rows] (A: the band, constants)  x  D1[32 rows x 8 cols] (B), once for
-//                                         the low and once for the high byte of the 16-bit D1: acc_lo + 256 acc_hi
-// A K window of 32 holds the 7-tap band of 24 (row pass) / 16 (column pass) outputs: 32 multiply-adds per output and
-// pass instead of 7 — the price of the tensor pipe, paid where it is idle; the ALU pipe, which bounds the dp4a kernel
-// (k_blur: 28.7 thread-instructions per pixel), is left with the loads, the byte shuffles and the final rounding.
+// Both passes are multiplications with banded matrices. They are chained in registers, transposed, so that the
+// accumulator layout of the first is the operand layout of the second (no shared-memory round trip, no shuffles):
+//   row pass     D1t[16 out cols x 8 rows] = Bh[16 out cols x 32 in cols] (A: the band, constants)
+//                                            x Int[32 in cols x 8 rows]   (B: 4 consecutive pixels of a row per register,
+//                                                                             exactly as they lie in memory)
+//                mma.sync.m16n8k32 u8 x u8 -> s32. A thread ends up with D1t[col g / g+8][rows 2t, 2t+1]: two consecutive
+//                ROWS of one column — which is what the A operand of m16n8k16 wants along K.
+//   column pass  Outt[16 cols x 8 out rows] = D1t[16 cols x 16 rows] (A: two row-pass tiles, from registers)
+//                                             x Bv[16 rows x 8 out rows] (B: the band, constants)
+//                mma.sync.m16n8k16 f16 x f16 -> f32, once for the low and once for the high byte of the 16-bit D1t. Bytes
+//                enter as the f16 numbers 1024 + b (bit pattern 0x6400 | b: no conversion instruction), weights are small
+//                integers, every partial sum is an integer below 2^24: the f32 accumulation is exact. The accumulator
+//                starts at 2^23 - 1024 * 256 (+ 32768 for the low byte), so the result's mantissa bits ARE the integer.
+// Output rows [8j+4, 8j+12) use row tiles j and j+1 (rows 8j .. 8j+15): each row tile serves two steps without moving.
+// A K window of 32 (16) holds the 7-tap band of 16 (8) outputs: 32 + 2 x 16 multiply-adds per pixel instead of 14 — the
+// price of the tensor pipe, paid where it is idle; the ALU pipe, which bounds the dp4a kernel (k_blur: 28.7
+// thread-instructions per pixel), is left with byte packing and the final shift.
 // Borders: REFLECT_101 folds the taps that fall outside back onto pixels inside, i.e. only the band matrices of the
-// first / last strip and of the first / last row step differ (weights of folded taps add up); pixels outside are
-// loaded as zero and carry zero weight.
-// A warp owns a strip of 24 output columns and walks down a band of rows in steps of 16; the row-pass results of the 32
-// rows a step needs live in a shared-memory ring (stored transposed, 16-bit), each step adds 16 new rows.
+// first / last strip and of the first / last steps differ (weights of folded taps add up, their sum stays 256); pixels
+// outside are loaded as zero and carry zero weight.
 #pragma once
+#include <cuda_fp16.h>
 
 namespace snk
 {
-constexpr int BM_COLS  = 24;   // output columns per strip (three n-tiles of 8)
-constexpr int BM_BAND  = 128;  // output rows per warp task
+constexpr int BM_COLS  = 16;   // output columns per strip (M of both contractions)
+constexpr int BM_BLOCKS = 16;  // 8-row output blocks per warp task (128 rows)
+constexpr int BM_BAND  = 8 * BM_BLOCKS;
 constexpr int BM_WARPS = 8;
-constexpr int BM_CSTRIDE = 36;  // u16 entries per ring column (32 row slots + padding): 72 bytes, keeps the stores conflict-free
 
 struct BlurTask
 {
@@ -36,11 +44,18 @@ __device__ __forceinline__ void mma_u8(int (&d)[4], const unsigned (&a)[4], unsi
                  : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
 }
+__device__ __forceinline__ void mma_f16(float (&d)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1,
+                                        float c)
+{
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c));
+}
 
 // weight with which input position `in` (inside [0, len)) enters output position `out` under reflect-101
 __device__ __forceinline__ unsigned band_weight(int in, int out, int len)
 {
-    if (in < 0 || in >= len) return 0u;
+    if (in < 0 || in >= len || out < 0 || out >= len) return 0u;
     unsigned s = 0;
 #pragma unroll
     for (int d = -3; d <= 3; ++d)
@@ -56,19 +71,25 @@ __device__ __forceinline__ unsigned tap_weight(int d)
     const unsigned j = (unsigned)(d + 3);
     return j <= 6u ? (unsigned)((0x12223038302212ull >> (8 * j)) & 0xffu) : 0u;
 }
-// four consecutive input positions in0 .. in0+3 -> one packed register (byte i = weight of in0 + i).
-// interior: no tap of this output is folded and every input it uses exists
+__device__ __forceinline__ unsigned weight_of(int in, int out, int len, bool interior)
+{
+    return interior ? tap_weight(in - out) : band_weight(in, out, len);
+}
+// four consecutive input positions in0 .. in0+3 as bytes of one register (u8 operand)
 __device__ __forceinline__ unsigned band_word(int in0, int out, int len, bool interior)
 {
-    if (interior)
-        return tap_weight(in0 - out) | (tap_weight(in0 + 1 - out) << 8) | (tap_weight(in0 + 2 - out) << 16) | (tap_weight(in0 + 3 - out) << 24);
-    return band_weight(in0, out, len) | (band_weight(in0 + 1, out, len) << 8) | (band_weight(in0 + 2, out, len) << 16) |
-           (band_weight(in0 + 3, out, len) << 24);
+    return weight_of(in0, out, len, interior) | (weight_of(in0 + 1, out, len, interior) << 8) |
+           (weight_of(in0 + 2, out, len, interior) << 16) | (weight_of(in0 + 3, out, len, interior) << 24);
+}
+// two consecutive input positions as an f16 pair (small integers: exact)
+__device__ __forceinline__ unsigned band_half2(int in0, int out, int len, bool interior)
+{
+    const __half2 h = __floats2half2_rn((float)weight_of(in0, out, len, interior), (float)weight_of(in0 + 1, out, len, interior));
+    return *reinterpret_cast<const unsigned*>(&h);
 }
 
 __global__ void __launch_bounds__(BM_WARPS * 32) k_blur_mma(PyrDev P, const BlurTask* __restrict__ tasks, int n_tasks)
 {
-    __shared__ __align__(16) uint16_t ring_all[BM_WARPS][BM_COLS * BM_CSTRIDE];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int task = blockIdx.x * BM_WARPS + wid;
     if (task >= n_tasks) return;
@@ -78,104 +99,63 @@ __global__ void __launch_bounds__(BM_WARPS * 32) k_blur_mma(PyrDev P, const Blur
     const int W = L.w, H = L.h, pitch = L.pitch, gpitch = L.gauss_pitch;
     const uint8_t* src = L.img + (size_t)img * L.img_stride;
     uint8_t* dst       = L.gauss + (size_t)img * L.gauss_stride;
-    uint16_t* ring     = ring_all[wid];
     const int g = lane >> 2, t = lane & 3;  // mma fragment coordinates: group id, thread in group
 
     const int c0   = T.strip * BM_COLS;   // first output column of the strip
-    const int cwin = c0 - 4;              // first input column of the 32-wide window (4-byte aligned)
-    const int rb   = T.band * BM_BAND, re = min(rb + BM_BAND, H);
+    const int cwin = c0 - 8;              // first input column of the 32-wide window (holds c0-3 .. c0+18; 8-byte aligned)
+    // output blocks jb .. je-1; block j = rows [8j+4, 8j+12) from row tiles j and j+1; block -1 holds rows 0..3
+    const int jb = T.band * BM_BLOCKS - 1, je = min(jb + BM_BLOCKS, (H + 3) / 8);
 
-    // ---- row-pass band: B fragments of the three n-tiles. b0: k = 4t..4t+3, b1: k = 16+4t..; n = g ----
-    unsigned bh[3][2];
+    // ---- row-pass band (A of the u8 mma): a0 (col g, k 4t..), a1 (col g+8, k 4t..), a2 / a3: k + 16 ----
     const bool strip_interior = c0 >= 3 && c0 + BM_COLS + 3 <= W;  // warp-uniform
-#pragma unroll
-    for (int nt = 0; nt < 3; ++nt)
-    {
-        const int out = c0 + 8 * nt + g;
-        bh[nt][0] = band_word(cwin + 4 * t, out, W, strip_interior);
-        bh[nt][1] = band_word(cwin + 16 + 4 * t, out, W, strip_interior);
-    }
-    // column-pass band away from the top / bottom of the image: the same registers for every step
-    unsigned av_in[4];
-    av_in[0] = band_word(4 * t, 8 + g, 0, true);
-    av_in[1] = band_word(4 * t, 16 + g, 0, true);
-    av_in[2] = band_word(16 + 4 * t, 8 + g, 0, true);
-    av_in[3] = band_word(16 + 4 * t, 16 + g, 0, true);
+    unsigned ah[4];
+    ah[0] = band_word(cwin + 4 * t, c0 + g, W, strip_interior);
+    ah[1] = band_word(cwin + 4 * t, c0 + g + 8, W, strip_interior);
+    ah[2] = band_word(cwin + 16 + 4 * t, c0 + g, W, strip_interior);
+    ah[3] = band_word(cwin + 16 + 4 * t, c0 + g + 8, W, strip_interior);
+    // ---- column-pass band away from the top / bottom (B of the f16 mma): b0 (k 2t, 2t+1; out row g), b1: k + 8;
+    //      window row k is image row 8j + k, output row g is image row 8j + 4 + g ----
+    const unsigned bv_in0 = band_half2(2 * t, 4 + g, 0, true), bv_in1 = band_half2(2 * t + 8, 4 + g, 0, true);
 
-    // one row-pass tile: 16 rows starting at rt -> ring slots (rt - origin) & 31 ..; origin = rb - 8
-    const int origin = rb - 8;
-    auto row_pass = [&](int rt) {
-        unsigned a[4];
-        const int r_lo = rt + g, r_hi = rt + g + 8;
-        const int cA = cwin + 4 * t, cB = cwin + 16 + 4 * t;
-        const bool rl = r_lo >= 0 && r_lo < H, rh = r_hi >= 0 && r_hi < H;
-        const bool ca = cA >= 0 && cA < pitch, cb = cB >= 0 && cB < pitch;
-        a[0] = (rl && ca) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r_lo * pitch + cA)) : 0u;
-        a[1] = (rh && ca) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r_hi * pitch + cA)) : 0u;
-        a[2] = (rl && cb) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r_lo * pitch + cB)) : 0u;
-        a[3] = (rh && cb) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r_hi * pitch + cB)) : 0u;
-        const int s_lo = (rt - origin + g) & 31, s_hi = (rt - origin + g + 8) & 31;
-#pragma unroll
-        for (int nt = 0; nt < 3; ++nt)
-        {
-            int d[4];
-            mma_u8(d, a, bh[nt][0], bh[nt][1]);
-            // d0: (row g, col 2t), d1: (row g, col 2t+1), d2 / d3: row g+8 — stored transposed: ring[col][row slot]
-            uint16_t* col = ring + (8 * nt + 2 * t) * BM_CSTRIDE;
-            col[s_lo]              = (uint16_t)d[0];
-            col[BM_CSTRIDE + s_lo] = (uint16_t)d[1];
-            col[s_hi]              = (uint16_t)d[2];
-            col[BM_CSTRIDE + s_hi] = (uint16_t)d[3];
-        }
+    // one row-pass tile: rows 8j .. 8j+7 -> f16 operand pairs (low byte, high byte) for columns g and g+8
+    const unsigned k64 = 0x64646464u;
+    auto row_tile = [&](int j, unsigned& lo_a, unsigned& lo_b, unsigned& hi_a, unsigned& hi_b) {
+        const int r = 8 * j + g, cA = cwin + 4 * t, cB = cwin + 16 + 4 * t;
+        const bool rv = r >= 0 && r < H;
+        const unsigned b0 = (rv && cA >= 0 && cA < pitch) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r * pitch + cA)) : 0u;
+        const unsigned b1 = (rv && cB >= 0 && cB < pitch) ? __ldg(reinterpret_cast<const unsigned*>(src + (size_t)r * pitch + cB)) : 0u;
+        int d[4];
+        mma_u8(d, ah, b0, b1);
+        // d0, d1: column g, rows 2t, 2t+1; d2, d3: column g+8. 16-bit values; bytes become f16 numbers 1024 + b
+        const unsigned pa = __byte_perm((unsigned)d[0], (unsigned)d[1], 0x5410), pb = __byte_perm((unsigned)d[2], (unsigned)d[3], 0x5410);
+        lo_a = __byte_perm(pa, k64, 0x4240), hi_a = __byte_perm(pa, k64, 0x4341);
+        lo_b = __byte_perm(pb, k64, 0x4240), hi_b = __byte_perm(pb, k64, 0x4341);
     };
 
-    row_pass(rb - 8);  // rows [rb-8, rb+8): the upper half of the first window
-    for (int r0 = rb; r0 < re; r0 += 16)
+    unsigned la0, lb0, ha0, hb0, la1, lb1, ha1, hb1;  // tile j (upper half of the window) and tile j+1
+    row_tile(jb, la0, lb0, ha0, hb0);
+    for (int j = jb; j < je; ++j)
     {
-        row_pass(r0 + 8);  // rows [r0+8, r0+24): the lower half of this step's window [r0-8, r0+24)
-        __syncwarp();
-        // ---- column-pass band: A fragment (rows of Out x rows of D1). a0: (out g, k 4t..), a1: (out g+8, k 4t..), a2 / a3: k+16
-        const int rwin = r0 - 8;
-        unsigned av[4] = {av_in[0], av_in[1], av_in[2], av_in[3]};
-        if (r0 < 3 || r0 + 16 + 3 > H)  // warp-uniform: a tap of this step's outputs is folded
+        row_tile(j + 1, la1, lb1, ha1, hb1);
+        unsigned bv0 = bv_in0, bv1 = bv_in1;
+        const int rout = 8 * j + 4;  // first output row of the block
+        if (rout < 3 || rout + 8 + 3 > H)  // warp-uniform: a tap of this block's outputs is folded (or the block leaves the image)
         {
-            av[0] = band_word(rwin + 4 * t, r0 + g, H, false);
-            av[1] = band_word(rwin + 4 * t, r0 + g + 8, H, false);
-            av[2] = band_word(rwin + 16 + 4 * t, r0 + g, H, false);
-            av[3] = band_word(rwin + 16 + 4 * t, r0 + g + 8, H, false);
+            bv0 = band_half2(8 * j + 2 * t, rout + g, H, false);
+            bv1 = band_half2(8 * j + 2 * t + 8, rout + g, H, false);
         }
-        const int s0 = (rwin - origin) & 31;  // ring slot of window row 0 (0 or 16)
+        float fl[4], fh[4];
+        mma_f16(fl, la0, lb0, la1, lb1, bv0, bv1, 8388608.0f - 262144.0f + 32768.0f);
+        mma_f16(fh, ha0, hb0, ha1, hb1, bv0, bv1, 8388608.0f - 262144.0f);
+        // d0: (col g, out row 2t), d1: (col g, out row 2t+1), d2 / d3: col g+8
 #pragma unroll
-        for (int nt = 0; nt < 3; ++nt)
+        for (int i = 0; i < 4; ++i)
         {
-            // B fragment: column n = g of this n-tile, rows k = 4t..4t+3 (b0) and 16+4t.. (b1): 4 consecutive ring slots each
-            const uint16_t* col = ring + (8 * nt + g) * BM_CSTRIDE;
-            const uint2 x0 = *reinterpret_cast<const uint2*>(col + ((s0 + 4 * t) & 31));
-            const uint2 x1 = *reinterpret_cast<const uint2*>(col + ((s0 + 16 + 4 * t) & 31));
-            const unsigned lo0 = __byte_perm(x0.x, x0.y, 0x6420), hi0 = __byte_perm(x0.x, x0.y, 0x7531);
-            const unsigned lo1 = __byte_perm(x1.x, x1.y, 0x6420), hi1 = __byte_perm(x1.x, x1.y, 0x7531);
-            int dl[4], dh[4];
-            mma_u8(dl, av, lo0, lo1);
-            mma_u8(dh, av, hi0, hi1);
-            const int col_out = c0 + 8 * nt + 2 * t;
-            if (col_out < W)
-            {
-                const unsigned v0 = (unsigned)(dl[0] + (dh[0] << 8) + 32768) >> 16, v1 = (unsigned)(dl[1] + (dh[1] << 8) + 32768) >> 16;
-                const unsigned v2 = (unsigned)(dl[2] + (dh[2] << 8) + 32768) >> 16, v3 = (unsigned)(dl[3] + (dh[3] << 8) + 32768) >> 16;
-                const int ra = r0 + g, rbb = r0 + g + 8;
-                if (col_out + 1 < W)
-                {
-                    if (ra < re) *reinterpret_cast<uint16_t*>(dst + (size_t)ra * gpitch + col_out) = (uint16_t)(v0 | (v1 << 8));
-                    if (rbb < re) *reinterpret_cast<uint16_t*>(dst + (size_t)rbb * gpitch + col_out) = (uint16_t)(v2 | (v3 << 8));
-                }
-                else
-                {
-                    if (ra < re) dst[(size_t)ra * gpitch + col_out] = (uint8_t)v0;
-                    if (rbb < re) dst[(size_t)rbb * gpitch + col_out] = (uint8_t)v2;
-                }
-            }
+            const unsigned v = (((unsigned)__float_as_int(fl[i]) & 0x7fffffu) + (((unsigned)__float_as_int(fh[i]) & 0x7fffffu) << 8)) >> 16;
+            const int row = rout + 2 * t + (i & 1), col = c0 + g + 8 * (i >> 1);
+            if (row >= 0 && row < H && col < W) dst[(size_t)row * gpitch + col] = (uint8_t)v;
         }
-        __syncwarp();  // the next step overwrites the half of the ring this step read first
+        la0 = la1, lb0 = lb1, ha0 = ha1, hb0 = hb1;
     }
 }
 }  // namespace snk

@@ -300,7 +300,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         sel_acc += lv.quota + 4;
         for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
-        for (int band = 0; band < (lv.h + BM_BAND - 1) / BM_BAND; ++band)
+        for (int band = 0; band < (lv.h + 4 + BM_BAND - 1) / BM_BAND; ++band)  // blocks start at row -4
             for (int strip = 0; strip < (lv.w + BM_COLS - 1) / BM_COLS; ++strip)
                 h->blur_tasks.push_back(BlurTask{(short)l, (short)strip, (short)band, 0});
     }
