@@ -107,7 +107,7 @@ struct snk_orb
     std::vector<TileDev> tiles;
     std::vector<BlurTask> blur_tasks;  // k_blur_mma: (level, 24-column strip, 128-row band)
     BlurTask* d_blur_tasks = nullptr;
-    bool blur_mma = true;              // SNK_BLUR_MMA=0 selects the dp4a kernel k_blur (A/B comparisons)
+    bool blur_mma = false;             // SNK_BLUR_MMA=1 selects the tensor-core kernel k_blur_mma (exact, measured slower: DESIGN.md 6b)
     int node_cap = 0;
     size_t qt_smem = 0;
     int qt_big_levels = 0, qt_big_cap = 0;  // levels [0, qt_big_levels) run in their own launch with qt_big_cap keypoints in smem
@@ -190,11 +190,11 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
     return SNK_OK;
 }
 
-// cv::GaussianBlur of every level (ORBExtractor.cpp:213): the tensor-core kernel, or the dp4a one for A/B runs
+// cv::GaussianBlur of every level (ORBExtractor.cpp:213): the dp4a kernel, or the tensor-core one (SNK_BLUR_MMA=1) for A/B runs
 static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
 {
     if (h->blur_mma)
-        k_blur_mma<<<dim3((unsigned)(h->blur_tasks.size() + BM_WARPS - 1) / BM_WARPS, n_imgs), BM_WARPS * 32, 0, st>>>(
+        k_blur_mma<<<dim3((unsigned)h->blur_tasks.size(), n_imgs), BM_WARPS * 32, 0, st>>>(
             P, h->d_blur_tasks, (int)h->blur_tasks.size());
     else
         k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
@@ -223,7 +223,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->blur_tasks.clear();
     {
         const char* e = getenv("SNK_BLUR_MMA");
-        h->blur_mma   = !(e && e[0] == '0');
+        h->blur_mma   = e && e[0] == '1';
     }
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
@@ -301,7 +301,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
         for (int band = 0; band < (lv.h + 4 + BM_BAND - 1) / BM_BAND; ++band)  // blocks start at row -4
-            for (int strip = 0; strip < (lv.w + BM_COLS - 1) / BM_COLS; ++strip)
+            for (int strip = 0; strip < (lv.w + BM_TILE_W - 1) / BM_TILE_W; ++strip)  // strip = CTA tile of 128 columns
                 h->blur_tasks.push_back(BlurTask{(short)l, (short)strip, (short)band, 0});
     }
     P.cells_per_img = (int)h->cells.size();
