@@ -59,8 +59,8 @@ __device__ __forceinline__ void mma_f16(float (&d)[4], unsigned a0, unsigned a1,
 // tap weight: w[d + 3] for -3 <= d <= 3, else 0
 __device__ __forceinline__ unsigned tap_weight(int d)
 {
-    const unsigned j = (unsigned)(d + 3);
-    return j <= 6u ? (unsigned)((0x12223038302212ull >> (8 * j)) & 0xffu) : 0u;
+    const unsigned j = (unsigned)(d < 0 ? -d : d);  // the kernel is symmetric: {56, 48, 34, 18} by |d|
+    return j <= 3u ? ((0x12223038u >> (8 * j)) & 0xffu) : 0u;
 }
 // weight with which input position `in` enters output position `out` under reflect-101: tap position p = out + d lands
 // on `in` directly (p == in), through the left mirror (p == -in, in > 0) or through the right one (p == 2 (len-1) - in,
@@ -87,107 +87,104 @@ __device__ __forceinline__ unsigned band_half2(int in0, int out, int len, bool i
     return *reinterpret_cast<const unsigned*>(&h);
 }
 
-// One CTA = BM_WARPS adjacent strips (128 output columns) walking down a band of rows, one 8-row block per step. The
-// CTA stages each 8-row input tile in shared memory with coalesced 16-byte cp.async copies (zero-filled outside the
-// image) two tiles ahead, the warps read their operand words from it without bank conflicts, write their 16 x 8 output
-// bytes into a shared tile, and the CTA stores that tile one step later as whole 128-byte rows.
-constexpr int BM_TILE_W   = BM_WARPS * BM_COLS;  // 128 output columns per CTA
-constexpr int BM_IN_CHUNKS = 10;                 // 16-byte chunks per staged row: columns ct0-16 .. ct0+143
-constexpr int BM_IN_WORDS = 44;                  // row stride in words (176 bytes): operand reads hit 32 different banks
-constexpr int BM_OUT_BYTES = 4 * (BM_TILE_W / 4 + 1);  // 132: the byte stores of a warp hit 8 different banks
+// A warp works alone on BM_STRIPS adjacent strips (64 output columns) and walks down a band of rows, one 8-row block
+// per step: no shared-memory staging, no barrier. Loads: lane (g, t) reads words t, t+4, .. of row g of the tile — every
+// word is the second operand register of one strip and the first of the next. Stores: a 4 x 4 byte transpose over four
+// lanes (two shuffles) turns the accumulator layout into whole words of four consecutive columns.
+constexpr int BM_STRIPS = 4;
+constexpr int BM_TILE_W = BM_STRIPS * BM_COLS;  // 64 output columns per warp
 
-__global__ void __launch_bounds__(BM_WARPS * 32) k_blur_mma(PyrDev P, const BlurTask* __restrict__ tasks, int n_tasks)
+__global__ void __launch_bounds__(BM_WARPS * 32, 4) k_blur_mma(PyrDev P, const BlurTask* __restrict__ tasks, int n_tasks)
 {
-    __shared__ __align__(16) unsigned s_in[2][8][BM_IN_WORDS];
-    __shared__ __align__(16) uint8_t s_out[2][8][BM_OUT_BYTES];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    __shared__ uint4 s_ah[BM_WARPS][BM_STRIPS][32];  // row-pass band registers per strip (they differ at the image's sides)
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int task = blockIdx.x * BM_WARPS + wid;
+    if (task >= n_tasks) return;
     const int img    = blockIdx.y;
-    const BlurTask T = tasks[blockIdx.x];
+    const BlurTask T = tasks[task];
     const LevelDev& L = P.lv[T.level];
     const int W = L.w, H = L.h, pitch = L.pitch, gpitch = L.gauss_pitch;
     const uint8_t* src = L.img + (size_t)img * L.img_stride;
     uint8_t* dst       = L.gauss + (size_t)img * L.gauss_stride;
     const int g = lane >> 2, t = lane & 3;  // mma fragment coordinates: group id, thread in group
 
-    const int ct0  = T.strip * BM_TILE_W;      // first output column of the CTA tile
-    const int c0   = ct0 + wid * BM_COLS;      // first output column of this warp's strip
-    const int cwin = c0 - 8;                   // first input column of the warp's 32-wide window (holds c0-3 .. c0+18)
+    const int ct0 = T.strip * BM_TILE_W;  // first output column of the warp's tile; strip s covers [ct0 + 16 s, +16)
     // output blocks jb .. je-1; block j = rows [8j+4, 8j+12) from row tiles j and j+1; block -1 holds rows 0..3
     const int jb = T.band * BM_BLOCKS - 1, je = min(jb + BM_BLOCKS, (H + 3) / 8);
 
-    // ---- staging: thread `tid` < 80 copies chunk tid % 10 of row tid / 10 of every tile (16 bytes, zero-filled outside) ----
-    const int st_r = tid / BM_IN_CHUNKS, st_c = tid - st_r * BM_IN_CHUNKS;
-    const int st_col = ct0 - 16 + 16 * st_c;
-    const bool st_on = tid < 8 * BM_IN_CHUNKS, st_col_ok = st_col >= 0 && st_col < pitch;
-    const unsigned st_dst = (unsigned)__cvta_generic_to_shared(&s_in[0][st_r][4 * st_c]);
-    const uint8_t* st_src = src + st_col;
-    auto stage = [&](int j) {
-        if (st_on)
+    // ---- row-pass band (A of the u8 mma) per strip: a0 (col g, k 4t..), a1 (col g+8, k 4t..), a2 / a3: k + 16;
+    //      the strip's 32-wide input window starts at c0 - 8 (holds c0-3 .. c0+18) ----
+    {
+        // away from the image's sides every strip has the same band: in - out = (4t + i - 8) - g
+        const uint4 a_in = make_uint4(band_word(4 * t - 8, g, 0, true), band_word(4 * t - 8, g + 8, 0, true),
+                                      band_word(4 * t + 8, g, 0, true), band_word(4 * t + 8, g + 8, 0, true));
+#pragma unroll
+        for (int s = 0; s < BM_STRIPS; ++s)
         {
-            const int row  = 8 * j + st_r;
-            const bool ok  = st_col_ok && row >= 0 && row < H;
-            const uint8_t* ga = ok ? st_src + (size_t)row * pitch : src;
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(st_dst + (unsigned)((j & 1) * (8 * BM_IN_WORDS * 4))), "l"(ga),
-                         "r"(ok ? 16 : 0)
-                         : "memory");
+            const int c0 = ct0 + s * BM_COLS, cwin = c0 - 8;
+            uint4 a = a_in;
+            if (!(c0 >= 3 && c0 + BM_COLS + 3 <= W))  // warp-uniform: a tap of this strip is folded at the left / right side
+                a = make_uint4(band_word(cwin + 4 * t, c0 + g, W, false), band_word(cwin + 4 * t, c0 + g + 8, W, false),
+                               band_word(cwin + 16 + 4 * t, c0 + g, W, false), band_word(cwin + 16 + 4 * t, c0 + g + 8, W, false));
+            s_ah[wid][s][lane] = a;
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-
-    // ---- row-pass band (A of the u8 mma): a0 (col g, k 4t..), a1 (col g+8, k 4t..), a2 / a3: k + 16 ----
-    const bool strip_interior = c0 >= 3 && c0 + BM_COLS + 3 <= W;  // warp-uniform
-    unsigned ah[4];
-    ah[0] = band_word(cwin + 4 * t, c0 + g, W, strip_interior);
-    ah[1] = band_word(cwin + 4 * t, c0 + g + 8, W, strip_interior);
-    ah[2] = band_word(cwin + 16 + 4 * t, c0 + g, W, strip_interior);
-    ah[3] = band_word(cwin + 16 + 4 * t, c0 + g + 8, W, strip_interior);
+    }
+    __syncwarp();
     // ---- column-pass band away from the top / bottom (B of the f16 mma): b0 (k 2t, 2t+1; out row g), b1: k + 8;
     //      window row k is image row 8j + k, output row g is image row 8j + 4 + g ----
     const unsigned bv_in0 = band_half2(2 * t, 4 + g, 0, true), bv_in1 = band_half2(2 * t + 8, 4 + g, 0, true);
 
-    // one row-pass tile from shared memory -> f16 operand pairs (low byte, high byte) for columns g and g+8
+    // loads: word k of the lane = columns ct0 - 8 + 4t + 16k .. +3 of row g of the tile
+    const int lcol = ct0 - 8 + 4 * t;
+    unsigned lmask = 0;  // words of the lane that lie inside the row
+#pragma unroll
+    for (int k = 0; k <= BM_STRIPS; ++k)
+        if (lcol + 16 * k >= 0 && lcol + 16 * k < pitch) lmask |= 1u << k;
+    const uint8_t* lsrc = src + lcol;
+    // stores after the transpose: this lane ends up with row 2t + (gi & 1), columns 4 q + 8 (gi >> 1) .. +3 of each strip
+    const int gi = g & 3, q = g >> 2;
+    const unsigned selA = (gi & 1) ? 0x3715u : 0x6240u, selB = (gi & 2) ? 0x3276u : 0x5410u;
+    const int srow = 2 * t + (gi & 1), scol = ct0 + 4 * q + 8 * (gi >> 1);
+    uint8_t* sdst = dst + scol;
+    unsigned sfull = 0, spart = 0;  // per strip: the lane's word lies fully / partly inside the image
+#pragma unroll
+    for (int s = 0; s < BM_STRIPS; ++s)
+    {
+        const int col = scol + s * BM_COLS;
+        if (col + 4 <= W) sfull |= 1u << s;
+        else if (col < W) spart |= 1u << s;
+    }
     const unsigned k64 = 0x64646464u;
-    const unsigned* in_w = &s_in[0][g][2 + 4 * wid + t];  // the warp's window starts 8 bytes into the staged row; bank 12g + 4 wid + t + 2
-    auto row_tile = [&](int j, unsigned& lo_a, unsigned& lo_b, unsigned& hi_a, unsigned& hi_b) {
-        const unsigned* rowp = in_w + (j & 1) * (8 * BM_IN_WORDS);
+
+    unsigned st[BM_STRIPS][4];  // per strip: f16 operand pairs of the upper row tile (lo / hi byte; columns g / g+8)
+    auto row_ops = [&](const unsigned (&w)[BM_STRIPS + 1], int s, unsigned (&o)[4]) {
+        const uint4 a4 = s_ah[wid][s][lane];
+        const unsigned a[4] = {a4.x, a4.y, a4.z, a4.w};
         int d[4];
-        mma_u8(d, ah, rowp[0], rowp[4]);
+        mma_u8(d, a, w[s], w[s + 1]);
         // d0, d1: column g, rows 2t, 2t+1; d2, d3: column g+8. 16-bit values; bytes become f16 numbers 1024 + b
         const unsigned pa = __byte_perm((unsigned)d[0], (unsigned)d[1], 0x5410), pb = __byte_perm((unsigned)d[2], (unsigned)d[3], 0x5410);
-        lo_a = __byte_perm(pa, k64, 0x4240), hi_a = __byte_perm(pa, k64, 0x4341);
-        lo_b = __byte_perm(pb, k64, 0x4240), hi_b = __byte_perm(pb, k64, 0x4341);
+        o[0] = __byte_perm(pa, k64, 0x4240), o[1] = __byte_perm(pb, k64, 0x4240);  // low bytes: columns g, g+8
+        o[2] = __byte_perm(pa, k64, 0x4341), o[3] = __byte_perm(pb, k64, 0x4341);  // high bytes
     };
-    // the CTA's output tile of block j (rows 8j+4 .. 8j+11): whole 128-byte rows, one word per thread
-    const int fl_col = ct0 + 4 * lane;
-    const unsigned* fl_src = reinterpret_cast<const unsigned*>(&s_out[0][wid][4 * lane]);
-    uint8_t* fl_dst = dst + fl_col;
-    auto flush = [&](int j) {
-        const int row = 8 * j + 4 + wid;
-        if (row >= 0 && row < H && fl_col < W)
-        {
-            const unsigned v = fl_src[(j & 1) * (8 * BM_OUT_BYTES / 4)];
-            uint8_t* o = fl_dst + (size_t)row * gpitch;
-            if (fl_col + 4 <= W)
-                *reinterpret_cast<unsigned*>(o) = v;
-            else
-                for (int b = 0; fl_col + b < W; ++b) o[b] = (uint8_t)(v >> (8 * b));
-        }
+    auto load_tile = [&](int j, unsigned (&w)[BM_STRIPS + 1]) {
+        const int r = 8 * j + g;
+        const unsigned m = (r >= 0 && r < H) ? lmask : 0u;
+        const uint8_t* p = lsrc + (size_t)(m ? r : 0) * pitch;
+#pragma unroll
+        for (int k = 0; k <= BM_STRIPS; ++k) w[k] = (m >> k & 1u) ? __ldg(reinterpret_cast<const unsigned*>(p + 16 * k)) : 0u;
     };
-    uint8_t* so = &s_out[0][2 * t][wid * BM_COLS + g];  // this thread's four output bytes: rows 2t, 2t+1, columns g, g+8
 
-    unsigned la0, lb0, ha0, hb0, la1, lb1, ha1, hb1;  // tile j (upper half of the window) and tile j+1
-    stage(jb);
-    stage(jb + 1);
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    __syncthreads();
-    row_tile(jb, la0, lb0, ha0, hb0);
+    {
+        unsigned w[BM_STRIPS + 1];
+        load_tile(jb, w);
+#pragma unroll
+        for (int s = 0; s < BM_STRIPS; ++s) row_ops(w, s, st[s]);
+    }
     for (int j = jb; j < je; ++j)
     {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncthreads();  // tile j+1 is in shared memory; every warp is done with tile j's buffer and with block j-1's output
-        if (j > jb) flush(j - 1);
-        stage(j + 2);     // into the buffer tile j occupied
-        row_tile(j + 1, la1, lb1, ha1, hb1);
+        unsigned w[BM_STRIPS + 1];
+        load_tile(j + 1, w);
         unsigned bv0 = bv_in0, bv1 = bv_in1;
         const int rout = 8 * j + 4;  // first output row of the block
         if (rout < 3 || rout + 8 + 3 > H)  // warp-uniform: a tap of this block's outputs is folded (or the block leaves the image)
@@ -195,21 +192,36 @@ __global__ void __launch_bounds__(BM_WARPS * 32) k_blur_mma(PyrDev P, const Blur
             bv0 = band_half2(8 * j + 2 * t, rout + g, H, false);
             bv1 = band_half2(8 * j + 2 * t + 8, rout + g, H, false);
         }
-        float fl[4], fh[4];
-        mma_f16(fl, la0, lb0, la1, lb1, bv0, bv1, 8388608.0f - 262144.0f + 32768.0f);
-        mma_f16(fh, ha0, hb0, ha1, hb1, bv0, bv1, 8388608.0f - 262144.0f);
-        // d0: (col g, out row 2t), d1: (col g, out row 2t+1), d2 / d3: col g+8 -> bytes of the CTA's output tile
-        uint8_t* sob = so + (j & 1) * (8 * BM_OUT_BYTES);
+        const int row = rout + srow;
+        const bool row_ok = row >= 0 && row < H;
+        uint8_t* orow = sdst + (size_t)(row_ok ? row : 0) * gpitch;
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int s = 0; s < BM_STRIPS; ++s)
         {
-            const unsigned v = (((unsigned)__float_as_int(fl[i]) & 0x7fffffu) + (((unsigned)__float_as_int(fh[i]) & 0x7fffffu) << 8)) >> 16;
-            sob[(i & 1) * BM_OUT_BYTES + 8 * (i >> 1)] = (uint8_t)v;
+            unsigned nx[4];
+            row_ops(w, s, nx);
+            float fl[4], fh[4];
+            mma_f16(fl, st[s][0], st[s][1], nx[0], nx[1], bv0, bv1, 8388608.0f - 262144.0f + 32768.0f);
+            mma_f16(fh, st[s][2], st[s][3], nx[2], nx[3], bv0, bv1, 8388608.0f - 262144.0f);
+            // result = (lo + 256 hi + 32768) >> 16 = byte 2 of lo_bits + (hi_bits << 8) (the 0x4B exponent bytes cancel out of
+            // byte 2: they sit in byte 3 of lo_bits and leave the word from hi_bits << 8)
+            unsigned sum[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sum[i] = (unsigned)__float_as_int(fl[i]) + ((unsigned)__float_as_int(fh[i]) << 8);
+            const unsigned x = __byte_perm(__byte_perm(sum[0], sum[1], 0x0062), __byte_perm(sum[2], sum[3], 0x0062), 0x5410);
+            // x = [ (row 2t, col g), (row 2t+1, col g), (row 2t, col g+8), (row 2t+1, col g+8) ] -> 4 x 4 transpose over lanes gi = 0..3
+            const unsigned y = __byte_perm(x, __shfl_xor_sync(0xffffffffu, x, 4), selA);
+            const unsigned z = __byte_perm(y, __shfl_xor_sync(0xffffffffu, y, 8), selB);
+            if (row_ok)
+            {
+                uint8_t* o = orow + s * BM_COLS;
+                if (sfull >> s & 1u)
+                    *reinterpret_cast<unsigned*>(o) = z;
+                else if (spart >> s & 1u)
+                    for (int b = 0; scol + s * BM_COLS + b < W; ++b) o[b] = (uint8_t)(z >> (8 * b));
+            }
+            st[s][0] = nx[0], st[s][1] = nx[1], st[s][2] = nx[2], st[s][3] = nx[3];
         }
-        la0 = la1, lb0 = lb1, ha0 = ha1, hb0 = hb1;
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    if (je > jb) flush(je - 1);
 }
 }  // namespace snk

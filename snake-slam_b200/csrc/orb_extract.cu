@@ -194,7 +194,7 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
 static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
 {
     if (h->blur_mma)
-        k_blur_mma<<<dim3((unsigned)h->blur_tasks.size(), n_imgs), BM_WARPS * 32, 0, st>>>(
+        k_blur_mma<<<dim3((unsigned)(h->blur_tasks.size() + BM_WARPS - 1) / BM_WARPS, n_imgs), BM_WARPS * 32, 0, st>>>(
             P, h->d_blur_tasks, (int)h->blur_tasks.size());
     else
         k_blur<<<dim3((unsigned)(h->tiles.size() + 7) / 8, n_imgs), 256, 0, st>>>(P, h->d_tiles, (int)h->tiles.size());
@@ -301,7 +301,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         for (int ty = 0; ty < (lv.h + BL_ROWS - 1) / BL_ROWS; ++ty)
             for (int tx = 0; tx < (lv.w + BL_TW - 1) / BL_TW; ++tx) h->tiles.push_back(TileDev{(short)l, (short)tx, (short)ty, 0});
         for (int band = 0; band < (lv.h + 4 + BM_BAND - 1) / BM_BAND; ++band)  // blocks start at row -4
-            for (int strip = 0; strip < (lv.w + BM_TILE_W - 1) / BM_TILE_W; ++strip)  // strip = CTA tile of 128 columns
+            for (int strip = 0; strip < (lv.w + BM_TILE_W - 1) / BM_TILE_W; ++strip)  // strip = a warp's tile of 64 columns
                 h->blur_tasks.push_back(BlurTask{(short)l, (short)strip, (short)band, 0});
     }
     P.cells_per_img = (int)h->cells.size();
