@@ -20,10 +20,12 @@
 // A K window of 32 (16) holds the 7-tap band of 16 (8) outputs: 32 + 2 x 16 multiply-adds per pixel instead of 14 — the
 // price of the tensor pipe, paid where it is idle; the ALU pipe, which bounds the dp4a kernel (k_blur: 28.7
 // thread-instructions per pixel), is left with byte packing and the final shift.
-// STATUS: an experiment that lost. Byte-exact on every shape and input of tests/test_gpu_extract.py, but 1.01 ms per 512
-// images against 0.62 ms for the dp4a kernel k_blur (B200, profiles/r2m_*): the three tensor instructions per 16 x 8
-// block are free, the 165 other instructions around them (staging, operand packing, un-biasing, byte stores, one
-// barrier per 8 rows) are not; k_blur needs 115 per 128 pixels. Selected with SNK_BLUR_MMA=1; k_blur stays the default.
+// STATUS: the default blur since round 2. Byte-exact on every shape and input of tests/test_gpu_extract.py; 0.586 ms per
+// 512 EuRoC images against 0.62 ms for the dp4a kernel k_blur (SNK_BLUR_MMA=0), 364 M against 513 M warp instructions.
+// Earlier variants on the way (git history): strips with a shared-memory ring between the passes 0.99 ms,
+// register chaining with direct byte stores 1.05 ms, CTA-staged tiles with a barrier per 8 rows 1.01 ms, this one at 92
+// registers 0.89 ms (latency-bound at 25 % occupancy); what is left around the three tensor instructions per 16 x 8 block
+// is ~80 instructions of operand packing, un-biasing, transposing and addressing.
 // Borders: REFLECT_101 folds the taps that fall outside back onto pixels inside, i.e. only the band matrices of the
 // first / last strip and of the first / last steps differ (weights of folded taps add up, their sum stays 256); pixels
 // outside are loaded as zero and carry zero weight.

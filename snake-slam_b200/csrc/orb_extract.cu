@@ -107,7 +107,7 @@ struct snk_orb
     std::vector<TileDev> tiles;
     std::vector<BlurTask> blur_tasks;  // k_blur_mma: (level, 24-column strip, 128-row band)
     BlurTask* d_blur_tasks = nullptr;
-    bool blur_mma = false;             // SNK_BLUR_MMA=1 selects the tensor-core kernel k_blur_mma (exact, measured slower: DESIGN.md 6b)
+    bool blur_mma = true;              // SNK_BLUR_MMA=0 selects the dp4a kernel k_blur (A/B runs; 0.62 against 0.586 ms per 512 images)
     int node_cap = 0;
     size_t qt_smem = 0;
     int qt_big_levels = 0, qt_big_cap = 0;  // levels [0, qt_big_levels) run in their own launch with qt_big_cap keypoints in smem
@@ -190,7 +190,7 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
     return SNK_OK;
 }
 
-// cv::GaussianBlur of every level (ORBExtractor.cpp:213): the dp4a kernel, or the tensor-core one (SNK_BLUR_MMA=1) for A/B runs
+// cv::GaussianBlur of every level (ORBExtractor.cpp:213): the tensor-core kernel, or the dp4a one (SNK_BLUR_MMA=0) for A/B runs
 static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
 {
     if (h->blur_mma)
@@ -223,7 +223,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->blur_tasks.clear();
     {
         const char* e = getenv("SNK_BLUR_MMA");
-        h->blur_mma   = e && e[0] == '1';
+        h->blur_mma   = !(e && e[0] == '0');
     }
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
