@@ -281,7 +281,7 @@ def run_c5(args, env):
     for f in range(rank, F, world):  # every rank writes its share of the frames
         c5_frame(distinct, f, seq.np[f])
     barrier()
-    DCH = max(CPc, 256)  # the device-resident pass has no upload to hide: larger chunks, two lanes
+    DCH = max(CPc, 256)  # the device-resident pass has no upload to hide: larger chunks
     lanes = [Lane(DCH) for _ in range(args.lanes)]
     dev_seq = torch.empty((F, 2, H, W), dtype=torch.uint8, device="cuda")  # 2.7 GB: the sequence resident in HBM
     rc = C.CDLL("libcudart.so").cudaMemcpy(C.c_void_p(dev_seq.data_ptr()), C.c_void_p(seq.ptr), C.c_size_t(seq.nbytes), 1)
@@ -330,12 +330,12 @@ def run_c5(args, env):
 
     for w in range(max(args.warmup, 1)):
         one_pass(f"c5_warm_{w}", False, CPc, len(lanes))
-        one_pass(f"c5_warmd_{w}", True, DCH, min(2, len(lanes)))
+        one_pass(f"c5_warmd_{w}", True, DCH, len(lanes))
     res = {}
     for mode, on_device in (("host", False), ("device", True)):
         times, chunks = [], None
         for k in range(max(args.steps, 1)):
-            dt, mine = one_pass(f"c5_{mode}_{k}", on_device, DCH if on_device else CPc, min(2, len(lanes)) if on_device else len(lanes))
+            dt, mine = one_pass(f"c5_{mode}_{k}", on_device, DCH if on_device else CPc, len(lanes))
             t = torch.tensor([dt], dtype=torch.float64, device="cuda")
             g = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
             if world > 1:
