@@ -139,6 +139,10 @@ SNK_API int snk_orb_fetch_async(snk_orb* h, snk_keypoint_f32* kps, uint64_t* des
  * returns SNK_ERR_CAPACITY (and clears the flag) if any batch since the last check hit one, SNK_OK otherwise. The
  * reference aborts through SAIGA_ASSERT at the equivalent places (ORBExtractor.cpp:184). */
 SNK_API int snk_orb_check(snk_orb* h);
+/* Test hook, no reference counterpart: writes `code` into the device-side fault flag the extraction kernels set when a
+ * capacity guard or the bounded wait on a tile load trips (they cannot be provoked with valid input: the capacities are
+ * proven bounds), so that the reporting paths — snk_orb_fetch, snk_orb_check — can be exercised. */
+SNK_API int snk_orb_debug_set_error(snk_orb* h, int code);
 /* Number of images of the last enqueue (0 before the first one / after an empty one). No reference counterpart. */
 SNK_API int snk_orb_last_batch(const snk_orb* h);
 /* Stream ordering for consumers of snk_orb_device_results (no reference counterpart: its extractors are synchronous).

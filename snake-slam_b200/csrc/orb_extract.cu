@@ -996,6 +996,15 @@ int snk_orb_check(snk_orb* h)
 
 int snk_orb_last_batch(const snk_orb* h) { return h ? h->last_n : 0; }
 
+int snk_orb_debug_set_error(snk_orb* h, int code)
+{
+    SNK_REQUIRE(h && h->rows, "no buffers yet: run one enqueue first");
+    SNK_CUDA(cudaSetDevice(h->prm.device));
+    SNK_CUDA(cudaMemcpyAsync(h->d_err, &code, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    SNK_CUDA(cudaStreamSynchronize(h->stream));
+    return SNK_OK;
+}
+
 int snk_orb_order_stream_after(snk_orb* h, void* stream)
 {
     SNK_REQUIRE(h, "null handle");

@@ -121,3 +121,32 @@ def test_matcher_entry_points_reject_bad_arguments(so, tmp_path):
     # the context still works
     got = ctx.matchKnn2(d, d)
     assert (got["idx0"] == np.arange(10)).all() and (got["dist0"] == 0).all()
+
+
+def test_device_fault_flag_is_reported_once_on_the_async_and_the_sync_path(so):
+    """The kernels' fault flag (capacity guards, bounded TMA wait) cannot be tripped with valid input, so it is injected
+    (snk_orb_debug_set_error): snk_orb_check after an enqueue + fetch_async reports it as SNK_ERR_CAPACITY and clears it;
+    the synchronous fetch does the same; a clean run afterwards is clean."""
+    import ctypes as C
+
+    from snakeorb import synthetic as S
+
+    img = S.image(77, 320, 240)
+    ex = so.ORBExtractor(500, 1.2, 4, 20, 7, max_batch=1)
+    want_k, want_d = ex.Detect(img)
+    lib = so.lib()
+    cap = ex.cap
+    kps, desc, cnt = np.zeros((1, cap), so.KP32), np.zeros((1, cap, 4), np.uint64), np.zeros(1, np.int32)
+    # asynchronous path
+    ex.enqueue_ptr(img.ctypes.data, 1, 240, 320, 320, 320 * 240, False)
+    assert lib.snk_orb_debug_set_error(ex.h, 4) == 0
+    assert lib.snk_orb_fetch_async(ex.h, C.c_void_p(kps.ctypes.data), C.c_void_p(desc.ctypes.data), cap, C.c_void_p(cnt.ctypes.data)) == 0
+    assert lib.snk_orb_check(ex.h) == -3 and b"capacity error 4" in lib.snk_last_error()  # SNK_ERR_CAPACITY
+    assert lib.snk_orb_check(ex.h) == 0  # reported once
+    # synchronous path
+    ex.enqueue_ptr(img.ctypes.data, 1, 240, 320, 320, 320 * 240, False)
+    assert lib.snk_orb_debug_set_error(ex.h, 2) == 0
+    with pytest.raises(so.SnakeOrbError):
+        ex.fetch(1)
+    k2, d2 = ex.Detect(img)
+    assert k2.tobytes() == want_k.tobytes() and d2.tobytes() == want_d.tobytes()
