@@ -352,3 +352,26 @@ def test_random_geometries_fuzz(so, oracle):
         assert_same_features(k, d, k2, d2)
         done += 1
     assert done >= 25
+
+
+def test_blur_every_level_byte_equal_on_random_sizes(so, oracle):
+    """cv::GaussianBlur of every pyramid level (the tensor-core kernel k_blur_mma by default, the dp4a kernel with
+    SNK_BLUR_MMA=0): byte-equal to the oracle on random image sizes — widths and heights of every residue mod 4 / 8 /
+    16 / 64, so that partial last strips, partial last words and the folded taps at all four borders are hit — on noise
+    (every byte matters) and in batches (the image index only offsets the pointers)."""
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(99)
+    for case in range(24):
+        w, h = int(rng.integers(80, 900)), int(rng.integers(80, 600))
+        nl = int(rng.integers(1, 6))
+        if min(w, h) / 1.2 ** (nl - 1) < 70:
+            nl = 1
+        imgs = np.stack([S.adversarial("noise", w, h, 100 + case), S.image(8000 + case, w, h)])
+        ex = so.ORBExtractor(300, 1.2, nl, 20, 7, max_batch=2)
+        ex.DetectBatch(imgs)
+        for b in range(2):
+            ref = oracle.Extractor(300, 1.2, nl, 20, 7, 1)
+            ref.detect(imgs[b])
+            for l in range(nl):
+                assert np.array_equal(ex.GetImage(l, img=b, blurred=True), ref.level(l, blurred=True)), (case, w, h, b, l)
