@@ -101,12 +101,15 @@ __global__ void __launch_bounds__(FASTG_NT) k_fast_group(PyrDev P, const __grid_
     if (tid == 0) s_n1 = s_n2 = 0;
     if (tid < FASTG_CELLS) s_ini[tid] = 0;
     for (int i = tid; i < FASTG_CELLS * 2 * FAST_BMW; i += FASTG_NT) (&bm[0][0][0])[i] = 0;
+    if (wid == 0)
     {
-        // bounded wait: a copy that never completes (bad descriptor) must not hang the device; it is reported instead
+        // bounded wait: a copy that never completes (bad descriptor) must not hang the device; it is reported instead.
+        // One warp polls, the others wait at the barrier below: a polling warp burns issue slots, the kernel's scarce
+        // resource, and the first tile of a CTA is a full DRAM latency away
         const unsigned bar = bar_addr0 + 8u * buf, parity = (unsigned)((kg >> 1) & 1);
         unsigned done = 0;
         for (int spin = 0; !done && spin < (1 << 22); ++spin)
-            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                          : "=r"(done)
                          : "r"(bar), "r"(parity)
                          : "memory");
