@@ -25,7 +25,10 @@
 // Earlier variants on the way (git history): strips with a shared-memory ring between the passes 0.99 ms,
 // register chaining with direct byte stores 1.05 ms, CTA-staged tiles with a barrier per 8 rows 1.01 ms, this one at 92
 // registers 0.89 ms (latency-bound at 25 % occupancy); what is left around the three tensor instructions per 16 x 8 block
-// is ~80 instructions of operand packing, un-biasing, transposing and addressing.
+// is ~80 instructions of operand packing, un-biasing, transposing and addressing. Tile shape sweep afterwards
+// (tools/scratch/blur_variants.sh; strips per warp x CTAs per SM x one-tile-ahead loads): 2/4/ahead 0.581, 3/4 0.617,
+// 3/4/ahead 0.629, 2/5/ahead 0.717, 3/5 0.806, 2/6/ahead 0.815 ms — nothing beyond noise over 4/4 (0.586); more CTAs per
+// SM spill.
 // Borders: REFLECT_101 folds the taps that fall outside back onto pixels inside, i.e. only the band matrices of the
 // first / last strip and of the first / last steps differ (weights of folded taps add up, their sum stays 256); pixels
 // outside are loaded as zero and carry zero weight.
