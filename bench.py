@@ -770,6 +770,18 @@ def main():
                 ctxn.MatchBoW(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
             next_rows["match_bow_c4"] = {"ms_per_call": (time.perf_counter() - t0) / 50 * 1e3, "features": [len(d1), len(d2)],
                                          "matches": int(mb[0]), "path": "host arrays in, host results out"}
+            # the loop detector's candidate loop in one call (snk_match_bow_batch): 20 candidates like the one above
+            cands20 = []
+            for _ in range(20):
+                dc = np.ascontiguousarray(np.concatenate([S.flip_bits(d1[rngn.permutation(1000)[:600]], rngn, 12), dk[1000:1400]]))
+                cands20.append((dc, MD.featvec(dc, rngn), v2))
+            for _ in range(3):
+                ctxn.MatchBoWBatch(d1, fv1, v1, cands20, 50, 0.75)
+            t0 = time.perf_counter()
+            for _ in range(20):
+                nmb, _m = ctxn.MatchBoWBatch(d1, fv1, v1, cands20, 50, 0.75)
+            next_rows["match_bow_c4"].update({"batch20_ms_per_candidate": (time.perf_counter() - t0) / 20 / 20 * 1e3,
+                                              "batch20_matches_mean": float(nmb.mean())})
             if not args.no_cpu:
                 t0 = time.perf_counter()
                 for _ in range(3):

@@ -468,6 +468,22 @@ SNK_API int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t
                           const snk_featvec_view* fv1, const snk_featvec_view* fv2, const uint8_t* valid1,
                           const uint8_t* valid2, int th, float ratio, int32_t* match12, int* n_matches);
 
+/* One keyframe against many: the loop LoopDetector::ComputeSim3(new_kf) runs over candidateKFs
+ * (Snake/LoopClosing/LoopDetector.cpp:384-391 -> :225) calls MatchBoW(new_kf, candidate, ...) once per candidate, and
+ * a call reads nothing an earlier one wrote, so all of them can be issued at once: one upload, one launch (a warp per
+ * (node of keyframe 1, candidate)), one download. match12 is n_cand x n1, row k = the match12 snk_match_bow returns
+ * for candidate k; n_matches[n_cand]. */
+typedef struct snk_bow_candidate
+{
+    const uint64_t* desc; /* n x 4 */
+    int32_t n;
+    const snk_featvec_view* fv;
+    const uint8_t* valid; /* n */
+} snk_bow_candidate;
+SNK_API int snk_match_bow_batch(snk_ctx* c, const uint64_t* d1, int n1, const snk_featvec_view* fv1,
+                                const uint8_t* valid1, const snk_bow_candidate* cands, int n_cand, int th, float ratio,
+                                int32_t* match12, int32_t* n_matches);
+
 /* ---- local-mapping and loop-closing searches -------------------------------------------------
  * All of them are independent per point / feature in the reference (its tmp_flags are never set), so the device
  * evaluates every point at once and the results are listed in the reference's iteration order. */

@@ -485,6 +485,28 @@ def ref_match_bow(d1, d2, fv1, fv2, valid1, valid2, th, ratio):
     return m, m12[:len(d1)]
 
 
+class BowCandidate(C.Structure):
+    """snk_bow_candidate (include/snakeorb.h)"""
+    _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("fv", C.c_void_p), ("valid", C.c_void_p)]
+
+
+def ref_match_bow_batch(d1, fv1, valid1, cands, th, ratio):
+    """The reference's candidate loop (LoopDetector.cpp:384-391 without the early exit): MatchBoW(kf1, cand) for every
+    (d2, fv2, valid2) of cands -> (n_matches[n_cand], match12[n_cand, n1])."""
+    d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+    arr, keep = (BowCandidate * max(len(cands), 1))(), []
+    for k, (d2, fv2, v2) in enumerate(cands):
+        d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+        v2 = np.ascontiguousarray(v2, np.uint8)
+        keep += [d2, v2, fv2]
+        arr[k].desc, arr[k].n, arr[k].fv, arr[k].valid = d2.ctypes.data, len(d2), C.addressof(fv2), v2.ctypes.data
+    m12 = np.zeros((len(cands), max(len(d1), 1)), np.int32)
+    nm = np.zeros(max(len(cands), 1), np.int32)
+    snake_ref().snkref_match_bow_batch(_p(d1), len(d1), C.byref(fv1), _p(np.ascontiguousarray(valid1, np.uint8)), arr, len(cands), th,
+                                       C.c_float(ratio), _p(m12), _p(nm))
+    return nm[:len(cands)], m12[:, :len(d1)]
+
+
 def ref_fuse_search(kf, mask, points, cam, pyr, th, obs_factor, feature_th):
     pts = np.ascontiguousarray(points)
     n = len(pts)

@@ -398,6 +398,53 @@ REF_API int snkref_match_bow(const uint64_t* d1, int n1, const uint64_t* d2, int
     return m;
 }
 
+// ---- the candidate loop around MatchBoW (LoopDetector.cpp:384-391 -> :225), every candidate evaluated ----
+REF_API int snkref_match_bow_batch(const uint64_t* d1, int n1, const snk_featvec_view* fv1, const uint8_t* valid1,
+                                   const snk_bow_candidate* cands, int n_cand, int th, float ratio, int32_t* match12,
+                                   int32_t* n_matches)
+{
+    std::vector<std::unique_ptr<MapPoint>> own;
+    auto fill = [&](Keyframe& kf, int frame_id, const uint64_t* d, int n, const snk_featvec_view* fv, const uint8_t* valid) {
+        kf.frame    = std::make_shared<Frame>(frame_id);
+        kf.frame->N = n;
+        kf.frame->descriptors.resize(n);
+        auto& obs = kf.MapPointRef();
+        obs.assign(n, nullptr);
+        for (int i = 0; i < n; ++i)
+        {
+            kf.frame->descriptors[i] = to_desc(d + 4 * (size_t)i);
+            if (valid[i])
+            {
+                own.push_back(std::make_unique<MapPoint>(i));
+                own.back()->valid = valid[i] == 1;
+                obs[i]            = own.back().get();
+            }
+        }
+        fill_featvec(kf.frame->bow_feature_vec, fv);
+    };
+    Keyframe kf1(0);
+    fill(kf1, 0, d1, n1, fv1, valid1);
+    std::vector<std::unique_ptr<Keyframe>> kfs;
+    std::vector<Keyframe*> ptrs;
+    for (int k = 0; k < n_cand; ++k)
+    {
+        kfs.push_back(std::make_unique<Keyframe>(k + 1));
+        fill(*kfs.back(), k + 1, cands[k].desc, cands[k].n, cands[k].fv, cands[k].valid);
+        ptrs.push_back(kfs.back().get());
+    }
+    std::vector<std::vector<MapPoint*>> all(n_cand);
+#ifdef SNK_USE_ADAPTER
+    snkadapter::LoopORBmatcherB200 lm;
+    const std::vector<int> counts = lm.MatchBoWBatch(&kf1, ptrs, all, th, ratio);
+    for (int k = 0; k < n_cand; ++k) n_matches[k] = counts[k];
+#else
+    for (int k = 0; k < n_cand; ++k) n_matches[k] = LoopORBmatcher::MatchBoW(&kf1, ptrs[k], all[k], th, ratio);
+#endif
+    for (int k = 0; k < n_cand; ++k)
+        for (int i = 0; i < n1; ++i) match12[(size_t)k * n1 + i] = all[k][i] ? all[k][i]->id() : -1;
+    return 0;
+}
+
 // ---- MappingORBMatcher::Fuse(kf, pose, point_mask, LocalMap<FusionPoint>, ...) (MappingORBMatcher.cpp:359-482) ----
 REF_API int snkref_fuse_search(const snk_frame_view* f, const uint8_t* mask, const snk_point_fusion* pts, int n,
                                const snk_camera* cam, const snk_scale_pyramid* sp, float th, float obs_factor,

@@ -23,6 +23,8 @@ struct snk_ctx
     size_t d_cap         = 0;
     int* d_err           = nullptr;
     int* h_pin           = nullptr;  // pinned, 16 ints
+    unsigned char* h_stage = nullptr;  // pinned, growable: host side of batched uploads
+    size_t h_stage_cap     = 0;
 };
 
 namespace
@@ -103,6 +105,7 @@ void snk_ctx_destroy(snk_ctx* c)
     if (c->d_buf) cudaFree(c->d_buf);
     if (c->d_err) cudaFree(c->d_err);
     if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }

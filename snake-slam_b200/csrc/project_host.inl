@@ -285,6 +285,99 @@ int snk_match_bow(snk_ctx* c, const uint64_t* d1, int n1, const uint64_t* d2, in
     return SNK_OK;
 }
 
+// One keyframe against n_cand candidates in one upload, one launch and one download.
+int snk_match_bow_batch(snk_ctx* c, const uint64_t* d1, int n1, const snk_featvec_view* fv1, const uint8_t* valid1,
+                        const snk_bow_candidate* cands, int n_cand, int th, float ratio, int32_t* match12, int32_t* n_matches)
+{
+    SNK_REQUIRE(c && fv1 && n1 >= 0 && n_cand >= 0, "bad argument");
+    SNK_REQUIRE(n_cand == 0 || (cands && n_matches), "null candidate arrays");
+    SNK_REQUIRE(n1 == 0 || n_cand == 0 || (d1 && valid1 && match12), "null keyframe-1 arrays");
+    SNK_REQUIRE(n_cand <= 65535, "at most 65535 candidates per call");
+    for (int k = 0; k < n_cand; ++k) n_matches[k] = 0;
+    for (size_t i = 0; i < (size_t)n_cand * n1; ++i) match12[i] = -1;
+    if (n1 == 0 || n_cand == 0 || fv1->n_nodes == 0) return SNK_OK;
+    const int e1 = fv1->offsets[fv1->n_nodes];
+    for (int i = 0; i < e1; ++i) SNK_REQUIRE(fv1->indices[i] >= 0 && fv1->indices[i] < n1, "fv1 index out of range");
+    // layout of the blob: keyframe 1 (descriptors, valid, node ids, offsets, indices), the candidate table, then each
+    // candidate's arrays; every array 16-byte aligned
+    size_t off = 0, m2 = 0;
+    auto put   = [&](size_t bytes) {
+        const size_t at = off;
+        off             = align_up(off + bytes, (size_t)16);
+        return at;
+    };
+    const size_t o_d1 = put(32 * (size_t)n1), o_v1 = put(n1), o_ids1 = put(4 * (size_t)fv1->n_nodes),
+                 o_of1 = put(4 * (size_t)(fv1->n_nodes + 1)), o_in1 = put(4 * (size_t)e1), o_tab = put(sizeof(BowCandDev) * (size_t)n_cand);
+    std::vector<BowCandDev> tab(n_cand);
+    for (int k = 0; k < n_cand; ++k)
+    {
+        const snk_bow_candidate& q = cands[k];
+        SNK_REQUIRE(q.n >= 0 && q.fv && (q.n == 0 || (q.desc && q.valid)), "candidate %d: null arrays", k);
+        const int nn = q.n == 0 ? 0 : q.fv->n_nodes, e2 = nn ? q.fv->offsets[nn] : 0;
+        SNK_REQUIRE(e2 < (1 << 20), "candidate %d: feature vector too long", k);
+        for (int i = 0; i < e2; ++i) SNK_REQUIRE(q.fv->indices[i] >= 0 && q.fv->indices[i] < q.n, "candidate %d: fv index out of range", k);
+        BowCandDev& t = tab[k];
+        t.n_nodes = nn, t.n2 = q.n, t.m2_off = (int)m2;
+        t.desc_off  = (int)put(32 * (size_t)q.n);
+        t.valid_off = (int)put(q.n);
+        t.ids_off   = (int)put(4 * (size_t)nn);
+        t.offs_off  = (int)put(4 * (size_t)(nn + 1));
+        t.inds_off  = (int)put(4 * (size_t)e2);
+        m2 += align_up((size_t)q.n, (size_t)16);
+        SNK_REQUIRE(off < ((size_t)1 << 31), "batch too large (2 GiB of candidate data)");
+    }
+    SNK_CUDA(cudaSetDevice(c->device));
+    if (off > c->h_stage_cap)
+    {
+        SNK_CUDA(cudaStreamSynchronize(c->stream));
+        if (c->h_stage) SNK_CUDA(cudaFreeHost(c->h_stage));
+        c->h_stage = nullptr, c->h_stage_cap = 0;
+        SNK_CUDA(cudaMallocHost(&c->h_stage, off + off / 4));
+        c->h_stage_cap = off + off / 4;
+    }
+    unsigned char* h = c->h_stage;
+    auto cp          = [&](size_t at, const void* src, size_t bytes) {
+        if (bytes) std::memcpy(h + at, src, bytes);
+    };
+    cp(o_d1, d1, 32 * (size_t)n1), cp(o_v1, valid1, n1), cp(o_ids1, fv1->node_ids, 4 * (size_t)fv1->n_nodes);
+    cp(o_of1, fv1->offsets, 4 * (size_t)(fv1->n_nodes + 1)), cp(o_in1, fv1->indices, 4 * (size_t)e1);
+    cp(o_tab, tab.data(), sizeof(BowCandDev) * (size_t)n_cand);
+    for (int k = 0; k < n_cand; ++k)
+    {
+        const snk_bow_candidate& q = cands[k];
+        const BowCandDev& t        = tab[k];
+        cp(t.desc_off, q.desc, 32 * (size_t)q.n), cp(t.valid_off, q.valid, q.n);
+        if (t.n_nodes)
+        {
+            cp(t.ids_off, q.fv->node_ids, 4 * (size_t)t.n_nodes), cp(t.offs_off, q.fv->offsets, 4 * (size_t)(t.n_nodes + 1));
+            cp(t.inds_off, q.fv->indices, 4 * (size_t)q.fv->offsets[t.n_nodes]);
+        }
+    }
+    int rc = ctx_reserve(c, padded<unsigned char>(off) + padded<uint8_t>(std::max(m2, (size_t)1)) + padded<int>((size_t)n_cand * n1) +
+                                padded<int>(n_cand));
+    if (rc) return rc;
+    Carver cv{c->d_buf};
+    auto* blob = cv.take<unsigned char>(off);
+    auto* dm2  = cv.take<uint8_t>(std::max(m2, (size_t)1));
+    int* m12   = cv.take<int>((size_t)n_cand * n1);
+    int* dn    = cv.take<int>(n_cand);
+    cudaStream_t st = c->stream;
+    SNK_CUDA(cudaMemcpyAsync(blob, h, off, cudaMemcpyHostToDevice, st));
+    SNK_CUDA(cudaMemsetAsync(dm2, 0, std::max(m2, (size_t)1), st));
+    SNK_CUDA(cudaMemsetAsync(m12, 0xff, 4 * (size_t)n_cand * n1, st));
+    SNK_CUDA(cudaMemsetAsync(dn, 0, 4 * (size_t)n_cand, st));
+    const FeatVecDev f1{fv1->n_nodes, reinterpret_cast<const int*>(blob + o_ids1), reinterpret_cast<const int*>(blob + o_of1),
+                        reinterpret_cast<const int*>(blob + o_in1)};
+    k_match_bow_batch<<<dim3((fv1->n_nodes + 3) / 4, n_cand), 128, 0, st>>>(blob, reinterpret_cast<const BowCandDev*>(blob + o_tab),
+                                                                             reinterpret_cast<const uint64_t*>(blob + o_d1), f1, blob + o_v1, n1,
+                                                                             th, ratio, m12, dm2, dn);
+    SNK_CUDA(cudaGetLastError());
+    SNK_CUDA(cudaMemcpyAsync(match12, m12, 4 * (size_t)n_cand * n1, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaMemcpyAsync(n_matches, dn, 4 * (size_t)n_cand, cudaMemcpyDeviceToHost, st));
+    SNK_CUDA(cudaStreamSynchronize(st));
+    return SNK_OK;
+}
+
 
 // ---- device-resident frame and local map (no reference counterpart: there both live in host memory, Snake/Map/Frame.h,
 // Snake/Map/LocalMap.h:83-186) -----------------------------------------------------------------------------------------

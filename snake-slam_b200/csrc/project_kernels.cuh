@@ -454,13 +454,11 @@ struct FeatVecDev
     const int* offsets;
     const int* indices;
 };
-__global__ void k_match_bow(const uint64_t* __restrict__ d1, const uint64_t* __restrict__ d2, FeatVecDev fv1, FeatVecDev fv2,
-                            const uint8_t* __restrict__ valid1, const uint8_t* __restrict__ valid2, int th, float ratio,
-                            int* __restrict__ match12, uint8_t* __restrict__ matched2, int* __restrict__ n_matches)
+__device__ __forceinline__ void match_bow_node(const uint64_t* __restrict__ d1, const uint64_t* __restrict__ d2, const FeatVecDev& fv1,
+                                               const FeatVecDev& fv2, const uint8_t* __restrict__ valid1,
+                                               const uint8_t* __restrict__ valid2, int th, float ratio, int* __restrict__ match12,
+                                               uint8_t* __restrict__ matched2, int* __restrict__ n_matches, int a, int lane)
 {
-    const int a    = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (a >= fv1.n_nodes) return;
     const int id = fv1.node_ids[a];
     int lo = 0, hi = fv2.n_nodes;
     while (lo < hi)
@@ -517,5 +515,34 @@ __global__ void k_match_bow(const uint64_t* __restrict__ d1, const uint64_t* __r
         __syncwarp();
     }
     if (lane == 0 && matches) atomicAdd(n_matches, matches);
+}
+__global__ void k_match_bow(const uint64_t* __restrict__ d1, const uint64_t* __restrict__ d2, FeatVecDev fv1, FeatVecDev fv2,
+                            const uint8_t* __restrict__ valid1, const uint8_t* __restrict__ valid2, int th, float ratio,
+                            int* __restrict__ match12, uint8_t* __restrict__ matched2, int* __restrict__ n_matches)
+{
+    const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (a >= fv1.n_nodes) return;
+    match_bow_node(d1, d2, fv1, fv2, valid1, valid2, th, ratio, match12, matched2, n_matches, a, threadIdx.x & 31);
+}
+
+// One keyframe against many (LoopDetector::ComputeSim3(new_kf) walks candidateKFs, LoopDetector.cpp:384-391; MatchBoW reads
+// nothing the previous candidate's pass wrote): blockIdx.y = candidate, all candidates' arrays in one uploaded blob.
+struct BowCandDev
+{
+    int desc_off, valid_off, ids_off, offs_off, inds_off;  // byte offsets into the blob
+    int n_nodes, n2, m2_off;                               // m2_off: offset of the candidate's vbMatched2 flags
+};
+__global__ void k_match_bow_batch(const unsigned char* __restrict__ blob, const BowCandDev* __restrict__ cands, const uint64_t* __restrict__ d1,
+                                  FeatVecDev fv1, const uint8_t* __restrict__ valid1, int n1, int th, float ratio,
+                                  int* __restrict__ match12, uint8_t* __restrict__ matched2, int* __restrict__ n_matches)
+{
+    const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (a >= fv1.n_nodes) return;
+    const BowCandDev cd = cands[blockIdx.y];
+    if (cd.n_nodes == 0 || cd.n2 == 0) return;
+    const FeatVecDev fv2{cd.n_nodes, reinterpret_cast<const int*>(blob + cd.ids_off), reinterpret_cast<const int*>(blob + cd.offs_off),
+                         reinterpret_cast<const int*>(blob + cd.inds_off)};
+    match_bow_node(d1, reinterpret_cast<const uint64_t*>(blob + cd.desc_off), fv1, fv2, valid1, blob + cd.valid_off, th, ratio,
+                   match12 + (size_t)blockIdx.y * n1, matched2 + cd.m2_off, n_matches + blockIdx.y, a, threadIdx.x & 31);
 }
 }  // namespace snk

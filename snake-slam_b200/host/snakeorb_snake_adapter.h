@@ -223,27 +223,6 @@ class LoopORBmatcherB200
 
     int MatchBoW(Snake::KeyFrame* pKF1, Snake::KeyFrame* pKF2, std::vector<Snake::MapPoint*>& vpMatches12, int threshold, float ratio)
     {
-        struct Csr
-        {
-            std::vector<int32_t> ids, off, idx;
-            snk_featvec_view view{};
-            explicit Csr(const Snake::FeatureVector& fv)
-            {
-                off.push_back(0);
-                for (auto& node : fv)
-                {
-                    ids.push_back((int32_t)node.first);
-                    for (int i : node.second) idx.push_back(i);
-                    off.push_back((int32_t)idx.size());
-                }
-                view = snk_featvec_view{(int32_t)ids.size(), ids.data(), off.data(), idx.data()};
-            }
-        };
-        auto valid = [](const std::vector<Snake::MapPoint*>& mps) {
-            std::vector<uint8_t> v(std::max<size_t>(mps.size(), 1), 0);
-            for (size_t i = 0; i < mps.size(); ++i) v[i] = (mps[i] && !mps[i]->isBad()) ? 1 : 0;
-            return v;
-        };
         auto& mp1 = pKF1->GetMapPointMatches();
         auto& mp2 = pKF2->GetMapPointMatches();
         Csr fv1(pKF1->frame->bow_feature_vec), fv2(pKF2->frame->bow_feature_vec);
@@ -260,6 +239,68 @@ class LoopORBmatcherB200
         return n;
     }
 
+    // MatchBoW(pKF1, candidates[k], vpMatches12[k], ...) for every k in one device call: what the candidate loop of
+    // LoopDetector::ComputeSim3(new_kf) (LoopDetector.cpp:384-391) asks for, ahead of its early exit. Returns the match counts.
+    std::vector<int> MatchBoWBatch(Snake::KeyFrame* pKF1, const std::vector<Snake::KeyFrame*>& candidates,
+                                   std::vector<std::vector<Snake::MapPoint*>>& vpMatches12, int threshold, float ratio)
+    {
+        auto& mp1 = pKF1->GetMapPointMatches();
+        Csr fv1(pKF1->frame->bow_feature_vec);
+        const auto v1 = valid(mp1);
+        const size_t K = candidates.size(), n1 = mp1.size();
+        std::vector<Csr> fvs;
+        std::vector<std::vector<uint8_t>> vs;
+        fvs.reserve(K), vs.reserve(K);  // the views point into the elements: no reallocation after this
+        std::vector<snk_bow_candidate> cs(K);
+        for (size_t k = 0; k < K; ++k)
+        {
+            auto& mp2 = candidates[k]->GetMapPointMatches();
+            fvs.emplace_back(candidates[k]->frame->bow_feature_vec);
+            fvs.back().rebind();
+            vs.push_back(valid(mp2));
+            cs[k] = snk_bow_candidate{reinterpret_cast<const uint64_t*>(candidates[k]->frame->descriptors.data()), (int32_t)mp2.size(),
+                                      &fvs[k].view, vs[k].data()};
+        }
+        std::vector<int32_t> m12(std::max<size_t>(K * n1, 1), -1);
+        std::vector<int> counts(std::max<size_t>(K, 1), 0);
+        check(snk_match_bow_batch(c_, reinterpret_cast<const uint64_t*>(pKF1->frame->descriptors.data()), (int)n1, &fv1.view, v1.data(),
+                                  cs.data(), (int)K, threshold, ratio, m12.data(), counts.data()),
+              "snk_match_bow_batch");
+        vpMatches12.assign(K, std::vector<Snake::MapPoint*>(n1, nullptr));
+        for (size_t k = 0; k < K; ++k)
+        {
+            auto& mp2 = candidates[k]->GetMapPointMatches();
+            for (size_t i = 0; i < n1; ++i)
+                if (m12[k * n1 + i] >= 0) vpMatches12[k][i] = mp2[m12[k * n1 + i]];
+        }
+        counts.resize(K);
+        return counts;
+    }
+
+   private:
+    struct Csr  // FeatureVector (MiniBow2.h:98-132) as the CSR arrays of snk_featvec_view
+    {
+        std::vector<int32_t> ids, off, idx;
+        snk_featvec_view view{};
+        explicit Csr(const Snake::FeatureVector& fv)
+        {
+            off.push_back(0);
+            for (auto& node : fv)
+            {
+                ids.push_back((int32_t)node.first);
+                for (int i : node.second) idx.push_back(i);
+                off.push_back((int32_t)idx.size());
+            }
+            rebind();
+        }
+        void rebind() { view = snk_featvec_view{(int32_t)ids.size(), ids.data(), off.data(), idx.data()}; }
+    };
+    static std::vector<uint8_t> valid(const std::vector<Snake::MapPoint*>& mps)
+    {
+        std::vector<uint8_t> v(std::max<size_t>(mps.size(), 1), 0);
+        for (size_t i = 0; i < mps.size(); ++i) v[i] = (mps[i] && !mps[i]->isBad()) ? 1 : 0;
+        return v;
+    }
    private:
     snk_ctx* c_ = nullptr;
 };

@@ -88,6 +88,11 @@ class FeatVecView(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("node_ids", C.c_void_p), ("offsets", C.c_void_p), ("indices", C.c_void_p)]
 
 
+class BowCandidate(C.Structure):
+    """snk_bow_candidate"""
+    _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("fv", C.POINTER(FeatVecView)), ("valid", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -519,6 +524,22 @@ class Context:
         _check(lib().snk_match_bow(self.c, _p(d1), len(d1), _p(d2), len(d2), C.byref(fv1), C.byref(fv2), _p(valid1),
                                    _p(valid2), th, C.c_float(ratio), _p(m12), C.byref(m)))
         return m.value, m12[:len(d1)]
+
+    def MatchBoWBatch(self, d1, fv1, valid1, cands, th, ratio):
+        """MatchBoW of one keyframe against every (d2, fv2, valid2) of `cands` in one call (snk_match_bow_batch) ->
+        (n_matches[n_cand], match12[n_cand, n1])."""
+        d1 = np.ascontiguousarray(d1, np.uint64).reshape(-1, 4)
+        keep, arr = [], (BowCandidate * max(len(cands), 1))()
+        for k, (d2, fv2, v2) in enumerate(cands):
+            d2 = np.ascontiguousarray(d2, np.uint64).reshape(-1, 4)
+            v2 = np.ascontiguousarray(v2, np.uint8)
+            keep += [d2, v2, fv2]
+            arr[k].desc, arr[k].n, arr[k].fv, arr[k].valid = d2.ctypes.data, len(d2), C.pointer(fv2), v2.ctypes.data
+        m12 = np.zeros((len(cands), max(len(d1), 1)), np.int32)
+        nm = np.zeros(max(len(cands), 1), np.int32)
+        _check(lib().snk_match_bow_batch(self.c, _p(d1), len(d1), C.byref(fv1), _p(np.ascontiguousarray(valid1, np.uint8)), arr,
+                                         len(cands), th, C.c_float(ratio), _p(m12), _p(nm)))
+        return nm[:len(cands)], m12[:, :len(d1)] if len(d1) else m12[:, :0]
 
     def computeFeatureGrid(self, bounds, kp_un):
         """FeatureGrid2::create -> (permutation, cells[rows*cols, 2]); `bounds` is a GridView (cells ignored)."""

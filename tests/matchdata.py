@@ -73,6 +73,13 @@ def kf_points(mp, rng, null_frac=0.1):
 
 
 def featvec(desc, rng, n_nodes=100):
+    if len(desc) == 0:  # a keyframe without features: no nodes, offsets = [0]
+        ids, off, idx = np.zeros(1, np.int32), np.zeros(1, np.int32), np.zeros(1, np.int32)
+        fv = snakeorb.FeatVecView()
+        fv.n_nodes = 0
+        fv.node_ids, fv.offsets, fv.indices = ids.ctypes.data, off.ctypes.data, idx.ctypes.data
+        fv._keep = (ids, off, idx)
+        return fv
     ids, off, idx = S.bow_feature_vector(desc, rng, n_nodes)
     fv = snakeorb.FeatVecView()
     fv.n_nodes = len(ids)

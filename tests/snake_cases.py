@@ -235,6 +235,29 @@ def case_bow(seed, big=False):
                 th=int(rng.choice([50, 40, 70])), ratio=float(rng.choice([0.75, 0.6, 0.9])))
 
 
+def case_bow_batch(seed, big=False):
+    """One keyframe against several loop candidates (LoopDetector.cpp:384-391): candidates of different sizes from the
+    same descriptor pool, now and then one without features or one that shares no vocabulary node."""
+    rng = np.random.default_rng([seed, 14])
+    n1 = int(rng.integers(30, 300)) if not big else int(rng.integers(900, 1300))
+    pool = max(4, n1 // 5)
+    base = rng.integers(0, 2**63, (pool, 4)).astype(np.uint64)
+    nodes = int(rng.integers(3, 60)) if not big else 100
+    d1 = np.ascontiguousarray(S.flip_bits(base[rng.integers(0, pool, n1)], rng, 12))
+    fv1 = M.featvec(d1, rng, nodes)
+    v1 = rng.choice([0, 1, 1, 1, 2], n1).astype(np.uint8)
+    cands = []
+    for k in range(int(rng.integers(1, 7)) if not big else 12):
+        kind = rng.random()
+        n2 = 0 if kind < 0.1 else (int(rng.integers(1, 300)) if not big else int(rng.integers(900, 1300)))
+        d2 = np.ascontiguousarray(S.flip_bits(base[rng.integers(0, pool, n2)], rng, 12)).reshape(-1, 4)
+        fv2 = M.featvec(d2, rng, nodes)
+        if 0.1 <= kind < 0.2:  # node ids the first keyframe does not have
+            fv2._keep[0][:] += 100000
+        cands.append((d2, fv2, rng.choice([0, 1, 1, 1, 2], n2).astype(np.uint8)))
+    return dict(d1=d1, fv1=fv1, v1=v1, cands=cands, th=int(rng.choice([50, 40, 70])), ratio=float(rng.choice([0.75, 0.6, 0.9])))
+
+
 def case_fuse(seed, big=False):
     rng, f, mp, cam, th = _projection_inputs(np.random.default_rng([seed, 7]), big, [3.0, 2.5, 4.0, 6.0])
     pts = M.fusion_points(mp, rng)

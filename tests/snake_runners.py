@@ -29,6 +29,15 @@ def _loop_fuse_state(c, bi, bd):
     return [np.array([fused], I32), state, bad]
 
 
+def _bow_loop(c, one):
+    """MatchBoW candidate by candidate -> the batch's output form (n_matches[n_cand], match12[n_cand, n1])."""
+    nm, rows = [], []
+    for d2, fv2, v2 in c["cands"]:
+        m, m12 = one(d2, fv2, (v2 == 1).astype(np.uint8))
+        nm.append(m), rows.append(np.asarray(m12, I32)[:len(c["d1"])])
+    return [np.array(nm, I32), np.stack(rows).astype(I32)]
+
+
 F32_12 = float(np.float32(1.2))
 
 MATCHERS = {
@@ -78,6 +87,16 @@ MATCHERS = {
         lambda O, c: list(O.ref_match_bow(c["d1"], c["d2"], c["fv1"], c["fv2"], c["v1"], c["v2"], c["th"], c["ratio"])),
         lambda O, c: list(O.match_bow(c["d1"], c["d2"], c["fv1"], c["fv2"], *_v01(c), c["th"], c["ratio"])[:2]),
         lambda so, ctx, c: list(ctx.MatchBoW(c["d1"], c["d2"], c["fv1"], c["fv2"], *_v01(c), c["th"], c["ratio"])),
+    ),
+    "match_bow_batch": (
+        SC.case_bow_batch,
+        lambda c: (c["d1"], c["v1"]) + c["fv1"]._keep + tuple(a for d2, fv2, v2 in c["cands"] for a in (d2, v2) + fv2._keep),
+        lambda O, c: list(O.ref_match_bow_batch(c["d1"], c["fv1"], c["v1"], c["cands"], c["th"], c["ratio"])),
+        lambda O, c: _bow_loop(c, lambda d2, fv2, v2: O.match_bow(c["d1"], d2, c["fv1"], fv2, (c["v1"] == 1).astype(np.uint8), v2,
+                                                                  c["th"], c["ratio"])[:2]),
+        lambda so, ctx, c: list(ctx.MatchBoWBatch(c["d1"], c["fv1"], (c["v1"] == 1).astype(np.uint8),
+                                                  [(d2, fv2, (v2 == 1).astype(np.uint8)) for d2, fv2, v2 in c["cands"]], c["th"],
+                                                  c["ratio"])),
     ),
     "mapping_fuse": (
         SC.case_fuse,

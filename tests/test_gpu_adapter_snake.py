@@ -15,7 +15,7 @@ import snake_runners as R
 from test_snake_golden import GOLD, frozen
 
 pytestmark = pytest.mark.gpu
-COVERED = ["stereo", "rgbd", "fine", "coarse", "frame_to_kf", "match_bow"]
+COVERED = ["stereo", "rgbd", "fine", "coarse", "frame_to_kf", "match_bow", "match_bow_batch"]
 
 
 @pytest.fixture(scope="module")

@@ -254,6 +254,35 @@ def test_match_bow(so, ctx, oracle, feats, seed):
     assert m == m2 and np.array_equal(m12, m122) and m > 20 and ops > 1000
 
 
+def test_match_bow_batch_equals_call_by_call(so, ctx, oracle, feats):
+    """snk_match_bow_batch on 20 loop candidates of ~1000 features: every row equals the single-candidate call and the
+    oracle; errors of one candidate are reported with its number."""
+    from snakeorb import synthetic as S
+
+    rng = np.random.default_rng(11)
+    d1 = feats["l"][1][:1000]
+    fv1 = M.featvec(d1, rng)
+    v1 = (rng.random(len(d1)) < 0.7).astype(np.uint8)
+    cands = []
+    for k in range(20):
+        n_true = int(rng.integers(0, 700))
+        d2 = np.concatenate([S.flip_bits(d1[rng.permutation(len(d1))[:n_true]], rng, 12), feats["o"][1][:1000 - n_true]])
+        cands.append((np.ascontiguousarray(d2), M.featvec(d2, rng), (rng.random(len(d2)) < 0.7).astype(np.uint8)))
+    nm, m12 = ctx.MatchBoWBatch(d1, fv1, v1, cands, 50, 0.75)
+    assert m12.shape == (20, 1000) and nm.max() > 100
+    for k, (d2, fv2, v2) in enumerate(cands):
+        m, row = ctx.MatchBoW(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+        mo, rowo, _ = oracle.match_bow(d1, d2, fv1, fv2, v1, v2, 50, 0.75)
+        assert nm[k] == m == mo and np.array_equal(m12[k], row) and np.array_equal(row, rowo), k
+    nm0, m0 = ctx.MatchBoWBatch(d1, fv1, v1, [], 50, 0.75)
+    assert len(nm0) == 0 and m0.shape[0] == 0
+    bad = cands[3][1]._keep[2].copy()
+    cands[3][1]._keep[2][0] = 5000  # feature index beyond the candidate's size
+    with pytest.raises(so.SnakeOrbError, match="candidate 3"):
+        ctx.MatchBoWBatch(d1, fv1, v1, cands, 50, 0.75)
+    cands[3][1]._keep[2][:] = bad
+
+
 def test_stereo_from_rgbd_c4(so, ctx, oracle):
     """Config C4: TUM-shaped RGB-D frame, depth planes 0.5-8 m with 5 % holes, depth camera with distortion."""
     from snakeorb import synthetic as S

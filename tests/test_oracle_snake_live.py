@@ -119,6 +119,21 @@ def test_live_match_bow(ref):
     assert total > 3 * N_CASES
 
 
+def test_live_match_bow_candidate_loop(ref):
+    """The candidate loop of LoopDetector::ComputeSim3 (LoopDetector.cpp:384-391) with every candidate evaluated: the
+    reference's MatchBoW call by call on one source keyframe — what snk_match_bow_batch must return row by row."""
+    import snake_runners as R
+
+    _, _, run_ref, run_oracle, _ = R.MATCHERS["match_bow_batch"]
+    total = 0
+    for seed in range(N_CASES // 4):
+        c = SC.case_bow_batch(seed)
+        want, got = R.norm(run_ref(ref, c)), R.norm(run_oracle(ref, c))
+        assert R.same(want, got), seed
+        total += int(want[0].sum())
+    assert total > N_CASES
+
+
 def test_live_mapping_fuse(ref):
     """MappingORBMatcher::Fuse (MappingORBMatcher.cpp:359-482)."""
     total = 0
