@@ -1,0 +1,391 @@
+// cv::GaussianBlur(7 x 7, sigma 2, BORDER_REFLECT_101) of u8 images on the 5th-generation tensor cores: tcgen05.mma
+// kind::i8 with the accumulators in tensor memory (ORBExtractor.cpp:213; semantics as k_blur / k_blur_mma).
+//
+// EXPERIMENT (round 2, verdict item 3b) — selected with SNK_BLUR_MMA=2; the default stays k_blur_mma (blur_mma.cuh).
+//
+// Both passes of the fixed-point blur are banded matrix products with u8 weights (56 48 34 18, sum 256):
+//   pass 1 (rows):     R[x][y]  = sum_k  Wc[x][k] * I[y][k]        Wc: band over image columns, reflect-101 folded in
+//   pass 2 (columns):  O[x][y'] = sum_y  R[x][y] * Wr[y'][y]       Wr: band over image rows
+//   out = (O + 32768) >> 16
+// Pass 1 is computed TRANSPOSED (M = output columns on the TMEM lanes, N = image rows): the image tile is then the B
+// operand exactly as it lies in memory (row = N index, columns = K, contiguous) and arrives by ONE TMA box with the
+// 128-byte swizzle the MMA wants; and the result has the image rows along the TMEM columns, i.e. along the K dimension
+// of an A operand read from tensor memory — pass 2 takes it from there without a trip through shared memory. R is 16
+// bits wide, the operands are 8: the epilogue of pass 1 reads the s32 accumulators (tcgen05.ld), splits them into low
+// and high bytes and writes two u8 A operands back (tcgen05.st); pass 2 runs once on each, O = O_lo + 256 O_hi.
+// Per tile (UB_OUT_COLS x UB_ROWS_OUT output pixels, UB_K x UB_ROWS_IN input pixels):
+//   TMA load -> 4 MMAs (M 128, N 96, K 32) -> ld / split / st -> 2 x 3 MMAs (M 128, N 80, K 32) -> ld, combine, bytes into
+//   a shared-memory tile -> TMA store (clipped at the image's sides by the tensor map).
+// A CTA owns one column strip of one image and walks down its row tiles: the column band Wc is built once, the row band
+// Wr only when a tile touches the top or the bottom; the next tile's load is in flight while the current one is worked on.
+// TMEM columns: [0,96) pass-1 accumulator, reused as O_lo; [96,120) R_lo, [120,144) R_hi as u8 x 4; [144,224) O_hi.
+#pragma once
+#include <cuda.h>
+
+#include <cstdint>
+
+#include "blur_weights.cuh"
+
+#ifdef UB_DEBUG_CLOCKS
+__device__ long long ub_clk[16];
+#define UB_T(i) { const long long t_ = clock64(); t_acc[i] += t_ - t_prev; t_prev = t_; }
+#else
+#define UB_T(i)
+#endif
+
+namespace snk
+{
+constexpr int UB_M        = 128;  // MMA M: TMEM lanes = output columns of the tile (UB_OUT_COLS used, the band of the rest is zero)
+constexpr int UB_OUT_COLS = 96;   // output columns per tile: a multiple of 16 (TMA coordinates), 16 + UB_OUT_COLS + 3 <= UB_K
+constexpr int UB_K        = 128;  // input columns per tile: [x0 - 16, x0 + 112) — one 128-byte swizzle row; the band needs [x0 - 3, x0 + 99)
+constexpr int UB_ROWS_IN  = 96;   // input rows per tile = N of pass 1 = K of pass 2: [y0 - 3, y0 + 93)
+constexpr int UB_ROWS_OUT = 80;   // output rows per tile = N of pass 2 (multiple of 16, <= UB_ROWS_IN - 6)
+constexpr int UB_EPI     = 256;  // 8 epilogue warps: warp w reads TMEM lanes 32 (w & 3) .. + 31; warps w and w + 4 share the columns of a tile
+constexpr int UB_NT      = UB_EPI + 32;  // + one warp whose lane 0 issues the TMA loads and the MMAs
+constexpr int UB_TMEM_COLS = 256;
+constexpr int UB_COL_D1 = 0, UB_COL_ALO = 96, UB_COL_AHI = 120, UB_COL_OHI = 144;
+// shared memory (all operand tiles 1024-byte aligned for the 128-byte swizzle)
+constexpr int UB_OFF_IMG0 = 0;                               // image tile, buffer 0: 96 rows x 128 B
+constexpr int UB_OFF_IMG1 = UB_ROWS_IN * 128;                // buffer 1
+constexpr int UB_OFF_WC   = 2 * UB_ROWS_IN * 128;            // column band: 128 rows (m) x 128 B (k)
+constexpr int UB_OFF_WR   = UB_OFF_WC + UB_M * 128;          // row band: 80 rows (n) x 128 B (k, 96 used)
+constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_ROWS_OUT * 128;   // output tile: 80 rows x 96 B, dense
+constexpr int UB_SMEM     = UB_OFF_OUT + UB_ROWS_OUT * UB_OUT_COLS + 1024;  // + alignment slack
+static_assert(UB_OFF_IMG1 % 1024 == 0 && UB_OFF_WC % 1024 == 0 && UB_OFF_WR % 1024 == 0 && UB_OFF_OUT % 1024 == 0, "swizzle alignment");
+
+struct UmmaBlurMaps
+{
+    CUtensorMap src[8];  // per level: (x, y, image) u8, box UB_K x UB_ROWS_IN x 1, SWIZZLE_128B
+    CUtensorMap dst[8];  // per level: box UB_OUT_COLS x UB_ROWS_OUT x 1, no swizzle
+};
+struct UmmaBlurTask  // one column strip of a level (of image blockIdx.y, or of image `img` if that is >= 0)
+{
+    short level, x0, w, h;
+    int img;
+    unsigned wc_off;  // byte offset of the strip's column band in the band table
+    unsigned wr_off;  // byte offset of the level's row bands (one per row tile, UB_WR_BYTES apart)
+};
+constexpr int UB_WC_BYTES = UB_M * 128, UB_WR_BYTES = UB_ROWS_OUT * 128;
+
+// byte offset of (row r, byte b) in a K-major operand tile with 128-byte rows and the 128-byte swizzle
+__device__ __forceinline__ unsigned ub_sw128(int r, int b)
+{
+    return (unsigned)((r >> 3) * 1024 + (r & 7) * 128 + ((((b >> 4) ^ (r & 7)) << 4) | (b & 15)));
+}
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 bytes apart, descriptor version 1 (sm_100)
+__device__ __forceinline__ unsigned long long ub_desc(unsigned smem_addr)
+{
+    return (unsigned long long)((smem_addr & 0x3ffffu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor: kind::i8, u8 x u8 -> s32, both operands K-major, M = 128
+__device__ __forceinline__ unsigned ub_idesc(int n) { return (2u << 4) | ((unsigned)(n >> 3) << 17) | ((unsigned)(UB_M >> 4) << 24); }
+
+__device__ __forceinline__ void ub_mma_ss(unsigned d_tmem, unsigned long long a_desc, unsigned long long b_desc, unsigned idesc, unsigned acc)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void ub_mma_ts(unsigned d_tmem, unsigned a_tmem, unsigned long long b_desc, unsigned idesc, unsigned acc)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void ub_commit(unsigned bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// bounded wait on an mbarrier phase: a copy or an MMA that never completes is reported, not waited for forever
+__device__ __forceinline__ bool ub_wait(unsigned bar, unsigned parity)
+{
+    unsigned done = 0;
+    for (int spin = 0; !done && spin < (1 << 18); ++spin)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x400;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+    return done != 0;
+}
+// 32 consecutive TMEM columns of this thread's lane
+__device__ __forceinline__ void ub_ld32(unsigned taddr, unsigned (&v)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
+        "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void ub_ld16(unsigned taddr, unsigned (&v)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void ub_ld8(unsigned taddr, unsigned (&v)[8])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void ub_st4(unsigned taddr, unsigned a, unsigned b, unsigned c, unsigned d)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// The band matrices of every (level, column strip) and (level, row tile) in the shared-memory layout of the MMA operands
+// (128-byte rows, 128-byte swizzle), built once per pyramid geometry; k_blur_umma copies them in.
+//   column band Wc[m][k]: weight of input column x0 - 16 + k in output column x0 + m (m < UB_OUT_COLS, else 0)
+//   row band    Wr[n][k]: weight of input row y0 - 3 + k in output row y0 + n; Wr[n][UB_ROWS_IN - 1] = 1 carries the
+//                         rounding constant (the high-byte operand holds 128 there: 128 * 256 = 32768)
+struct UmmaBandJob
+{
+    unsigned off;         // byte offset in the table
+    short origin, len;    // x0 (or y0) and the level's width (height)
+    short is_rows, _pad;
+};
+__global__ void k_umma_bands(const UmmaBandJob* __restrict__ jobs, unsigned char* __restrict__ table)
+{
+    const UmmaBandJob J = jobs[blockIdx.x];
+    const int r = threadIdx.x;  // one band row per thread, 128 threads
+    const int rows = J.is_rows ? UB_ROWS_OUT : UB_M, used = J.is_rows ? UB_ROWS_OUT : UB_OUT_COLS, lead = J.is_rows ? 3 : 16;
+    if (r >= rows) return;
+    unsigned char* base = table + J.off;
+    for (int kw = 0; kw < 32; ++kw)
+    {
+        unsigned w = (r < used) ? band_word(J.origin - lead + 4 * kw, J.origin + r, J.len, false) : 0u;
+        // k = UB_ROWS_IN - 1 lies outside every band (k <= n + 6 <= 85): the constant's row
+        if (J.is_rows && kw == (UB_ROWS_IN - 1) / 4) w |= 1u << (8 * ((UB_ROWS_IN - 1) & 3));
+        *reinterpret_cast<unsigned*>(base + ub_sw128(r, 4 * kw)) = w;
+    }
+}
+
+__device__ __forceinline__ void ub_arrive(unsigned bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+
+__global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ UmmaBlurMaps maps, const UmmaBlurTask* __restrict__ tasks,
+                                                        int n_tasks, const unsigned char* __restrict__ bands, int* __restrict__ err)
+{
+    extern __shared__ unsigned char ub_smem_raw[];
+    // [0], [1]: image tile buffers (TMA); [2]: pass-1 MMAs done, [3]: pass-2 MMAs done (tcgen05.commit);
+    // [4]: the A operands of pass 2 are written, [5]: the accumulators of pass 2 are read (UB_EPI arrivals each)
+    __shared__ __align__(8) unsigned long long s_bar[6];
+    __shared__ unsigned s_tmem;
+    const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    if ((int)blockIdx.x >= n_tasks) return;
+    const UmmaBlurTask T = tasks[blockIdx.x];
+    const int img        = T.img >= 0 ? T.img : (int)blockIdx.y;
+    const unsigned smem0 = ((unsigned)__cvta_generic_to_shared(ub_smem_raw) + 1023u) & ~1023u;
+    unsigned char* smem  = ub_smem_raw + (smem0 - (unsigned)__cvta_generic_to_shared(ub_smem_raw));
+    const unsigned bar0  = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
+    const unsigned bar_p1 = bar0 + 16u, bar_p2 = bar0 + 24u, bar_e1 = bar0 + 32u, bar_e2 = bar0 + 40u;
+    const CUtensorMap* map_src = &maps.src[T.level];
+    const CUtensorMap* map_dst = &maps.dst[T.level];
+    const int H = T.h, x0 = T.x0;
+    const int n_tiles = (H + UB_ROWS_OUT - 1) / UB_ROWS_OUT;
+
+    if (tid == 0)
+    {
+        for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * i));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar_e1), "r"(UB_EPI));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar_e2), "r"(UB_EPI));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (wid == UB_EPI / 32)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_tmem)),
+                     "n"(UB_TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // the strip's column band
+        const uint4* src = reinterpret_cast<const uint4*>(bands + T.wc_off);
+        uint4* dst       = reinterpret_cast<uint4*>(smem + UB_OFF_WC);
+        for (int i = tid; i < UB_WC_BYTES / 16; i += UB_NT) dst[i] = __ldg(src + i);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the band was written by ordinary stores
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = s_tmem;
+
+    if (wid == UB_EPI / 32)
+    {
+        // ================= the issuing warp: lane 0 feeds the TMA and the tensor core, everything it waits for is a barrier =========
+        if (lane == 0)
+        {
+            auto issue_load = [&](int tile) {
+                const int buf      = tile & 1;
+                const unsigned bar = bar0 + 8u * buf, dst = smem0 + (unsigned)(buf ? UB_OFF_IMG1 : UB_OFF_IMG0);
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)(UB_ROWS_IN * 128)) : "memory");
+                asm volatile(
+                    "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+                    "l"(reinterpret_cast<unsigned long long>(map_src)), "r"(x0 - 16), "r"(tile * UB_ROWS_OUT - 3), "r"(img), "r"(bar)
+                    : "memory");
+            };
+            const unsigned idesc1 = ub_idesc(UB_ROWS_IN), idesc2 = ub_idesc(UB_ROWS_OUT);
+            const unsigned long long dwc = ub_desc(smem0 + UB_OFF_WC), dwr = ub_desc(smem0 + UB_OFF_WR);
+            issue_load(0);
+            if (n_tiles > 1) issue_load(1);
+            int failed = 0;
+#pragma unroll 1
+            for (int tile = 0; tile < n_tiles && !failed; ++tile)
+            {
+                const int buf = tile & 1;
+                // pass 1: D1[m][n] = sum_k Wc[m][k] I[n][k], four K slices of 32 columns; its columns double as O_lo of the
+                // previous tile, which the epilogue must have read
+                if (!ub_wait(bar0 + 8u * buf, (unsigned)((tile >> 1) & 1))) { failed = 1; break; }
+                if (tile > 0 && !ub_wait(bar_e2, (unsigned)((tile - 1) & 1))) { failed = 4; break; }
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const unsigned long long b = ub_desc(smem0 + (buf ? UB_OFF_IMG1 : UB_OFF_IMG0));
+#pragma unroll
+                for (int k = 0; k < UB_K / 32; ++k) ub_mma_ss(tmem + UB_COL_D1, dwc + 2ull * k, b + 2ull * k, idesc1, k > 0);
+                ub_commit(bar_p1);
+                // pass 2 once the epilogue has written R_lo / R_hi (which also says pass 1 is complete: the tile buffer is free)
+                if (!ub_wait(bar_e1, (unsigned)(tile & 1))) { failed = 4; break; }
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (tile + 2 < n_tiles) issue_load(tile + 2);
+#pragma unroll
+                for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_D1, tmem + UB_COL_ALO + 8 * k, dwr + 2ull * k, idesc2, k > 0);
+#pragma unroll
+                for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_OHI, tmem + UB_COL_AHI + 8 * k, dwr + 2ull * k, idesc2, k > 0);
+                ub_commit(bar_p2);
+            }
+            if (failed) atomicExch(err, 4 + failed);  // 5: a tile never arrived, 8: the epilogue never answered
+        }
+    }
+    else
+    {
+        // ================= the epilogue warps =================
+        const int quarter = wid & 3, half = wid >> 2;  // TMEM lanes 32 quarter .. + 31; first / second half of a tile's rows
+        const unsigned tlane = tmem + ((unsigned)(quarter * 32) << 16);
+        int wr_tile = -1;  // row tile whose band lies in shared memory (interior tiles share one band)
+        int failed  = 0;
+#ifdef UB_DEBUG_CLOCKS
+        long long t_prev = clock64(), t_acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#endif
+#pragma unroll 1
+        for (int tile = 0; tile < n_tiles; ++tile)
+        {
+            const int y0 = tile * UB_ROWS_OUT;
+            const unsigned par = (unsigned)(tile & 1);
+            // the row band of this tile; away from the top and the bottom all tiles share the band of the first such tile.
+            // The previous tile's pass-2 MMAs, its only readers, have completed (bar_p2 was waited for)
+            const bool interior = y0 >= 3 && y0 + UB_ROWS_OUT + 3 <= H;
+            const bool have     = interior && wr_tile >= 0 && wr_tile * UB_ROWS_OUT >= 3 && wr_tile * UB_ROWS_OUT + UB_ROWS_OUT + 3 <= H;
+            if (!have)
+            {
+                const unsigned char* src = bands + T.wr_off + (size_t)tile * UB_WR_BYTES;
+                for (int i = tid; i < UB_WR_BYTES / 16; i += UB_EPI)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem0 + UB_OFF_WR + 16u * i), "l"(src + 16 * i) : "memory");
+                wr_tile = tile;
+            }
+            UB_T(0)
+            if (!ub_wait(bar_p1, par)) failed = 2;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            UB_T(1)
+            // ---- split the 16-bit row sums into two u8 operands: image rows 4c .. 4c+3 -> bytes of TMEM column c.
+            //      This warp: rows 48 half .. + 47 ----
+            {
+                unsigned v[3][16];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) ub_ld16(tlane + UB_COL_D1 + 48 * half + 16 * c, v[c]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                UB_T(2)
+                if (half) v[2][15] = 0x8000u;  // row 95 is outside every band: its high byte feeds the rounding constant
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                {
+                    unsigned lo[4], hi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                    {
+                        lo[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0040), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0040), 0x5410);
+                        hi[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0051), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0051), 0x5410);
+                    }
+                    ub_st4(tlane + UB_COL_ALO + 12 * half + 4 * c, lo[0], lo[1], lo[2], lo[3]);
+                    ub_st4(tlane + UB_COL_AHI + 12 * half + 4 * c, hi[0], hi[1], hi[2], hi[3]);
+                }
+            }
+            if (!have)
+            {
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            ub_arrive(bar_e1);
+            UB_T(3)
+            if (!ub_wait(bar_p2, par)) failed = 3;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            UB_T(4)
+            // ---- this warp's accumulators (output rows 40 half .. + 39) into registers: the next tile's pass 1 takes the
+            //      columns over ----
+            unsigned ol0[32], ol1[8], oh0[32], oh1[8];
+            ub_ld32(tlane + UB_COL_D1 + 40 * half, ol0), ub_ld8(tlane + UB_COL_D1 + 40 * half + 32, ol1);
+            ub_ld32(tlane + UB_COL_OHI + 40 * half, oh0), ub_ld8(tlane + UB_COL_OHI + 40 * half + 32, oh1);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            ub_arrive(bar_e2);
+            UB_T(5)
+            // the previous tile's store must have read the output tile before it is overwritten; and nobody goes on alone
+            // after a barrier that never completed
+            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            {
+                unsigned all_ok;
+                asm volatile("{\n\t.reg .pred p, q;\n\tsetp.eq.u32 p, %1, 0;\n\tbarrier.cta.red.and.pred q, 1, %2, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
+                             : "=r"(all_ok)
+                             : "r"((unsigned)failed), "n"(UB_EPI)
+                             : "memory");
+                if (!all_ok)
+                {
+                    if (failed && lane == 0) atomicExch(err, 4 + failed);  // 6 / 7: the MMAs of pass 1 / 2 never completed
+                    break;
+                }
+            }
+            UB_T(6)
+            // ---- combine (the rounding constant is in already) and lay the bytes out as image rows: this thread is column
+            //      32 quarter + lane of the tile ----
+            if (quarter * 32 + lane < UB_OUT_COLS)
+            {
+                unsigned char* out = smem + UB_OFF_OUT + (40 * half) * UB_OUT_COLS + quarter * 32 + lane;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) out[j * UB_OUT_COLS] = (unsigned char)((ol0[j] + (oh0[j] << 8)) >> 16);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) out[(32 + j) * UB_OUT_COLS] = (unsigned char)((ol1[j] + (oh1[j] << 8)) >> 16);
+            }
+            UB_T(7)
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("barrier.cta.sync 1, %0;" ::"n"(UB_EPI) : "memory");
+            UB_T(8)
+            if (tid == 0)
+            {
+                asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(
+                                 reinterpret_cast<unsigned long long>(map_dst)),
+                             "r"(x0), "r"(y0), "r"(img), "r"(smem0 + UB_OFF_OUT)
+                             : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+#ifdef UB_DEBUG_CLOCKS
+        if (tid == 0 && blockIdx.x == 1 && blockIdx.y == gridDim.y / 2)
+            for (int i = 0; i < 9; ++i) ub_clk[i] = t_acc[i];
+#endif
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (wid == UB_EPI / 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(UB_TMEM_COLS) : "memory");
+}
+}  // namespace snk

@@ -108,6 +108,12 @@ struct snk_orb
     std::vector<BlurTask> blur_tasks;  // k_blur_mma: (level, 24-column strip, 128-row band)
     BlurTask* d_blur_tasks = nullptr;
     bool blur_mma = true;              // SNK_BLUR_MMA=0 selects the dp4a kernel k_blur (A/B runs; 0.62 against 0.586 ms per 512 images)
+    // SNK_BLUR_MMA=2: the tcgen05 experiment k_blur_umma (blur_umma.cuh)
+    bool blur_umma = false;
+    UmmaBlurMaps umma_maps{};
+    std::vector<UmmaBlurTask> umma_tasks;
+    UmmaBlurTask* d_umma_tasks   = nullptr;
+    unsigned char* d_umma_bands = nullptr;
     int node_cap = 0;
     size_t qt_smem = 0;
     int qt_big_levels = 0, qt_big_cap = 0;  // levels [0, qt_big_levels) run in their own launch with qt_big_cap keypoints in smem
@@ -152,7 +158,7 @@ struct snk_orb
             if (p) cudaFree(p);
             p = nullptr;
         };
-        F(d_pyr), F(d_gauss), F(d_cells), F(d_groups), F(d_tiles), F(d_blur_tasks), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
+        F(d_pyr), F(d_gauss), F(d_cells), F(d_groups), F(d_tiles), F(d_blur_tasks), F(d_umma_tasks), F(d_umma_bands), F(d_cand), F(d_workA), F(d_workB), F(d_sel), F(d_cell_count),
             F(d_cell_off), F(d_sel_count), F(d_counts), F(d_err), F(d_kps), F(d_desc);
         for (int l = 0; l < SNK_MAX_LEVELS; ++l) F(d_quads[l]), F(d_rows[l]);
         rows = cols = 0;
@@ -190,10 +196,47 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
     return SNK_OK;
 }
 
+// tensor maps of k_blur_umma for one level: the source as 128 x 96 boxes with the 128-byte swizzle of the MMA operands,
+// the destination (the level's blurred copy) as dense 96 x 80 boxes
+static int encode_umma_maps(snk_orb* h, int l, const void* src, int pitch, size_t img_stride, bool with_dst)
+{
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    SNK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    SNK_REQUIRE(p && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+    EncodeTiledFn fn  = (EncodeTiledFn)p;
+    const LevelDev& L = h->P.lv[l];
+    SNK_REQUIRE(((uintptr_t)src % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
+    const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)h->prm.max_batch};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    {
+        const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
+        const cuuint32_t box[3]     = {UB_K, UB_ROWS_IN, 1};
+        CUresult r = fn(&h->umma_maps.src[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur source of level %d (CUresult %d)", l, (int)r);
+    }
+    if (with_dst)
+    {
+        const cuuint64_t strides[2] = {(cuuint64_t)L.gauss_pitch, (cuuint64_t)L.gauss_stride};
+        const cuuint32_t box[3]     = {UB_OUT_COLS, UB_ROWS_OUT, 1};
+        SNK_REQUIRE(((uintptr_t)L.gauss % 16) == 0 && L.gauss_stride % 16 == 0, "internal: TMA alignment");
+        CUresult r = fn(&h->umma_maps.dst[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.gauss, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur destination of level %d (CUresult %d)", l, (int)r);
+    }
+    return SNK_OK;
+}
+
 // cv::GaussianBlur of every level (ORBExtractor.cpp:213): the tensor-core kernel, or the dp4a one (SNK_BLUR_MMA=0) for A/B runs
 static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
 {
-    if (h->blur_mma)
+    if (h->blur_umma)
+        k_blur_umma<<<dim3((unsigned)h->umma_tasks.size(), n_imgs), UB_NT, UB_SMEM, st>>>(h->umma_maps, h->d_umma_tasks,
+                                                                                          (int)h->umma_tasks.size(), h->d_umma_bands, h->d_err);
+    else if (h->blur_mma)
         k_blur_mma<<<dim3((unsigned)(h->blur_tasks.size() + BM_WARPS - 1) / BM_WARPS, n_imgs), BM_WARPS * 32, 0, st>>>(
             P, h->d_blur_tasks, (int)h->blur_tasks.size());
     else
@@ -224,6 +267,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     {
         const char* e = getenv("SNK_BLUR_MMA");
         h->blur_mma   = !(e && e[0] == '0');
+        h->blur_umma  = e && e[0] == '2';
+        h->umma_tasks.clear();
     }
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
@@ -353,6 +398,42 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         if (rc) return rc;
     }
     h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
+    if (h->blur_umma)
+    {
+        // per level: tensor maps, one task per column strip, the band matrices of its strips and row tiles
+        SNK_REQUIRE(L <= 8, "SNK_BLUR_MMA=2 (k_blur_umma) handles at most 8 levels");
+        std::vector<UmmaBandJob> jobs;
+        unsigned off = 0;
+        for (int l = 0; l < L; ++l)
+        {
+            int rc = encode_umma_maps(h, l, P.lv[l].img, P.lv[l].pitch, P.lv[l].img_stride, true);
+            if (rc) return rc;
+            const int n_strips = (P.lv[l].w + UB_OUT_COLS - 1) / UB_OUT_COLS, n_row_tiles = (P.lv[l].h + UB_ROWS_OUT - 1) / UB_ROWS_OUT;
+            const unsigned wr_off = off + (unsigned)n_strips * UB_WC_BYTES;
+            for (int sidx = 0; sidx < n_strips; ++sidx)
+            {
+                h->umma_tasks.push_back(UmmaBlurTask{(short)l, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, (short)P.lv[l].h, -1, off, wr_off});
+                jobs.push_back(UmmaBandJob{off, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, 0, 0});
+                off += UB_WC_BYTES;
+            }
+            for (int t = 0; t < n_row_tiles; ++t)
+            {
+                jobs.push_back(UmmaBandJob{off, (short)(t * UB_ROWS_OUT), (short)P.lv[l].h, 1, 0});
+                off += UB_WR_BYTES;
+            }
+        }
+        UmmaBandJob* d_jobs = nullptr;
+        SNK_CUDA(cudaMalloc(&h->d_umma_tasks, h->umma_tasks.size() * sizeof(UmmaBlurTask)));
+        SNK_CUDA(cudaMemcpy(h->d_umma_tasks, h->umma_tasks.data(), h->umma_tasks.size() * sizeof(UmmaBlurTask), cudaMemcpyHostToDevice));
+        SNK_CUDA(cudaMalloc(&h->d_umma_bands, off));
+        SNK_CUDA(cudaMalloc(&d_jobs, jobs.size() * sizeof(UmmaBandJob)));
+        SNK_CUDA(cudaMemcpy(d_jobs, jobs.data(), jobs.size() * sizeof(UmmaBandJob), cudaMemcpyHostToDevice));
+        k_umma_bands<<<(unsigned)jobs.size(), 128>>>(d_jobs, h->d_umma_bands);
+        SNK_CUDA(cudaGetLastError());
+        SNK_CUDA(cudaDeviceSynchronize());
+        SNK_CUDA(cudaFree(d_jobs));
+        SNK_CUDA(cudaFuncSetAttribute(k_blur_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, UB_SMEM));
+    }
     for (int l = 1; l < L; ++l)
     {
         std::vector<int> xo, yo;
@@ -749,6 +830,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         const size_t stride0 = (n_imgs == 1 && P.lv[0].img_stride % 16) ? (size_t)P.lv[0].pitch * rows : P.lv[0].img_stride;
         rc = encode_level_map(h, 0, P.lv[0].img, P.lv[0].pitch, stride0);
         if (rc) return rc;
+        if (h->blur_umma && (rc = encode_umma_maps(h, 0, P.lv[0].img, P.lv[0].pitch, stride0, false))) return rc;
         h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
     }
     if (prof) cudaEventRecord(ev[1], st);

@@ -1149,3 +1149,4 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
 }  // namespace snk
 
 #include "blur_mma.cuh"
+#include "blur_umma.cuh"
