@@ -16,8 +16,10 @@
 // Per tile (UB_OUT_COLS x UB_ROWS_OUT output pixels, UB_K x UB_ROWS_IN input pixels):
 //   TMA load -> 4 MMAs (M 128, N 96, K 32) -> ld / split / st -> 2 x 3 MMAs (M 128, N 80, K 32) -> ld, combine, bytes into
 //   a shared-memory tile -> TMA store (clipped at the image's sides by the tensor map).
-// A CTA owns one column strip of one image and walks down its row tiles: the column band Wc is built once, the row band
-// Wr only when a tile touches the top or the bottom; the next tile's load is in flight while the current one is worked on.
+// Persistent CTAs (two per SM: 224 of the 512 TMEM columns each) walk equal shares of the tile list; warp 8's lane 0 issues
+// the TMA loads (two tiles ahead) and the MMAs and waits only on barriers, the eight other warps are the two epilogues.
+// The band matrices come from a table built once per pyramid geometry (k_umma_bands), copied in when the strip / the row
+// tile kind changes.
 // TMEM columns: [0,96) pass-1 accumulator, reused as O_lo; [96,120) R_lo, [120,144) R_hi as u8 x 4; [144,224) O_hi.
 #pragma once
 #include <cuda.h>
@@ -26,30 +28,28 @@
 
 #include "blur_weights.cuh"
 
-#ifdef UB_DEBUG_CLOCKS
-__device__ long long ub_clk[16];
-#define UB_T(i) { const long long t_ = clock64(); t_acc[i] += t_ - t_prev; t_prev = t_; }
-#else
-#define UB_T(i)
-#endif
 
 namespace snk
 {
 constexpr int UB_M        = 128;  // MMA M: TMEM lanes = output columns of the tile (UB_OUT_COLS used, the band of the rest is zero)
 constexpr int UB_OUT_COLS = 96;   // output columns per tile: a multiple of 16 (TMA coordinates), 16 + UB_OUT_COLS + 3 <= UB_K
 constexpr int UB_K        = 128;  // input columns per tile: [x0 - 16, x0 + 112) — one 128-byte swizzle row; the band needs [x0 - 3, x0 + 99)
-constexpr int UB_ROWS_IN  = 96;   // input rows per tile = N of pass 1 = K of pass 2: [y0 - 3, y0 + 93)
-constexpr int UB_ROWS_OUT = 80;   // output rows per tile = N of pass 2 (multiple of 16, <= UB_ROWS_IN - 6)
-constexpr int UB_EPI     = 256;  // 8 epilogue warps: warp w reads TMEM lanes 32 (w & 3) .. + 31; warps w and w + 4 share the columns of a tile
-constexpr int UB_NT      = UB_EPI + 32;  // + one warp whose lane 0 issues the TMA loads and the MMAs
-constexpr int UB_TMEM_COLS = 256;
-constexpr int UB_COL_D1 = 0, UB_COL_ALO = 96, UB_COL_AHI = 120, UB_COL_OHI = 144;
+constexpr int UB_ROWS_IN  = 64;   // input rows per tile = N of pass 1 = K of pass 2: [y0 - 3, y0 + 61)
+constexpr int UB_ROWS_OUT = 48;   // output rows per tile = N of pass 2 (multiple of 16, <= UB_ROWS_IN - 6 - 1: the last row carries the rounding constant)
+constexpr int UB_EPI      = 128;  // 4 epilogue warps: warp w reads TMEM lanes 32 w .. + 31, a thread is one output column
+constexpr int UB_NT       = UB_EPI + 32;  // + one warp whose lane 0 issues the TMA loads and the MMAs
+constexpr int UB_CTAS_PER_SM = 4;
+// 128 TMEM columns per CTA, four CTAs per SM. [0, 64): pass-1 accumulator D1; once the epilogue holds it in registers the
+// columns are reused: [0, 16) R_lo and [16, 32) R_hi as u8 x 4 (A operands of pass 2), [32, 80) O_lo, [80, 128) O_hi
+constexpr int UB_TMEM_COLS = 128;
+constexpr int UB_COL_D1 = 0, UB_COL_ALO = 0, UB_COL_AHI = UB_ROWS_IN / 4, UB_COL_OLO = UB_ROWS_IN / 2, UB_COL_OHI = UB_ROWS_IN / 2 + UB_ROWS_OUT;
+static_assert(UB_COL_OHI + UB_ROWS_OUT <= UB_TMEM_COLS && UB_ROWS_OUT + 7 <= UB_ROWS_IN && UB_ROWS_IN % 32 == 0 && UB_ROWS_OUT % 16 == 0, "tile shape");
 // shared memory (all operand tiles 1024-byte aligned for the 128-byte swizzle)
-constexpr int UB_OFF_IMG0 = 0;                               // image tile, buffer 0: 96 rows x 128 B
+constexpr int UB_OFF_IMG0 = 0;                               // image tile, buffer 0: UB_ROWS_IN rows x 128 B
 constexpr int UB_OFF_IMG1 = UB_ROWS_IN * 128;                // buffer 1
 constexpr int UB_OFF_WC   = 2 * UB_ROWS_IN * 128;            // column band: 128 rows (m) x 128 B (k)
-constexpr int UB_OFF_WR   = UB_OFF_WC + UB_M * 128;          // row band: 80 rows (n) x 128 B (k, 96 used)
-constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_ROWS_OUT * 128;   // output tile: 80 rows x 96 B, dense
+constexpr int UB_OFF_WR   = UB_OFF_WC + UB_M * 128;          // row band: UB_ROWS_OUT rows (n) x 128 B (k, UB_ROWS_IN used)
+constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_ROWS_OUT * 128;   // output tile: UB_ROWS_OUT rows x UB_OUT_COLS B, dense
 constexpr int UB_SMEM     = UB_OFF_OUT + UB_ROWS_OUT * UB_OUT_COLS + 1024;  // + alignment slack
 static_assert(UB_OFF_IMG1 % 1024 == 0 && UB_OFF_WC % 1024 == 0 && UB_OFF_WR % 1024 == 0 && UB_OFF_OUT % 1024 == 0, "swizzle alignment");
 
@@ -58,12 +58,40 @@ struct UmmaBlurMaps
     CUtensorMap src[8];  // per level: (x, y, image) u8, box UB_K x UB_ROWS_IN x 1, SWIZZLE_128B
     CUtensorMap dst[8];  // per level: box UB_OUT_COLS x UB_ROWS_OUT x 1, no swizzle
 };
-struct UmmaBlurTask  // one column strip of a level (of image blockIdx.y, or of image `img` if that is >= 0)
+struct UmmaBlurTask  // one column strip of a level
 {
     short level, x0, w, h;
-    int img;
+    int n_row_tiles;
     unsigned wc_off;  // byte offset of the strip's column band in the band table
     unsigned wr_off;  // byte offset of the level's row bands (one per row tile, UB_WR_BYTES apart)
+};
+// The tiles of a launch in the order the CTAs walk them: strip by strip, inside a strip image by image, inside an image
+// from the top down. CTA c of G takes the tiles [c n / G, (c + 1) n / G): long runs inside one strip (the column band
+// stays), every CTA the same number of tiles, the pipeline never drains between strips or images.
+struct UmmaTileIter
+{
+    int task, img, row;
+    UmmaBlurTask T;
+    __device__ void seek(const UmmaBlurTask* __restrict__ tasks, int n_imgs, long long g)
+    {
+        task = 0;
+        T    = tasks[0];
+        while (g >= (long long)n_imgs * T.n_row_tiles)
+        {
+            g -= (long long)n_imgs * T.n_row_tiles;
+            T = tasks[++task];
+        }
+        img = (int)(g / T.n_row_tiles);
+        row = (int)(g - (long long)img * T.n_row_tiles);
+    }
+    __device__ void next(const UmmaBlurTask* __restrict__ tasks, int n_tasks, int n_imgs)
+    {
+        if (++row < T.n_row_tiles) return;
+        row = 0;
+        if (++img < n_imgs) return;
+        img = 0;
+        if (++task < n_tasks) T = tasks[task];
+    }
 };
 constexpr int UB_WC_BYTES = UB_M * 128, UB_WR_BYTES = UB_ROWS_OUT * 128;
 
@@ -174,8 +202,9 @@ __global__ void k_umma_bands(const UmmaBandJob* __restrict__ jobs, unsigned char
 
 __device__ __forceinline__ void ub_arrive(unsigned bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 
-__global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ UmmaBlurMaps maps, const UmmaBlurTask* __restrict__ tasks,
-                                                        int n_tasks, const unsigned char* __restrict__ bands, int* __restrict__ err)
+__global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __grid_constant__ UmmaBlurMaps maps, const UmmaBlurTask* __restrict__ tasks,
+                                                        int n_tasks, int n_imgs, int tiles_per_img,
+                                                        const unsigned char* __restrict__ bands, int* __restrict__ err)
 {
     extern __shared__ unsigned char ub_smem_raw[];
     // [0], [1]: image tile buffers (TMA); [2]: pass-1 MMAs done, [3]: pass-2 MMAs done (tcgen05.commit);
@@ -183,17 +212,14 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
     __shared__ __align__(8) unsigned long long s_bar[6];
     __shared__ unsigned s_tmem;
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
-    if ((int)blockIdx.x >= n_tasks) return;
-    const UmmaBlurTask T = tasks[blockIdx.x];
-    const int img        = T.img >= 0 ? T.img : (int)blockIdx.y;
+    const long long total = (long long)n_imgs * tiles_per_img;
+    const long long g0 = total * blockIdx.x / gridDim.x, g1 = total * (blockIdx.x + 1) / gridDim.x;
+    const int n_local = (int)(g1 - g0);
+    if (n_local <= 0) return;
     const unsigned smem0 = ((unsigned)__cvta_generic_to_shared(ub_smem_raw) + 1023u) & ~1023u;
     unsigned char* smem  = ub_smem_raw + (smem0 - (unsigned)__cvta_generic_to_shared(ub_smem_raw));
     const unsigned bar0  = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
     const unsigned bar_p1 = bar0 + 16u, bar_p2 = bar0 + 24u, bar_e1 = bar0 + 32u, bar_e2 = bar0 + 40u;
-    const CUtensorMap* map_src = &maps.src[T.level];
-    const CUtensorMap* map_dst = &maps.dst[T.level];
-    const int H = T.h, x0 = T.x0;
-    const int n_tiles = (H + UB_ROWS_OUT - 1) / UB_ROWS_OUT;
 
     if (tid == 0)
     {
@@ -209,8 +235,10 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    {   // the strip's column band
-        const uint4* src = reinterpret_cast<const uint4*>(bands + T.wc_off);
+    UmmaTileIter it;
+    it.seek(tasks, n_imgs, g0);
+    {   // the first strip's column band
+        const uint4* src = reinterpret_cast<const uint4*>(bands + it.T.wc_off);
         uint4* dst       = reinterpret_cast<uint4*>(smem + UB_OFF_WC);
         for (int i = tid; i < UB_WC_BYTES / 16; i += UB_NT) dst[i] = __ldg(src + i);
     }
@@ -225,39 +253,43 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
         // ================= the issuing warp: lane 0 feeds the TMA and the tensor core, everything it waits for is a barrier =========
         if (lane == 0)
         {
-            auto issue_load = [&](int tile) {
-                const int buf      = tile & 1;
+            int n_loaded = 0;  // `it` runs ahead of the MMAs: it is the next tile to load
+            auto issue_load = [&]() {
+                const int buf      = n_loaded & 1;
                 const unsigned bar = bar0 + 8u * buf, dst = smem0 + (unsigned)(buf ? UB_OFF_IMG1 : UB_OFF_IMG0);
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)(UB_ROWS_IN * 128)) : "memory");
                 asm volatile(
                     "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
-                    "l"(reinterpret_cast<unsigned long long>(map_src)), "r"(x0 - 16), "r"(tile * UB_ROWS_OUT - 3), "r"(img), "r"(bar)
+                    "l"(reinterpret_cast<unsigned long long>(&maps.src[it.T.level])), "r"(it.T.x0 - 16), "r"(it.row * UB_ROWS_OUT - 3),
+                    "r"(it.img), "r"(bar)
                     : "memory");
+                ++n_loaded;
+                it.next(tasks, n_tasks, n_imgs);
             };
             const unsigned idesc1 = ub_idesc(UB_ROWS_IN), idesc2 = ub_idesc(UB_ROWS_OUT);
             const unsigned long long dwc = ub_desc(smem0 + UB_OFF_WC), dwr = ub_desc(smem0 + UB_OFF_WR);
-            issue_load(0);
-            if (n_tiles > 1) issue_load(1);
+            issue_load();
+            if (n_local > 1) issue_load();
             int failed = 0;
 #pragma unroll 1
-            for (int tile = 0; tile < n_tiles && !failed; ++tile)
+            for (int i = 0; i < n_local; ++i)
             {
-                const int buf = tile & 1;
+                const int buf = i & 1;
                 // pass 1: D1[m][n] = sum_k Wc[m][k] I[n][k], four K slices of 32 columns; its columns double as O_lo of the
                 // previous tile, which the epilogue must have read
-                if (!ub_wait(bar0 + 8u * buf, (unsigned)((tile >> 1) & 1))) { failed = 1; break; }
-                if (tile > 0 && !ub_wait(bar_e2, (unsigned)((tile - 1) & 1))) { failed = 4; break; }
+                if (!ub_wait(bar0 + 8u * buf, (unsigned)((i >> 1) & 1))) { failed = 1; break; }
+                if (i > 0 && !ub_wait(bar_e2, (unsigned)((i - 1) & 1))) { failed = 4; break; }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned long long b = ub_desc(smem0 + (buf ? UB_OFF_IMG1 : UB_OFF_IMG0));
 #pragma unroll
                 for (int k = 0; k < UB_K / 32; ++k) ub_mma_ss(tmem + UB_COL_D1, dwc + 2ull * k, b + 2ull * k, idesc1, k > 0);
                 ub_commit(bar_p1);
                 // pass 2 once the epilogue has written R_lo / R_hi (which also says pass 1 is complete: the tile buffer is free)
-                if (!ub_wait(bar_e1, (unsigned)(tile & 1))) { failed = 4; break; }
+                if (!ub_wait(bar_e1, (unsigned)(i & 1))) { failed = 4; break; }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (tile + 2 < n_tiles) issue_load(tile + 2);
+                if (n_loaded < n_local) issue_load();
 #pragma unroll
-                for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_D1, tmem + UB_COL_ALO + 8 * k, dwr + 2ull * k, idesc2, k > 0);
+                for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_OLO, tmem + UB_COL_ALO + 8 * k, dwr + 2ull * k, idesc2, k > 0);
 #pragma unroll
                 for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_OHI, tmem + UB_COL_AHI + 8 * k, dwr + 2ull * k, idesc2, k > 0);
                 ub_commit(bar_p2);
@@ -268,44 +300,50 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
     else
     {
         // ================= the epilogue warps =================
-        const int quarter = wid & 3, half = wid >> 2;  // TMEM lanes 32 quarter .. + 31; first / second half of a tile's rows
-        const unsigned tlane = tmem + ((unsigned)(quarter * 32) << 16);
-        int wr_tile = -1;  // row tile whose band lies in shared memory (interior tiles share one band)
-        int failed  = 0;
-#ifdef UB_DEBUG_CLOCKS
-        long long t_prev = clock64(), t_acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-#endif
+        const unsigned tlane = tmem + ((unsigned)(wid * 32) << 16);  // warp w reads lanes 32 w .. + 31
+        int wr_level = -1, wr_row = -1;  // which row band lies in shared memory (interior tiles of a level share one)
+        int failed   = 0;
 #pragma unroll 1
-        for (int tile = 0; tile < n_tiles; ++tile)
+        for (int i = 0; i < n_local; ++i)
         {
-            const int y0 = tile * UB_ROWS_OUT;
-            const unsigned par = (unsigned)(tile & 1);
-            // the row band of this tile; away from the top and the bottom all tiles share the band of the first such tile.
-            // The previous tile's pass-2 MMAs, its only readers, have completed (bar_p2 was waited for)
+            const int y0 = it.row * UB_ROWS_OUT, H = it.T.h;
+            const unsigned par = (unsigned)(i & 1);
+            // the row band of this tile; away from the top and the bottom all tiles of a level share the band of the first
+            // such tile. The previous tile's pass-2 MMAs, its only readers, have completed (bar_p2 was waited for)
             const bool interior = y0 >= 3 && y0 + UB_ROWS_OUT + 3 <= H;
-            const bool have     = interior && wr_tile >= 0 && wr_tile * UB_ROWS_OUT >= 3 && wr_tile * UB_ROWS_OUT + UB_ROWS_OUT + 3 <= H;
+            const bool have     = wr_level == it.T.level &&
+                              (wr_row == it.row || (interior && wr_row * UB_ROWS_OUT >= 3 && wr_row * UB_ROWS_OUT + UB_ROWS_OUT + 3 <= H));
             if (!have)
             {
-                const unsigned char* src = bands + T.wr_off + (size_t)tile * UB_WR_BYTES;
-                for (int i = tid; i < UB_WR_BYTES / 16; i += UB_EPI)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem0 + UB_OFF_WR + 16u * i), "l"(src + 16 * i) : "memory");
-                wr_tile = tile;
+                const unsigned char* src = bands + it.T.wr_off + (size_t)it.row * UB_WR_BYTES;
+                for (int j = tid; j < UB_WR_BYTES / 16; j += UB_EPI)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem0 + UB_OFF_WR + 16u * j), "l"(src + 16 * j) : "memory");
+                wr_level = it.T.level, wr_row = it.row;
             }
-            UB_T(0)
+            // this tile's output coordinates; then look at the next tile: a new strip needs its column band
+            const int out_x = it.T.x0, out_img = it.img;
+            const CUtensorMap* map_dst = &maps.dst[it.T.level];
+            const int cur_task = it.task;
+            it.next(tasks, n_tasks, n_imgs);
+            const bool new_strip = i + 1 < n_local && it.task != cur_task;
             if (!ub_wait(bar_p1, par)) failed = 2;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            UB_T(1)
-            // ---- split the 16-bit row sums into two u8 operands: image rows 4c .. 4c+3 -> bytes of TMEM column c.
-            //      This warp: rows 48 half .. + 47 ----
+            if (new_strip)  // pass 1 of this tile, the last reader of the old band, has completed
             {
-                unsigned v[3][16];
+                const unsigned char* src = bands + it.T.wc_off;
+                for (int j = tid; j < UB_WC_BYTES / 16; j += UB_EPI)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem0 + UB_OFF_WC + 16u * j), "l"(src + 16 * j) : "memory");
+            }
+            // ---- split the 16-bit row sums into two u8 operands: image rows 4c .. 4c+3 -> bytes of TMEM column c. All of
+            //      D1 goes into registers first: the operands are written over its columns ----
+            {
+                unsigned v[UB_ROWS_IN / 16][16];
 #pragma unroll
-                for (int c = 0; c < 3; ++c) ub_ld16(tlane + UB_COL_D1 + 48 * half + 16 * c, v[c]);
+                for (int c = 0; c < UB_ROWS_IN / 16; ++c) ub_ld16(tlane + UB_COL_D1 + 16 * c, v[c]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                UB_T(2)
-                if (half) v[2][15] = 0x8000u;  // row 95 is outside every band: its high byte feeds the rounding constant
+                v[UB_ROWS_IN / 16 - 1][15] = 0x8000u;  // the last row is outside every band: its high byte feeds the rounding constant
 #pragma unroll
-                for (int c = 0; c < 3; ++c)
+                for (int c = 0; c < UB_ROWS_IN / 16; ++c)
                 {
                     unsigned lo[4], hi[4];
 #pragma unroll
@@ -314,11 +352,11 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
                         lo[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0040), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0040), 0x5410);
                         hi[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0051), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0051), 0x5410);
                     }
-                    ub_st4(tlane + UB_COL_ALO + 12 * half + 4 * c, lo[0], lo[1], lo[2], lo[3]);
-                    ub_st4(tlane + UB_COL_AHI + 12 * half + 4 * c, hi[0], hi[1], hi[2], hi[3]);
+                    ub_st4(tlane + UB_COL_ALO + 4 * c, lo[0], lo[1], lo[2], lo[3]);
+                    ub_st4(tlane + UB_COL_AHI + 4 * c, hi[0], hi[1], hi[2], hi[3]);
                 }
             }
-            if (!have)
+            if (!have || new_strip)
             {
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -326,21 +364,10 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             ub_arrive(bar_e1);
-            UB_T(3)
-            if (!ub_wait(bar_p2, par)) failed = 3;
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            UB_T(4)
-            // ---- this warp's accumulators (output rows 40 half .. + 39) into registers: the next tile's pass 1 takes the
-            //      columns over ----
-            unsigned ol0[32], ol1[8], oh0[32], oh1[8];
-            ub_ld32(tlane + UB_COL_D1 + 40 * half, ol0), ub_ld8(tlane + UB_COL_D1 + 40 * half + 32, ol1);
-            ub_ld32(tlane + UB_COL_OHI + 40 * half, oh0), ub_ld8(tlane + UB_COL_OHI + 40 * half + 32, oh1);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            ub_arrive(bar_e2);
-            UB_T(5)
             // the previous tile's store must have read the output tile before it is overwritten; and nobody goes on alone
             // after a barrier that never completed
+            if (!ub_wait(bar_p2, par)) failed = 3;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             {
                 unsigned all_ok;
@@ -354,35 +381,38 @@ __global__ void __launch_bounds__(UB_NT, 2) k_blur_umma(const __grid_constant__ 
                     break;
                 }
             }
-            UB_T(6)
-            // ---- combine (the rounding constant is in already) and lay the bytes out as image rows: this thread is column
-            //      32 quarter + lane of the tile ----
-            if (quarter * 32 + lane < UB_OUT_COLS)
+            // ---- the accumulators, 16 output rows at a time: combine (the rounding constant is in already) and lay the
+            //      bytes out as image rows; this thread is column tid of the tile. After the last load the next tile's pass 1
+            //      may take the columns over ----
+            unsigned char* out = smem + UB_OFF_OUT + tid;
+#pragma unroll
+            for (int c = 0; c < UB_ROWS_OUT / 16; ++c)
             {
-                unsigned char* out = smem + UB_OFF_OUT + (40 * half) * UB_OUT_COLS + quarter * 32 + lane;
+                unsigned ol[16], oh[16];
+                ub_ld16(tlane + UB_COL_OLO + 16 * c, ol);
+                ub_ld16(tlane + UB_COL_OHI + 16 * c, oh);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (c == UB_ROWS_OUT / 16 - 1)
+                {
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    ub_arrive(bar_e2);
+                }
+                if (tid < UB_OUT_COLS)
 #pragma unroll
-                for (int j = 0; j < 32; ++j) out[j * UB_OUT_COLS] = (unsigned char)((ol0[j] + (oh0[j] << 8)) >> 16);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) out[(32 + j) * UB_OUT_COLS] = (unsigned char)((ol1[j] + (oh1[j] << 8)) >> 16);
+                    for (int j = 0; j < 16; ++j) out[(16 * c + j) * UB_OUT_COLS] = (unsigned char)((ol[j] + (oh[j] << 8)) >> 16);
             }
-            UB_T(7)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             asm volatile("barrier.cta.sync 1, %0;" ::"n"(UB_EPI) : "memory");
-            UB_T(8)
             if (tid == 0)
             {
                 asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(
                                  reinterpret_cast<unsigned long long>(map_dst)),
-                             "r"(x0), "r"(y0), "r"(img), "r"(smem0 + UB_OFF_OUT)
+                             "r"(out_x), "r"(y0), "r"(out_img), "r"(smem0 + UB_OFF_OUT)
                              : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
         }
         if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-#ifdef UB_DEBUG_CLOCKS
-        if (tid == 0 && blockIdx.x == 1 && blockIdx.y == gridDim.y / 2)
-            for (int i = 0; i < 9; ++i) ub_clk[i] = t_acc[i];
-#endif
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();

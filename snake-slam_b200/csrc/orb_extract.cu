@@ -113,6 +113,8 @@ struct snk_orb
     UmmaBlurMaps umma_maps{};
     std::vector<UmmaBlurTask> umma_tasks;
     UmmaBlurTask* d_umma_tasks   = nullptr;
+    int umma_tiles_per_img      = 0;
+    int n_sm                    = 148;
     unsigned char* d_umma_bands = nullptr;
     int node_cap = 0;
     size_t qt_smem = 0;
@@ -234,8 +236,12 @@ static int encode_umma_maps(snk_orb* h, int l, const void* src, int pitch, size_
 static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st)
 {
     if (h->blur_umma)
-        k_blur_umma<<<dim3((unsigned)h->umma_tasks.size(), n_imgs), UB_NT, UB_SMEM, st>>>(h->umma_maps, h->d_umma_tasks,
-                                                                                          (int)h->umma_tasks.size(), h->d_umma_bands, h->d_err);
+    {
+        // persistent: two CTAs per SM (their TMEM columns), each with an equal share of the launch's tiles
+        const long long total = (long long)h->umma_tiles_per_img * n_imgs;
+        k_blur_umma<<<(unsigned)std::min<long long>((long long)UB_CTAS_PER_SM * h->n_sm, total), UB_NT, UB_SMEM, st>>>(
+            h->umma_maps, h->d_umma_tasks, (int)h->umma_tasks.size(), n_imgs, h->umma_tiles_per_img, h->d_umma_bands, h->d_err);
+    }
     else if (h->blur_mma)
         k_blur_mma<<<dim3((unsigned)(h->blur_tasks.size() + BM_WARPS - 1) / BM_WARPS, n_imgs), BM_WARPS * 32, 0, st>>>(
             P, h->d_blur_tasks, (int)h->blur_tasks.size());
@@ -269,6 +275,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         h->blur_mma   = !(e && e[0] == '0');
         h->blur_umma  = e && e[0] == '2';
         h->umma_tasks.clear();
+        h->umma_tiles_per_img = 0;
     }
     size_t pyr_bytes = 0, gauss_bytes = 0;
     std::vector<size_t> pyr_off(L), gauss_off(L);
@@ -402,6 +409,7 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     {
         // per level: tensor maps, one task per column strip, the band matrices of its strips and row tiles
         SNK_REQUIRE(L <= 8, "SNK_BLUR_MMA=2 (k_blur_umma) handles at most 8 levels");
+        SNK_CUDA(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->prm.device));
         std::vector<UmmaBandJob> jobs;
         unsigned off = 0;
         for (int l = 0; l < L; ++l)
@@ -412,7 +420,8 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             const unsigned wr_off = off + (unsigned)n_strips * UB_WC_BYTES;
             for (int sidx = 0; sidx < n_strips; ++sidx)
             {
-                h->umma_tasks.push_back(UmmaBlurTask{(short)l, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, (short)P.lv[l].h, -1, off, wr_off});
+                h->umma_tasks.push_back(UmmaBlurTask{(short)l, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, (short)P.lv[l].h, n_row_tiles, off, wr_off});
+                h->umma_tiles_per_img += n_row_tiles;
                 jobs.push_back(UmmaBandJob{off, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, 0, 0});
                 off += UB_WC_BYTES;
             }

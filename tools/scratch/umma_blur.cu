@@ -6,9 +6,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <vector>
 
-#define UB_DEBUG_CLOCKS
 #include "../../snake-slam_b200/csrc/blur_umma.cuh"
 
 #define CK(x)                                                                                       \
@@ -93,7 +93,7 @@ int main(int argc, char** argv)
     const unsigned wr_off = (unsigned)((W + snk::UB_OUT_COLS - 1) / snk::UB_OUT_COLS) * snk::UB_WC_BYTES;
     for (int x0 = 0; x0 < W; x0 += snk::UB_OUT_COLS)
     {
-        tasks.push_back(snk::UmmaBlurTask{0, (short)x0, (short)W, (short)H, -1, off, wr_off});
+        tasks.push_back(snk::UmmaBlurTask{0, (short)x0, (short)W, (short)H, n_row_tiles, off, wr_off});
         jobs.push_back(snk::UmmaBandJob{off, (short)x0, (short)W, 0, 0});
         off += snk::UB_WC_BYTES;
     }
@@ -112,8 +112,12 @@ int main(int argc, char** argv)
     CK(cudaMemcpy(d_jobs, jobs.data(), jobs.size() * sizeof(jobs[0]), cudaMemcpyHostToDevice));
     snk::k_umma_bands<<<(int)jobs.size(), 128>>>(d_jobs, d_bands);
     CK(cudaGetLastError());
+    const int tiles_per_img = (int)tasks.size() * n_row_tiles;
+    int n_sm = 0;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+    const int grid = (int)std::min<long long>((long long)snk::UB_CTAS_PER_SM * n_sm, (long long)tiles_per_img * NIMG);
     CK(cudaFuncSetAttribute(snk::k_blur_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, snk::UB_SMEM));
-    snk::k_blur_umma<<<dim3((unsigned)tasks.size(), NIMG), snk::UB_NT, snk::UB_SMEM>>>(maps, d_tasks, (int)tasks.size(), d_bands, d_err);
+    snk::k_blur_umma<<<grid, snk::UB_NT, snk::UB_SMEM>>>(maps, d_tasks, (int)tasks.size(), NIMG, tiles_per_img, d_bands, d_err);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     int err = 0;
@@ -131,14 +135,6 @@ int main(int argc, char** argv)
                     ++bad;
                 }
             }
-    {
-        long long clk[16];
-        cudaMemcpyFromSymbol(clk, ub_clk, sizeof(clk));
-        const int nt = (H + snk::UB_ROWS_OUT - 1) / snk::UB_ROWS_OUT;
-        printf("clocks per tile of CTA (0,0):");
-        for (int i = 0; i < 12; ++i) printf(" [%d] %lld", i, clk[i] / nt);
-        printf("\n");
-    }
     printf("W %d H %d images %d tasks %zu err %d mismatches %zu", W, H, NIMG, tasks.size(), err, bad);
     if (bad)
     {
@@ -156,7 +152,7 @@ int main(int argc, char** argv)
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0), cudaEventCreate(&e1);
         cudaEventRecord(e0);
-        for (int k = 0; k < reps; ++k) snk::k_blur_umma<<<dim3((unsigned)tasks.size(), NIMG), snk::UB_NT, snk::UB_SMEM>>>(maps, d_tasks, (int)tasks.size(), d_bands, d_err);
+        for (int k = 0; k < reps; ++k) snk::k_blur_umma<<<grid, snk::UB_NT, snk::UB_SMEM>>>(maps, d_tasks, (int)tasks.size(), NIMG, tiles_per_img, d_bands, d_err);
         cudaEventRecord(e1);
         CK(cudaDeviceSynchronize());
         float ms = 0;
