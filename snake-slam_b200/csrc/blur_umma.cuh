@@ -50,7 +50,8 @@ constexpr int UB_OFF_IMG1 = UB_ROWS_IN * 128;                // buffer 1
 constexpr int UB_OFF_WC   = 2 * UB_ROWS_IN * 128;            // column band: 128 rows (m) x 128 B (k)
 constexpr int UB_OFF_WR   = UB_OFF_WC + UB_M * 128;          // row band: UB_ROWS_OUT rows (n) x 128 B (k, UB_ROWS_IN used)
 constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_ROWS_OUT * 128;   // output tile: UB_ROWS_OUT rows x UB_OUT_COLS B, dense
-constexpr int UB_SMEM     = UB_OFF_OUT + UB_ROWS_OUT * UB_OUT_COLS + 1024;  // + alignment slack
+constexpr int UB_OUT_BYTES = (UB_ROWS_OUT * UB_OUT_COLS + 127) / 128 * 128;
+constexpr int UB_SMEM     = UB_OFF_OUT + 2 * UB_OUT_BYTES + 1024;  // two output tiles + alignment slack
 static_assert(UB_OFF_IMG1 % 1024 == 0 && UB_OFF_WC % 1024 == 0 && UB_OFF_WR % 1024 == 0 && UB_OFF_OUT % 1024 == 0, "swizzle alignment");
 
 struct UmmaBlurMaps
@@ -156,6 +157,16 @@ __device__ __forceinline__ void ub_ld16(unsigned taddr, unsigned (&v)[16])
 {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+// the low 16 bits of 32 consecutive TMEM columns of this thread's lane, two columns per register
+__device__ __forceinline__ void ub_ld16_pack(unsigned taddr, unsigned (&v)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
           "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr)
@@ -287,12 +298,12 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
                 // pass 2 once the epilogue has written R_lo / R_hi (which also says pass 1 is complete: the tile buffer is free)
                 if (!ub_wait(bar_e1, (unsigned)(i & 1))) { failed = 4; break; }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (n_loaded < n_local) issue_load();
 #pragma unroll
                 for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_OLO, tmem + UB_COL_ALO + 8 * k, dwr + 2ull * k, idesc2, k > 0);
 #pragma unroll
                 for (int k = 0; k < UB_ROWS_IN / 32; ++k) ub_mma_ts(tmem + UB_COL_OHI, tmem + UB_COL_AHI + 8 * k, dwr + 2ull * k, idesc2, k > 0);
                 ub_commit(bar_p2);
+                if (n_loaded < n_local) issue_load();  // after the MMAs: the epilogue is waiting for them
             }
             if (failed) atomicExch(err, 4 + failed);  // 5: a tile never arrived, 8: the epilogue never answered
         }
@@ -337,23 +348,26 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             // ---- split the 16-bit row sums into two u8 operands: image rows 4c .. 4c+3 -> bytes of TMEM column c. All of
             //      D1 goes into registers first: the operands are written over its columns ----
             {
-                unsigned v[UB_ROWS_IN / 16][16];
+                unsigned v[UB_ROWS_IN / 32][16];  // (row 2j, row 2j + 1) as 16-bit halves: the sums are below 2^16
 #pragma unroll
-                for (int c = 0; c < UB_ROWS_IN / 16; ++c) ub_ld16(tlane + UB_COL_D1 + 16 * c, v[c]);
+                for (int c = 0; c < UB_ROWS_IN / 32; ++c) ub_ld16_pack(tlane + UB_COL_D1 + 32 * c, v[c]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                v[UB_ROWS_IN / 16 - 1][15] = 0x8000u;  // the last row is outside every band: its high byte feeds the rounding constant
+                // the last row is outside every band: its high byte feeds the rounding constant
+                v[UB_ROWS_IN / 32 - 1][15] = (v[UB_ROWS_IN / 32 - 1][15] & 0xffffu) | 0x80000000u;
 #pragma unroll
-                for (int c = 0; c < UB_ROWS_IN / 16; ++c)
+                for (int c = 0; c < UB_ROWS_IN / 32; ++c)
                 {
-                    unsigned lo[4], hi[4];
+                    unsigned lo[8], hi[8];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
+                    for (int j = 0; j < 8; ++j)
                     {
-                        lo[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0040), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0040), 0x5410);
-                        hi[j] = __byte_perm(__byte_perm(v[c][4 * j], v[c][4 * j + 1], 0x0051), __byte_perm(v[c][4 * j + 2], v[c][4 * j + 3], 0x0051), 0x5410);
+                        lo[j] = __byte_perm(v[c][2 * j], v[c][2 * j + 1], 0x6420);
+                        hi[j] = __byte_perm(v[c][2 * j], v[c][2 * j + 1], 0x7531);
                     }
-                    ub_st4(tlane + UB_COL_ALO + 4 * c, lo[0], lo[1], lo[2], lo[3]);
-                    ub_st4(tlane + UB_COL_AHI + 4 * c, hi[0], hi[1], hi[2], hi[3]);
+                    ub_st4(tlane + UB_COL_ALO + 8 * c, lo[0], lo[1], lo[2], lo[3]);
+                    ub_st4(tlane + UB_COL_ALO + 8 * c + 4, lo[4], lo[5], lo[6], lo[7]);
+                    ub_st4(tlane + UB_COL_AHI + 8 * c, hi[0], hi[1], hi[2], hi[3]);
+                    ub_st4(tlane + UB_COL_AHI + 8 * c + 4, hi[4], hi[5], hi[6], hi[7]);
                 }
             }
             if (!have || new_strip)
@@ -364,27 +378,12 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             ub_arrive(bar_e1);
-            // the previous tile's store must have read the output tile before it is overwritten; and nobody goes on alone
-            // after a barrier that never completed
             if (!ub_wait(bar_p2, par)) failed = 3;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            {
-                unsigned all_ok;
-                asm volatile("{\n\t.reg .pred p, q;\n\tsetp.eq.u32 p, %1, 0;\n\tbarrier.cta.red.and.pred q, 1, %2, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
-                             : "=r"(all_ok)
-                             : "r"((unsigned)failed), "n"(UB_EPI)
-                             : "memory");
-                if (!all_ok)
-                {
-                    if (failed && lane == 0) atomicExch(err, 4 + failed);  // 6 / 7: the MMAs of pass 1 / 2 never completed
-                    break;
-                }
-            }
             // ---- the accumulators, 16 output rows at a time: combine (the rounding constant is in already) and lay the
             //      bytes out as image rows; this thread is column tid of the tile. After the last load the next tile's pass 1
             //      may take the columns over ----
-            unsigned char* out = smem + UB_OFF_OUT + tid;
+            unsigned char* out = smem + UB_OFF_OUT + (i & 1) * UB_OUT_BYTES + tid;  // two tiles: the store of the last one may still read
 #pragma unroll
             for (int c = 0; c < UB_ROWS_OUT / 16; ++c)
             {
@@ -402,12 +401,24 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
                     for (int j = 0; j < 16; ++j) out[(16 * c + j) * UB_OUT_COLS] = (unsigned char)((ol[j] + (oh[j] << 8)) >> 16);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("barrier.cta.sync 1, %0;" ::"n"(UB_EPI) : "memory");
+            // one barrier per tile: the tile is complete; the store before the last one (the only one pending) has read its
+            // buffer, which the next tile writes; and nobody goes on alone after a barrier that never completed
+            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            unsigned all_ok;
+            asm volatile("{\n\t.reg .pred p, q;\n\tsetp.eq.u32 p, %1, 0;\n\tbarrier.cta.red.and.pred q, 1, %2, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
+                         : "=r"(all_ok)
+                         : "r"((unsigned)failed), "n"(UB_EPI)
+                         : "memory");
+            if (!all_ok)
+            {
+                if (failed && lane == 0) atomicExch(err, 4 + failed);  // 6 / 7: the MMAs of pass 1 / 2 never completed
+                break;
+            }
             if (tid == 0)
             {
                 asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(
                                  reinterpret_cast<unsigned long long>(map_dst)),
-                             "r"(out_x), "r"(y0), "r"(out_img), "r"(smem0 + UB_OFF_OUT)
+                             "r"(out_x), "r"(y0), "r"(out_img), "r"(smem0 + UB_OFF_OUT + (unsigned)((i & 1) * UB_OUT_BYTES))
                              : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
