@@ -31,9 +31,11 @@
 
 namespace snk
 {
-constexpr int UB_M        = 128;  // MMA M: TMEM lanes = output columns of the tile (UB_OUT_COLS used, the band of the rest is zero)
-constexpr int UB_OUT_COLS = 96;   // output columns per tile: a multiple of 16 (TMA coordinates), 16 + UB_OUT_COLS + 3 <= UB_K
-constexpr int UB_K        = 128;  // input columns per tile: [x0 - 16, x0 + 112) — one 128-byte swizzle row; the band needs [x0 - 3, x0 + 99)
+constexpr int UB_M        = 128;  // MMA M: TMEM lanes = output columns of the tile
+constexpr int UB_OUT_COLS = 128;  // output columns per tile [x0, x0 + 128), x0 a multiple of 16 (TMA coordinates)
+constexpr int UB_K        = 160;  // input columns per tile [x0 - 16, x0 + 144): the band needs [x0 - 3, x0 + 131); as two boxes,
+constexpr int UB_K0       = 128;  //   128 columns with the 128-byte swizzle (four K slices of 32)
+constexpr int UB_K1       = 32;   //   and 32 columns with the 32-byte swizzle (the fifth)
 constexpr int UB_ROWS_IN  = 64;   // input rows per tile = N of pass 1 = K of pass 2: [y0 - 3, y0 + 61)
 constexpr int UB_ROWS_OUT = 48;   // output rows per tile = N of pass 2 (multiple of 16, <= UB_ROWS_IN - 6 - 1: the last row carries the rounding constant)
 constexpr int UB_EPI      = 128;  // 4 epilogue warps: warp w reads TMEM lanes 32 w .. + 31, a thread is one output column
@@ -44,20 +46,26 @@ constexpr int UB_CTAS_PER_SM = 4;
 constexpr int UB_TMEM_COLS = 128;
 constexpr int UB_COL_D1 = 0, UB_COL_ALO = 0, UB_COL_AHI = UB_ROWS_IN / 4, UB_COL_OLO = UB_ROWS_IN / 2, UB_COL_OHI = UB_ROWS_IN / 2 + UB_ROWS_OUT;
 static_assert(UB_COL_OHI + UB_ROWS_OUT <= UB_TMEM_COLS && UB_ROWS_OUT + 7 <= UB_ROWS_IN && UB_ROWS_IN % 32 == 0 && UB_ROWS_OUT % 16 == 0, "tile shape");
-// shared memory (all operand tiles 1024-byte aligned for the 128-byte swizzle)
-constexpr int UB_OFF_IMG0 = 0;                               // image tile, buffer 0: UB_ROWS_IN rows x 128 B
-constexpr int UB_OFF_IMG1 = UB_ROWS_IN * 128;                // buffer 1
-constexpr int UB_OFF_WC   = 2 * UB_ROWS_IN * 128;            // column band: 128 rows (m) x 128 B (k)
-constexpr int UB_OFF_WR   = UB_OFF_WC + UB_M * 128;          // row band: UB_ROWS_OUT rows (n) x 128 B (k, UB_ROWS_IN used)
-constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_ROWS_OUT * 128;   // output tile: UB_ROWS_OUT rows x UB_OUT_COLS B, dense
-constexpr int UB_OUT_BYTES = (UB_ROWS_OUT * UB_OUT_COLS + 127) / 128 * 128;
-constexpr int UB_SMEM     = UB_OFF_OUT + 2 * UB_OUT_BYTES + 1024;  // two output tiles + alignment slack
-static_assert(UB_OFF_IMG1 % 1024 == 0 && UB_OFF_WC % 1024 == 0 && UB_OFF_WR % 1024 == 0 && UB_OFF_OUT % 1024 == 0, "swizzle alignment");
+// shared memory (operand tiles 1024-byte aligned for the swizzles)
+constexpr int UB_IMG_BYTES = UB_ROWS_IN * (UB_K0 + UB_K1);      // an image tile: UB_ROWS_IN rows x 128 B, then UB_ROWS_IN rows x 32 B
+constexpr int UB_WC_BYTES  = UB_M * (UB_K0 + UB_K1);            // column band: 128 rows (m) x 128 B, then 128 rows x 32 B
+constexpr int UB_WR_BYTES  = UB_ROWS_OUT * 128;                 // row band: UB_ROWS_OUT rows (n) x 128 B (k, UB_ROWS_IN used)
+constexpr int UB_OFF_IMG0 = 0;
+constexpr int UB_OFF_IMG1 = UB_IMG_BYTES;
+constexpr int UB_OFF_WC   = 2 * UB_IMG_BYTES;
+constexpr int UB_OFF_WR   = UB_OFF_WC + UB_WC_BYTES;
+constexpr int UB_OFF_OUT  = UB_OFF_WR + UB_WR_BYTES;            // output tile: UB_ROWS_OUT rows x UB_OUT_COLS B, dense
+constexpr int UB_OFF_BAR  = UB_OFF_OUT + UB_ROWS_OUT * UB_OUT_COLS;  // six mbarriers, the TMEM address
+constexpr int UB_SMEM     = UB_OFF_BAR + 64 + 1024;  // + alignment slack
+static_assert(UB_OFF_IMG1 % 1024 == 0 && UB_OFF_WC % 1024 == 0 && UB_OFF_WR % 1024 == 0 && UB_OFF_OUT % 1024 == 0 &&
+                  (UB_ROWS_IN * UB_K0) % 1024 == 0 && (UB_M * UB_K0) % 1024 == 0,
+              "swizzle alignment");
 
 struct UmmaBlurMaps
 {
-    CUtensorMap src[8];  // per level: (x, y, image) u8, box UB_K x UB_ROWS_IN x 1, SWIZZLE_128B
-    CUtensorMap dst[8];  // per level: box UB_OUT_COLS x UB_ROWS_OUT x 1, no swizzle
+    CUtensorMap src[8];   // per level: (x, y, image) u8, box UB_K0 x UB_ROWS_IN x 1, SWIZZLE_128B
+    CUtensorMap srcx[8];  // the same tensor, box UB_K1 x UB_ROWS_IN x 1, SWIZZLE_32B
+    CUtensorMap dst[8];   // per level: box UB_OUT_COLS x UB_ROWS_OUT x 1, no swizzle
 };
 struct UmmaBlurTask  // one column strip of a level
 {
@@ -94,17 +102,23 @@ struct UmmaTileIter
         if (++task < n_tasks) T = tasks[task];
     }
 };
-constexpr int UB_WC_BYTES = UB_M * 128, UB_WR_BYTES = UB_ROWS_OUT * 128;
 
 // byte offset of (row r, byte b) in a K-major operand tile with 128-byte rows and the 128-byte swizzle
 __device__ __forceinline__ unsigned ub_sw128(int r, int b)
 {
     return (unsigned)((r >> 3) * 1024 + (r & 7) * 128 + ((((b >> 4) ^ (r & 7)) << 4) | (b & 15)));
 }
+// the same for 32-byte rows and the 32-byte swizzle
+__device__ __forceinline__ unsigned ub_sw32(int r, int b) { return (unsigned)(r * 32 + ((((b >> 4) ^ ((r >> 2) & 1)) << 4) | (b & 15))); }
 // shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 bytes apart, descriptor version 1 (sm_100)
 __device__ __forceinline__ unsigned long long ub_desc(unsigned smem_addr)
 {
     return (unsigned long long)((smem_addr & 0x3ffffu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// K-major, SWIZZLE_32B, 8-row groups 256 bytes apart
+__device__ __forceinline__ unsigned long long ub_desc32(unsigned smem_addr)
+{
+    return (unsigned long long)((smem_addr & 0x3ffffu) >> 4) | (1ull << 16) | (16ull << 32) | (1ull << 46) | (6ull << 61);
 }
 // instruction descriptor: kind::i8, u8 x u8 -> s32, both operands K-major, M = 128
 __device__ __forceinline__ unsigned ub_idesc(int n) { return (2u << 4) | ((unsigned)(n >> 3) << 17) | ((unsigned)(UB_M >> 4) << 24); }
@@ -199,15 +213,26 @@ __global__ void k_umma_bands(const UmmaBandJob* __restrict__ jobs, unsigned char
 {
     const UmmaBandJob J = jobs[blockIdx.x];
     const int r = threadIdx.x;  // one band row per thread, 128 threads
-    const int rows = J.is_rows ? UB_ROWS_OUT : UB_M, used = J.is_rows ? UB_ROWS_OUT : UB_OUT_COLS, lead = J.is_rows ? 3 : 16;
-    if (r >= rows) return;
     unsigned char* base = table + J.off;
-    for (int kw = 0; kw < 32; ++kw)
+    if (J.is_rows)
     {
-        unsigned w = (r < used) ? band_word(J.origin - lead + 4 * kw, J.origin + r, J.len, false) : 0u;
-        // k = UB_ROWS_IN - 1 lies outside every band (k <= n + 6 <= 85): the constant's row
-        if (J.is_rows && kw == (UB_ROWS_IN - 1) / 4) w |= 1u << (8 * ((UB_ROWS_IN - 1) & 3));
-        *reinterpret_cast<unsigned*>(base + ub_sw128(r, 4 * kw)) = w;
+        if (r >= UB_ROWS_OUT) return;
+        for (int kw = 0; kw < 32; ++kw)
+        {
+            unsigned w = band_word(J.origin - 3 + 4 * kw, J.origin + r, J.len, false);
+            // k = UB_ROWS_IN - 1 lies outside every band (k <= n + 6): the constant's row
+            if (kw == (UB_ROWS_IN - 1) / 4) w |= 1u << (8 * ((UB_ROWS_IN - 1) & 3));
+            *reinterpret_cast<unsigned*>(base + ub_sw128(r, 4 * kw)) = w;
+        }
+    }
+    else
+    {
+        for (int kw = 0; kw < UB_K / 4; ++kw)
+        {
+            const unsigned w = band_word(J.origin - 16 + 4 * kw, J.origin + r, J.len, false);
+            unsigned char* at = kw < UB_K0 / 4 ? base + ub_sw128(r, 4 * kw) : base + UB_M * UB_K0 + ub_sw32(r, 4 * kw - UB_K0);
+            *reinterpret_cast<unsigned*>(at) = w;
+        }
     }
 }
 
@@ -218,17 +243,17 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
                                                         const unsigned char* __restrict__ bands, int* __restrict__ err)
 {
     extern __shared__ unsigned char ub_smem_raw[];
+    const unsigned smem0 = ((unsigned)__cvta_generic_to_shared(ub_smem_raw) + 1023u) & ~1023u;  // the swizzles want 1024-byte alignment
+    unsigned char* smem  = ub_smem_raw + (smem0 - (unsigned)__cvta_generic_to_shared(ub_smem_raw));
     // [0], [1]: image tile buffers (TMA); [2]: pass-1 MMAs done, [3]: pass-2 MMAs done (tcgen05.commit);
     // [4]: the A operands of pass 2 are written, [5]: the accumulators of pass 2 are read (UB_EPI arrivals each)
-    __shared__ __align__(8) unsigned long long s_bar[6];
-    __shared__ unsigned s_tmem;
+    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(smem + UB_OFF_BAR);
+    unsigned& s_tmem          = *reinterpret_cast<unsigned*>(smem + UB_OFF_BAR + 48);
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     const long long total = (long long)n_imgs * tiles_per_img;
     const long long g0 = total * blockIdx.x / gridDim.x, g1 = total * (blockIdx.x + 1) / gridDim.x;
     const int n_local = (int)(g1 - g0);
     if (n_local <= 0) return;
-    const unsigned smem0 = ((unsigned)__cvta_generic_to_shared(ub_smem_raw) + 1023u) & ~1023u;
-    unsigned char* smem  = ub_smem_raw + (smem0 - (unsigned)__cvta_generic_to_shared(ub_smem_raw));
     const unsigned bar0  = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
     const unsigned bar_p1 = bar0 + 16u, bar_p2 = bar0 + 24u, bar_e1 = bar0 + 32u, bar_e2 = bar0 + 40u;
 
@@ -268,17 +293,24 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             auto issue_load = [&]() {
                 const int buf      = n_loaded & 1;
                 const unsigned bar = bar0 + 8u * buf, dst = smem0 + (unsigned)(buf ? UB_OFF_IMG1 : UB_OFF_IMG0);
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)(UB_ROWS_IN * 128)) : "memory");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)UB_IMG_BYTES) : "memory");
                 asm volatile(
                     "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
                     "l"(reinterpret_cast<unsigned long long>(&maps.src[it.T.level])), "r"(it.T.x0 - 16), "r"(it.row * UB_ROWS_OUT - 3),
                     "r"(it.img), "r"(bar)
                     : "memory");
+                asm volatile(
+                    "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                        dst + (unsigned)(UB_ROWS_IN * UB_K0)),
+                    "l"(reinterpret_cast<unsigned long long>(&maps.srcx[it.T.level])), "r"(it.T.x0 - 16 + UB_K0),
+                    "r"(it.row * UB_ROWS_OUT - 3), "r"(it.img), "r"(bar)
+                    : "memory");
                 ++n_loaded;
                 it.next(tasks, n_tasks, n_imgs);
             };
             const unsigned idesc1 = ub_idesc(UB_ROWS_IN), idesc2 = ub_idesc(UB_ROWS_OUT);
-            const unsigned long long dwc = ub_desc(smem0 + UB_OFF_WC), dwr = ub_desc(smem0 + UB_OFF_WR);
+            const unsigned long long dwc = ub_desc(smem0 + UB_OFF_WC), dwcx = ub_desc32(smem0 + UB_OFF_WC + UB_M * UB_K0);
+            const unsigned long long dwr = ub_desc(smem0 + UB_OFF_WR);
             issue_load();
             if (n_local > 1) issue_load();
             int failed = 0;
@@ -286,14 +318,16 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             for (int i = 0; i < n_local; ++i)
             {
                 const int buf = i & 1;
-                // pass 1: D1[m][n] = sum_k Wc[m][k] I[n][k], four K slices of 32 columns; its columns double as O_lo of the
+                // pass 1: D1[m][n] = sum_k Wc[m][k] I[n][k], five K slices of 32 columns; its columns double as O_lo / O_hi of the
                 // previous tile, which the epilogue must have read
                 if (!ub_wait(bar0 + 8u * buf, (unsigned)((i >> 1) & 1))) { failed = 1; break; }
                 if (i > 0 && !ub_wait(bar_e2, (unsigned)((i - 1) & 1))) { failed = 4; break; }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const unsigned long long b = ub_desc(smem0 + (buf ? UB_OFF_IMG1 : UB_OFF_IMG0));
+                const unsigned img_at = smem0 + (unsigned)(buf ? UB_OFF_IMG1 : UB_OFF_IMG0);
+                const unsigned long long b = ub_desc(img_at);
 #pragma unroll
-                for (int k = 0; k < UB_K / 32; ++k) ub_mma_ss(tmem + UB_COL_D1, dwc + 2ull * k, b + 2ull * k, idesc1, k > 0);
+                for (int k = 0; k < UB_K0 / 32; ++k) ub_mma_ss(tmem + UB_COL_D1, dwc + 2ull * k, b + 2ull * k, idesc1, k > 0);
+                ub_mma_ss(tmem + UB_COL_D1, dwcx, ub_desc32(img_at + UB_ROWS_IN * UB_K0), idesc1, 1u);
                 ub_commit(bar_p1);
                 // pass 2 once the epilogue has written R_lo / R_hi (which also says pass 1 is complete: the tile buffer is free)
                 if (!ub_wait(bar_e1, (unsigned)(i & 1))) { failed = 4; break; }
@@ -377,13 +411,16 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            // the previous tile's store must have read the output tile before this tile's bytes go there: thread 0 vouches for
+            // it with its arrival — nobody gets past bar_p2 (pass 2 follows bar_e1) before
+            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             ub_arrive(bar_e1);
             if (!ub_wait(bar_p2, par)) failed = 3;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // ---- the accumulators, 16 output rows at a time: combine (the rounding constant is in already) and lay the
             //      bytes out as image rows; this thread is column tid of the tile. After the last load the next tile's pass 1
             //      may take the columns over ----
-            unsigned char* out = smem + UB_OFF_OUT + (i & 1) * UB_OUT_BYTES + tid;  // two tiles: the store of the last one may still read
+            unsigned char* out = smem + UB_OFF_OUT + tid;
 #pragma unroll
             for (int c = 0; c < UB_ROWS_OUT / 16; ++c)
             {
@@ -396,14 +433,11 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     ub_arrive(bar_e2);
                 }
-                if (tid < UB_OUT_COLS)
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) out[(16 * c + j) * UB_OUT_COLS] = (unsigned char)((ol[j] + (oh[j] << 8)) >> 16);
+                for (int j = 0; j < 16; ++j) out[(16 * c + j) * UB_OUT_COLS] = (unsigned char)((ol[j] + (oh[j] << 8)) >> 16);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            // one barrier per tile: the tile is complete; the store before the last one (the only one pending) has read its
-            // buffer, which the next tile writes; and nobody goes on alone after a barrier that never completed
-            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            // one barrier per tile: the tile is complete; and nobody goes on alone after a barrier that never completed
             unsigned all_ok;
             asm volatile("{\n\t.reg .pred p, q;\n\tsetp.eq.u32 p, %1, 0;\n\tbarrier.cta.red.and.pred q, 1, %2, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
                          : "=r"(all_ok)
@@ -418,7 +452,7 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             {
                 asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(
                                  reinterpret_cast<unsigned long long>(map_dst)),
-                             "r"(out_x), "r"(y0), "r"(out_img), "r"(smem0 + UB_OFF_OUT + (unsigned)((i & 1) * UB_OUT_BYTES))
+                             "r"(out_x), "r"(y0), "r"(out_img), "r"(smem0 + UB_OFF_OUT)
                              : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }

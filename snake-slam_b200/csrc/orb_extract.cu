@@ -107,9 +107,10 @@ struct snk_orb
     std::vector<TileDev> tiles;
     std::vector<BlurTask> blur_tasks;  // k_blur_mma: (level, 24-column strip, 128-row band)
     BlurTask* d_blur_tasks = nullptr;
-    bool blur_mma = true;              // SNK_BLUR_MMA=0 selects the dp4a kernel k_blur (A/B runs; 0.62 against 0.586 ms per 512 images)
-    // SNK_BLUR_MMA=2: the tcgen05 experiment k_blur_umma (blur_umma.cuh)
-    bool blur_umma = false;
+    // blur kernel (SNK_BLUR_MMA): default k_blur_umma (tcgen05, 0.39 ms per 512 EuRoC images); 1 = k_blur_mma (mma.sync, 0.585 ms;
+    // also taken for pyramids of more than 8 levels); 0 = k_blur (dp4a, 0.62 ms)
+    bool blur_mma  = true;
+    bool blur_umma = true;
     UmmaBlurMaps umma_maps{};
     std::vector<UmmaBlurTask> umma_tasks;
     UmmaBlurTask* d_umma_tasks   = nullptr;
@@ -213,11 +214,14 @@ static int encode_umma_maps(snk_orb* h, int l, const void* src, int pitch, size_
     const cuuint32_t estr[3] = {1, 1, 1};
     {
         const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
-        const cuuint32_t box[3]     = {UB_K, UB_ROWS_IN, 1};
+        const cuuint32_t box[3]     = {UB_K0, UB_ROWS_IN, 1}, boxx[3] = {UB_K1, UB_ROWS_IN, 1};
         CUresult r = fn(&h->umma_maps.src[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur source of level %d (CUresult %d)", l, (int)r);
+        r = fn(&h->umma_maps.srcx[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, boxx, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur source (side box) of level %d (CUresult %d)", l, (int)r);
     }
     if (with_dst)
     {
@@ -272,8 +276,10 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     h->blur_tasks.clear();
     {
         const char* e = getenv("SNK_BLUR_MMA");
+        // default: the tcgen05 kernel (k_blur_umma; its tensor-map parameter block holds 8 levels); 1: the mma.sync kernel
+        // k_blur_mma, also the fallback for deeper pyramids; 0: the dp4a kernel k_blur
         h->blur_mma   = !(e && e[0] == '0');
-        h->blur_umma  = e && e[0] == '2';
+        h->blur_umma  = !(e && (e[0] == '0' || e[0] == '1')) && L <= 8;
         h->umma_tasks.clear();
         h->umma_tiles_per_img = 0;
     }
@@ -408,7 +414,6 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     if (h->blur_umma)
     {
         // per level: tensor maps, one task per column strip, the band matrices of its strips and row tiles
-        SNK_REQUIRE(L <= 8, "SNK_BLUR_MMA=2 (k_blur_umma) handles at most 8 levels");
         SNK_CUDA(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, h->prm.device));
         std::vector<UmmaBandJob> jobs;
         unsigned off = 0;

@@ -354,10 +354,10 @@ def test_random_geometries_fuzz(so, oracle):
     assert done >= 25
 
 
-@pytest.mark.parametrize("mode", ["1", "0", "2"])
+@pytest.mark.parametrize("mode", ["2", "1", "0"])
 def test_blur_every_level_byte_equal_on_random_sizes(so, oracle, monkeypatch, mode):
-    """cv::GaussianBlur of every pyramid level (SNK_BLUR_MMA, read when an extractor allocates its pyramid: 1 = the
-    default mma.sync tensor-core kernel k_blur_mma, 0 = the dp4a kernel k_blur, 2 = the tcgen05 kernel k_blur_umma): byte-equal to the oracle on random image sizes — widths and heights of every residue mod 4 / 8 /
+    """cv::GaussianBlur of every pyramid level (SNK_BLUR_MMA, read when an extractor allocates its pyramid: unset or 2 = the
+    tcgen05 kernel k_blur_umma, 1 = the mma.sync tensor-core kernel k_blur_mma, 0 = the dp4a kernel k_blur): byte-equal to the oracle on random image sizes — widths and heights of every residue mod 4 / 8 /
     16 / 64, so that partial last strips, partial last words and the folded taps at all four borders are hit — on noise
     (every byte matters) and in batches (the image index only offsets the pointers)."""
     from snakeorb import synthetic as S

@@ -78,10 +78,13 @@ int main(int argc, char** argv)
     const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)NIMG};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
     const cuuint32_t estr[3] = {1, 1, 1};
-    const cuuint32_t box_in[3] = {snk::UB_K, snk::UB_ROWS_IN, 1}, box_out[3] = {snk::UB_OUT_COLS, snk::UB_ROWS_OUT, 1};
+    const cuuint32_t box_in[3] = {snk::UB_K0, snk::UB_ROWS_IN, 1}, box_inx[3] = {snk::UB_K1, snk::UB_ROWS_IN, 1}, box_out[3] = {snk::UB_OUT_COLS, snk::UB_ROWS_OUT, 1};
     CUresult r = fn(&maps.src[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, d_src, dims, strides, box_in, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return printf("encode src failed %d\n", (int)r), 2;
+    r = fn(&maps.srcx[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, d_src, dims, strides, box_inx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return printf("encode srcx failed %d\n", (int)r), 2;
     r = fn(&maps.dst[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, d_dst, dims, strides, box_out, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return printf("encode dst failed %d\n", (int)r), 2;
