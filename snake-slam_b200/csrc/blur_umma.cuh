@@ -1,33 +1,41 @@
 // cv::GaussianBlur(7 x 7, sigma 2, BORDER_REFLECT_101) of u8 images on the 5th-generation tensor cores: tcgen05.mma
-// kind::i8 with the accumulators in tensor memory (ORBExtractor.cpp:213; semantics as k_blur / k_blur_mma).
-//
-// EXPERIMENT (round 2, verdict item 3b) — selected with SNK_BLUR_MMA=2; the default stays k_blur_mma (blur_mma.cuh).
+// kind::i8, operands by TMA, accumulators in tensor memory (ORBExtractor.cpp:213; semantics as k_blur / k_blur_mma).
+// The default blur since round 2 (SNK_BLUR_MMA=1 selects k_blur_mma, 0 k_blur); byte-equal to the oracle on every shape of
+// tests/test_gpu_extract.py. 0.39 ms per 512 EuRoC images against 0.585 ms (mma.sync) and 0.62 ms (dp4a).
 //
 // Both passes of the fixed-point blur are banded matrix products with u8 weights (56 48 34 18, sum 256):
 //   pass 1 (rows):     R[x][y]  = sum_k  Wc[x][k] * I[y][k]        Wc: band over image columns, reflect-101 folded in
 //   pass 2 (columns):  O[x][y'] = sum_y  R[x][y] * Wr[y'][y]       Wr: band over image rows
 //   out = (O + 32768) >> 16
 // Pass 1 is computed TRANSPOSED (M = output columns on the TMEM lanes, N = image rows): the image tile is then the B
-// operand exactly as it lies in memory (row = N index, columns = K, contiguous) and arrives by ONE TMA box with the
-// 128-byte swizzle the MMA wants; and the result has the image rows along the TMEM columns, i.e. along the K dimension
-// of an A operand read from tensor memory — pass 2 takes it from there without a trip through shared memory. R is 16
-// bits wide, the operands are 8: the epilogue of pass 1 reads the s32 accumulators (tcgen05.ld), splits them into low
-// and high bytes and writes two u8 A operands back (tcgen05.st); pass 2 runs once on each, O = O_lo + 256 O_hi.
-// Per tile (UB_OUT_COLS x UB_ROWS_OUT output pixels, UB_K x UB_ROWS_IN input pixels):
-//   TMA load -> 4 MMAs (M 128, N 96, K 32) -> ld / split / st -> 2 x 3 MMAs (M 128, N 80, K 32) -> ld, combine, bytes into
-//   a shared-memory tile -> TMA store (clipped at the image's sides by the tensor map).
-// Persistent CTAs (two per SM: 224 of the 512 TMEM columns each) walk equal shares of the tile list; warp 8's lane 0 issues
-// the TMA loads (two tiles ahead) and the MMAs and waits only on barriers, the eight other warps are the two epilogues.
-// The band matrices come from a table built once per pyramid geometry (k_umma_bands), copied in when the strip / the row
-// tile kind changes.
-// TMEM columns: [0,96) pass-1 accumulator, reused as O_lo; [96,120) R_lo, [120,144) R_hi as u8 x 4; [144,224) O_hi.
+// operand exactly as it lies in memory (row = N index, columns = K, contiguous) and arrives by TMA with the swizzle the
+// MMA wants; and the result has the image rows along the TMEM columns, i.e. along the K dimension of an A operand read
+// from tensor memory — pass 2 takes it from there without a trip through shared memory. R is 16 bits wide, the operands
+// are 8: the epilogue of pass 1 reads the accumulators (tcgen05.ld, two 16-bit values per register), splits them into low
+// and high bytes (one PRMT each per four rows) and writes two u8 A operands back (tcgen05.st); pass 2 runs once on each,
+// O = O_lo + 256 O_hi. The rounding constant rides along: the last input row of a tile lies outside every band, its high
+// byte is set to 128 and its band weight to 1 (128 * 256 = 32768).
+// Per tile (128 x 48 output pixels from 160 x 64 input pixels):
+//   two TMA boxes (128 columns with the 128-byte swizzle, 32 with the 32-byte one) -> 5 MMAs (M 128, N 64, K 32) -> ld /
+//   split / st -> 2 x 2 MMAs (M 128, N 48, K 32) -> ld, combine, bytes into a shared-memory tile -> TMA store (clipped at
+//   the image's sides by the tensor map).
+// TMEM: 128 columns per CTA, so that FOUR CTAs share an SM — the per-tile chain (MMA -> epilogue -> MMA -> epilogue) is
+// latency, and tiles in flight are what hides it; the columns are reused inside a tile: [0,64) pass-1 accumulator, then
+// [0,16) R_lo, [16,32) R_hi (u8 x 4), [32,80) O_lo, [80,128) O_hi.
+// Persistent CTAs walk equal shares of the tile list (strip by strip, image by image, top down); warp 4's lane 0 issues the
+// TMA loads (two tiles ahead) and the MMAs and waits only on mbarriers, warps 0-3 are the epilogue (a thread = an output
+// column = a TMEM lane). The band matrices come from a table built once per pyramid geometry (k_umma_bands) and are
+// copied in (cp.async) when the strip / the row-tile kind changes.
+// Steps on the way (B200, 512 EuRoC images, all byte-equal): one CTA per strip with sequential phases 0.68 ms; warp-
+// specialised 0.68; persistent over a tile list 0.70 (256 TMEM columns, two CTAs per SM: the chain of a tile is ~4400
+// cycles whatever the schedule); 128 TMEM columns, four CTAs per SM 0.49; packed TMEM loads, one barrier per tile 0.47;
+// 128 instead of 96 output columns per tile 0.39.
 #pragma once
 #include <cuda.h>
 
 #include <cstdint>
 
 #include "blur_weights.cuh"
-
 
 namespace snk
 {
@@ -70,13 +78,14 @@ struct UmmaBlurMaps
 struct UmmaBlurTask  // one column strip of a level
 {
     short level, x0, w, h;
-    int n_row_tiles;
+    short n_row_tiles, strip, n_strips, wc_interior;  // wc_interior: no tap of the strip is folded (all such strips share one band)
     unsigned wc_off;  // byte offset of the strip's column band in the band table
     unsigned wr_off;  // byte offset of the level's row bands (one per row tile, UB_WR_BYTES apart)
 };
-// The tiles of a launch in the order the CTAs walk them: strip by strip, inside a strip image by image, inside an image
-// from the top down. CTA c of G takes the tiles [c n / G, (c + 1) n / G): long runs inside one strip (the column band
-// stays), every CTA the same number of tiles, the pipeline never drains between strips or images.
+// The tiles of a launch in the order the CTAs walk them: level by level, inside a level image by image, inside an image
+// strip by strip, inside a strip from the top down. CTA c of G takes the tiles [c n / G, (c + 1) n / G): every CTA the same
+// number of tiles, the pipeline never drains between strips or images, and a tile's halo — the rows it shares with the
+// tile above, the columns it shares with the strip to the left — was read by the same CTA moments ago (L2 hits).
 struct UmmaTileIter
 {
     int task, img, row;
@@ -85,21 +94,39 @@ struct UmmaTileIter
     {
         task = 0;
         T    = tasks[0];
-        while (g >= (long long)n_imgs * T.n_row_tiles)
+        for (;;)  // levels
         {
-            g -= (long long)n_imgs * T.n_row_tiles;
-            T = tasks[++task];
+            const long long level_tiles = (long long)T.n_strips * T.n_row_tiles;
+            if (g < n_imgs * level_tiles)
+            {
+                img = (int)(g / level_tiles);
+                const int r = (int)(g - img * level_tiles);
+                task += r / T.n_row_tiles;
+                row = r % T.n_row_tiles;
+                T   = tasks[task];
+                return;
+            }
+            g -= n_imgs * level_tiles;
+            task += T.n_strips;
+            T = tasks[task];
         }
-        img = (int)(g / T.n_row_tiles);
-        row = (int)(g - (long long)img * T.n_row_tiles);
     }
     __device__ void next(const UmmaBlurTask* __restrict__ tasks, int n_tasks, int n_imgs)
     {
         if (++row < T.n_row_tiles) return;
         row = 0;
-        if (++img < n_imgs) return;
-        img = 0;
-        if (++task < n_tasks) T = tasks[task];
+        if (T.strip + 1 < T.n_strips)
+        {
+            T = tasks[++task];
+            return;
+        }
+        task -= T.strip;  // first strip of the level
+        if (++img == n_imgs)
+        {
+            img = 0;
+            task += T.n_strips;  // next level
+        }
+        if (task < n_tasks) T = tasks[task];
     }
 };
 
@@ -368,9 +395,10 @@ __global__ void __launch_bounds__(UB_NT, UB_CTAS_PER_SM) k_blur_umma(const __gri
             // this tile's output coordinates; then look at the next tile: a new strip needs its column band
             const int out_x = it.T.x0, out_img = it.img;
             const CUtensorMap* map_dst = &maps.dst[it.T.level];
-            const int cur_task = it.task;
+            const int cur_task = it.task, cur_level = it.T.level;
+            const bool cur_interior = it.T.wc_interior != 0;
             it.next(tasks, n_tasks, n_imgs);
-            const bool new_strip = i + 1 < n_local && it.task != cur_task;
+            const bool new_strip = i + 1 < n_local && it.task != cur_task && !(cur_interior && it.T.wc_interior && it.T.level == cur_level);
             if (!ub_wait(bar_p1, par)) failed = 2;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (new_strip)  // pass 1 of this tile, the last reader of the old band, has completed

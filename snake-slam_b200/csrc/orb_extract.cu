@@ -425,7 +425,9 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             const unsigned wr_off = off + (unsigned)n_strips * UB_WC_BYTES;
             for (int sidx = 0; sidx < n_strips; ++sidx)
             {
-                h->umma_tasks.push_back(UmmaBlurTask{(short)l, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, (short)P.lv[l].h, n_row_tiles, off, wr_off});
+                h->umma_tasks.push_back(UmmaBlurTask{(short)l, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, (short)P.lv[l].h, (short)n_row_tiles, (short)sidx,
+                                                     (short)n_strips, (short)(sidx * UB_OUT_COLS >= 3 && sidx * UB_OUT_COLS + UB_OUT_COLS + 3 <= P.lv[l].w), off,
+                                                     wr_off});
                 h->umma_tiles_per_img += n_row_tiles;
                 jobs.push_back(UmmaBandJob{off, (short)(sidx * UB_OUT_COLS), (short)P.lv[l].w, 0, 0});
                 off += UB_WC_BYTES;

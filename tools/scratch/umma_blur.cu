@@ -96,7 +96,9 @@ int main(int argc, char** argv)
     const unsigned wr_off = (unsigned)((W + snk::UB_OUT_COLS - 1) / snk::UB_OUT_COLS) * snk::UB_WC_BYTES;
     for (int x0 = 0; x0 < W; x0 += snk::UB_OUT_COLS)
     {
-        tasks.push_back(snk::UmmaBlurTask{0, (short)x0, (short)W, (short)H, n_row_tiles, off, wr_off});
+        tasks.push_back(snk::UmmaBlurTask{0, (short)x0, (short)W, (short)H, (short)n_row_tiles, (short)(x0 / snk::UB_OUT_COLS),
+                                          (short)((W + snk::UB_OUT_COLS - 1) / snk::UB_OUT_COLS),
+                                          (short)(x0 >= 3 && x0 + snk::UB_OUT_COLS + 3 <= W), off, wr_off});
         jobs.push_back(snk::UmmaBandJob{off, (short)x0, (short)W, 0, 0});
         off += snk::UB_WC_BYTES;
     }
