@@ -212,15 +212,16 @@ static int encode_umma_maps(snk_orb* h, int l, const void* src, int pitch, size_
     SNK_REQUIRE(((uintptr_t)src % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
     const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)h->prm.max_batch};
     const cuuint32_t estr[3] = {1, 1, 1};
+    // (L2 promotion 64 / 128 / 256 B measured: 0.352 / 0.355 / 0.377 ms against 0.356 ms without)
+    const CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_NONE;
     {
         const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
         const cuuint32_t box[3]     = {UB_K0, UB_ROWS_IN, 1}, boxx[3] = {UB_K1, UB_ROWS_IN, 1};
         CUresult r = fn(&h->umma_maps.src[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur source of level %d (CUresult %d)", l, (int)r);
         r = fn(&h->umma_maps.srcx[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, boxx, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the blur source (side box) of level %d (CUresult %d)", l, (int)r);
     }
     if (with_dst)
