@@ -862,8 +862,12 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         // (measured on 512 images: 32/16/8 rows by level size 0.573 ms, 16 everywhere 0.554, 8 everywhere 0.552, 4: 0.590)
         const int rps = RS_ROWS / 4;
         dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + rps - 1) / rps + 3) / 4, n_imgs);
-        k_resize<<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
-                                       h->d_quads[l], h->d_rows[l], rps);
+        if (l == 1 && s.img != h->own_l0.img)  // level 0 is the caller's device buffer: nothing may be read behind its last row
+            k_resize<true><<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
+                                                 h->d_quads[l], h->d_rows[l], rps);
+        else
+            k_resize<false><<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
+                                                  h->d_quads[l], h->d_rows[l], rps);
         ++nl[1];
     }
     if (prof) cudaEventRecord(ev[2], st);

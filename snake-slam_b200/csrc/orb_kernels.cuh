@@ -109,6 +109,11 @@ __device__ __forceinline__ unsigned mad_hi(unsigned a, unsigned b, unsigned c)
     return d;
 }
 
+// CLAMP: the source may end with its last row (level 0 aliasing a caller's buffer): the window's second and third word
+// are clamped to the row. Otherwise the source is one of the pyramid's own buffers — rows are followed by pitch padding, the
+// next row, or the allocation's slack — and the three words are read at fixed offsets from one address (a word past the
+// row only ever meets a zero coefficient or a selector that does not pick it).
+template <bool CLAMP>
 __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src, size_t src_stride, int spitch, int sh,
                                                 uint8_t* __restrict__ dst, size_t dst_stride, int dpitch, int dw, int dh,
                                                 const ResizeQuad* __restrict__ quads, const ResizeRow* __restrict__ rows,
@@ -128,9 +133,20 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
     const bool full = x + 4 <= dw;
 
     // horizontal pass of one source row: the four sums, already >> 4 as the vertical pass consumes them
+    const uint32_t* S0 = reinterpret_cast<const uint32_t*>(S) + q.word;
+    const int pitch_w  = spitch >> 2;
     auto hrow = [&](int sy, unsigned (&h)[4]) {
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)sy * spitch);
-        const unsigned w0 = __ldg(row + i0), w1 = __ldg(row + i1), w2 = __ldg(row + i2);
+        unsigned w0, w1, w2;
+        if (CLAMP)
+        {
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)sy * spitch);
+            w0 = __ldg(row + i0), w1 = __ldg(row + i1), w2 = __ldg(row + i2);
+        }
+        else
+        {
+            const uint32_t* row = S0 + sy * pitch_w;
+            w0 = __ldg(row), w1 = __ldg(row + 1), w2 = __ldg(row + 2);
+        }
         const unsigned v0 = __funnelshift_r(w0, w1, q.shift_bits), v1 = __funnelshift_r(w1, w2, q.shift_bits);
         const unsigned r01 = __byte_perm(v0, v1, sel01), r23 = __byte_perm(v0, v1, sel23);
         h[0] = __dp2a_lo(q.coef[0], r01, 0u) >> 4;
