@@ -129,6 +129,10 @@ struct snk_orb
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
     ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
     ResizeRow* d_rows[SNK_MAX_LEVELS]{};
+    // k_resize_tma (default; SNK_RESIZE_TMA=0 selects k_resize): per destination level the source's tensor map and its box
+    bool resize_tma = true;
+    CUtensorMap rs_map[SNK_MAX_LEVELS]{};
+    int rs_box_w[SNK_MAX_LEVELS]{}, rs_box_h[SNK_MAX_LEVELS]{};
     uint2* d_moment_tab = nullptr;  // ComputeAngle disc as per-word dp4a weights (orb_kernels.cuh: DS_MOM_TABLE)
     float2* d_pattern_t = nullptr;  // rBRIEF pattern as float2, transposed to [point-in-byte][lane]
     CellDev* d_cells = nullptr;
@@ -196,6 +200,26 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
+    return SNK_OK;
+}
+
+// tensor map of k_resize_tma for destination level l: the source level as rs_box_w x rs_box_h boxes, no swizzle
+static int encode_resize_map(snk_orb* h, int l, const void* src, int pitch, size_t img_stride)
+{
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    SNK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    SNK_REQUIRE(p && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+    const LevelDev& S = h->P.lv[l - 1];
+    SNK_REQUIRE(((uintptr_t)src % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
+    const cuuint64_t dims[3]    = {(cuuint64_t)S.w, (cuuint64_t)S.h, (cuuint64_t)h->prm.max_batch};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
+    const cuuint32_t box[3]     = {(cuuint32_t)h->rs_box_w[l], (cuuint32_t)h->rs_box_h[l], 1};
+    const cuuint32_t estr[3]    = {1, 1, 1};
+    CUresult r = ((EncodeTiledFn)p)(&h->rs_map[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the resize source of level %d (CUresult %d)", l, (int)r);
     return SNK_OK;
 }
 
@@ -451,6 +475,10 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
         SNK_CUDA(cudaFree(d_jobs));
         SNK_CUDA(cudaFuncSetAttribute(k_blur_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, UB_SMEM));
     }
+    {
+        const char* e = getenv("SNK_RESIZE_TMA");
+        h->resize_tma = !(e && e[0] == '0');
+    }
     for (int l = 1; l < L; ++l)
     {
         std::vector<int> xo, yo;
@@ -493,10 +521,29 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
             rows[y].b0  = (unsigned)yb[2 * y] << 16;
             rows[y].b1  = (unsigned)yb[2 * y + 1] << 16;
         }
+        // k_resize_tma: the largest source window of a 128 x 32 output tile (start rounded down to 16 bytes; a quad reads 3 words)
+        {
+            int bw = 16, bh = 1;
+            for (int tx = 0; tx * (RT_W / 4) < (int)quads.size(); ++tx)
+            {
+                const int first = (quads[tx * (RT_W / 4)].word * 4) & ~15;
+                const int lastq = std::min(tx * (RT_W / 4) + RT_W / 4 - 1, (int)quads.size() - 1);
+                bw              = std::max(bw, quads[lastq].word * 4 + 12 - first);
+            }
+            for (int ty = 0; ty * RT_H < dh; ++ty)
+                bh = std::max(bh, rows[std::min(ty * RT_H + RT_H - 1, dh - 1)].sy1 - rows[ty * RT_H].sy0 + 1);
+            h->rs_box_w[l] = align_up(bw, 16), h->rs_box_h[l] = bh;
+            if (h->rs_box_w[l] > 256 || bh > 256 || h->rs_box_w[l] * bh > 48 * 1024) h->resize_tma = false;  // beyond a TMA box: the plain kernel
+        }
         SNK_CUDA(cudaMalloc(&h->d_quads[l], quads.size() * sizeof(ResizeQuad)));
         SNK_CUDA(cudaMalloc(&h->d_rows[l], rows.size() * sizeof(ResizeRow)));
         SNK_CUDA(cudaMemcpy(h->d_quads[l], quads.data(), quads.size() * sizeof(ResizeQuad), cudaMemcpyHostToDevice));
         SNK_CUDA(cudaMemcpy(h->d_rows[l], rows.data(), rows.size() * sizeof(ResizeRow), cudaMemcpyHostToDevice));
+    }
+    for (int l = 1; l < L && h->resize_tma; ++l)
+    {
+        int rc = encode_resize_map(h, l, P.lv[l - 1].img, P.lv[l - 1].pitch, P.lv[l - 1].img_stride);
+        if (rc) return rc;
     }
     h->fast_rows = align_up(h->fast_rows, 8);  // keeps every tile buffer 128-byte aligned (8 rows x 96 or 176 bytes)
     h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
@@ -848,6 +895,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         rc = encode_level_map(h, 0, P.lv[0].img, P.lv[0].pitch, stride0);
         if (rc) return rc;
         if (h->blur_umma && (rc = encode_umma_maps(h, 0, P.lv[0].img, P.lv[0].pitch, stride0, false))) return rc;
+        if (h->resize_tma && P.nlevels > 1 && (rc = encode_resize_map(h, 1, P.lv[0].img, P.lv[0].pitch, stride0))) return rc;
         h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
     }
     if (prof) cudaEventRecord(ev[1], st);
@@ -862,7 +910,10 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         // (measured on 512 images: 32/16/8 rows by level size 0.573 ms, 16 everywhere 0.554, 8 everywhere 0.552, 4: 0.590)
         const int rps = RS_ROWS / 4;
         dim3 grid((d.w + RS_TW - 1) / RS_TW, ((d.h + rps - 1) / rps + 3) / 4, n_imgs);
-        if (l == 1 && s.img != h->own_l0.img)  // level 0 is the caller's device buffer: nothing may be read behind its last row
+        if (h->resize_tma)
+            k_resize_tma<<<dim3((d.w + RT_W - 1) / RT_W, (d.h + RT_H - 1) / RT_H, n_imgs), 128, (size_t)h->rs_box_w[l] * h->rs_box_h[l], st>>>(
+                h->rs_map[l], d.img, d.img_stride, d.pitch, d.w, d.h, h->d_quads[l], h->d_rows[l], h->rs_box_w[l], h->rs_box_h[l], h->d_err);
+        else if (l == 1 && s.img != h->own_l0.img)  // level 0 is the caller's device buffer: nothing may be read behind its last row
             k_resize<true><<<grid, 128, 0, st>>>(s.img, s.img_stride, s.pitch, s.h, d.img, d.img_stride, d.pitch, d.w, d.h,
                                                  h->d_quads[l], h->d_rows[l], rps);
         else
