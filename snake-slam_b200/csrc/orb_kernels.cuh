@@ -114,7 +114,13 @@ __device__ __forceinline__ unsigned mad_hi(unsigned a, unsigned b, unsigned c)
 // zero coefficient) while the threads fetch their table entries; the arithmetic then runs on shared memory — no
 // global-load latency in the row loop, no 64-bit address arithmetic (k_resize: 26 thread-instructions per pixel, 60 % of
 // the issue slots busy, the rest waiting on loads). Box sizes per level from the host (largest window of any tile).
-constexpr int RT_W = 128, RT_H = 32;
+#ifndef SNK_RT_H
+#define SNK_RT_H 64
+#endif
+#ifndef SNK_RT_UNROLL
+#define SNK_RT_UNROLL 4
+#endif
+constexpr int RT_W = 128, RT_H = SNK_RT_H, RT_UNROLL = SNK_RT_UNROLL;
 __global__ void __launch_bounds__(128) k_resize_tma(const __grid_constant__ CUtensorMap map, uint8_t* __restrict__ dst, size_t dst_stride,
                                                     int dpitch, int dw, int dh, const ResizeQuad* __restrict__ quads,
                                                     const ResizeRow* __restrict__ rows, int box_w, int box_h, int* __restrict__ err)
@@ -164,14 +170,24 @@ __global__ void __launch_bounds__(128) k_resize_tma(const __grid_constant__ CUte
         h[2] = __dp2a_lo(q.coef[2], r23, 0u) >> 4;
         h[3] = __dp2a_hi(q.coef[3], r23, 0u) >> 4;
     };
-    unsigned ha[4], hb[4];
+    // consecutive output rows mostly share a source row (sy0 of a row is sy1 of the row above unless the step skips one):
+    // its horizontal sums are kept — a uniform branch, and shared-memory latency is short enough for the serial chain
+    unsigned ha[4], hb[4] = {0u, 0u, 0u, 0u};
+    int have = -1;  // source row whose sums are in hb
     const int y1 = min(y0 + RT_H / 4, dh);
-#pragma unroll 4
+#pragma unroll RT_UNROLL
     for (int y = y0; y < y1; ++y, D += dpitch)
     {
         const int4 rt = __ldg(reinterpret_cast<const int4*>(rows) + y);
-        hrow(rt.x, ha);
+        if (rt.x == have)
+        {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ha[j] = hb[j];
+        }
+        else
+            hrow(rt.x, ha);
         hrow(rt.y, hb);
+        have = rt.y;
         unsigned v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = mad_hi(hb[j], (unsigned)rt.w, mad_hi(ha[j], (unsigned)rt.z, 2u)) >> 2;  // as in k_resize
