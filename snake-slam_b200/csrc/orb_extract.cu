@@ -129,6 +129,9 @@ struct snk_orb
     LevelDev own_l0{};           // level-0 descriptor of the internal buffer
     ResizeQuad* d_quads[SNK_MAX_LEVELS]{};
     ResizeRow* d_rows[SNK_MAX_LEVELS]{};
+    // k_describe_tma (default for up to 8 levels; SNK_DESCRIBE_TMA=0 selects k_describe): per level the tensor maps of its patches
+    bool describe_tma = true;
+    DescMaps desc_maps{};
     // k_resize_tma (default; SNK_RESIZE_TMA=0 selects k_resize): per destination level the source's tensor map and its box
     bool resize_tma = true;
     CUtensorMap rs_map[SNK_MAX_LEVELS]{};
@@ -200,6 +203,37 @@ static int encode_level_map(snk_orb* h, int l, const void* base, int pitch, size
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
+    return SNK_OK;
+}
+
+// tensor maps of k_describe_tma for one level: the level image as 48 x 31 boxes, its blurred copy as 64 x 39 boxes
+static int encode_describe_maps(snk_orb* h, int l, const void* src, int pitch, size_t img_stride, bool with_gauss)
+{
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    SNK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    SNK_REQUIRE(p && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+    const LevelDev& L = h->P.lv[l];
+    SNK_REQUIRE(((uintptr_t)src % 16) == 0 && pitch % 16 == 0 && img_stride % 16 == 0, "internal: TMA alignment");
+    const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)h->prm.max_batch};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    {
+        const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)img_stride};
+        const cuuint32_t box[3]     = {DT_IMG_W, DT_IMG_H, 1};
+        CUresult r = ((EncodeTiledFn)p)(&h->desc_maps.img[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(src), dims, strides, box,
+                                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the moment patches of level %d (CUresult %d)", l, (int)r);
+    }
+    if (with_gauss)
+    {
+        const cuuint64_t strides[2] = {(cuuint64_t)L.gauss_pitch, (cuuint64_t)L.gauss_stride};
+        const cuuint32_t box[3]     = {DT_G_W, DT_G_H, 1};
+        CUresult r = ((EncodeTiledFn)p)(&h->desc_maps.gauss[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.gauss, dims, strides, box, estr,
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        SNK_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for the descriptor patches of level %d (CUresult %d)", l, (int)r);
+    }
     return SNK_OK;
 }
 
@@ -544,6 +578,16 @@ static int orb_allocate(snk_orb* h, int rows, int cols)
     {
         int rc = encode_resize_map(h, l, P.lv[l - 1].img, P.lv[l - 1].pitch, P.lv[l - 1].img_stride);
         if (rc) return rc;
+    }
+    {
+        const char* e   = getenv("SNK_DESCRIBE_TMA");
+        h->describe_tma = !(e && e[0] == '0') && L <= 8;
+        for (int l = 0; l < L && h->describe_tma; ++l)
+        {
+            int rc = encode_describe_maps(h, l, P.lv[l].img, P.lv[l].pitch, P.lv[l].img_stride, true);
+            if (rc) return rc;
+        }
+        if (h->describe_tma) SNK_CUDA(cudaFuncSetAttribute(k_describe_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, DT_SMEM));
     }
     h->fast_rows = align_up(h->fast_rows, 8);  // keeps every tile buffer 128-byte aligned (8 rows x 96 or 176 bytes)
     h->fast_smem = 3 * (size_t)h->fast_rows * FAST_PITCH + 4 * (size_t)h->fast_list;
@@ -896,6 +940,7 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
         if (rc) return rc;
         if (h->blur_umma && (rc = encode_umma_maps(h, 0, P.lv[0].img, P.lv[0].pitch, stride0, false))) return rc;
         if (h->resize_tma && P.nlevels > 1 && (rc = encode_resize_map(h, 1, P.lv[0].img, P.lv[0].pitch, stride0))) return rc;
+        if (h->describe_tma && (rc = encode_describe_maps(h, 0, P.lv[0].img, P.lv[0].pitch, stride0, false))) return rc;
         h->map0_ptr = P.lv[0].img, h->map0_pitch = P.lv[0].pitch, h->map0_stride = P.lv[0].img_stride;
     }
     if (prof) cudaEventRecord(ev[1], st);
@@ -982,8 +1027,12 @@ int snk_orb_enqueue(snk_orb* h, const uint8_t* imgs, int n_imgs, int rows, int c
 
     nvtx_stage.next("snk:describe");
     // stage 5: orientation + descriptors + output records
-    k_describe<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, 0, st>>>(
-        P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t, h->d_moment_tab);
+    if (h->describe_tma)
+        k_describe_tma<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, DT_SMEM, st>>>(
+            P, h->desc_maps, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t, h->d_moment_tab, h->d_err);
+    else
+        k_describe<<<dim3((P.kp_stride + DS_WARPS * DS_KP_PER_WARP - 1) / (DS_WARPS * DS_KP_PER_WARP), n_imgs), DS_WARPS * 32, 0, st>>>(
+            P, h->d_sel, h->d_sel_count, h->d_kps, h->d_desc, h->d_counts, h->d_pattern_t, h->d_moment_tab);
     ++nl[5];
     if (prof)
     {

@@ -1256,3 +1256,4 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe(PyrDev P, const uint
 
 #include "blur_mma.cuh"
 #include "blur_umma.cuh"
+#include "describe_tma.cuh"
