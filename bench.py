@@ -889,12 +889,12 @@ def main():
         extraction_ms = sum(stage.values())
         kname = {"fast": "k_fast_group", "pyramid": "k_resize"}.get(dom, "k_" + dom)
         # DRAM traffic of that kernel: dram__bytes_read + dram__bytes_write of the committed `ncu --set full` capture of THIS
-        # command at THIS launch shape (profiles/r2n_ncu_summary.csv: 512 images per launch, base units), per launch
+        # command at THIS launch shape (profiles/r2x_ncu_summary.csv: 512 images per launch, base units), per launch
         traffic, traffic_src, limiter = None, None, None
         try:
             import csv
 
-            cap_csv = os.path.join(ROOT, "profiles", "r2n_ncu_summary.csv")
+            cap_csv = os.path.join(ROOT, "profiles", "r2x_ncu_summary.csv")
             cap_images = 512
             rows_ = [r for r in csv.reader(open(cap_csv)) if r and r[0] == kname and float(r[9]) > 5e6]  # skip launches whose blocks return at once
             if rows_:
