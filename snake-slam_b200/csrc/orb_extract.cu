@@ -302,7 +302,11 @@ static void launch_blur(snk_orb* h, const PyrDev& P, int n_imgs, cudaStream_t st
     {
         // persistent: two CTAs per SM (their TMEM columns), each with an equal share of the launch's tiles
         const long long total = (long long)h->umma_tiles_per_img * n_imgs;
-        k_blur_umma<<<(unsigned)std::min<long long>((long long)UB_CTAS_PER_SM * h->n_sm, total), UB_NT, UB_SMEM, st>>>(
+        static const int ctas_per_sm = [] {
+            const char* e = getenv("SNK_UMMA_CTAS");
+            return e && e[0] >= '1' && e[0] <= '4' ? e[0] - '0' : UB_CTAS_PER_SM;
+        }();
+        k_blur_umma<<<(unsigned)std::min<long long>((long long)ctas_per_sm * h->n_sm, total), UB_NT, UB_SMEM, st>>>(
             h->umma_maps, h->d_umma_tasks, (int)h->umma_tasks.size(), n_imgs, h->umma_tiles_per_img, h->d_umma_bands, h->d_err);
     }
     else if (h->blur_mma)
