@@ -36,6 +36,12 @@ struct GroupDev  // 48 bytes
 };
 static_assert(sizeof(GroupDev) == 48, "GroupDev layout");
 
+// CHUNK (SNK_FAST_CHUNK=1, an A/B variant): the compass pass takes 16 pixels (one aligned 16-byte chunk of a tile row) per
+// task instead of 4 (one word) — 5 loads instead of 20 per 16 pixels, no per-word index arithmetic, one scan and one atomic
+// per warp — and the group's zn_word0 / zn_words / zn_inv then count chunks (orb_extract.cu). Parity green, but 1.179 ms
+// against 1.137 ms per 512 images: the loop over the set bits of a lane's 16-pixel mask runs as long as the warp's densest
+// lane (corners cluster), which costs more than the arithmetic it saves.
+template <bool CHUNK>
 __global__ void __launch_bounds__(FASTG_NT) k_fast_group(PyrDev P, const __grid_constant__ TmaMaps maps,
                                                          const GroupDev* __restrict__ groups, int groups_per_img,
                                                          uint32_t* __restrict__ cand, int* __restrict__ cell_count,
@@ -121,7 +127,67 @@ __global__ void __launch_bounds__(FASTG_NT) k_fast_group(PyrDev P, const __grid_
     // ---- A: compass test, 4 pixels (one aligned tile word) per task, tasks = zone rows x words of the zone span ----
     // |p - v| per byte with VABSDIFF4; "byte > t" as bit 7 of ((x & 0x7f) + (127 - t)) | x  (no carry between bytes);
     // a corner needs (S or N beyond the threshold) and (E or W beyond the threshold).
-    if (zh > 0 && zx1 > zx0)
+    if (CHUNK && zh > 0 && zx1 > zx0)
+    {
+        // 16 pixels per task: the centre, south and north chunks as three 16-byte loads, the words left and right of the
+        // centre chunk for the x-3 / x+3 bytes; four flag nibbles -> a 16-bit mask of the task's candidates; the list
+        // positions from one warp scan and ONE atomic per warp, the entries by a loop over the mask's set bits
+        const int c0 = a + zx0, c1 = a + zx1;  // zone columns [c0, c1) in tile coordinates
+        const int qa = g.zn_word0, nq = g.zn_words, ntask = zh * nq;
+        const unsigned addc = (unsigned)(127 - min(t, 127)) * 0x01010101u;
+        const unsigned first_mask = 0xffffu << max(c0 - 16 * qa, 0);
+        const unsigned last_mask  = 0xffffu >> max(16 * (qa + nq) - c1, 0);
+        const int niter = (ntask + FASTG_NT - 1) / FASTG_NT;
+        for (int it = 0; it < niter; ++it)
+        {
+            const int task = it * FASTG_NT + tid;
+            unsigned mask16 = 0;
+            int e0 = 0;
+            if (task < ntask)
+            {
+                const int ry = (int)(((unsigned)task * g.zn_inv) >> 20);  // task / nq
+                const int qr = task - ry * nq;
+                const int y  = 3 + ry;
+                const uint8_t* rc = &tile[y][16 * (qa + qr)];
+                const uint4 V = *reinterpret_cast<const uint4*>(rc);
+                const uint4 S = *reinterpret_cast<const uint4*>(rc + 3 * FASTG_PITCH);
+                const uint4 N = *reinterpret_cast<const uint4*>(rc - 3 * FASTG_PITCH);
+                // unclamped as in the word-wise pass: foreign bytes only reach pixels the zone mask drops
+                const unsigned Lw = *reinterpret_cast<const unsigned*>(rc - 4), Rw = *reinterpret_cast<const unsigned*>(rc + 16);
+                const unsigned v[6] = {Lw, V.x, V.y, V.z, V.w, Rw}, s4[4] = {S.x, S.y, S.z, S.w}, n4[4] = {N.x, N.y, N.z, N.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    const unsigned c  = v[j + 1];
+                    const unsigned pE = __funnelshift_r(c, v[j + 2], 24);  // bytes x+3
+                    const unsigned pW = __funnelshift_r(v[j], c, 8);       // bytes x-3
+                    const unsigned dS = __vabsdiffu4(s4[j], c), dN = __vabsdiffu4(n4[j], c), dE = __vabsdiffu4(pE, c), dW = __vabsdiffu4(pW, c);
+                    const unsigned fS = ((dS & 0x7f7f7f7fu) + addc) | dS, fN = ((dN & 0x7f7f7f7fu) + addc) | dN;
+                    const unsigned fE = ((dE & 0x7f7f7f7fu) + addc) | dE, fW = ((dW & 0x7f7f7f7fu) + addc) | dW;
+                    const unsigned m4 = ((fS | fN) & (fE | fW) & 0x80808080u) >> 7;  // bit 8j: pixel j of the word is a candidate
+                    mask16 |= ((m4 * 0x01020408u) >> 24) << (4 * j);                 // bits 24..27 of the product: the four flags
+                }
+                mask16 &= (qr == 0 ? first_mask : 0xffffu) & (qr == nq - 1 ? last_mask : 0xffffu);
+                e0 = (y << 8) + (16 * (qa + qr) - a);  // (the chunk may start left of the ROI: a sum, not an OR)
+            }
+            const int cnt  = __popc(mask16);
+            const int incl = warp_incl_scan(cnt, lane);
+            const int tot  = __shfl_sync(0xffffffffu, incl, 31);
+            if (tot)
+            {
+                int base = 0;
+                if (lane == 31) base = atomicAdd(&s_n1, tot);
+                int off = __shfl_sync(0xffffffffu, base, 31) + incl - cnt;
+                while (mask16)
+                {
+                    const int b = __ffs(mask16) - 1;
+                    mask16 &= mask16 - 1;
+                    list1[off++] = (uint16_t)(e0 + b);
+                }
+            }
+        }
+    }
+    if (!CHUNK && zh > 0 && zx1 > zx0)
     {
         const int c0 = a + zx0, c1 = a + zx1;  // zone columns [c0, c1) in tile coordinates
         const int wz0 = g.zn_word0, nwz = g.zn_words, ntask = zh * nwz;
