@@ -377,3 +377,37 @@ def test_blur_every_level_byte_equal_on_random_sizes(so, oracle, monkeypatch, mo
             ref.detect(imgs[b])
             for l in range(nl):
                 assert np.array_equal(ex.GetImage(l, img=b, blurred=True), ref.level(l, blurred=True)), (case, w, h, b, l)
+
+
+def test_more_than_eight_levels_take_the_fallback_kernels(so, oracle):
+    """The tcgen05 blur and the TMA descriptor kernel carry their tensor maps in the kernel parameters, eight levels'
+    worth; a deeper pyramid runs k_blur_mma and k_describe (and still the TMA resize) — same bytes."""
+    from snakeorb import synthetic as S
+
+    img = S.image(4242, 1600, 1200)
+    ex = so.ORBExtractor(2000, 1.2, 10, 20, 7)
+    k, d = ex.Detect(img)
+    ref = oracle.Extractor(2000, 1.2, 10, 20, 7, 2)
+    k2, d2 = ref.detect(img)
+    assert len(k) > 1500 and int(k["octave"].max()) == 9
+    assert_same_features(k, d, k2, d2)
+    for l in (0, 5, 9):
+        assert np.array_equal(ex.GetImage(l, blurred=True), ref.level(l, blurred=True)), l
+
+
+@pytest.mark.parametrize("env", [{"SNK_RESIZE_TMA": "0"}, {"SNK_DESCRIBE_TMA": "0"}, {"SNK_BLUR_MMA": "1"}, {"SNK_FAST_CHUNK": "1"},
+                                 {"SNK_RESIZE_TMA": "0", "SNK_DESCRIBE_TMA": "0", "SNK_BLUR_MMA": "0", "SNK_FAST_PER_CELL": "1"}])
+def test_kernel_variants_selected_by_environment_give_the_same_bytes(so, oracle, monkeypatch, env):
+    """Every A/B kernel the environment can select (read when an extractor allocates its pyramid) against the oracle, on a
+    batch of two different images — the plain-load resize, the global-memory descriptor kernel, the mma.sync and dp4a blurs,
+    the chunk-wise FAST compass pass, the per-cell FAST kernel."""
+    from snakeorb import synthetic as S
+
+    for name, value in env.items():
+        monkeypatch.setenv(name, value)
+    imgs = np.stack([S.image(5151, 752, 480), S.adversarial("noise", 752, 480, 7)])
+    ex = so.ORBExtractor(1000, 1.2, 8, 20, 7, max_batch=2)
+    res = ex.DetectBatch(imgs)
+    for b in range(2):
+        k2, d2 = oracle.Extractor(1000, 1.2, 8, 20, 7, 2).detect(imgs[b])
+        assert_same_features(res[b][0], res[b][1], k2, d2)
