@@ -896,7 +896,8 @@ def main():
 
             cap_csv = os.path.join(ROOT, "profiles", "r2x_ncu_summary.csv")
             cap_images = 512
-            rows_ = [r for r in csv.reader(open(cap_csv)) if r and r[0] == kname and float(r[9]) > 5e6]  # skip launches whose blocks return at once
+            # (template kernels are listed as `void name<args>`; skip launches whose blocks return at once)
+            rows_ = [r for r in csv.reader(open(cap_csv)) if r and any(tok.startswith(kname) for tok in r[0].split("<")[0].split()) and float(r[9]) > 5e6]
             if rows_:
                 per_img = sum(float(r[2]) + float(r[3]) for r in rows_) / cap_images
                 traffic = per_img * NI / len(rows_)
