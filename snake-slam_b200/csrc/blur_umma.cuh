@@ -181,19 +181,7 @@ __device__ __forceinline__ bool ub_wait(unsigned bar, unsigned parity)
                      : "memory");
     return done != 0;
 }
-// 32 consecutive TMEM columns of this thread's lane
-__device__ __forceinline__ void ub_ld32(unsigned taddr, unsigned (&v)[32])
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
-        "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
-          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
-          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
+// 16 consecutive TMEM columns of this thread's lane
 __device__ __forceinline__ void ub_ld16(unsigned taddr, unsigned (&v)[16])
 {
     asm volatile(
@@ -212,13 +200,6 @@ __device__ __forceinline__ void ub_ld16_pack(unsigned taddr, unsigned (&v)[16])
           "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr)
         : "memory");
-}
-__device__ __forceinline__ void ub_ld8(unsigned taddr, unsigned (&v)[8])
-{
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
-                 : "r"(taddr)
-                 : "memory");
 }
 __device__ __forceinline__ void ub_st4(unsigned taddr, unsigned a, unsigned b, unsigned c, unsigned d)
 {
