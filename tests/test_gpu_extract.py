@@ -411,3 +411,20 @@ def test_kernel_variants_selected_by_environment_give_the_same_bytes(so, oracle,
     for b in range(2):
         k2, d2 = oracle.Extractor(1000, 1.2, 8, 20, 7, 2).detect(imgs[b])
         assert_same_features(res[b][0], res[b][1], k2, d2)
+
+
+def test_uhd_image_through_the_tma_and_tcgen05_kernels(so, oracle):
+    """3840 x 2160: 30 column strips and 45 row tiles at level 0 of the tcgen05 blur, TMA windows of the resize and
+    descriptor kernels far from the origin, 16-bit coordinates everywhere — same bytes as the oracle."""
+    from snakeorb import synthetic as S
+
+    img = S.image(777, 3840, 2160)
+    ex = so.ORBExtractor(5000, 1.2, 8, 20, 7)
+    k, d = ex.Detect(img)
+    ref = oracle.Extractor(5000, 1.2, 8, 20, 7, 4)
+    k2, d2 = ref.detect(img)
+    assert len(k) > 4000
+    assert_same_features(k, d, k2, d2)
+    for l in (0, 3, 7):
+        assert np.array_equal(ex.GetImage(l), ref.level(l)), l
+        assert np.array_equal(ex.GetImage(l, blurred=True), ref.level(l, blurred=True)), l
