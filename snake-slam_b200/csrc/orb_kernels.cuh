@@ -148,7 +148,6 @@ __global__ void __launch_bounds__(128) k_resize_tma(const __grid_constant__ CUte
     uint8_t* D         = dst + (size_t)blockIdx.z * dst_stride + (size_t)y0 * dpitch + x;
     const ResizeQuad q = quads[x >> 2];
     const unsigned sel01 = q.sel & 0xffffu, sel23 = q.sel >> 16;
-    const bool full = x + 4 <= dw;
     const int pitch_w = box_w >> 2;
     const uint32_t* T0 = reinterpret_cast<const uint32_t*>(rs_smem) + (q.word - (tile_x0 >> 2)) - tile_y0 * pitch_w;
     {
@@ -192,10 +191,10 @@ __global__ void __launch_bounds__(128) k_resize_tma(const __grid_constant__ CUte
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = mad_hi(hb[j], (unsigned)rt.w, mad_hi(ha[j], (unsigned)rt.z, 2u)) >> 2;  // as in k_resize
         const unsigned packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
-        if (full)
-            *reinterpret_cast<uint32_t*>(D) = packed;
-        else
-            for (int j = 0; j < 4 && x + j < dw; ++j) D[j] = (uint8_t)(packed >> (8 * j));
+        // whole words always: the destination is one of the pyramid's own levels, whose pitch is a multiple of 64 — the
+        // bytes of a row's last word beyond the width land in the pitch padding, which nothing reads as pixels (the
+        // byte-wise tail of k_resize cost 11 % of this kernel's instructions: every warp at the right edge ran both paths)
+        *reinterpret_cast<uint32_t*>(D) = packed;
     }
 }
 
