@@ -174,8 +174,8 @@ __device__ __forceinline__ void ub_commit(unsigned bar)
 __device__ __forceinline__ bool ub_wait(unsigned bar, unsigned parity)
 {
     unsigned done = 0;
-    for (int spin = 0; !done && spin < (1 << 18); ++spin)
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x400;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+    for (int spin = 0; !done && spin < (1 << 12); ++spin)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x186a0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done)
                      : "r"(bar), "r"(parity)
                      : "memory");
