@@ -219,7 +219,6 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
     const int wlast = (spitch >> 2) - 1;
     const int i0 = min(q.word, wlast), i1 = min(q.word + 1, wlast), i2 = min(q.word + 2, wlast);
     const unsigned sel01 = q.sel & 0xffffu, sel23 = q.sel >> 16;
-    const bool full = x + 4 <= dw;
 
     // horizontal pass of one source row: the four sums, already >> 4 as the vertical pass consumes them
     const uint32_t* S0 = reinterpret_cast<const uint32_t*>(S) + q.word;
@@ -261,10 +260,7 @@ __global__ void __launch_bounds__(128) k_resize(const uint8_t* __restrict__ src,
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = mad_hi(hb[j], b1, mad_hi(ha[j], b0, 2u)) >> 2;
         const unsigned packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
-        if (full)
-            *reinterpret_cast<uint32_t*>(D) = packed;  // dpitch and x are multiples of 4
-        else
-            for (int j = 0; j < 4 && x + j < dw; ++j) D[j] = (uint8_t)(packed >> (8 * j));
+        *reinterpret_cast<uint32_t*>(D) = packed;  // whole words always, as in k_resize_tma (the tail lands in the pitch padding)
     }
 }
 
