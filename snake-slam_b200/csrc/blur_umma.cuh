@@ -1,7 +1,7 @@
 // cv::GaussianBlur(7 x 7, sigma 2, BORDER_REFLECT_101) of u8 images on the 5th-generation tensor cores: tcgen05.mma
 // kind::i8, operands by TMA, accumulators in tensor memory (ORBExtractor.cpp:213; semantics as k_blur / k_blur_mma).
 // The default blur since round 2 (SNK_BLUR_MMA=1 selects k_blur_mma, 0 k_blur); byte-equal to the oracle on every shape of
-// tests/test_gpu_extract.py. 0.39 ms per 512 EuRoC images against 0.585 ms (mma.sync) and 0.62 ms (dp4a).
+// tests/test_gpu_extract.py. 0.356 ms per 512 EuRoC images against 0.585 ms (mma.sync) and 0.62 ms (dp4a).
 //
 // Both passes of the fixed-point blur are banded matrix products with u8 weights (56 48 34 18, sum 256):
 //   pass 1 (rows):     R[x][y]  = sum_k  Wc[x][k] * I[y][k]        Wc: band over image columns, reflect-101 folded in
@@ -22,14 +22,14 @@
 // TMEM: 128 columns per CTA, so that FOUR CTAs share an SM — the per-tile chain (MMA -> epilogue -> MMA -> epilogue) is
 // latency, and tiles in flight are what hides it; the columns are reused inside a tile: [0,64) pass-1 accumulator, then
 // [0,16) R_lo, [16,32) R_hi (u8 x 4), [32,80) O_lo, [80,128) O_hi.
-// Persistent CTAs walk equal shares of the tile list (strip by strip, image by image, top down); warp 4's lane 0 issues the
+// Persistent CTAs walk equal shares of the tile list (level by level, image by image, strip by strip, top down); warp 4's lane 0 issues the
 // TMA loads (two tiles ahead) and the MMAs and waits only on mbarriers, warps 0-3 are the epilogue (a thread = an output
 // column = a TMEM lane). The band matrices come from a table built once per pyramid geometry (k_umma_bands) and are
 // copied in (cp.async) when the strip / the row-tile kind changes.
 // Steps on the way (B200, 512 EuRoC images, all byte-equal): one CTA per strip with sequential phases 0.68 ms; warp-
 // specialised 0.68; persistent over a tile list 0.70 (256 TMEM columns, two CTAs per SM: the chain of a tile is ~4400
 // cycles whatever the schedule); 128 TMEM columns, four CTAs per SM 0.49; packed TMEM loads, one barrier per tile 0.47;
-// 128 instead of 96 output columns per tile 0.39.
+// 128 instead of 96 output columns per tile 0.39; tiles walked image by image (halo rows and columns from L2) 0.356.
 #pragma once
 #include <cuda.h>
 
