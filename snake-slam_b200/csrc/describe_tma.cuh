@@ -13,7 +13,10 @@ namespace snk
 {
 constexpr int DT_IMG_W = 48, DT_IMG_H = 31, DT_IMG_BYTES = 1536;  // 48 x 31 = 1488, slots 128-byte aligned
 constexpr int DT_G_W = 64, DT_G_H = 39, DT_G_BYTES = 2560;        // 64 x 39 = 2496
-constexpr int DT_WARP_BYTES = 2 * DT_IMG_BYTES + 2 * DT_G_BYTES;  // per warp: two slots of each kind
+// per warp two slots, each holding first a moment patch and later a blurred patch: the two phases of a warp's batch do not
+// overlap, and shared memory is what limits the resident warps (8 KB per warp: 24 warps per SM, 0.548 ms; with 16 warps
+// 0.670 ms) — a slot takes its first blurred patch as soon as its last moment patch has been read
+constexpr int DT_WARP_BYTES = 2 * DT_G_BYTES;
 constexpr int DT_SMEM = DS_WARPS * DT_WARP_BYTES;
 struct DescMaps
 {
@@ -77,7 +80,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe_tma(PyrDev P, const 
         {
             const int x = (int)(p & 0xfffu) + 16, y = (int)((p >> 12) & 0xfffu) + 16;
             const unsigned bar = bar_a + 8u * ((blurred ? 2 : 0) + (kk & 1));
-            const unsigned dst = slots_a + (unsigned)(blurred ? 2 * DT_IMG_BYTES + (kk & 1) * DT_G_BYTES : (kk & 1) * DT_IMG_BYTES);
+            const unsigned dst = slots_a + (unsigned)((kk & 1) * DT_G_BYTES);
             const CUtensorMap* m = blurred ? &maps.gauss[level] : &maps.img[level];
             const int bx = blurred ? ((x - 19) & ~15) : ((x - 15) & ~15), by = blurred ? y - 19 : y - 15;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
@@ -102,8 +105,6 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe_tma(PyrDev P, const 
     };
     fetch(0, false);
     if (nk > 1) fetch(1, false);
-    fetch(0, true);  // the blurred patches of the first two keypoints arrive while the moments are computed
-    if (nk > 1) fetch(1, true);
 
     // ---- ORB::ComputeAngle: integer moments over the radius-15 disc of the un-blurred level ----
     int my_m10 = 0, my_m01 = 0;
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe_tma(PyrDev P, const 
         const int x      = (int)(p & 0xfffu) + 16;
         const int al     = (x - 15) & 3;
         // word 0 of the 36-byte window inside the box: the box starts at the 16-byte boundary below x - 15
-        const unsigned* base = reinterpret_cast<const unsigned*>(slots + (kk & 1) * DT_IMG_BYTES) + (((x - 15 - al) - ((x - 15) & ~15)) >> 2);
+        const unsigned* base = reinterpret_cast<const unsigned*>(slots + (kk & 1) * DT_G_BYTES) + (((x - 15 - al) - ((x - 15) & ~15)) >> 2);
         const uint2* tab     = moment_tab + al * DS_MOM_TASKS;
         wait(kk, false);
         int m10 = 0, m01 = 0;
@@ -136,7 +137,10 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe_tma(PyrDev P, const 
         m01 = warp_sum(m01);
         if (lane == kk) my_m10 = m10, my_m01 = m01;
         __syncwarp();  // the slot is read: the keypoint after next may land in it
-        if (kk + 2 < nk) fetch(kk + 2, false);
+        if (kk + 2 < nk)
+            fetch(kk + 2, false);
+        else
+            fetch(kk & 1, true);  // the slot's last moment patch: the blurred patch of keypoint 0 or 1 arrives during the trigonometry
     }
 
     // ---- angle, sine and cosine of all keypoints of the warp at once (lane kk computes keypoint kk) ----
@@ -160,7 +164,7 @@ __global__ void __launch_bounds__(DS_WARPS * 32) k_describe_tma(PyrDev P, const 
         const int x = (int)(p & 0xfffu) + 16, y = (int)((p >> 12) & 0xfffu) + 16;
         const float resp = (float)(p >> 24);
         // sample (ix, iy) of the level lies at [iy - (y - 19)][ix - box start] of the slot
-        const uint8_t* gs = slots + 2 * DT_IMG_BYTES + (kk & 1) * DT_G_BYTES - ((y - 19) * DT_G_W + ((x - 19) & ~15));
+        const uint8_t* gs = slots + (kk & 1) * DT_G_BYTES - ((y - 19) * DT_G_W + ((x - 19) & ~15));
         const float px = (float)x, py = (float)y;
         wait(kk, true);
         uint32_t byte = 0;
